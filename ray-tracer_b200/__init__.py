@@ -1,0 +1,266 @@
+"""ray-tracer_b200 — ctypes binding of librt_b200.so (include/rt_b200.h, include/rt_b200_host.h).
+
+This is harness plumbing over the C ABI (the product is the shared library): it loads the in-tree
+`librt_b200.so`, mirrors the POD structs, and offers `Device`, `FlatScene`, `Scene` wrappers used by
+tests/, bench.py and __graft_entry__.py.  There is no CPU fallback: if the library is missing the
+import raises, and `Device()` raises without a CUDA device.
+
+Import with `importlib.import_module("ray-tracer_b200")` (the directory name is not an identifier).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+
+RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM = 0, -1, -2, -3, -4, -5
+PRIM_SPHERE, PRIM_RECT, PRIM_MEDIUM_SPHERE = 0, 1, 2
+MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT, MAT_ISOTROPIC = 0, 1, 2, 3, 4
+TEX_SOLID, TEX_CHECKER, TEX_IMAGE = 0, 1, 2
+
+PRIM_DTYPE = np.dtype([("kind", "<u4"), ("material", "<i4"), ("order", "<u4"), ("flags", "<u4"), ("param", "<f4", 4),
+                       ("local_from_world", "<f4", 12), ("world_from_local", "<f4", 12)])
+MATERIAL_DTYPE = np.dtype([("kind", "<u4"), ("texture", "<i4"), ("fuzz", "<f4"), ("ior", "<f4")])
+TEXTURE_DTYPE = np.dtype([("kind", "<u4"), ("a", "<i4"), ("b", "<i4"), ("width", "<u4"), ("height", "<u4"), ("reserved", "<u4"),
+                          ("texel_offset", "<u8"), ("rgb", "<f4", 4)])
+RAY_DTYPE = np.dtype([("origin", "<f4", 3), ("direction", "<f4", 3)])
+HIT_DTYPE = np.dtype([("hit", "<i4"), ("prim", "<i4"), ("t", "<f4"), ("p", "<f4", 3), ("n", "<f4", 3), ("uv", "<f4", 2), ("material", "<i4")])
+assert PRIM_DTYPE.itemsize == 128 and MATERIAL_DTYPE.itemsize == 16 and TEXTURE_DTYPE.itemsize == 48
+assert RAY_DTYPE.itemsize == 24 and HIT_DTYPE.itemsize == 48
+
+
+class RtSceneDesc(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("n_prims", C.c_uint32), ("n_materials", C.c_uint32), ("n_textures", C.c_uint32),
+                ("prims", C.c_void_p), ("materials", C.c_void_p), ("textures", C.c_void_p), ("texels", C.c_void_p), ("n_texels", C.c_uint64)]
+
+
+class RtCamera(C.Structure):
+    _fields_ = [("eye", C.c_float * 3), ("lower_left", C.c_float * 3), ("horizontal", C.c_float * 3), ("vertical", C.c_float * 3),
+                ("lens_radius", C.c_float), ("reserved", C.c_float * 3)]
+
+
+class RtRenderParams(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("spp", C.c_uint32), ("max_depth", C.c_uint32), ("seed", C.c_uint64),
+                ("row_begin", C.c_uint32), ("row_stride", C.c_uint32), ("queue_capacity", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class RtStats(C.Structure):
+    _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("iterations", C.c_uint64), ("launches", C.c_uint64), ("ms_total", C.c_float),
+                ("ms_generate", C.c_float), ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_accumulate", C.c_float),
+                ("bvh_nodes", C.c_uint32), ("bvh_always", C.c_uint32)]
+
+
+class RthCameraArgs(C.Structure):
+    _fields_ = [("eye", C.c_double * 3), ("center", C.c_double * 3), ("up", C.c_double * 3), ("fov", C.c_double), ("aspect", C.c_double),
+                ("focus_distance", C.c_double), ("lens_radius", C.c_double)]
+
+
+# every symbol include/rt_b200.h and include/rt_b200_host.h declare
+ABI_SYMBOLS = ["rt_init", "rt_shutdown", "rt_scene_create", "rt_scene_destroy", "rt_render", "rt_render_device", "rt_trace", "rt_resolve_u8",
+               "rt_scene_bvh_info", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
+               "rth_flat_desc", "rth_scene_upload", "rth_camera"]
+
+
+class BackendError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"rt_b200 error {code}: {message}")
+        self.code = code
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `make -C {_HERE}` (or __graft_entry__.build()); "
+                          "this backend has no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+    L.rt_init.argtypes = [C.c_int, C.POINTER(vp)]
+    L.rt_shutdown.argtypes = [vp]
+    L.rt_shutdown.restype = None
+    L.rt_scene_create.argtypes = [vp, C.POINTER(RtSceneDesc), C.POINTER(vp)]
+    L.rt_scene_destroy.argtypes = [vp]
+    L.rt_scene_destroy.restype = None
+    L.rt_render.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
+    L.rt_render_device.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, vp, C.POINTER(RtStats)]
+    L.rt_trace.argtypes = [vp, vp, u64, u64, vp]
+    L.rt_resolve_u8.argtypes = [vp, vp, u32, u32, u32, vp]
+    L.rt_scene_bvh_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
+    L.rt_last_error.restype = C.c_char_p
+    L.rt_abi_version.restype = u32
+    L.rth_example_scene.argtypes = [C.c_char_p, u64, C.POINTER(vp)]
+    L.rth_flat_destroy.argtypes = [vp]
+    L.rth_flat_destroy.restype = None
+    L.rth_flat_camera_args.argtypes = [vp, C.c_double, C.POINTER(RthCameraArgs)]
+    L.rth_flat_desc.argtypes = [vp, C.POINTER(RtSceneDesc)]
+    L.rth_scene_upload.argtypes = [vp, vp, C.POINTER(vp)]
+    L.rth_camera.argtypes = [C.POINTER(RthCameraArgs), C.POINTER(RtCamera)]
+    return L
+
+
+lib = _load()
+
+
+def _check(rc):
+    if rc != RT_OK:
+        raise BackendError(rc, (lib.rt_last_error() or b"").decode())
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Device:
+    """RtContext bound to one CUDA device (one per process / rank)."""
+
+    def __init__(self, device_id=0):
+        self._h = C.c_void_p()
+        _check(lib.rt_init(int(device_id), C.byref(self._h)))
+        self.device_id = device_id
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.rt_shutdown(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    def resolve_u8(self, sum_rgb, spp):
+        s = np.ascontiguousarray(sum_rgb, dtype=np.float32)
+        h, w, _ = s.shape
+        out = np.zeros((h, w, 3), dtype=np.uint8)
+        _check(lib.rt_resolve_u8(self._h, _ptr(s), w, h, int(spp), _ptr(out)))
+        return out
+
+
+def camera_args(eye, center, up, fov, aspect, focus, lens):
+    a = RthCameraArgs()
+    a.eye[:], a.center[:], a.up[:] = eye, center, up
+    a.fov, a.aspect, a.focus_distance, a.lens_radius = fov, aspect, focus, lens
+    return a
+
+
+def make_camera(args):
+    """PerspectiveCamera::new (src/camera.rs:25-59) -> RtCamera constants."""
+    cam = RtCamera()
+    rc = lib.rth_camera(C.byref(args), C.byref(cam))
+    if rc != RT_OK:
+        raise BackendError(rc, "rth_camera")
+    return cam
+
+
+class FlatScene:
+    """An example scene built through the host mirror of the reference API and flattened (CPU only)."""
+
+    def __init__(self, name, seed=1):
+        self.name, self.seed = name, seed
+        self._h = C.c_void_p()
+        rc = lib.rth_example_scene(name.encode(), int(seed), C.byref(self._h))
+        if rc != RT_OK:
+            raise BackendError(rc, f"cannot build example scene {name!r}")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.rth_flat_destroy(self._h)
+            self._h = None
+
+    def desc(self):
+        d = RtSceneDesc()
+        lib.rth_flat_desc(self._h, C.byref(d))
+        return d
+
+    def _table(self, ptr, n, dtype):
+        if not n:
+            return np.zeros(0, dtype=dtype)
+        buf = (C.c_char * (n * dtype.itemsize)).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype).copy()
+
+    def prims(self):
+        d = self.desc()
+        return self._table(d.prims, d.n_prims, PRIM_DTYPE)
+
+    def materials(self):
+        d = self.desc()
+        return self._table(d.materials, d.n_materials, MATERIAL_DTYPE)
+
+    def textures(self):
+        d = self.desc()
+        return self._table(d.textures, d.n_textures, TEXTURE_DTYPE)
+
+    def camera_args(self, aspect):
+        a = RthCameraArgs()
+        lib.rth_flat_camera_args(self._h, float(aspect), C.byref(a))
+        return a
+
+    def camera(self, aspect):
+        return make_camera(self.camera_args(aspect))
+
+
+class Scene:
+    """A device-resident scene (RtScene): flattened tables + the rebuilt device BVH."""
+
+    def __init__(self, device, flat=None, desc=None, keepalive=None):
+        self.device = device
+        self.flat = flat
+        self._keep = keepalive
+        self._h = C.c_void_p()
+        if flat is not None:
+            _check(lib.rth_scene_upload(device._h, flat._h, C.byref(self._h)))
+        else:
+            _check(lib.rt_scene_create(device._h, C.byref(desc), C.byref(self._h)))
+
+    @classmethod
+    def example(cls, device, name, seed=1):
+        return cls(device, flat=FlatScene(name, seed))
+
+    @classmethod
+    def from_tables(cls, device, prims, materials, textures, texels=None):
+        prims = np.ascontiguousarray(prims, dtype=PRIM_DTYPE)
+        materials = np.ascontiguousarray(materials, dtype=MATERIAL_DTYPE)
+        textures = np.ascontiguousarray(textures, dtype=TEXTURE_DTYPE)
+        texels = np.ascontiguousarray(texels if texels is not None else np.zeros((0, 4)), dtype=np.float32)
+        d = RtSceneDesc(lib.rt_abi_version(), len(prims), len(materials), len(textures), prims.ctypes.data, materials.ctypes.data,
+                        textures.ctypes.data, texels.ctypes.data, texels.size // 4)
+        return cls(device, desc=d, keepalive=(prims, materials, textures, texels))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.rt_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    def bvh_info(self):
+        n, a, d = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _check(lib.rt_scene_bvh_info(self._h, C.byref(n), C.byref(a), C.byref(d)))
+        return {"nodes": n.value, "always": a.value, "depth": d.value}
+
+    @staticmethod
+    def params(width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0):
+        return RtRenderParams(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity, 0)
+
+    def render(self, cam, width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, want_sumsq=True):
+        """rt_render with host buffers: returns (sum[rows,W,3], sumsq or None, RtStats); rows y = row_begin + k*row_stride."""
+        prm = self.params(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity)
+        rows = len(range(row_begin, height, row_stride))
+        s = np.zeros((rows, width, 3), dtype=np.float32)
+        q = np.zeros((rows, width, 3), dtype=np.float32) if want_sumsq else None
+        st = RtStats()
+        _check(lib.rt_render(self._h, C.byref(cam), C.byref(prm), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
+        return s, q, st
+
+    def render_device(self, cam, prm, d_sum_ptr, d_sumsq_ptr=None, stream=None):
+        """rt_render_device: outputs stay in HBM (raw device pointers, e.g. torch tensor .data_ptr())."""
+        st = RtStats()
+        _check(lib.rt_render_device(self._h, C.byref(cam), C.byref(prm), C.c_void_p(d_sum_ptr), C.c_void_p(d_sumsq_ptr) if d_sumsq_ptr else None,
+                                    C.c_void_p(stream) if stream else None, C.byref(st)))
+        return st
+
+    def trace(self, rays, seed=1):
+        """rt_trace: rays [n,6] (origin, direction) f32 -> structured array HIT_DTYPE."""
+        r = np.ascontiguousarray(np.asarray(rays, dtype=np.float32).reshape(-1, 6))
+        out = np.zeros(len(r), dtype=HIT_DTYPE)
+        _check(lib.rt_trace(self._h, _ptr(r), len(r), int(seed), _ptr(out)))
+        return out

@@ -1,0 +1,444 @@
+// C ABI of the backend (include/rt_b200.h): context / scene lifetime, the wavefront render loop,
+// trace and resolve.  No CPU fallback: every entry point needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "bvh_build.h"
+#include "device_scene.h"
+#include "kernels.h"
+
+using namespace rtb;
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+#define RT_CUDA(call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) return fail(RT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t ensure(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+        cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+}  // namespace
+
+struct RtContext {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // wavefront state (sized on demand for the requested queue capacity)
+    DevBuf<float4> qa[2], qb[2], qc[2], done;
+    DevBuf<float2> hits;
+    DevBuf<WaveCounters> counters;
+    DevBuf<float> fb_sum, fb_sumsq;
+    DevBuf<uint8_t> scratch;
+    WaveCounters* h_status = nullptr;  // pinned
+    bool stage_timing = false;
+    uint32_t default_capacity = 1u << 20;
+};
+
+struct RtScene {
+    RtContext* ctx = nullptr;
+    DScene d{};
+    DevBuf<float4> nodes, prim_head, texels;
+    DevBuf<uint2> prim_meta;
+    DevBuf<RtPrim> gen;
+    DevBuf<DMaterial> mats;
+    DevBuf<RtTexture> texs;
+    uint32_t bvh_depth = 0;
+    size_t staged_bytes = 0;
+};
+
+namespace {
+
+// World-space box of a flattened primitive: the 8 corners of the local box pushed through the forward
+// matrix (what Bound for Sprite does, src/optimize.rs:128-185), padded for f32 traversal.
+Box3 primBox(const RtPrim& p) {
+    double lx, ly, lz;
+    if (p.kind == RT_PRIM_RECT) { lx = 0.5 * std::fabs((double)p.param[0]); ly = 0.5 * std::fabs((double)p.param[1]); lz = 1e-6; }  // optimize.rs:115-126
+    else { lx = ly = lz = std::fabs((double)p.param[0]); }                                                                            // optimize.rs:104-113
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    const float* m = p.world_from_local;
+    for (int c = 0; c < 8; ++c) {
+        const double x = (c & 1) ? lx : -lx, y = (c & 2) ? ly : -ly, z = (c & 4) ? lz : -lz;
+        for (int a = 0; a < 3; ++a) {
+            const double v = (double)m[4 * a] * x + (double)m[4 * a + 1] * y + (double)m[4 * a + 2] * z + (double)m[4 * a + 3];
+            lo[a] = std::min(lo[a], v);
+            hi[a] = std::max(hi[a], v);
+        }
+    }
+    Box3 b;
+    for (int a = 0; a < 3; ++a) {
+        const double pad = 4e-6 * std::max(1.0, std::max(std::fabs(lo[a]), std::fabs(hi[a])));
+        b.lo[a] = std::nextafter((float)(lo[a] - pad), -INFINITY);
+        b.hi[a] = std::nextafter((float)(hi[a] + pad), INFINITY);
+    }
+    return b;
+}
+
+bool translationOnly(const RtPrim& p) {
+    const float* m = p.local_from_world;
+    const float* w = p.world_from_local;
+    return m[0] == 1.f && m[1] == 0.f && m[2] == 0.f && m[4] == 0.f && m[5] == 1.f && m[6] == 0.f && m[8] == 0.f && m[9] == 0.f && m[10] == 1.f &&
+           w[0] == 1.f && w[1] == 0.f && w[2] == 0.f && w[4] == 0.f && w[5] == 1.f && w[6] == 0.f && w[8] == 0.f && w[9] == 0.f && w[10] == 1.f;
+}
+
+int validateDesc(const RtSceneDesc* d) {
+    if (!d) return fail(RT_ERR_INVALID, "scene descriptor is null");
+    if (d->abi_version != RT_ABI_VERSION) return fail(RT_ERR_INVALID, "ABI version %u, library is %u", d->abi_version, RT_ABI_VERSION);
+    if (d->n_prims == 0) return fail(RT_ERR_INVALID, "scene has no primitives");
+    if (!d->prims) return fail(RT_ERR_INVALID, "prims is null");
+    if (d->n_materials && !d->materials) return fail(RT_ERR_INVALID, "materials is null");
+    if (d->n_textures && !d->textures) return fail(RT_ERR_INVALID, "textures is null");
+    if (d->n_texels && !d->texels) return fail(RT_ERR_INVALID, "texels is null");
+    for (uint32_t i = 0; i < d->n_prims; ++i) {
+        const RtPrim& p = d->prims[i];
+        if (p.kind > RT_PRIM_MEDIUM_SPHERE) return fail(RT_ERR_UNSUPPORTED, "prim %u: unknown kind %u", i, p.kind);
+        if (p.material >= (int32_t)d->n_materials) return fail(RT_ERR_INVALID, "prim %u: material %d out of range", i, p.material);
+        if (p.kind == RT_PRIM_MEDIUM_SPHERE && !(p.param[1] > 0.0f)) return fail(RT_ERR_INVALID, "prim %u: medium density must be > 0", i);
+        for (int k = 0; k < 12; ++k)
+            if (!std::isfinite(p.local_from_world[k]) || !std::isfinite(p.world_from_local[k])) return fail(RT_ERR_INVALID, "prim %u: non-finite transform", i);
+    }
+    for (uint32_t i = 0; i < d->n_materials; ++i) {
+        const RtMaterial& m = d->materials[i];
+        if (m.kind > RT_MAT_ISOTROPIC) return fail(RT_ERR_UNSUPPORTED, "material %u: unknown kind %u", i, m.kind);
+        if (m.kind != RT_MAT_DIELECTRIC && (m.texture < 0 || m.texture >= (int32_t)d->n_textures))
+            return fail(RT_ERR_INVALID, "material %u: texture %d out of range", i, m.texture);
+    }
+    for (uint32_t i = 0; i < d->n_textures; ++i) {
+        const RtTexture& t = d->textures[i];
+        if (t.kind > RT_TEX_IMAGE) return fail(RT_ERR_UNSUPPORTED, "texture %u: unknown kind %u", i, t.kind);
+        if (t.kind == RT_TEX_CHECKER && (t.a < 0 || t.b < 0 || t.a >= (int32_t)d->n_textures || t.b >= (int32_t)d->n_textures))
+            return fail(RT_ERR_INVALID, "texture %u: checker child out of range", i);
+        if (t.kind == RT_TEX_IMAGE && (t.width == 0 || t.height == 0 || t.texel_offset + (uint64_t)t.width * t.height > d->n_texels))
+            return fail(RT_ERR_INVALID, "texture %u: texel range out of bounds", i);
+    }
+    return RT_OK;
+}
+
+template <class T>
+cudaError_t upload(DevBuf<T>& buf, const T* src, size_t n) {
+    cudaError_t e = buf.ensure(n);
+    if (e != cudaSuccess || n == 0) return e;
+    return cudaMemcpy(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rt_last_error(void) { return g_error.c_str(); }
+uint32_t rt_abi_version(void) { return RT_ABI_VERSION; }
+
+int rt_init(int device_id, RtContext** out) {
+    if (!out) return fail(RT_ERR_INVALID, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return fail(RT_ERR_NO_DEVICE, "no CUDA device (%s); this backend has no CPU fallback", cudaGetErrorString(e));
+    if (device_id < 0 || device_id >= count) return fail(RT_ERR_INVALID, "device %d out of range (have %d)", device_id, count);
+    RT_CUDA(cudaSetDevice(device_id));
+    cudaDeviceProp prop;
+    RT_CUDA(cudaGetDeviceProperties(&prop, device_id));
+    if (prop.major < 10) return fail(RT_ERR_NO_DEVICE, "device %d is sm_%d%d; the kernels are built for sm_100a only", device_id, prop.major, prop.minor);
+    RtContext* ctx = new (std::nothrow) RtContext();
+    if (!ctx) return fail(RT_ERR_OOM, "out of host memory");
+    ctx->device = device_id;
+    RT_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    RT_CUDA(cudaEventCreate(&ctx->ev0));
+    RT_CUDA(cudaEventCreate(&ctx->ev1));
+    for (auto& ev : ctx->evs) RT_CUDA(cudaEventCreate(&ev));
+    RT_CUDA(cudaMallocHost(&ctx->h_status, sizeof(WaveCounters)));
+    const char* st = std::getenv("RT_B200_STAGE_TIMING");
+    ctx->stage_timing = st && st[0] == '1';
+    if (const char* cap = std::getenv("RT_B200_QUEUE_CAPACITY")) {
+        const long v = std::atol(cap);
+        if (v > 0) ctx->default_capacity = (uint32_t)v;
+    }
+    *out = ctx;
+    return RT_OK;
+}
+
+void rt_shutdown(RtContext* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    for (int i = 0; i < 2; ++i) { ctx->qa[i].release(); ctx->qb[i].release(); ctx->qc[i].release(); }
+    ctx->done.release(); ctx->hits.release(); ctx->counters.release(); ctx->fb_sum.release(); ctx->fb_sumsq.release(); ctx->scratch.release();
+    if (ctx->h_status) cudaFreeHost(ctx->h_status);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (auto& ev : ctx->evs) if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
+    if (!ctx || !out) return fail(RT_ERR_INVALID, "ctx/out is null");
+    *out = nullptr;
+    if (int rc = validateDesc(desc)) return rc;
+    RT_CUDA(cudaSetDevice(ctx->device));
+
+    const uint32_t n = desc->n_prims;
+    std::vector<Box3> boxes(n);
+    for (uint32_t i = 0; i < n; ++i) boxes[i] = primBox(desc->prims[i]);
+    BvhOptions opt;
+    if (const char* ml = std::getenv("RT_B200_BVH_MAX_LEAF")) { const int v = std::atoi(ml); if (v >= 1 && v <= 16) opt.max_leaf = (uint32_t)v; }
+    const BvhResult bvh = build_bvh(boxes, opt);
+    if (bvh.depth + 2 > (uint32_t)RT_STACK_DEPTH) return fail(RT_ERR_UNSUPPORTED, "BVH depth %u exceeds the traversal stack", bvh.depth);
+
+    // primitives in leaf order
+    std::vector<float4> head(n);
+    std::vector<uint2> meta(n);
+    std::vector<RtPrim> gen;
+    bool has_media = false;
+    for (uint32_t i = 0; i < n; ++i) {
+        const RtPrim& p = desc->prims[bvh.order[i]];
+        meta[i] = make_uint2(p.order, (uint32_t)p.material);
+        if (p.kind == RT_PRIM_SPHERE && p.param[0] > 0.0f && translationOnly(p)) {
+            head[i] = make_float4(p.world_from_local[3], p.world_from_local[7], p.world_from_local[11], p.param[0]);
+        } else {
+            uint32_t gi = (uint32_t)gen.size(), kind = p.kind;
+            float fx, fy;
+            std::memcpy(&fx, &gi, 4);
+            std::memcpy(&fy, &kind, 4);
+            head[i] = make_float4(fx, fy, 0.0f, -1.0f);
+            gen.push_back(p);
+            has_media |= (p.kind == RT_PRIM_MEDIUM_SPHERE);
+        }
+    }
+    // materials with the solid colour inlined
+    std::vector<DMaterial> mats(desc->n_materials);
+    for (uint32_t i = 0; i < desc->n_materials; ++i) {
+        const RtMaterial& m = desc->materials[i];
+        DMaterial d{};
+        d.kind = m.kind; d.fuzz = m.fuzz; d.ior = m.ior; d.texture = m.texture;
+        if (m.kind == RT_MAT_DIELECTRIC) { d.texture = -1; d.r = d.g = d.b = 1.0f; }
+        else if (desc->textures[m.texture].kind == RT_TEX_SOLID) {
+            d.texture = -1;
+            d.r = desc->textures[m.texture].rgb[0]; d.g = desc->textures[m.texture].rgb[1]; d.b = desc->textures[m.texture].rgb[2];
+        }
+        mats[i] = d;
+    }
+
+    RtScene* s = new (std::nothrow) RtScene();
+    if (!s) return fail(RT_ERR_OOM, "out of host memory");
+    s->ctx = ctx;
+    s->bvh_depth = bvh.depth;
+    cudaError_t e = cudaSuccess;
+    static_assert(sizeof(BvhNode32) == 2 * sizeof(float4), "node layout");
+    if (e == cudaSuccess) e = upload(s->nodes, reinterpret_cast<const float4*>(bvh.nodes.data()), bvh.nodes.size() * 2);
+    if (e == cudaSuccess) e = upload(s->prim_head, head.data(), head.size());
+    if (e == cudaSuccess) e = upload(s->prim_meta, meta.data(), meta.size());
+    if (e == cudaSuccess) e = upload(s->gen, gen.data(), gen.size());
+    if (e == cudaSuccess) e = upload(s->mats, mats.data(), mats.size());
+    if (e == cudaSuccess) e = upload(s->texs, desc->textures, (size_t)desc->n_textures);
+    if (e == cudaSuccess) e = upload(s->texels, reinterpret_cast<const float4*>(desc->texels), (size_t)desc->n_texels);
+    if (e != cudaSuccess) {
+        rt_scene_destroy(s);
+        return fail(e == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(e));
+    }
+    DScene& d = s->d;
+    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p;
+    d.mats = s->mats.p; d.texs = s->texs.p; d.texels = s->texels.p;
+    d.n_nodes = (uint32_t)bvh.nodes.size(); d.n_prims = n; d.n_always = bvh.n_always; d.n_gen = (uint32_t)gen.size();
+    d.n_mats = desc->n_materials; d.n_texs = desc->n_textures;
+    d.root_is_leaf = bvh.root_is_leaf ? 1u : 0u;
+    uint32_t staged = std::min<uint32_t>(d.n_nodes, RT_MAX_STAGED_NODES);
+    if (const char* sn = std::getenv("RT_B200_STAGED_NODES")) staged = std::min<uint32_t>(d.n_nodes, (uint32_t)std::max(0, std::atoi(sn)));
+    d.n_staged_nodes = staged & ~1u;
+    d.has_media = has_media ? 1u : 0u;
+    s->staged_bytes = (size_t)d.n_staged_nodes * 32;
+    *out = s;
+    return RT_OK;
+}
+
+void rt_scene_destroy(RtScene* s) {
+    if (!s) return;
+    if (s->ctx) cudaSetDevice(s->ctx->device);
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    delete s;
+}
+
+int rt_scene_bvh_info(const RtScene* s, uint32_t* n_nodes, uint32_t* n_always, uint32_t* max_depth) {
+    if (!s) return fail(RT_ERR_INVALID, "scene is null");
+    if (n_nodes) *n_nodes = s->d.n_nodes;
+    if (n_always) *n_always = s->d.n_always;
+    if (max_depth) *max_depth = s->bvh_depth;
+    return RT_OK;
+}
+
+int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
+    if (!scene || !cam || !prm || !d_sum) return fail(RT_ERR_INVALID, "null argument");
+    RtContext* ctx = scene->ctx;
+    if (prm->width == 0 || prm->height == 0 || prm->spp == 0) return fail(RT_ERR_INVALID, "width/height/spp must be > 0");
+    if (prm->row_stride == 0 || prm->row_begin >= prm->height) return fail(RT_ERR_INVALID, "bad row_begin/row_stride");
+    if (prm->max_depth > 255u) return fail(RT_ERR_UNSUPPORTED, "max_depth %u > 255", prm->max_depth);
+    if (prm->spp >= (1u << 24)) return fail(RT_ERR_UNSUPPORTED, "spp %u >= 2^24", prm->spp);
+    if ((uint64_t)prm->width * prm->height >= (1ull << 32)) return fail(RT_ERR_UNSUPPORTED, "image too large");
+    RT_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+
+    RenderConst rc{};
+    rc.cam = *cam;
+    rc.width = prm->width; rc.height = prm->height; rc.spp = prm->spp; rc.max_depth = prm->max_depth;
+    rc.seed_lo = (uint32_t)prm->seed; rc.seed_hi = (uint32_t)(prm->seed >> 32);
+    rc.row_begin = prm->row_begin; rc.row_stride = prm->row_stride;
+    rc.rows_local = (prm->height - prm->row_begin + prm->row_stride - 1) / prm->row_stride;
+    uint32_t cap = prm->queue_capacity ? prm->queue_capacity : ctx->default_capacity;
+    cap = std::max(1024u, std::min(cap, 1u << 26)) & ~31u;
+    rc.capacity = cap;
+    rc.pixels_local = (uint64_t)rc.width * rc.rows_local;
+    rc.paths_total = rc.pixels_local * rc.spp;
+
+    for (int i = 0; i < 2; ++i) { RT_CUDA(ctx->qa[i].ensure(cap)); RT_CUDA(ctx->qb[i].ensure(cap)); RT_CUDA(ctx->qc[i].ensure(cap)); }
+    RT_CUDA(ctx->hits.ensure(cap));
+    RT_CUDA(ctx->done.ensure(cap));
+    RT_CUDA(ctx->counters.ensure(1));
+    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes));
+
+    const size_t fb_bytes = (size_t)rc.pixels_local * 3 * sizeof(float);
+    RT_CUDA(cudaMemsetAsync(ctx->counters.p, 0, sizeof(WaveCounters), st));
+    RT_CUDA(cudaMemsetAsync(d_sum, 0, fb_bytes, st));
+    if (d_sumsq) RT_CUDA(cudaMemsetAsync(d_sumsq, 0, fb_bytes, st));
+
+    const RayQueue q[2] = {{ctx->qa[0].p, ctx->qb[0].p, ctx->qc[0].p}, {ctx->qa[1].p, ctx->qb[1].p, ctx->qc[1].p}};
+    WaveCounters* wc = ctx->counters.p;
+    float ms_stage[4] = {0, 0, 0, 0};
+    uint64_t launches = 0;
+    const uint64_t min_iters = (rc.paths_total + cap - 1) / cap;
+    const uint32_t poll = 8;
+    uint32_t max_depth_iters = prm->max_depth ? prm->max_depth : 1;
+    // hard bound on the number of iterations: every iteration either issues `cap` paths or the queue is draining
+    const uint64_t iter_limit = (min_iters + 2) * (uint64_t)(max_depth_iters + 1) + 64;
+
+    RT_CUDA(cudaEventRecord(ctx->ev0, st));
+    uint64_t k = 0;
+    bool finished = false;
+    while (!finished) {
+        const uint32_t ku = (uint32_t)k;
+        const RayQueue& qin = q[k & 1];
+        const RayQueue& qout = q[(k + 1) & 1];
+        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[0], st));
+        launch_generate(rc, qin, wc, ku, st);
+        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[1], st));
+        launch_extend(scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, st);
+        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[2], st));
+        launch_shade(scene->d, rc, qin, qout, ctx->hits.p, ctx->done.p, wc, ku, st);
+        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[3], st));
+        launch_accumulate(rc, ctx->done.p, wc, ku, d_sum, d_sumsq, st);
+        launches += 4;
+        if (ctx->stage_timing) {
+            RT_CUDA(cudaEventRecord(ctx->evs[4], st));
+            RT_CUDA(cudaEventSynchronize(ctx->evs[4]));
+            for (int i = 0; i < 4; ++i) { float ms = 0; RT_CUDA(cudaEventElapsedTime(&ms, ctx->evs[i], ctx->evs[i + 1])); ms_stage[i] += ms; }
+        }
+        ++k;
+        if (k >= min_iters && ((k - min_iters) % poll == 0)) {
+            RT_CUDA(cudaMemcpyAsync(ctx->h_status, wc, sizeof(WaveCounters), cudaMemcpyDeviceToHost, st));
+            RT_CUDA(cudaStreamSynchronize(st));
+            if (ctx->h_status->st_issued == rc.paths_total && ctx->h_status->st_total == 0) finished = true;
+            else if (k > iter_limit) return fail(RT_ERR_CUDA, "wavefront did not terminate after %llu iterations", (unsigned long long)k);
+        }
+    }
+    RT_CUDA(cudaEventRecord(ctx->ev1, st));
+    RT_CUDA(cudaEventSynchronize(ctx->ev1));
+    RT_CUDA(cudaGetLastError());
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        float ms = 0;
+        RT_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        stats->paths = rc.paths_total;
+        stats->rays = ctx->h_status->st_rays;
+        stats->iterations = k;
+        stats->launches = launches;
+        stats->ms_total = ms;
+        stats->ms_generate = ms_stage[0]; stats->ms_extend = ms_stage[1]; stats->ms_shade = ms_stage[2]; stats->ms_accumulate = ms_stage[3];
+        stats->bvh_nodes = scene->d.n_nodes; stats->bvh_always = scene->d.n_always;
+    }
+    return RT_OK;
+}
+
+int rt_render(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* out_sum, float* out_sumsq, RtStats* stats) {
+    if (!scene || !prm || !out_sum) return fail(RT_ERR_INVALID, "null argument");
+    if (prm->row_stride == 0 || prm->row_begin >= prm->height) return fail(RT_ERR_INVALID, "bad row_begin/row_stride");
+    RtContext* ctx = scene->ctx;
+    RT_CUDA(cudaSetDevice(ctx->device));
+    const uint32_t rows = (prm->height - prm->row_begin + prm->row_stride - 1) / prm->row_stride;
+    const size_t n = (size_t)prm->width * rows * 3;
+    RT_CUDA(ctx->fb_sum.ensure(n));
+    if (out_sumsq) RT_CUDA(ctx->fb_sumsq.ensure(n));
+    const int rc = rt_render_device(scene, cam, prm, ctx->fb_sum.p, out_sumsq ? ctx->fb_sumsq.p : nullptr, nullptr, stats);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(cudaMemcpy(out_sum, ctx->fb_sum.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+    if (out_sumsq) RT_CUDA(cudaMemcpy(out_sumsq, ctx->fb_sumsq.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtHitOut* out) {
+    if (!scene || (n && (!rays || !out))) return fail(RT_ERR_INVALID, "null argument");
+    if (n == 0) return RT_OK;
+    RtContext* ctx = scene->ctx;
+    RT_CUDA(cudaSetDevice(ctx->device));
+    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes));
+    const size_t in_bytes = n * sizeof(RtRayIn), out_bytes = n * sizeof(RtHitOut);
+    RT_CUDA(ctx->scratch.ensure(in_bytes + out_bytes + 256));
+    RtRayIn* d_rays = reinterpret_cast<RtRayIn*>(ctx->scratch.p);
+    RtHitOut* d_out = reinterpret_cast<RtHitOut*>(ctx->scratch.p + ((in_bytes + 255) & ~(size_t)255));
+    RT_CUDA(cudaMemcpyAsync(d_rays, rays, in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    launch_trace(scene->d, d_rays, n, (uint32_t)seed, (uint32_t)(seed >> 32), d_out, ctx->stream);
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+int rt_resolve_u8(RtContext* ctx, const float* sum_rgb, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out) {
+    if (!ctx || !sum_rgb || !out || !width || !height || !spp) return fail(RT_ERR_INVALID, "bad argument");
+    RT_CUDA(cudaSetDevice(ctx->device));
+    RT_CUDA(kernels_configure(ctx->device, 0));
+    const size_t n = (size_t)width * height * 3;
+    RT_CUDA(ctx->fb_sum.ensure(n));
+    RT_CUDA(ctx->scratch.ensure(n));
+    RT_CUDA(cudaMemcpyAsync(ctx->fb_sum.p, sum_rgb, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    launch_resolve_u8(ctx->fb_sum.p, width, height, spp, ctx->scratch.p, ctx->stream);
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(out, ctx->scratch.p, n, cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+}  // extern "C"

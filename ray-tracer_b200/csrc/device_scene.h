@@ -1,0 +1,81 @@
+// Device-resident scene layout (HBM) and wavefront state shared by the kernels and the C ABI.
+//
+// Layout decisions (DESIGN.md "Data layout in HBM"):
+//  * BVH: 32-byte nodes of two float4 {lo.xyz, leftOrFirst} {hi.xyz, count}; the two children of an
+//    interior node are adjacent (one 64-byte aligned pair), nodes are emitted breadth-first so the top
+//    levels form a prefix that the extend kernel stages into shared memory.
+//  * Primitives are reordered into leaf order.  `prim_head[i]` (float4) is all the extend kernel needs
+//    for the common case — a translation-only sphere (cx, cy, cz, r>0).  Anything else (rectangles,
+//    rotated / scaled spheres, media) stores w = -1 and the index of a 128-byte general record in x.
+//  * `prim_meta[i]` = {order (reference DFS rank), material index} is read by shade / on exact t ties.
+//  * Materials are 32-byte records with the solid colour inlined (no texture hop for SolidColor).
+#pragma once
+#include <stdint.h>
+
+#include <cuda_runtime.h>
+
+#include "../../include/rt_b200.h"
+
+namespace rtb {
+
+constexpr uint32_t RT_NO_PRIM = 0xFFFFFFFFu;
+constexpr int RT_STACK_DEPTH = 64;       // traversal stack entries (builder caps tree depth below this)
+constexpr uint32_t RT_RING = 4;          // ring length of the per-iteration queue counters
+constexpr uint32_t RT_MAX_STAGED_NODES = 2048;  // 64 KB of BVH prefix staged in shared memory by extend
+constexpr uint32_t RT_MAX_STAGED_MATS = 512;    // 16 KB of material records staged in shared memory by shade
+
+struct DMaterial {       // 32 B, read as two float4
+    uint32_t kind;       // RtMaterialKind
+    int32_t texture;     // -1: solid colour inlined in rgb; else texture table index
+    float fuzz, ior;
+    float r, g, b, pad;
+};
+
+struct DScene {
+    const float4* nodes;       // 2 float4 per node
+    const float4* prim_head;   // per device primitive
+    const uint2* prim_meta;    // {order, material (int32 bits)}
+    const RtPrim* gen;         // general records (non translation-only-sphere primitives)
+    const DMaterial* mats;
+    const RtTexture* texs;
+    const float4* texels;
+    uint32_t n_nodes, n_prims, n_always, n_gen, n_mats, n_texs;
+    uint32_t root_is_leaf;     // BVH over < 2 primitives: node 0 is a leaf
+    uint32_t n_staged_nodes;   // prefix of `nodes` staged in shared memory
+    uint32_t has_media;
+};
+
+// One queue buffer of live rays, SoA of three float4 streams (48 B per ray):
+//   a = origin.xyz, prev primitive (uint bits; RT_NO_PRIM = none)
+//   b = direction.xyz, local pixel index (uint bits)
+//   c = throughput.rgb, (sample << 8 | segment) (uint bits)
+struct RayQueue {
+    float4* a;
+    float4* b;
+    float4* c;
+};
+
+// Per-iteration counters live in a ring so no kernel ever has to reset a counter it also reads.
+struct WaveCounters {
+    uint32_t surv[RT_RING];    // rays appended by shade of iteration k-1 into queue k
+    uint32_t total[RT_RING];   // surv + regenerated camera rays = size of queue k
+    uint32_t done[RT_RING];    // finished-path records produced by shade k
+    uint64_t issued[RT_RING];  // camera samples issued before iteration k
+    // status block copied to the host when polling for termination
+    uint64_t st_issued;
+    uint64_t st_rays;
+    uint32_t st_total;
+    uint32_t st_iter;
+};
+
+struct RenderConst {
+    RtCamera cam;
+    uint32_t width, height, spp, max_depth;
+    uint32_t seed_lo, seed_hi;
+    uint32_t row_begin, row_stride, rows_local;
+    uint32_t capacity;
+    uint64_t paths_total;   // width * rows_local * spp
+    uint64_t pixels_local;  // width * rows_local
+};
+
+}  // namespace rtb

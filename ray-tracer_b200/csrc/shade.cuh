@@ -1,0 +1,217 @@
+// Device shading routines: hit-record reconstruction (point, normal, uv), textures, material
+// scatter / emission, camera ray generation and the direct samplers.
+//
+// Reference semantics:
+//   Sprite::hit point/normal back-transform  src/sprite.rs:108-126 (forward matrix, not renormalised)
+//   unitSphereUv                             src/geometry.rs:35-39
+//   Lambertian / Metal / Dielectric / DiffuseLight / Isotropic   src/material.rs:60-70, 98-119, 140-193, 274-298, 317-326
+//   SolidColor / CheckerTexture / ImageTexture src/material.rs:200-265, lookup examples/main.rs:267-280
+//   PerspectiveCamera::ray                   src/camera.rs:90-107 (scalar lens offset broadcast over xyz)
+//   randomInUnitSphere / randomInUnitDisk    src/util.rs:6-42 — replaced by direct (non-rejection)
+//     samplers with the identical distribution, driven by Philox (philox.h).
+#pragma once
+#include "intersect.cuh"
+
+namespace rtb {
+
+constexpr float RT_PI = 3.14159265358979323846f;
+
+struct HitDetail {
+    float3 p, n;
+    float u, v;
+    bool uv_valid;
+};
+
+__device__ __forceinline__ void sphere_uv(float3 unit, float& u, float& v) {  // geometry.rs:35-39, acos clamped (A.11)
+    u = 0.5f + atan2f(unit.x, unit.z) * (1.0f / (2.0f * RT_PI));
+    v = 1.0f - acosf(fminf(fmaxf(unit.y, -1.0f), 1.0f)) * (1.0f / RT_PI);
+}
+
+// Rebuild the reference's HitRecord for (ray, t, prim).  `want_uv` skips the atan2/acos when the
+// material's texture does not read uv.
+__device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, float3 o, float3 d, float t, bool want_uv, const MediumKey& key) {
+    HitDetail h;
+    h.u = h.v = 0.0f;
+    h.uv_valid = want_uv;
+    const float4 head = __ldg(&S.prim_head[i]);
+    if (head.w > 0.0f) {  // translation-only sphere
+        const float3 c = f3(head.x, head.y, head.z);
+        const float3 unit = normalize3(fma3(t, d, o) - c);  // geometry.rs:68 normalize(p / r)
+        h.n = unit;
+        h.p = fma3(head.w, unit, c);  // re-projected onto the surface (removes the radial f32 error of o + t d)
+        if (want_uv) sphere_uv(unit, h.u, h.v);
+        return h;
+    }
+    const RtPrim* __restrict__ g = &S.gen[__float_as_uint(head.x)];
+    const float3 lo = xform_point(g->local_from_world, o);
+    const float3 ld = xform_vector(g->local_from_world, d);
+    const uint32_t kind = g->kind;
+    if (kind == RT_PRIM_RECT) {
+        float3 lp = fma3(t, ld, lo);
+        lp.z = 0.0f;  // on the plane by construction
+        h.p = xform_point(g->world_from_local, lp);
+        h.n = xform_vector(g->world_from_local, f3(0.0f, 0.0f, 1.0f));  // forward matrix (A.5)
+        h.u = (lp.x + 0.5f * g->param[0]) / g->param[0];                  // geometry.rs:170-171
+        h.v = (lp.y + 0.5f * g->param[1]) / g->param[1];
+        return h;
+    }
+    if (kind == RT_PRIM_SPHERE) {
+        const float r = g->param[0];
+        const float3 q = fma3(t, ld, lo) * (1.0f / r);
+        const float3 unit = normalize3(q);
+        h.p = xform_point(g->world_from_local, unit * r);
+        h.n = xform_vector(g->world_from_local, unit);
+        if (want_uv) sphere_uv(q, h.u, h.v);
+        return h;
+    }
+    // constant medium: redo the boundary query (same arithmetic as extend) for t1 and the branch
+    float t1 = 0.0f;
+    bool entering = false;
+    const float r = g->param[0];
+    medium_sphere_hit(lo, ld, r, g->param[1], g->order, key, &t1, &entering);
+    float tn = 0.0f, tf = 0.0f;
+    sphere_roots(lo, ld, r, tn, tf);
+    if (entering) {
+        // volume.rs:69 evaluates `ray.at(t1 + distance)` on the SHADOWED ray that starts at p1 + 1e-6 d:
+        // point = o + (t1 + 1e-6 + t) d with t = t1 + distance (A.9 ii)
+        const float3 lp = fma3(t1 + 1e-6f + t, ld, lo);
+        const float3 n1 = normalize3(fma3(tn, ld, lo) * (1.0f / r)), n2 = normalize3(fma3(tf, ld, lo) * (1.0f / r));
+        h.p = xform_point(g->world_from_local, lp);
+        h.n = xform_vector(g->world_from_local, (n1 + n2) * 0.5f);
+        if (want_uv) { float u1, v1, u2, v2; sphere_uv(n1, u1, v1); sphere_uv(n2, u2, v2); h.u = u1 + u2; h.v = v1 + v2; }
+    } else {
+        const float3 lp = fma3(t, ld, lo);
+        const float3 n1 = normalize3(fma3(t1, ld, lo) * (1.0f / r));
+        h.p = xform_point(g->world_from_local, lp);
+        h.n = xform_vector(g->world_from_local, n1);
+        if (want_uv) sphere_uv(n1, h.u, h.v);
+    }
+    return h;
+}
+
+// ---- textures ------------------------------------------------------------------------------------
+
+__device__ __forceinline__ float3 texture_value(const DScene& S, int32_t tex, float u, float v) {
+    // CheckerTexture nests (material.rs:217-245): walk down at most 8 levels
+    for (int depth = 0; depth < 8; ++depth) {
+        const RtTexture* __restrict__ t = &S.texs[tex];
+        const uint32_t kind = t->kind;
+        if (kind == RT_TEX_SOLID) return f3(t->rgb[0], t->rgb[1], t->rgb[2]);
+        if (kind == RT_TEX_CHECKER) {
+            const float sine = sinpif(20.0f * u) * sinpif(20.0f * v);  // sin(2 pi 10 u) sin(2 pi 10 v), material.rs:238
+            tex = sine > 0.0f ? t->a : t->b;
+            continue;
+        }
+        // baked image, nearest texel, clamped (main.rs:271-274; A.11)
+        const float fx = u * (float)t->width, fy = (1.0f - v) * (float)t->height;
+        uint32_t px = fx > 0.0f ? (uint32_t)fx : 0u, py = fy > 0.0f ? (uint32_t)fy : 0u;
+        px = min(px, t->width - 1u);
+        py = min(py, t->height - 1u);
+        const float4 c = __ldg(&S.texels[t->texel_offset + (uint64_t)py * t->width + px]);
+        return f3(c.x, c.y, c.z);
+    }
+    return f3(0.0f, 0.0f, 0.0f);
+}
+
+// ---- samplers (identical in distribution to util.rs:6-42; identical variates to the oracle's PAIRED mode) ----
+
+__device__ __forceinline__ float3 ball_from_uniforms(float u0, float u1, float u2) {
+    const float z = 1.0f - 2.0f * u0, rho = sqrtf(fmaxf(0.0f, 1.0f - z * z)), r = cbrtf(u2);
+    float s, c;
+    sincospif(2.0f * u1, &s, &c);
+    return f3(r * rho * c, r * rho * s, r * z);
+}
+__device__ __forceinline__ float2 disk_from_uniforms(float u0, float u1) {
+    const float r = sqrtf(u0);
+    float s, c;
+    sincospif(2.0f * u1, &s, &c);
+    return make_float2(r * c, r * s);
+}
+
+// ---- camera (camera.rs:90-107 + the driver's jitter, examples/book-one.rs:71-72) --------------------
+
+__device__ __forceinline__ void camera_ray(const RtCamera& cam, uint32_t x, uint32_t y, uint32_t width, uint32_t height, const Philox4& rnd,
+                                           float3& o, float3& d) {
+    const float u = ((float)x + u24f(rnd.x)) / (float)width;
+    const float v = ((float)y + u24f(rnd.y)) / (float)height;
+    const float3 eye = f3(cam.eye[0], cam.eye[1], cam.eye[2]);
+    const float3 ll = f3(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
+    const float3 hz = f3(cam.horizontal[0], cam.horizontal[1], cam.horizontal[2]);
+    const float3 vt = f3(cam.vertical[0], cam.vertical[1], cam.vertical[2]);
+    const float3 target = fma3(v, vt, fma3(u, hz, ll));
+    if (cam.lens_radius == 0.0f) {
+        o = eye;
+        d = normalize3(target - eye);
+        return;
+    }
+    const float2 rd = disk_from_uniforms(u24f(rnd.z), u24f(rnd.w));
+    const float offset = cam.lens_radius * (rd.x * u + rd.y * v);  // scalar, broadcast over xyz (A.7)
+    o = f3(eye.x + offset, eye.y + offset, eye.z + offset);
+    d = normalize3(target - o);
+}
+
+// ---- materials -----------------------------------------------------------------------------------
+
+struct ScatterResult {
+    bool scattered;
+    float3 dir;          // next direction (unit)
+    float3 attenuation;  // or emission when !scattered
+};
+
+__device__ __forceinline__ float3 reflect3(float3 v, float3 n) { return fma3(-2.0f * dot3(v, n), n, v); }  // vec3.rs:100-102
+
+// material.scatter + material.emitted for one hit.  `rnd` = Philox(segment, RT_DIM_SHADE).
+__device__ __forceinline__ ScatterResult shade_material(const DScene& S, const DMaterial& m, float3 d, const HitDetail& h, const Philox4& rnd) {
+    ScatterResult r;
+    r.scattered = false;
+    r.dir = f3(0.0f, 0.0f, 0.0f);
+    const float3 tex = (m.texture < 0) ? f3(m.r, m.g, m.b) : texture_value(S, m.texture, h.u, h.v);
+    r.attenuation = tex;
+    switch (m.kind) {
+        case RT_MAT_LAMBERTIAN: {
+            r.dir = normalize3(h.n + ball_from_uniforms(u24f(rnd.x), u24f(rnd.y), u24f(rnd.z)));
+            r.scattered = true;
+        } break;
+        case RT_MAT_METAL: {
+            if (dot3(d, h.n) < 0.0f) {
+                const float3 refl = reflect3(normalize3(d), h.n);
+                r.dir = (m.fuzz == 0.0f) ? refl : normalize3(fma3(m.fuzz, ball_from_uniforms(u24f(rnd.x), u24f(rnd.y), u24f(rnd.z)), refl));
+                r.scattered = true;
+            } else {
+                r.attenuation = f3(0.0f, 0.0f, 0.0f);  // absorbed; emitted() is black
+            }
+        } break;
+        case RT_MAT_DIELECTRIC: {
+            r.attenuation = f3(1.0f, 1.0f, 1.0f);
+            r.scattered = true;
+            float ratio;
+            float3 n = h.n;
+            if (dot3(d, h.n) < 0.0f) ratio = 1.0f / m.ior;
+            else { ratio = m.ior; n = -n; }
+            const float3 unit = normalize3(d);
+            const float dt = dot3(unit, n);
+            const float disc = 1.0f - ratio * ratio * (1.0f - dt * dt);
+            if (disc > 0.0f) {
+                const float r0s = (ratio - 1.0f) / (ratio + 1.0f), r0 = r0s * r0s;
+                const float om = 1.0f - fminf(fmaxf(-dot3(d, n), -1.0f), 1.0f);  // 1 - cos(acos(-d.n)), material.rs:163
+                const float om2 = om * om;
+                const float prob = r0 + (1.0f - r0) * om2 * om2 * om;
+                if (u24f(rnd.x) < prob) r.dir = reflect3(d, h.n);
+                else r.dir = normalize3(fma3(-sqrtf(disc), n, (d - n * dt) * ratio));  // vec3.rs:113-124
+            } else {
+                r.dir = reflect3(d, n);  // total internal reflection
+            }
+        } break;
+        case RT_MAT_DIFFUSE_LIGHT:
+            break;  // never scatters; attenuation carries the emission
+        case RT_MAT_ISOTROPIC: {
+            r.dir = normalize3(ball_from_uniforms(u24f(rnd.x), u24f(rnd.y), u24f(rnd.z)));
+            r.scattered = true;
+        } break;
+        default:
+            r.attenuation = f3(0.0f, 0.0f, 0.0f);
+    }
+    return r;
+}
+
+}  // namespace rtb

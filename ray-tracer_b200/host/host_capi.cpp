@@ -1,0 +1,102 @@
+// extern "C" surface of the host mirror (include/rt_b200_host.h): example scenes built through the
+// mirrored reference API, flattened, and uploaded through the C ABI.
+#include <cstring>
+#include <memory>
+#include <string>
+
+#include "../../include/rt_b200_host.h"
+#include "../examples/scenes.hpp"
+#include "flatten.hpp"
+#include "gpu.hpp"
+
+namespace {
+
+struct HostApi {  // the type bundle scenes.hpp is instantiated with
+    using Vec3 = rtb::host::Vec3;
+    using Mat4 = rtb::host::Mat4;
+    using BoundPtr = rtb::host::BoundPtr;
+    using Sphere = rtb::host::Sphere;
+    using Rectangle = rtb::host::Rectangle;
+    using Cube = rtb::host::Cube;
+    using Sprite = rtb::host::Sprite;
+    using ConstantMedium = rtb::host::ConstantMedium;
+    using BoundingVolumeHierarchyNode = rtb::host::BoundingVolumeHierarchyNode;
+    using Lambertian = rtb::host::Lambertian;
+    using Metal = rtb::host::Metal;
+    using Dielectric = rtb::host::Dielectric;
+    using DiffuseLight = rtb::host::DiffuseLight;
+    using Isotropic = rtb::host::Isotropic;
+    using ImageTexture = rtb::host::ImageTexture;
+    using CheckerTexture = rtb::host::CheckerTexture;
+};
+
+thread_local std::string g_host_error;
+
+}  // namespace
+
+struct RthFlatScene {
+    rtb::host::FlatScene flat;
+    rtscenes::CameraSpec cam;
+};
+
+extern "C" {
+
+int rth_example_scene(const char* name, uint64_t seed, RthFlatScene** out) {
+    if (!name || !out) return RT_ERR_INVALID;
+    *out = nullptr;
+    try {
+        auto res = std::make_unique<RthFlatScene>();
+        std::vector<rtb::host::BoundPtr> list;
+        rtb::host::BuildAxisStream axes(seed ^ 0xA11CE5EEDull);
+        rtb::host::currentAxisStream() = &axes;
+        const bool ok = rtscenes::Scenes<HostApi>::byName(name, seed, &list, &res->cam);
+        std::shared_ptr<const rtb::host::BoundingVolumeHierarchyNode> world;
+        if (ok) world = rtb::host::BoundingVolumeHierarchyNode::make(list);  // examples/book-one.rs:32
+        rtb::host::currentAxisStream() = nullptr;
+        if (!ok || !world) return RT_ERR_INVALID;
+        res->flat = rtb::host::flattenWorld(*world);
+        *out = res.release();
+        return RT_OK;
+    } catch (const rtb::host::FlattenError&) {
+        rtb::host::currentAxisStream() = nullptr;
+        return RT_ERR_UNSUPPORTED;
+    } catch (...) {
+        rtb::host::currentAxisStream() = nullptr;
+        return RT_ERR_INVALID;
+    }
+}
+
+void rth_flat_destroy(RthFlatScene* flat) { delete flat; }
+
+int rth_flat_camera_args(const RthFlatScene* flat, double aspect, RthCameraArgs* out) {
+    if (!flat || !out) return RT_ERR_INVALID;
+    const auto& c = flat->cam;
+    for (int i = 0; i < 3; ++i) { out->eye[i] = c.eye[i]; out->center[i] = c.center[i]; out->up[i] = c.up[i]; }
+    out->fov = rtscenes::to_radians(c.fov_degrees);
+    out->aspect = aspect;
+    out->focus_distance = c.focusDistance;
+    out->lens_radius = c.lensRadius;
+    return RT_OK;
+}
+
+int rth_flat_desc(const RthFlatScene* flat, RtSceneDesc* out) {
+    if (!flat || !out) return RT_ERR_INVALID;
+    *out = flat->flat.desc();
+    return RT_OK;
+}
+
+int rth_scene_upload(RtContext* ctx, const RthFlatScene* flat, RtScene** out) {
+    if (!flat) return RT_ERR_INVALID;
+    const RtSceneDesc d = flat->flat.desc();
+    return rt_scene_create(ctx, &d, out);
+}
+
+int rth_camera(const RthCameraArgs* a, RtCamera* out) {
+    if (!a || !out) return RT_ERR_INVALID;
+    const rtb::host::PerspectiveCamera cam({a->eye[0], a->eye[1], a->eye[2]}, {a->center[0], a->center[1], a->center[2]}, {a->up[0], a->up[1], a->up[2]},
+                                           a->fov, a->aspect, a->focus_distance, a->lens_radius);
+    *out = rtb::host::flattenCamera(cam);
+    return RT_OK;
+}
+
+}  // extern "C"
