@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py — Mpaths/s of the B200 wavefront path tracer on BASELINE.json's workload, one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+A step = one render of the workload image (every path of every pixel) = the `for y / for x / for spp` nest of
+the reference's example drivers (examples/cornell-box.rs:155-181).  Default workload: BASELINE.json configs[1],
+cornell-box 600x600, 1024 spp, depth 50 (368.6 M paths per step).
+
+  value      Mpaths/s, whole job over all N GPUs, scene resident in HBM, framebuffer left in HBM (rt_render_device
+             + for N>1 the NCCL all-gather and the de-interleave kernel), timed with CUDA events on the stream the
+             kernels run on, max over ranks.  N>1 shards the SAME image by interleaved rows -> "scaling": "strong".
+  e2e        same metric through the host-buffer C-ABI calls a reference user would make: every step uploads the
+             flat scene tables from host memory (rt_scene_create: device BVH build + H2D), renders, and brings
+             the framebuffer back to pinned host memory (D2H).
+  roofline   the dominant kernel (k_extend) — its launches are bracketed by CUDA events live in the timed region
+             (RT_RENDER_STAGE_TIMING).  The contract's hbm form is reported (algorithmic queue bytes per ray / time)
+             although the kernel is FP32-issue / latency bound; `roofline_fp32` states that fraction.
+  cpu_baseline  the f64 oracle in FAITHFUL mode (the reference's algorithm: unpruned recursive BVH, Mat4 per sprite,
+             rejection sampling), one thread per host core, on a bounded sample of the same image (fewer spp).
+--impl reference times that CPU implementation as its own arm (the Rust reference cannot be built in this image).
+"""
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (scene, width, height, spp, depth, BASELINE.json config it is)
+    "cornell-box": ("cornell-box", 600, 600, 1024, 50, "configs[1] examples/cornell-box.rs 600x600 1024spp depth50"),
+    "book-one": ("book-one", 400, 225, 100, 50, "configs[0] examples/book-one.rs 400x225 100spp depth50"),
+    "book-two": ("book-two", 800, 800, 1024, 50, "configs[2] examples/main.rs 800x800 1024spp depth50, synthetic 1024x512 earth texture"),
+    "stress-1m": ("stress:1000000", 3840, 2160, 256, 16, "configs[3] 1M random spheres 3840x2160 256spp depth16"),
+    "book-one-4k": ("book-one", 3840, 2160, 1024, 50, "configs[4] book-one 3840x2160 1024spp depth50"),
+}
+# algorithmic HBM bytes per ray segment of k_extend: reads a (16 B) + b (16 B) of the ray queue, writes the hit (8 B)
+EXTEND_BYTES_PER_RAY = 40
+# SURVEY §8(d) per-unit FP32 work of the extend kernel (lane-instructions)
+FP32_PER_BOX, FP32_PER_SPHERE, FP32_PER_RECT = 20, 30, 35
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", float(p.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        threading.Thread(target=self._read, daemon=True).start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        sm, reasons, mx = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for name, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": mx, "reasons": [], "samples": 0}
+        busy = sorted(sm)[len(sm) // 4:]  # drop the idle tail of the first samples
+        return {"sm_mhz": statistics.median(busy), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference(args, wl):
+    """The reference's own CPU implementation of the path, restated (oracle FAITHFUL mode), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as orc  # the one place besides cpu_baseline where bench.py executes oracle/
+
+    scene_name, w, h, spp, depth, cfg = wl
+    cores = os.cpu_count() or 1
+    s = orc.Scene(scene_name, 1)
+    # bounded sample: the same image at a few spp (throughput in paths/s does not depend on spp)
+    probe_spp = 1
+    t0 = time.time()
+    _, _, st = s.render(w, h, probe_spp, depth, seed=1, mode=orc.FAITHFUL, threads=cores)
+    rate = st.paths / max(time.time() - t0, 1e-6)
+    budget_s = 150.0 / max(args.steps + args.warmup, 1)
+    step_spp = max(1, min(spp, int(rate * min(budget_s, 20.0) / (w * h))))
+    for i in range(args.warmup):
+        s.render(w, h, step_spp, depth, seed=100 + i, mode=orc.FAITHFUL, threads=cores)
+    paths = rays = 0
+    t0 = time.time()
+    for i in range(args.steps):
+        _, _, st = s.render(w, h, step_spp, depth, seed=200 + i, mode=orc.FAITHFUL, threads=cores)
+        paths += st.paths
+        rays += st.segments
+    dt = time.time() - t0
+    value = paths / dt / 1e6
+    sample = f"{w}x{h}, {step_spp} of {spp} spp per step, depth {depth} (paths/s is spp-independent)"
+    line = {
+        "impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": cfg, "scene": scene_name, "width": w, "height": h, "spp": spp, "max_depth": depth, "sample": sample},
+        "grays_per_s": rays / dt / 1e9,
+        "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "CPU restatement (oracle FAITHFUL mode) of the Rust reference, which cannot be built here (no cargo/rustc, rand not vendored)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(wl):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as orc
+
+    scene_name, w, h, spp, depth, _ = wl
+    cores = os.cpu_count() or 1
+    s = orc.Scene(scene_name, 1)
+    t0 = time.time()
+    _, _, st = s.render(w, h, 1, depth, seed=1, mode=orc.FAITHFUL, threads=cores)
+    rate = st.paths / max(time.time() - t0, 1e-6)
+    sample_spp = max(1, min(spp, int(rate * 15.0 / (w * h))))
+    t0 = time.time()
+    _, _, st = s.render(w, h, sample_spp, depth, seed=2, mode=orc.FAITHFUL, threads=cores)
+    dt = time.time() - t0
+    return {"value": st.paths / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
+            "sample": f"{w}x{h}, {sample_spp} of {spp} spp, depth {depth}, {dt:.1f} s of CPU time on {cores} threads",
+            "grays_per_s": st.segments / dt / 1e9, "box_tests_per_ray": st.box_tests / st.segments, "prim_tests_per_ray": st.prim_tests / st.segments}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cornell-box", choices=sorted(WORKLOADS))
+    ap.add_argument("--queue-capacity", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rt = importlib.import_module("ray-tracer_b200")  # raises if librt_b200.so is missing: there is no fallback
+    rtdist = importlib.import_module("ray-tracer_b200.dist")
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    scene_name, W, H, spp, depth, cfg = wl
+
+    dev = rt.Device(local_rank)
+    flat = rt.FlatScene(scene_name, 1)
+    scene = rt.Scene(dev, flat=flat)
+    cam = flat.camera(W / H)
+    stream = torch.cuda.current_stream()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(seed, flags=0):
+        flush.zero_()
+        return rtdist.render_sharded(scene, cam, W, H, spp, depth, seed, rank, world, args.queue_capacity, flags)
+
+    for i in range(args.warmup):
+        step(1000 + i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    paths = rays = launches = iters = 0
+    ms_stage = np.zeros(4)
+    for i in range(args.steps):
+        full, st = step(2000 + i, rt.RENDER_STAGE_TIMING)
+        paths += st.paths
+        rays += st.rays
+        iters += st.iterations
+        launches += st.launches + (1 if world > 1 else 0) + 1  # + de-interleave kernel, + the L2-flush memset
+        ms_stage += [st.ms_generate, st.ms_extend, st.ms_shade, st.ms_accumulate]
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = ev0.elapsed_time(ev1)
+    counts = torch.tensor([ms, float(paths), float(rays), float(launches), float(ms_stage[1]), float(iters)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = counts.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+        ms_all = float(mx[0])
+        ms_extend_max = float(mx[4])
+    else:
+        ms_all, ms_extend_max = ms, float(ms_stage[1])
+    tot_paths, tot_rays, tot_launches = float(counts[1]), float(counts[2]), int(counts[3])
+    value = tot_paths / (ms_all * 1e-3) / 1e6
+    mean_check = float(full.mean()) / spp
+
+    # ---- algorithmic work per ray: one instrumented render outside the timed region (counts are spp-independent) ----
+    _, stw = rtdist.render_sharded(scene, cam, W, H, min(spp, 16), depth, 4000, rank, world, args.queue_capacity, rt.RENDER_COUNT_WORK)
+    work = torch.tensor([float(stw.box_tests), float(stw.prim_tests), float(stw.rays)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(work, op=dist.ReduceOp.SUM)
+    box_per_ray, prim_per_ray = float(work[0] / work[2]), float(work[1] / work[2])
+
+    # ---- e2e: host tables in, host framebuffer out, every step ------------------------------------
+    host_fb = torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True)
+    scene_bytes = scene.device_bytes()
+
+    def e2e_step(seed):
+        sc = rt.Scene(dev, flat=flat)  # rt_scene_create: SAH build on the host + H2D of every table
+        out, _ = rtdist.render_sharded(sc, cam, W, H, spp, depth, seed, rank, world, args.queue_capacity)
+        if rank == 0:
+            host_fb.copy_(out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        sc.close()
+
+    e2e_step(3000)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(3001 + i)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = (W * H * spp * args.steps) / float(e2e_t[0]) / 1e6
+
+    if rank == 0:
+        hbm_peak, peak_src, sm_max = load_peaks()
+        n_extend = float(counts[5])  # extend launches = wavefront iterations, summed over ranks
+        rays_per_launch = tot_rays / max(n_extend, 1)
+        # per-launch duration: summed extend time of the slowest rank / its launches (ranks have equal iteration counts to within a few)
+        extend_s = ms_extend_max * 1e-3
+        extend_launches_rank = n_extend / world
+        dur = extend_s / max(extend_launches_rank, 1)
+        achieved = EXTEND_BYTES_PER_RAY * rays_per_launch / max(dur, 1e-12) / 1e9
+        sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
+        line = {
+            "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_all / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": cfg, "scene": scene_name, "width": W, "height": H, "spp": spp, "max_depth": depth, "seed_scene": 1,
+                       "sharding": f"rows y % {world} == rank, NCCL all-gather + de-interleave" if world > 1 else "single GPU",
+                       "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": scene.bvh_info()},
+            "grays_per_s": tot_rays / (ms_all * 1e-3) / 1e9, "rays_per_path": tot_rays / tot_paths, "mean_radiance": mean_check,
+            "gpu_launches": tot_launches,
+            "stage_ms_per_step": {"generate": ms_stage[0] / args.steps, "extend": ms_stage[1] / args.steps, "shade": ms_stage[2] / args.steps,
+                                  "accumulate": ms_stage[3] / args.steps},
+            "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": scene_bytes + 64 + 40,
+                    "d2h_bytes_per_step": W * H * 3 * 4, "ms_per_step": float(e2e_t[0]) / args.steps * 1e3},
+            "roofline": {"kernel": "k_extend", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "traffic": None, "peak_source": peak_src, "launch_us": dur * 1e6, "rays_per_launch": rays_per_launch,
+                         "note": "extend is FP32-issue/latency bound, not HBM bound; see roofline_fp32 and DESIGN.md"},
+            "clocks": clocks,
+        }
+        kinds = flat.prims()["kind"]
+        rect_frac = float(np.mean(kinds == rt.PRIM_RECT))
+        instr_per_ray = box_per_ray * FP32_PER_BOX + prim_per_ray * (rect_frac * FP32_PER_RECT + (1 - rect_frac) * FP32_PER_SPHERE)
+        rays_per_s_kernel = tot_rays / world / max(extend_s, 1e-12)  # per GPU, inside k_extend
+        fp32_peak = 148 * 128 * sm_mhz * 1e6
+        line["roofline_fp32"] = {"kernel": "k_extend", "bound": "fp32-issue", "box_tests_per_ray": box_per_ray, "prim_tests_per_ray": prim_per_ray,
+                                 "algorithmic_lane_instr_per_ray": instr_per_ray, "grays_per_s_in_kernel": rays_per_s_kernel / 1e9,
+                                 "achieved": rays_per_s_kernel * instr_per_ray / 1e12, "peak": fp32_peak / 1e12, "unit": "T lane-instr/s",
+                                 "frac": rays_per_s_kernel * instr_per_ray / fp32_peak, "sm_mhz": sm_mhz,
+                                 "l2_bytes_per_ray": box_per_ray * 32 + prim_per_ray * (rect_frac * 128 + (1 - rect_frac) * 16)}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

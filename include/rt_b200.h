@@ -110,8 +110,13 @@ typedef struct RtRenderParams {
     uint32_t row_begin, row_stride; /* this call renders rows y = row_begin + k*row_stride (multi-GPU sharding,
                                        the reference's thread partition examples/book-one.rs:63) */
     uint32_t queue_capacity;        /* live-ray queue size; 0 = default */
-    uint32_t reserved;
+    uint32_t flags;                 /* RtRenderFlags */
 } RtRenderParams;
+
+typedef enum RtRenderFlags {
+    RT_RENDER_STAGE_TIMING = 1u, /* bracket every stage launch with CUDA events (no extra syncs) and fill RtStats.ms_<stage> */
+    RT_RENDER_COUNT_WORK = 2u    /* run the instrumented extend kernel and fill RtStats.box_tests / prim_tests (slower; not for timing) */
+} RtRenderFlags;
 
 typedef struct RtStats {
     uint64_t paths;      /* camera samples traced */
@@ -119,8 +124,9 @@ typedef struct RtStats {
     uint64_t iterations; /* wavefront iterations */
     uint64_t launches;   /* kernels launched */
     float ms_total;      /* device time of the whole render (CUDA events on the render stream) */
-    float ms_generate, ms_extend, ms_shade, ms_accumulate; /* filled when RT_B200_STAGE_TIMING=1, else 0 */
+    float ms_generate, ms_extend, ms_shade, ms_accumulate; /* summed over iterations; filled with RT_RENDER_STAGE_TIMING, else 0 */
     uint32_t bvh_nodes, bvh_always; /* device BVH size / primitives in the always-tested list */
+    uint64_t box_tests, prim_tests; /* ray/AABB and ray/primitive tests of the whole render (RT_RENDER_COUNT_WORK), else 0 */
 } RtStats;
 
 typedef struct RtRayIn {
@@ -175,8 +181,18 @@ int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtH
 int rt_resolve_u8(RtContext* ctx, const float* sum_rgb, uint32_t width, uint32_t height, uint32_t spp,
                   uint8_t* out_rgb_top_down);
 
+/* Multi-GPU reassembly of the reference's row partition (thread i owns rows y % n == i, examples/book-one.rs:63):
+ * d_gathered holds the n_shards row shards back to back, each padded to ceil(height / n_shards) rows
+ * ([n_shards][rows_padded][width][3] f32, e.g. the output of one NCCL all-gather of the rt_render_device
+ * buffers); d_full receives [height][width][3] with row y taken from shard y % n_shards, row y / n_shards.
+ * Enqueued on `cuda_stream` (0 = the context's stream, which is then drained before returning). */
+int rt_deinterleave_rows(RtContext* ctx, const float* d_gathered, float* d_full, uint32_t width, uint32_t height, uint32_t n_shards,
+                         void* cuda_stream);
+
 /* Introspection used by tests / the roofline accounting. */
 int rt_scene_bvh_info(const RtScene* scene, uint32_t* n_nodes, uint32_t* n_always, uint32_t* max_depth);
+/* Bytes of device memory the scene occupies (= host->device bytes rt_scene_create copied). */
+uint64_t rt_scene_device_bytes(const RtScene* scene);
 const char* rt_last_error(void);
 uint32_t rt_abi_version(void);
 

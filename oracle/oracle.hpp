@@ -181,6 +181,9 @@ struct PathRng {
     uint32_t bounce = 0;           // 0 = camera; k >= 1 = k-th path segment
     uint32_t seq = 0;              // FAITHFUL: position in the sequential stream
     Counters counters;
+    // trace diagnostics: every successful leaf hit (t, leaf id) of the current query, so the caller can
+    // find the runner-up primitive (near-tie policy of the fixed-ray-set tests); null = off
+    std::vector<std::pair<double, int>>* leaf_log = nullptr;
 
     static constexpr uint32_t DIM_CAMERA = 0, DIM_SHADE = 1, DIM_SEQ = 2, DIM_MEDIUM = 0x80000000u;
 
@@ -354,6 +357,7 @@ struct Sphere : Bound {  // geometry.rs:11-74, optimize.rs:104-113
         const auto uv = unitSphereUv((rec.intersection - center) / radius);
         rec.u = uv.first; rec.v = uv.second;
         rec.prim = id;
+        if (id >= 0) if (PathRng* g = tls_rng()) if (g->leaf_log) g->leaf_log->emplace_back(t, id);
         return rec;
     }
     std::optional<AABB> bound() const override {
@@ -381,6 +385,7 @@ struct Rectangle : Bound {  // geometry.rs:126-181, optimize.rs:115-126
         rec.u = (x - ax) / (bx - ax);
         rec.v = (y - ay) / (by - ay);
         rec.prim = id;
+        if (id >= 0) if (PathRng* g = tls_rng()) if (g->leaf_log) g->leaf_log->emplace_back(t, id);
         return rec;
     }
     std::optional<AABB> bound() const override {
@@ -618,6 +623,7 @@ struct ConstantMedium : Bound {
             rec.u = record1->u + record2->u;
             rec.v = record1->v + record2->v;
             rec.prim = id;
+            if (PathRng* g = tls_rng()) if (g->leaf_log) g->leaf_log->emplace_back(rec.t, id);
             return rec;
         }
         // origin inside the boundary (volume.rs:77-96)
@@ -631,6 +637,7 @@ struct ConstantMedium : Bound {
         rec.material = nullptr;
         rec.u = record1->u; rec.v = record1->v;
         rec.prim = id;
+        if (PathRng* g = tls_rng()) if (g->leaf_log) g->leaf_log->emplace_back(rec.t, id);
         return rec;
     }
     std::optional<AABB> bound() const override { return boundary->bound(); }

@@ -65,6 +65,8 @@ struct OrcHit {
     int32_t stable;  // 1 if hit/miss and prim are unchanged under small perturbations of the ray
     int32_t material_kind;
     double t, p[3], n[3], u, v;
+    double t_second;  // smallest t among the OTHER leaf primitives the ray hits (+inf if none): near-tie margin
+    double t_sens, p_sens, n_sens;  // largest change of t / point / normal under the perturbations (conditioning of the query)
 };
 
 struct OrcScene {
@@ -247,21 +249,36 @@ int orc_paths(const OrcScene* s, const OrcCameraArgs* camArgs, const OrcRenderPa
 
 // Closest-hit query on caller-supplied rays (6 doubles each: origin, direction), full record out.
 // Medium free-flight draws are keyed by (ray index, primitive id) so they do not depend on traversal
-// order.  `stable` implements the margin policy of SURVEY §7.2-2: the ray is re-traced under 8 small
-// perturbations; only rays whose hit/miss + primitive id never change are in the bit-exact set.
-int orc_trace(const OrcScene* s, const double* rays, uint64_t n, uint64_t seed, double rel_perturb, OrcHit* out) {
+// order.  Margin policy of the fixed-ray-set tests, all decided here in f64:
+//   * `t_second`: the nearest hit among the other leaf primitives — a runner-up within `tie_rel` of the
+//     winner is a near-tie (coplanar cube faces, a sphere resting on the ground) and is not in the bit-exact set;
+//   * the ray is re-traced under 8 perturbations of relative size `rel_perturb` (a few f32 ulps of the
+//     inputs); hit/miss or primitive changes make it unstable, and the largest change of t / p / n is
+//     reported as the query's conditioning (`*_sens`).
+int orc_trace(const OrcScene* s, const double* rays, uint64_t n, uint64_t seed, double rel_perturb, double tie_rel, OrcHit* out) {
     if (!s || !rays || !out) return -1;
     orc::PathRng g;
     g.mode = orc::PAIRED;
     g.seed_lo = (uint32_t)seed; g.seed_hi = (uint32_t)(seed >> 32);
+    std::vector<std::pair<double, int>> log;
     orc::tls_rng() = &g;
     for (uint64_t i = 0; i < n; ++i) {
         const double* r = rays + 6 * i;
         const orc::Ray ray{{r[0], r[1], r[2]}, {r[3], r[4], r[5]}};
         g.key0 = (uint32_t)i; g.key1 = (uint32_t)(i >> 32); g.bounce = 1;
+        log.clear();
+        g.leaf_log = &log;
         const auto rec = s->world->hit(ray);
+        g.leaf_log = nullptr;
         fillHit(rec, &out[i]);
         int stable = 1;
+        double second = orc::INF;
+        if (rec)
+            for (const auto& e : log)
+                if (e.second != rec->prim && e.first < second) second = e.first;
+        out[i].t_second = second;
+        if (rec && second - rec->t <= tie_rel * std::max(std::fabs(rec->t), 1e-3)) stable = 0;
+        double ts = 0.0, ps = 0.0, ns = 0.0;
         if (rel_perturb > 0.0) {
             const double so = rel_perturb * std::max(1.0, ray.origin.length());
             const double sd = rel_perturb * ray.direction.length();
@@ -274,9 +291,14 @@ int orc_trace(const OrcScene* s, const double* rays, uint64_t n, uint64_t seed, 
                 const auto prec = s->world->hit(pr);
                 if ((bool)prec != (bool)rec) stable = 0;
                 else if (rec && prec->prim != rec->prim) stable = 0;
-                else if (rec && std::fabs(prec->t - rec->t) > 1e-2 * std::max(std::fabs(rec->t), 1e-3)) stable = 0;  // jumped to another root/branch
+                else if (rec) {
+                    ts = std::max(ts, std::fabs(prec->t - rec->t));
+                    ps = std::max(ps, (prec->intersection - rec->intersection).length());
+                    ns = std::max(ns, (prec->normal - rec->normal).length());
+                }
             }
         }
+        out[i].t_sens = ts; out[i].p_sens = ps; out[i].n_sens = ns;
         out[i].stable = stable;
     }
     orc::tls_rng() = nullptr;
@@ -348,6 +370,20 @@ int orc_prim_hit(int kind, const double* param, const double ray6[6], OrcHit* ou
         return out->hit;
     }
     return -1;
+}
+// ConstantMedium<Sphere>(r, density)::hit for one ray with the free-flight draw of path key `key` (A.9 KATs).
+int orc_medium_hit(double r, double density, const double ray6[6], int sampler_mode, uint64_t seed, uint32_t key, OrcHit* out) {
+    orc::PathRng g;
+    g.mode = (orc::SamplerMode)sampler_mode;
+    g.seed_lo = (uint32_t)seed; g.seed_hi = (uint32_t)(seed >> 32);
+    g.key0 = key; g.key1 = 0; g.bounce = 1;
+    orc::tls_rng() = &g;
+    orc::ConstantMedium m(std::make_shared<orc::Sphere>(r), density);
+    m.id = 0;
+    const orc::Ray ray{{ray6[0], ray6[1], ray6[2]}, {ray6[3], ray6[4], ray6[5]}};
+    fillHit(m.hit(ray), out);
+    orc::tls_rng() = nullptr;
+    return out->hit;
 }
 // Scatter one ray off a material (distribution tests).  kind: 0 lambertian, 1 metal(fuzz), 2 dielectric(ior), 4 isotropic.
 // Returns 1 if scattered; out6 = scattered origin+direction, att3 = attenuation.

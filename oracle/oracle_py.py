@@ -36,11 +36,14 @@ class OrcStats(C.Structure):
 
 class OrcHit(C.Structure):
     _fields_ = [("hit", C.c_int32), ("prim", C.c_int32), ("stable", C.c_int32), ("material_kind", C.c_int32),
-                ("t", C.c_double), ("p", C.c_double * 3), ("n", C.c_double * 3), ("u", C.c_double), ("v", C.c_double)]
+                ("t", C.c_double), ("p", C.c_double * 3), ("n", C.c_double * 3), ("u", C.c_double), ("v", C.c_double),
+                ("t_second", C.c_double), ("t_sens", C.c_double), ("p_sens", C.c_double), ("n_sens", C.c_double)]
 
 
 HIT_DTYPE = np.dtype([("hit", "<i4"), ("prim", "<i4"), ("stable", "<i4"), ("material_kind", "<i4"), ("t", "<f8"),
-                      ("p", "<f8", 3), ("n", "<f8", 3), ("u", "<f8"), ("v", "<f8")])
+                      ("p", "<f8", 3), ("n", "<f8", 3), ("u", "<f8"), ("v", "<f8"), ("t_second", "<f8"), ("t_sens", "<f8"),
+                      ("p_sens", "<f8"), ("n_sens", "<f8")])
+assert HIT_DTYPE.itemsize == C.sizeof(OrcHit)
 PRIM_DTYPE = np.dtype([("kind", "<i4"), ("material_kind", "<i4"), ("world_from_local", "<f8", 16), ("param", "<f8", 4)])
 FAITHFUL, PAIRED = 0, 1
 
@@ -74,7 +77,7 @@ def lib():
                              C.POINTER(OrcStats)]
     L.orc_paths.argtypes = [C.c_void_p, C.POINTER(OrcCameraArgs), C.POINTER(OrcRenderParams), C.c_void_p, C.c_void_p,
                             C.c_uint64, C.c_void_p, C.c_void_p]
-    L.orc_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double, C.c_void_p]
+    L.orc_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double, C.c_double, C.c_void_p]
     L.orc_resolve_u8.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
     L.orc_philox.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.orc_mat4_translation.argtypes = [C.c_void_p, C.c_void_p]
@@ -84,6 +87,7 @@ def lib():
     L.orc_vec4_transformed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.orc_cube_faces.argtypes = [C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
     L.orc_prim_hit.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.POINTER(OrcHit)]
+    L.orc_medium_hit.argtypes = [C.c_double, C.c_double, C.c_void_p, C.c_int, C.c_uint64, C.c_uint32, C.POINTER(OrcHit)]
     L.orc_scatter.argtypes = [C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64,
                               C.c_uint32, C.c_void_p, C.c_void_p]
     L.orc_camera_ray.argtypes = [C.POINTER(OrcCameraArgs), C.c_double, C.c_double, C.c_int, C.c_uint64, C.c_uint32,
@@ -152,10 +156,11 @@ class Scene:
         assert rc == 0
         return rgb, seg
 
-    def trace(self, rays, seed=1, rel_perturb=4e-6):
+    def trace(self, rays, seed=1, rel_perturb=1e-6, tie_rel=1e-4):
+        """Closest hit per ray plus the margin diagnostics (stable, t_second, *_sens) of orc_trace."""
         rays = _f8(rays).reshape(-1, 6)
         out = np.zeros(len(rays), dtype=HIT_DTYPE)
-        rc = lib().orc_trace(self._h, _p(rays), len(rays), seed, float(rel_perturb), _p(out))
+        rc = lib().orc_trace(self._h, _p(rays), len(rays), seed, float(rel_perturb), float(tie_rel), _p(out))
         assert rc == 0
         return out
 
@@ -245,6 +250,12 @@ def cube_faces(w, h, d):
 def prim_hit(kind, param, ray):
     h = OrcHit()
     lib().orc_prim_hit(kind, _p(_f8(param)), _p(_f8(ray)), C.byref(h))
+    return h
+
+
+def medium_hit(r, density, ray, mode=PAIRED, seed=1, key=0):
+    h = OrcHit()
+    lib().orc_medium_hit(float(r), float(density), _p(_f8(ray)), mode, seed, key, C.byref(h))
     return h
 
 

@@ -15,6 +15,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librt_b200.so")
 
+RENDER_STAGE_TIMING, RENDER_COUNT_WORK = 1, 2
 RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM = 0, -1, -2, -3, -4, -5
 PRIM_SPHERE, PRIM_RECT, PRIM_MEDIUM_SPHERE = 0, 1, 2
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT, MAT_ISOTROPIC = 0, 1, 2, 3, 4
@@ -43,13 +44,13 @@ class RtCamera(C.Structure):
 
 class RtRenderParams(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("spp", C.c_uint32), ("max_depth", C.c_uint32), ("seed", C.c_uint64),
-                ("row_begin", C.c_uint32), ("row_stride", C.c_uint32), ("queue_capacity", C.c_uint32), ("reserved", C.c_uint32)]
+                ("row_begin", C.c_uint32), ("row_stride", C.c_uint32), ("queue_capacity", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class RtStats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("iterations", C.c_uint64), ("launches", C.c_uint64), ("ms_total", C.c_float),
                 ("ms_generate", C.c_float), ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_accumulate", C.c_float),
-                ("bvh_nodes", C.c_uint32), ("bvh_always", C.c_uint32)]
+                ("bvh_nodes", C.c_uint32), ("bvh_always", C.c_uint32), ("box_tests", C.c_uint64), ("prim_tests", C.c_uint64)]
 
 
 class RthCameraArgs(C.Structure):
@@ -59,7 +60,7 @@ class RthCameraArgs(C.Structure):
 
 # every symbol include/rt_b200.h and include/rt_b200_host.h declare
 ABI_SYMBOLS = ["rt_init", "rt_shutdown", "rt_scene_create", "rt_scene_destroy", "rt_render", "rt_render_device", "rt_trace", "rt_resolve_u8",
-               "rt_scene_bvh_info", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
+               "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
                "rth_flat_desc", "rth_scene_upload", "rth_camera"]
 
 
@@ -85,6 +86,9 @@ def _load():
     L.rt_render_device.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, vp, C.POINTER(RtStats)]
     L.rt_trace.argtypes = [vp, vp, u64, u64, vp]
     L.rt_resolve_u8.argtypes = [vp, vp, u32, u32, u32, vp]
+    L.rt_deinterleave_rows.argtypes = [vp, vp, vp, u32, u32, u32, vp]
+    L.rt_scene_device_bytes.argtypes = [vp]
+    L.rt_scene_device_bytes.restype = u64
     L.rt_scene_bvh_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
     L.rt_last_error.restype = C.c_char_p
     L.rt_abi_version.restype = u32
@@ -125,6 +129,11 @@ class Device:
 
     def __del__(self):
         self.close()
+
+    def deinterleave_rows(self, d_gathered_ptr, d_full_ptr, width, height, n_shards, stream=None):
+        """rt_deinterleave_rows on raw device pointers (multi-GPU framebuffer reassembly)."""
+        _check(lib.rt_deinterleave_rows(self._h, C.c_void_p(d_gathered_ptr), C.c_void_p(d_full_ptr), width, height, n_shards,
+                                        C.c_void_p(stream) if stream else None))
 
     def resolve_u8(self, sum_rgb, spp):
         s = np.ascontiguousarray(sum_rgb, dtype=np.float32)
@@ -237,13 +246,16 @@ class Scene:
         _check(lib.rt_scene_bvh_info(self._h, C.byref(n), C.byref(a), C.byref(d)))
         return {"nodes": n.value, "always": a.value, "depth": d.value}
 
-    @staticmethod
-    def params(width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0):
-        return RtRenderParams(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity, 0)
+    def device_bytes(self):
+        return int(lib.rt_scene_device_bytes(self._h))
 
-    def render(self, cam, width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, want_sumsq=True):
+    @staticmethod
+    def params(width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, flags=0):
+        return RtRenderParams(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity, flags)
+
+    def render(self, cam, width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, want_sumsq=True, flags=0):
         """rt_render with host buffers: returns (sum[rows,W,3], sumsq or None, RtStats); rows y = row_begin + k*row_stride."""
-        prm = self.params(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity)
+        prm = self.params(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity, flags)
         rows = len(range(row_begin, height, row_stride))
         s = np.zeros((rows, width, 3), dtype=np.float32)
         q = np.zeros((rows, width, 3), dtype=np.float32) if want_sumsq else None

@@ -59,7 +59,8 @@ struct DevBuf {
 struct RtContext {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<cudaEvent_t> stage_events;  // 5 per wavefront iteration when stage timing is on (no sync until the render ends)
     // wavefront state (sized on demand for the requested queue capacity)
     DevBuf<float4> qa[2], qb[2], qc[2], done;
     DevBuf<float2> hits;
@@ -181,7 +182,6 @@ int rt_init(int device_id, RtContext** out) {
     RT_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     RT_CUDA(cudaEventCreate(&ctx->ev0));
     RT_CUDA(cudaEventCreate(&ctx->ev1));
-    for (auto& ev : ctx->evs) RT_CUDA(cudaEventCreate(&ev));
     RT_CUDA(cudaMallocHost(&ctx->h_status, sizeof(WaveCounters)));
     const char* st = std::getenv("RT_B200_STAGE_TIMING");
     ctx->stage_timing = st && st[0] == '1';
@@ -201,7 +201,7 @@ void rt_shutdown(RtContext* ctx) {
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-    for (auto& ev : ctx->evs) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->stage_events) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -301,6 +301,24 @@ int rt_scene_bvh_info(const RtScene* s, uint32_t* n_nodes, uint32_t* n_always, u
     return RT_OK;
 }
 
+uint64_t rt_scene_device_bytes(const RtScene* s) {
+    if (!s) return 0;
+    return (uint64_t)s->nodes.n * sizeof(float4) + (uint64_t)s->prim_head.n * sizeof(float4) + (uint64_t)s->prim_meta.n * sizeof(uint2) +
+           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
+           (uint64_t)s->texels.n * sizeof(float4);
+}
+
+int rt_deinterleave_rows(RtContext* ctx, const float* d_gathered, float* d_full, uint32_t width, uint32_t height, uint32_t n_shards, void* cuda_stream) {
+    if (!ctx || !d_gathered || !d_full || !width || !height || !n_shards) return fail(RT_ERR_INVALID, "bad argument");
+    RT_CUDA(cudaSetDevice(ctx->device));
+    RT_CUDA(kernels_init(ctx->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+    launch_deinterleave(d_gathered, d_full, width, height, n_shards, st);
+    RT_CUDA(cudaGetLastError());
+    if (!cuda_stream) RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
 int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
     if (!scene || !cam || !prm || !d_sum) return fail(RT_ERR_INVALID, "null argument");
     RtContext* ctx = scene->ctx;
@@ -345,6 +363,19 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     // hard bound on the number of iterations: every iteration either issues `cap` paths or the queue is draining
     const uint64_t iter_limit = (min_iters + 2) * (uint64_t)(max_depth_iters + 1) + 64;
 
+    const bool timing = ctx->stage_timing || (prm->flags & RT_RENDER_STAGE_TIMING);
+    const bool count_work = (prm->flags & RT_RENDER_COUNT_WORK) != 0;
+    auto stage_event = [&](uint64_t iter, int which) -> cudaError_t {
+        const size_t idx = (size_t)iter * 5 + (size_t)which;
+        while (ctx->stage_events.size() <= idx) {
+            cudaEvent_t ev = nullptr;
+            const cudaError_t e = cudaEventCreate(&ev);
+            if (e != cudaSuccess) return e;
+            ctx->stage_events.push_back(ev);
+        }
+        return cudaEventRecord(ctx->stage_events[idx], st);
+    };
+
     RT_CUDA(cudaEventRecord(ctx->ev0, st));
     uint64_t k = 0;
     bool finished = false;
@@ -352,20 +383,16 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
         const uint32_t ku = (uint32_t)k;
         const RayQueue& qin = q[k & 1];
         const RayQueue& qout = q[(k + 1) & 1];
-        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[0], st));
+        if (timing) RT_CUDA(stage_event(k, 0));
         launch_generate(rc, qin, wc, ku, st);
-        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[1], st));
-        launch_extend(scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, st);
-        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[2], st));
+        if (timing) RT_CUDA(stage_event(k, 1));
+        launch_extend(scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, count_work, st);
+        if (timing) RT_CUDA(stage_event(k, 2));
         launch_shade(scene->d, rc, qin, qout, ctx->hits.p, ctx->done.p, wc, ku, st);
-        if (ctx->stage_timing) RT_CUDA(cudaEventRecord(ctx->evs[3], st));
+        if (timing) RT_CUDA(stage_event(k, 3));
         launch_accumulate(rc, ctx->done.p, wc, ku, d_sum, d_sumsq, st);
+        if (timing) RT_CUDA(stage_event(k, 4));
         launches += 4;
-        if (ctx->stage_timing) {
-            RT_CUDA(cudaEventRecord(ctx->evs[4], st));
-            RT_CUDA(cudaEventSynchronize(ctx->evs[4]));
-            for (int i = 0; i < 4; ++i) { float ms = 0; RT_CUDA(cudaEventElapsedTime(&ms, ctx->evs[i], ctx->evs[i + 1])); ms_stage[i] += ms; }
-        }
         ++k;
         if (k >= min_iters && ((k - min_iters) % poll == 0)) {
             RT_CUDA(cudaMemcpyAsync(ctx->h_status, wc, sizeof(WaveCounters), cudaMemcpyDeviceToHost, st));
@@ -377,6 +404,14 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     RT_CUDA(cudaEventRecord(ctx->ev1, st));
     RT_CUDA(cudaEventSynchronize(ctx->ev1));
     RT_CUDA(cudaGetLastError());
+    if (timing) {
+        for (uint64_t it = 0; it < k; ++it)
+            for (int i = 0; i < 4; ++i) {
+                float ms = 0;
+                RT_CUDA(cudaEventElapsedTime(&ms, ctx->stage_events[it * 5 + i], ctx->stage_events[it * 5 + i + 1]));
+                ms_stage[i] += ms;
+            }
+    }
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
         float ms = 0;
@@ -388,6 +423,7 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
         stats->ms_total = ms;
         stats->ms_generate = ms_stage[0]; stats->ms_extend = ms_stage[1]; stats->ms_shade = ms_stage[2]; stats->ms_accumulate = ms_stage[3];
         stats->bvh_nodes = scene->d.n_nodes; stats->bvh_always = scene->d.n_always;
+        stats->box_tests = ctx->h_status->st_box_tests; stats->prim_tests = ctx->h_status->st_prim_tests;
     }
     return RT_OK;
 }
@@ -429,7 +465,7 @@ int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtH
 int rt_resolve_u8(RtContext* ctx, const float* sum_rgb, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out) {
     if (!ctx || !sum_rgb || !out || !width || !height || !spp) return fail(RT_ERR_INVALID, "bad argument");
     RT_CUDA(cudaSetDevice(ctx->device));
-    RT_CUDA(kernels_configure(ctx->device, 0));
+    RT_CUDA(kernels_init(ctx->device));
     const size_t n = (size_t)width * height * 3;
     RT_CUDA(ctx->fb_sum.ensure(n));
     RT_CUDA(ctx->scratch.ensure(n));

@@ -66,6 +66,7 @@ struct WaveCounters {
     uint64_t st_rays;
     uint32_t st_total;
     uint32_t st_iter;
+    unsigned long long st_box_tests, st_prim_tests;  // RT_RENDER_COUNT_WORK only
 };
 
 struct RenderConst {

@@ -90,6 +90,32 @@ __device__ __forceinline__ float sphere_hit(float3 oc, float3 d, float r, bool i
     return CUDART_INF_F;
 }
 
+// Same test in f64 for the primitives of the always-tested list (sky / ground spheres of radius 1e3):
+// a ray that starts 1e-3 above the r = 1000 ground and grazes it has c = |oc|^2 - r^2 ~ 2 against an f32
+// rounding error of |oc|^2 ~ 0.1, i.e. t would be off by percents.  o - c is exact in f64 for f32 inputs.
+__device__ __forceinline__ float sphere_hit_f64(float3 o, float3 ctr, float3 d, float r, bool is_self) {
+    const double ox = (double)o.x - (double)ctr.x, oy = (double)o.y - (double)ctr.y, oz = (double)o.z - (double)ctr.z;
+    const double dx = d.x, dy = d.y, dz = d.z;
+    const double a = dx * dx + dy * dy + dz * dz;
+    const double b = ox * dx + oy * dy + oz * dz;  // half-b
+    if (is_self) {
+        if (b >= 0.0) return CUDART_INF_F;
+        const float t = (float)(-2.0 * b / a);
+        return t > RT_T_EPS ? t : CUDART_INF_F;
+    }
+    const double c = ox * ox + oy * oy + oz * oz - (double)r * (double)r;
+    const double disc = b * b - a * c;
+    if (!(disc >= 0.0)) return CUDART_INF_F;
+    const double sq = sqrt(disc);
+    const double q = (b > 0.0) ? (-b - sq) : (sq - b);  // stable: no cancellation in q
+    double t0 = q / a, t1 = (q != 0.0) ? c / q : 0.0;
+    if (t0 > t1) { const double s = t0; t0 = t1; t1 = s; }
+    const float tn = (float)t0, tf = (float)t1;
+    if (tn > RT_T_EPS) return tn;
+    if (tf > RT_T_EPS) return tf;
+    return CUDART_INF_F;
+}
+
 // Rectangle::hit in object space (plane z = 0).  Returns t or +inf.
 __device__ __forceinline__ float rect_hit(float3 o, float3 d, float w, float h) {
     const float t = (0.0f - o.z) / d.z;
@@ -135,10 +161,14 @@ __device__ __forceinline__ float medium_sphere_hit(float3 o, float3 d, float r, 
     return entering ? t1 + distance : distance;
 }
 
-// Test device primitive `i`.  Returns t or +inf.
+// Test device primitive `i`.  Returns t or +inf.  BIG = primitive of the always-tested list (f64 sphere test).
+template <bool BIG = false>
 __device__ __forceinline__ float prim_hit(const DScene& S, uint32_t i, float3 o, float3 d, uint32_t self_prim, const MediumKey& key) {
     const float4 h = __ldg(&S.prim_head[i]);
-    if (h.w > 0.0f) return sphere_hit(o - f3(h.x, h.y, h.z), d, h.w, i == self_prim);
+    if (h.w > 0.0f) {
+        if (BIG) return sphere_hit_f64(o, f3(h.x, h.y, h.z), d, h.w, i == self_prim);
+        return sphere_hit(o - f3(h.x, h.y, h.z), d, h.w, i == self_prim);
+    }
     const RtPrim* __restrict__ g = &S.gen[__float_as_uint(h.x)];
     const float3 lo = xform_point(g->local_from_world, o);
     const float3 ld = xform_vector(g->local_from_world, d);
@@ -178,8 +208,15 @@ struct ClosestHit {
     uint32_t prim;  // device primitive index or RT_NO_PRIM
 };
 
+// Work counters of the instrumented traversal (RT_RENDER_COUNT_WORK): the algorithmic units of SURVEY §8(d).
+struct TraversalWork {
+    uint32_t box_tests;   // ray/AABB slab tests (two per visited node pair)
+    uint32_t prim_tests;  // primitive intersection tests
+};
+
+template <bool BIG = false>
 __device__ __forceinline__ void consider(const DScene& S, uint32_t i, float3 o, float3 d, uint32_t self_prim, const MediumKey& key, ClosestHit& best) {
-    const float t = prim_hit(S, i, o, d, self_prim, key);
+    const float t = prim_hit<BIG>(S, i, o, d, self_prim, key);
     if (t < best.t) { best.t = t; best.prim = i; }
     else if (t == best.t && t < CUDART_INF_F && best.prim != RT_NO_PRIM) {
         // exact tie: the reference keeps the DFS-earlier leaf (optimize.rs:475,484)
@@ -192,10 +229,12 @@ __device__ __forceinline__ float4 load_node(const DScene& S, const float4* __res
     return (idx4 < 2u * S.n_staged_nodes) ? snodes[idx4] : __ldg(&S.nodes[idx4]);
 }
 
+template <bool COUNT = false>
 __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const float4* __restrict__ snodes, float3 o, float3 d, uint32_t self_prim,
-                                                  const MediumKey& key) {
+                                                  const MediumKey& key, TraversalWork* work = nullptr) {
     ClosestHit best{CUDART_INF_F, RT_NO_PRIM};
-    for (uint32_t i = 0; i < S.n_always; ++i) consider(S, i, o, d, self_prim, key, best);
+    for (uint32_t i = 0; i < S.n_always; ++i) consider<true>(S, i, o, d, self_prim, key, best);
+    if (COUNT) work->prim_tests += S.n_always;
     if (S.n_nodes == 0) return best;
 
     RayBox rb;
@@ -208,9 +247,11 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const float4*
 
     if (S.root_is_leaf) {
         const float4 lo = load_node(S, snodes, 0), hi = load_node(S, snodes, 1);
+        if (COUNT) work->box_tests += 1;
         if (slab(lo, hi, rb, best.t) < CUDART_INF_F) {
             const uint32_t first = __float_as_uint(lo.w), cnt = __float_as_uint(hi.w);
             for (uint32_t i = first; i < first + cnt; ++i) consider(S, i, o, d, self_prim, key, best);
+            if (COUNT) work->prim_tests += cnt;
         }
         return best;
     }
@@ -223,6 +264,7 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const float4*
         const float4 rlo = load_node(S, snodes, 2u * pair + 2u), rhi = load_node(S, snodes, 2u * pair + 3u);
         const float tl = slab(llo, lhi, rb, best.t);
         const float tr = slab(rlo, rhi, rb, best.t);
+        if (COUNT) work->box_tests += 2;
         // near child first so that the far one can be pruned by what the near one finds
         const bool swap = tr < tl;
         const float t_far = swap ? tl : tr, t_near = swap ? tr : tl;
@@ -230,12 +272,16 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const float4*
         const uint32_t far_ref = __float_as_uint(swap ? llo.w : rlo.w), far_cnt = __float_as_uint(swap ? lhi.w : rhi.w);
         uint32_t next_near = RT_NO_PRIM, next_far = RT_NO_PRIM;
         if (t_near < CUDART_INF_F) {
-            if (near_cnt) { for (uint32_t i = near_ref; i < near_ref + near_cnt; ++i) consider(S, i, o, d, self_prim, key, best); }
-            else next_near = near_ref;
+            if (near_cnt) {
+                for (uint32_t i = near_ref; i < near_ref + near_cnt; ++i) consider(S, i, o, d, self_prim, key, best);
+                if (COUNT) work->prim_tests += near_cnt;
+            } else next_near = near_ref;
         }
         if (t_far <= best.t && t_far < CUDART_INF_F) {
-            if (far_cnt) { for (uint32_t i = far_ref; i < far_ref + far_cnt; ++i) consider(S, i, o, d, self_prim, key, best); }
-            else next_far = far_ref;
+            if (far_cnt) {
+                for (uint32_t i = far_ref; i < far_ref + far_cnt; ++i) consider(S, i, o, d, self_prim, key, best);
+                if (COUNT) work->prim_tests += far_cnt;
+            } else next_far = far_ref;
         }
         // interior children: descend into the nearer, push the farther (its children are re-tested against best.t on pop)
         if (next_near != RT_NO_PRIM) {

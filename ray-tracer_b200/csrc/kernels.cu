@@ -101,13 +101,15 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
 
 // ---- extend ----------------------------------------------------------------------------------------
 
-__global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits,
-                                                          const WaveCounters* __restrict__ wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
+                                                          uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
     extern __shared__ float4 snodes[];
     for (uint32_t i = threadIdx.x; i < 2u * S.n_staged_nodes; i += blockDim.x) snodes[i] = S.nodes[i];
     __syncthreads();
     const uint32_t n = wc->total[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x;
+    TraversalWork work{0u, 0u};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const float4 a = q.a[i], b = q.b[i];
         MediumKey key{0u, 0u, 0u, seed_lo, seed_hi};
@@ -117,8 +119,13 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_extend(const DScene S, cons
             key.k1 = sb >> 8;
             key.segment = sb & 0xFFu;
         }
-        const ClosestHit h = closest_hit(S, snodes, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key);
+        const ClosestHit h = closest_hit<COUNT>(S, snodes, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
         hits[i] = make_float2(h.t, __uint_as_float(h.prim));
+    }
+    if (COUNT) {  // instrumented build only (RT_RENDER_COUNT_WORK): one atomic pair per warp
+        uint32_t bt = work.box_tests, pt = work.prim_tests;
+        for (int off = 16; off > 0; off >>= 1) { bt += __shfl_down_sync(0xFFFFFFFFu, bt, off); pt += __shfl_down_sync(0xFFFFFFFFu, pt, off); }
+        if (lane_id() == 0) { atomicAdd(&wc->st_box_tests, (unsigned long long)bt); atomicAdd(&wc->st_prim_tests, (unsigned long long)pt); }
     }
 }
 
@@ -227,6 +234,19 @@ __global__ void k_resolve_u8(const float* __restrict__ sum, uint32_t width, uint
     }
 }
 
+// ---- de-interleave of gathered row shards (multi-GPU framebuffer reassembly) ----------------------------
+
+__global__ void __launch_bounds__(256) k_deinterleave(const float* __restrict__ gathered, float* __restrict__ full, uint32_t width, uint32_t height,
+                                                      uint32_t n_shards, uint32_t rows_padded) {
+    const size_t row_elems = (size_t)width * 3, n = row_elems * height;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t y = (uint32_t)(i / row_elems);
+        const size_t within = i - (size_t)y * row_elems;
+        const uint32_t shard = y % n_shards, k = y / n_shards;
+        full[i] = gathered[((size_t)shard * rows_padded + k) * row_elems + within];
+    }
+}
+
 // ---- trace (parity harness; batched `world.hit(&ray)`) -------------------------------------------------
 
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const RtRayIn* __restrict__ rays, uint64_t n, uint32_t seed_lo,
@@ -246,7 +266,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
         if (h.prim != RT_NO_PRIM) {
             const uint2 meta = __ldg(&S.prim_meta[h.prim]);
             const HitDetail hd = hit_detail(S, h.prim, o, d, h.t, true, key);
-            res.hit = 1; res.prim = (int32_t)meta.x; res.t = h.t; res.material = (int32_t)meta.y;
+            res.hit = 1; res.prim = (int32_t)meta.x; res.t = hd.t; res.material = (int32_t)meta.y;
             res.p[0] = hd.p.x; res.p[1] = hd.p.y; res.p[2] = hd.p.z;
             res.n[0] = hd.n.x; res.n[1] = hd.n.y; res.n[2] = hd.n.z;
             res.uv[0] = hd.u; res.uv[1] = hd.v;
@@ -261,17 +281,26 @@ static int g_num_sms = 0;
 static int g_extend_blocks_per_sm = 0, g_trace_blocks_per_sm = 0;
 static size_t g_extend_smem = ~(size_t)0;
 
-cudaError_t kernels_configure(int device, size_t staged_bytes) {
-    cudaDeviceProp prop;
-    cudaError_t e = cudaGetDeviceProperties(&prop, device);
+cudaError_t kernels_init(int device) {
+    if (g_num_sms > 0) return cudaSuccess;
+    int sms = 0;
+    const cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     if (e != cudaSuccess) return e;
-    g_num_sms = prop.multiProcessorCount;
+    g_num_sms = sms;
+    return cudaSuccess;
+}
+
+cudaError_t kernels_configure(int device, size_t staged_bytes) {
+    cudaError_t e = kernels_init(device);
+    if (e != cudaSuccess) return e;
     if (staged_bytes != g_extend_smem) {
-        e = cudaFuncSetAttribute(k_extend, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
+        e = cudaFuncSetAttribute(k_extend<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_extend<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_extend_blocks_per_sm, k_extend, RT_EXTEND_BLOCK, staged_bytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_extend_blocks_per_sm, k_extend<false>, RT_EXTEND_BLOCK, staged_bytes);
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_trace_blocks_per_sm, k_trace, RT_EXTEND_BLOCK, staged_bytes);
         if (e != cudaSuccess) return e;
@@ -287,9 +316,10 @@ int kernels_num_sms() { return g_num_sms; }
 void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st) {
     k_generate<<<g_num_sms * 4, 256, 0, st>>>(rc, q, wc, k);
 }
-void launch_extend(const DScene& S, const RayQueue& q, float2* hits, const WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
-                   cudaStream_t st) {
-    k_extend<<<g_num_sms * g_extend_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
+                   bool count_work, cudaStream_t st) {
+    if (count_work) k_extend<true><<<g_num_sms * g_extend_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else k_extend<false><<<g_num_sms * g_extend_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st) {
@@ -300,6 +330,10 @@ void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCoun
 }
 void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st) {
     k_resolve_u8<<<g_num_sms * 4, 256, 0, st>>>(sum, width, height, 1.0f / (float)spp, out);
+}
+void launch_deinterleave(const float* gathered, float* full, uint32_t width, uint32_t height, uint32_t n_shards, cudaStream_t st) {
+    const uint32_t rows_padded = (height + n_shards - 1) / n_shards;
+    k_deinterleave<<<g_num_sms * 4, 256, 0, st>>>(gathered, full, width, height, n_shards, rows_padded);
 }
 void launch_trace(const DScene& S, const RtRayIn* rays, uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* out, cudaStream_t st) {
     k_trace<<<g_num_sms * g_trace_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, rays, n, seed_lo, seed_hi, out);

@@ -12,15 +12,18 @@ namespace rtb {
 
 // Must be called (per process) before any launch; `staged_bytes` = shared-memory bytes of BVH prefix.
 cudaError_t kernels_configure(int device, size_t staged_bytes);
+// SM count only (kernels without dynamic shared memory).
+cudaError_t kernels_init(int device);
 int kernels_num_sms();
 
 void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st);
-void launch_extend(const DScene& S, const RayQueue& q, float2* hits, const WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
-                   cudaStream_t st);
+void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
+                   bool count_work, cudaStream_t st);
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st);
 void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, float* sum, float* sumsq, cudaStream_t st);
 void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st);
+void launch_deinterleave(const float* gathered, float* full, uint32_t width, uint32_t height, uint32_t n_shards, cudaStream_t st);
 void launch_trace(const DScene& S, const RtRayIn* rays, uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* out, cudaStream_t st);
 
 }  // namespace rtb

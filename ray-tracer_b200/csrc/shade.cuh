@@ -18,9 +18,33 @@ constexpr float RT_PI = 3.14159265358979323846f;
 
 struct HitDetail {
     float3 p, n;
+    float t;  // t of the record (refined in f64 for translation-only spheres)
     float u, v;
     bool uv_valid;
 };
+
+// Hit point and unit normal of a translation-only sphere, re-solved in f64 for the primitive extend chose.
+// A far, small sphere (r = 0.2 seen from 15 units, r = 0.25 from 200) leaves f32 only ~1e-5 of absolute
+// position accuracy, i.e. up to 1e-4 of normal error; this runs once per path SEGMENT (not per candidate), so
+// ~100 DFMA-class instructions here are noise next to the traversal, and they make point and normal as exact
+// as their f32 storage allows.  `t32` (extend's answer) only selects which root is meant.
+__device__ __forceinline__ void sphere_record_f64(float3 o, float3 d, float3 ctr, float r, float t32, float3& p, float3& unit, float& t_out) {
+    const double ox = (double)o.x - (double)ctr.x, oy = (double)o.y - (double)ctr.y, oz = (double)o.z - (double)ctr.z;
+    const double dx = d.x, dy = d.y, dz = d.z;
+    const double a = dx * dx + dy * dy + dz * dz;
+    const double b = ox * dx + oy * dy + oz * dz;
+    const double c = ox * ox + oy * oy + oz * oz - (double)r * (double)r;
+    const double sq = sqrt(fmax(b * b - a * c, 0.0));
+    const double q = (b > 0.0) ? (-b - sq) : (sq - b);
+    const double t0 = q / a, t1 = (q != 0.0) ? c / q : 0.0;
+    const double t = (fabs(t0 - (double)t32) <= fabs(t1 - (double)t32)) ? t0 : t1;
+    const double qx = fma(t, dx, ox), qy = fma(t, dy, oy), qz = fma(t, dz, oz);
+    const double inv = 1.0 / sqrt(qx * qx + qy * qy + qz * qz);
+    const double ux = qx * inv, uy = qy * inv, uz = qz * inv;
+    unit = f3((float)ux, (float)uy, (float)uz);  // geometry.rs:68 normalize(p / r)
+    p = f3((float)fma((double)r, ux, (double)ctr.x), (float)fma((double)r, uy, (double)ctr.y), (float)fma((double)r, uz, (double)ctr.z));
+    t_out = (float)t;
+}
 
 __device__ __forceinline__ void sphere_uv(float3 unit, float& u, float& v) {  // geometry.rs:35-39, acos clamped (A.11)
     u = 0.5f + atan2f(unit.x, unit.z) * (1.0f / (2.0f * RT_PI));
@@ -32,14 +56,12 @@ __device__ __forceinline__ void sphere_uv(float3 unit, float& u, float& v) {  //
 __device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, float3 o, float3 d, float t, bool want_uv, const MediumKey& key) {
     HitDetail h;
     h.u = h.v = 0.0f;
+    h.t = t;
     h.uv_valid = want_uv;
     const float4 head = __ldg(&S.prim_head[i]);
     if (head.w > 0.0f) {  // translation-only sphere
-        const float3 c = f3(head.x, head.y, head.z);
-        const float3 unit = normalize3(fma3(t, d, o) - c);  // geometry.rs:68 normalize(p / r)
-        h.n = unit;
-        h.p = fma3(head.w, unit, c);  // re-projected onto the surface (removes the radial f32 error of o + t d)
-        if (want_uv) sphere_uv(unit, h.u, h.v);
+        sphere_record_f64(o, d, f3(head.x, head.y, head.z), head.w, t, h.p, h.n, h.t);
+        if (want_uv) sphere_uv(h.n, h.u, h.v);
         return h;
     }
     const RtPrim* __restrict__ g = &S.gen[__float_as_uint(head.x)];

@@ -1,0 +1,209 @@
+"""CPU-side tests of the product: the C ABI surface (symbols, struct layouts, C-cleanliness of the headers),
+the host mirror of the reference's scene API and its flattener.  No compute entry point is called (no GPU)."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+INC = os.path.join(ROOT, "include")
+
+
+def _declared_functions(path):
+    src = open(path).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return re.findall(r"^\s*(?:const\s+)?(?:int|void|uint32_t|uint64_t|char\s*\*)\s*\*?\s*(rt[h]?_[a-z0-9_]+)\s*\(", src, flags=re.M)
+
+
+def test_library_exports_every_declared_symbol(rt):
+    declared = _declared_functions(os.path.join(INC, "rt_b200.h")) + _declared_functions(os.path.join(INC, "rt_b200_host.h"))
+    assert len(declared) >= 17
+    assert sorted(set(declared)) == sorted(set(rt.ABI_SYMBOLS))
+    for name in declared:
+        assert hasattr(rt.lib, name), f"librt_b200.so does not export {name}"
+    assert rt.lib.rt_abi_version() == 1
+
+
+def test_headers_are_plain_c_and_layouts_match_ctypes(rt, tmp_path):
+    prog = tmp_path / "layout.c"
+    prog.write_text(r'''
+#include <stdio.h>
+#include "rt_b200.h"
+#include "rt_b200_host.h"
+int main(void) {
+    printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(RtPrim), sizeof(RtMaterial), sizeof(RtTexture), sizeof(RtSceneDesc),
+           sizeof(RtCamera), sizeof(RtRenderParams), sizeof(RtStats), sizeof(RtRayIn), sizeof(RtHitOut), sizeof(RthCameraArgs));
+    return 0;
+}''')
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", INC, str(prog), "-o", str(exe)])
+    sizes = [int(v) for v in subprocess.check_output([str(exe)]).split()]
+    expect = [rt.PRIM_DTYPE.itemsize, rt.MATERIAL_DTYPE.itemsize, rt.TEXTURE_DTYPE.itemsize, C.sizeof(rt.RtSceneDesc), C.sizeof(rt.RtCamera),
+              C.sizeof(rt.RtRenderParams), C.sizeof(rt.RtStats), rt.RAY_DTYPE.itemsize, rt.HIT_DTYPE.itemsize, C.sizeof(rt.RthCameraArgs)]
+    assert sizes == expect
+    assert sizes[0] == 128 and sizes[1] == 16 and sizes[4] == 64
+
+
+def test_product_never_touches_the_oracle():
+    """The shipped path must not import, link or execute anything under oracle/ (and has no CPU fallback)."""
+    pkg = os.path.join(ROOT, "ray-tracer_b200")
+    for base, _, files in os.walk(pkg):
+        if os.path.basename(base) == "build":
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")) or f == "Makefile":
+                text = open(os.path.join(base, f), errors="ignore").read()
+                code = [ln for ln in text.splitlines() if re.search(r"#\s*include|\bimport\b|CDLL|dlopen|-l\w|\.so\b", ln)]
+                assert not any("oracle" in ln for ln in code), f"{f} pulls in the oracle"
+    ldd = subprocess.check_output(["ldd", os.path.join(pkg, "librt_b200.so")]).decode()
+    assert "oracle" not in ldd
+
+
+def test_missing_device_fails_loudly(rt):
+    try:
+        import torch
+
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present")
+    except ImportError:
+        pass
+    with pytest.raises(rt.BackendError) as e:
+        rt.Device(0)
+    assert e.value.code == rt.RT_ERR_NO_DEVICE and "no CPU fallback" in str(e.value)
+
+
+def test_unknown_scene_and_null_arguments(rt):
+    with pytest.raises(rt.BackendError):
+        rt.FlatScene("no-such-scene")
+    assert rt.lib.rt_render(None, None, None, None, None, None) == rt.RT_ERR_INVALID
+    assert rt.lib.rt_trace(None, None, 5, 0, None) == rt.RT_ERR_INVALID
+    assert rt.lib.rt_scene_create(None, None, None) == rt.RT_ERR_INVALID
+    assert b"null" in rt.lib.rt_last_error()
+
+
+# ---- flattener vs the oracle's own DFS enumeration of the same scene graph ----------------------------
+@pytest.mark.parametrize("name", ["book-one", "cornell-box", "book-two", "stress:300"])
+def test_flatten_matches_scene_graph(rt, orc, name):
+    flat = rt.FlatScene(name, 1)
+    prims, mats, texs = flat.prims(), flat.materials(), flat.textures()
+    ref = orc.Scene(name, 1).prims()
+    assert len(prims) == len(ref)
+    assert list(prims["order"]) == list(range(len(ref)))  # DFS rank = tie-break id (optimize.rs:475,484)
+    kind_map = {0: rt.PRIM_SPHERE, 1: rt.PRIM_RECT, 2: rt.PRIM_MEDIUM_SPHERE}
+    assert [kind_map[k] for k in ref["kind"]] == list(prims["kind"])
+    # composed transforms: oracle is column-major 4x4 f64, the flat record row-major 3x4 f32
+    wfl = ref["world_from_local"].reshape(-1, 4, 4).transpose(0, 2, 1)[:, :3, :]
+    got = prims["world_from_local"].reshape(-1, 3, 4)
+    assert np.allclose(got, wfl, rtol=1e-6, atol=1e-6)
+    inv = np.linalg.inv(ref["world_from_local"].reshape(-1, 4, 4).transpose(0, 2, 1))[:, :3, :]
+    assert np.allclose(prims["local_from_world"].reshape(-1, 3, 4), inv, rtol=1e-5, atol=1e-4)
+    assert np.allclose(prims["param"][:, 0], ref["param"][:, 0], rtol=1e-6)
+    # the OUTERMOST sprite's material wins (sprite.rs:124)
+    mat_kind = np.where(prims["material"] >= 0, mats["kind"][np.maximum(prims["material"], 0)].astype(np.int64), -1)
+    assert list(mat_kind) == list(ref["material_kind"])
+    assert np.all((mats["texture"] >= 0) | (mats["kind"] == rt.MAT_DIELECTRIC))
+    assert np.all(mats["texture"] < len(texs))
+
+
+def test_book_one_scene_shape(rt):  # examples/book-one.rs:103-205
+    flat = rt.FlatScene("book-one", 1)
+    prims, mats = flat.prims(), flat.materials()
+    assert 470 <= len(prims) <= 489
+    r = prims["param"][:, 0]
+    assert sorted(np.unique(r).tolist()) == pytest.approx([0.2, 1.0, 1000.0, 2000.0])
+    kinds = mats["kind"][prims["material"]]
+    small = r == np.float32(0.2)
+    frac = [np.mean(kinds[small] == k) for k in (rt.MAT_LAMBERTIAN, rt.MAT_METAL, rt.MAT_DIELECTRIC)]
+    assert abs(frac[0] - 0.3) < 0.08 and abs(frac[1] - 0.3) < 0.08 and abs(frac[2] - 0.4) < 0.08
+    assert np.sum(kinds == rt.MAT_DIFFUSE_LIGHT) == 1
+    a = flat.camera_args(16 / 9)
+    assert list(a.eye) == [13.0, 2.0, 3.0] and a.lens_radius == 0.05 and a.focus_distance == 10.0
+
+
+def test_book_two_texture_baking(rt):  # ImageTexture closure baked at texel centres (main.rs:267-280)
+    flat = rt.FlatScene("book-two", 1)
+    texs = flat.textures()
+    img = texs[texs["kind"] == rt.TEX_IMAGE]
+    assert len(img) == 1 and (img["width"][0], img["height"][0]) == (1024, 512)
+    d = flat.desc()
+    assert d.n_texels == 1024 * 512
+    texels = np.frombuffer((C.c_float * (4 * d.n_texels)).from_address(d.texels), dtype=np.float32).reshape(512, 1024, 4)
+    assert texels[..., :3].min() >= 0.0 and texels[..., :3].max() <= 1.0
+    assert np.all(texels[..., :3] * 255 == np.round(texels[..., :3] * 255))  # 8-bit source values / 255
+    kinds = flat.prims()["kind"]
+    assert np.sum(kinds == rt.PRIM_MEDIUM_SPHERE) == 2 and np.sum(kinds == rt.PRIM_RECT) == 2401 and np.sum(kinds == rt.PRIM_SPHERE) == 1005
+
+
+def test_camera_constants_match_oracle(rt, orc):  # camera.rs:34-45 in f64, rounded to f32
+    flat = rt.FlatScene("book-one", 1)
+    cam = flat.camera(400 / 225)
+    ll, hz, vt = orc.camera_frame(orc.Scene("book-one", 1).camera(400 / 225))
+    assert np.array_equal(np.array(cam.lower_left[:]), ll.astype(np.float32))
+    assert np.array_equal(np.array(cam.horizontal[:]), hz.astype(np.float32))
+    assert np.array_equal(np.array(cam.vertical[:]), vt.astype(np.float32))
+    assert cam.lens_radius == np.float32(0.05)
+
+
+# ---- independent numpy brute force over the FLATTENED tables vs the oracle's BVH traversal -------------
+def _brute_force(prims, rays):
+    """Closest hit by testing every flattened primitive (f64 numpy, written from SURVEY Appendix A):
+    pins scene-graph flattening, transform composition and the oracle's BVH recursion against each other."""
+    n = len(rays)
+    best_t = np.full(n, np.inf)
+    best_order = np.full(n, -1, dtype=np.int64)
+    o, d = rays[:, :3], rays[:, 3:]
+    for p in prims:
+        if p["kind"] == 2:
+            continue  # media are stochastic; tested separately
+        m = p["local_from_world"].reshape(3, 4).astype(np.float64)
+        lo = o @ m[:, :3].T + m[:, 3]
+        ld = d @ m[:, :3].T
+        if p["kind"] == 0:
+            r = float(p["param"][0])
+            a = np.sum(ld * ld, axis=1)
+            b = 2 * np.sum(lo * ld, axis=1)
+            c = np.sum(lo * lo, axis=1) - r * r
+            disc = b * b - 4 * a * c
+            ok = disc >= 0
+            sq = np.sqrt(np.where(ok, disc, 0))
+            t1, t2 = (-b - sq) / (2 * a), (-b + sq) / (2 * a)
+            t = np.where(t1 > 1e-6, t1, np.where(t2 > 1e-6, t2, np.inf))
+            t = np.where(ok, t, np.inf)
+        else:
+            w, h = float(p["param"][0]), float(p["param"][1])
+            with np.errstate(divide="ignore", invalid="ignore"):
+                t = -lo[:, 2] / ld[:, 2]
+            x, y = lo[:, 0] + ld[:, 0] * t, lo[:, 1] + ld[:, 1] * t
+            bad = ~np.isfinite(t) | (t < 1e-6) | (x < -w / 2) | (x > w / 2) | (y < -h / 2) | (y > h / 2)
+            t = np.where(bad, np.inf, t)
+        win = t < best_t
+        best_t = np.where(win, t, best_t)
+        best_order = np.where(win, p["order"], best_order)
+    return best_t, best_order
+
+
+@pytest.mark.parametrize("name", ["book-one", "cornell-box"])
+def test_oracle_bvh_agrees_with_bruteforce_over_flat_tables(rt, orc, name):
+    prims = rt.FlatScene(name, 1).prims()
+    s = orc.Scene(name, 1)
+    rays = orc.camera_rays(s.camera(1.5), 30, 20)
+    hits = s.trace(rays)
+    pts = hits["p"][hits["hit"] == 1]
+    rng = np.random.default_rng(2)
+    dirs = rng.normal(size=(len(pts), 3))
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    bounce = np.concatenate([pts + 1e-3 * dirs * np.maximum(1.0, np.abs(pts).max(axis=1, keepdims=True)), dirs], axis=1)
+    rays = np.concatenate([rays, bounce])
+    hits = s.trace(rays)
+    t, order = _brute_force(prims, rays)
+    st = hits["stable"] == 1
+    assert st.mean() > 0.9
+    assert np.array_equal(np.isfinite(t)[st], hits["hit"][st] == 1)
+    assert np.array_equal(order[st], hits["prim"][st])
+    both = st & np.isfinite(t)
+    tol = 1e-4 * np.maximum(hits["t"][both], 1e-3) + 64 * hits["t_sens"][both]  # f32 matrices in the flat tables
+    assert np.all(np.abs(t[both] - hits["t"][both]) <= tol)
