@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")  # override: tuning variants only
 
 RENDER_STAGE_TIMING, RENDER_COUNT_WORK = 1, 2
 RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM = 0, -1, -2, -3, -4, -5
@@ -256,9 +256,9 @@ class Scene:
     def render(self, cam, width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, want_sumsq=True, flags=0):
         """rt_render with host buffers: returns (sum[rows,W,3], sumsq or None, RtStats); rows y = row_begin + k*row_stride."""
         prm = self.params(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity, flags)
-        rows = len(range(row_begin, height, row_stride))
-        s = np.zeros((rows, width, 3), dtype=np.float32)
-        q = np.zeros((rows, width, 3), dtype=np.float32) if want_sumsq else None
+        rows = len(range(row_begin, height, row_stride)) if row_stride > 0 else 0  # the library rejects stride 0 / empty shards
+        s = np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows]
+        q = np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows] if want_sumsq else None
         st = RtStats()
         _check(lib.rt_render(self._h, C.byref(cam), C.byref(prm), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
         return s, q, st

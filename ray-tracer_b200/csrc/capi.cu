@@ -66,6 +66,7 @@ struct RtContext {
     DevBuf<float2> hits;
     DevBuf<WaveCounters> counters;
     DevBuf<float> fb_sum, fb_sumsq;
+    DevBuf<double> acc;  // f64 per-pixel accumulators (sum, then sum of squares)
     DevBuf<uint8_t> scratch;
     WaveCounters* h_status = nullptr;  // pinned
     bool stage_timing = false;
@@ -75,7 +76,7 @@ struct RtContext {
 struct RtScene {
     RtContext* ctx = nullptr;
     DScene d{};
-    DevBuf<float4> nodes, prim_head, texels;
+    DevBuf<float4> nodes, prim_head, texels, rects;
     DevBuf<uint2> prim_meta;
     DevBuf<RtPrim> gen;
     DevBuf<DMaterial> mats;
@@ -197,7 +198,7 @@ void rt_shutdown(RtContext* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     for (int i = 0; i < 2; ++i) { ctx->qa[i].release(); ctx->qb[i].release(); ctx->qc[i].release(); }
-    ctx->done.release(); ctx->hits.release(); ctx->counters.release(); ctx->fb_sum.release(); ctx->fb_sumsq.release(); ctx->scratch.release();
+    ctx->done.release(); ctx->hits.release(); ctx->counters.release(); ctx->fb_sum.release(); ctx->fb_sumsq.release(); ctx->acc.release(); ctx->scratch.release();
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -217,25 +218,52 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     for (uint32_t i = 0; i < n; ++i) boxes[i] = primBox(desc->prims[i]);
     BvhOptions opt;
     if (const char* ml = std::getenv("RT_B200_BVH_MAX_LEAF")) { const int v = std::atoi(ml); if (v >= 1 && v <= 16) opt.max_leaf = (uint32_t)v; }
-    const BvhResult bvh = build_bvh(boxes, opt);
+    opt.max_always = RT_MAX_ALWAYS;
+    uint32_t small_limit = RT_SMALL_SCENE;
+    if (const char* sl = std::getenv("RT_B200_SMALL_SCENE")) small_limit = (uint32_t)std::max(0, std::min(std::atoi(sl), (int)RT_SMALL_SCENE));
+    const bool small = n <= small_limit;
+    BvhResult bvh;
+    if (small) {
+        // no tree: primitives sorted by the reference's DFS rank, so a strict `<` scan reproduces its tie rule
+        bvh.order.resize(n);
+        for (uint32_t i = 0; i < n; ++i) bvh.order[i] = i;
+        std::stable_sort(bvh.order.begin(), bvh.order.end(), [&](uint32_t a, uint32_t b) { return desc->prims[a].order < desc->prims[b].order; });
+    } else {
+        bvh = build_bvh(boxes, opt);
+    }
     if (bvh.depth + 2 > (uint32_t)RT_STACK_DEPTH) return fail(RT_ERR_UNSUPPORTED, "BVH depth %u exceeds the traversal stack", bvh.depth);
 
     // primitives in leaf order
     std::vector<float4> head(n);
     std::vector<uint2> meta(n);
     std::vector<RtPrim> gen;
+    std::vector<float4> rects;
     bool has_media = false;
+    float always_k[RT_MAX_ALWAYS] = {0};
     for (uint32_t i = 0; i < n; ++i) {
         const RtPrim& p = desc->prims[bvh.order[i]];
         meta[i] = make_uint2(p.order, (uint32_t)p.material);
         if (p.kind == RT_PRIM_SPHERE && p.param[0] > 0.0f && translationOnly(p)) {
             head[i] = make_float4(p.world_from_local[3], p.world_from_local[7], p.world_from_local[11], p.param[0]);
+            if (i < bvh.n_always) {
+                const double cx = head[i].x, cy = head[i].y, cz = head[i].z, r = head[i].w;
+                always_k[i] = (float)(cx * cx + cy * cy + cz * cz - r * r);
+            }
         } else {
-            uint32_t gi = (uint32_t)gen.size(), kind = p.kind;
-            float fx, fy;
+            uint32_t gi = (uint32_t)gen.size(), kind = p.kind, ri = 0;
+            if (p.kind == RT_PRIM_RECT) {
+                ri = (uint32_t)(rects.size() / 4);
+                const float* m = p.local_from_world;
+                rects.push_back(make_float4(m[8], m[9], m[10], m[11]));
+                rects.push_back(make_float4(m[0], m[1], m[2], m[3]));
+                rects.push_back(make_float4(m[4], m[5], m[6], m[7]));
+                rects.push_back(make_float4(0.5f * p.param[0], 0.5f * p.param[1], 0.0f, 0.0f));
+            }
+            float fx, fy, fz;
             std::memcpy(&fx, &gi, 4);
             std::memcpy(&fy, &kind, 4);
-            head[i] = make_float4(fx, fy, 0.0f, -1.0f);
+            std::memcpy(&fz, &ri, 4);
+            head[i] = make_float4(fx, fy, fz, -1.0f);
             gen.push_back(p);
             has_media |= (p.kind == RT_PRIM_MEDIUM_SPHERE);
         }
@@ -264,6 +292,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     if (e == cudaSuccess) e = upload(s->prim_head, head.data(), head.size());
     if (e == cudaSuccess) e = upload(s->prim_meta, meta.data(), meta.size());
     if (e == cudaSuccess) e = upload(s->gen, gen.data(), gen.size());
+    if (e == cudaSuccess) e = upload(s->rects, rects.data(), rects.size());
     if (e == cudaSuccess) e = upload(s->mats, mats.data(), mats.size());
     if (e == cudaSuccess) e = upload(s->texs, desc->textures, (size_t)desc->n_textures);
     if (e == cudaSuccess) e = upload(s->texels, reinterpret_cast<const float4*>(desc->texels), (size_t)desc->n_texels);
@@ -272,16 +301,23 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
         return fail(e == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(e));
     }
     DScene& d = s->d;
-    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p;
+    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.rects = s->rects.p;
     d.mats = s->mats.p; d.texs = s->texs.p; d.texels = s->texels.p;
     d.n_nodes = (uint32_t)bvh.nodes.size(); d.n_prims = n; d.n_always = bvh.n_always; d.n_gen = (uint32_t)gen.size();
     d.n_mats = desc->n_materials; d.n_texs = desc->n_textures;
     d.root_is_leaf = bvh.root_is_leaf ? 1u : 0u;
-    uint32_t staged = std::min<uint32_t>(d.n_nodes, RT_MAX_STAGED_NODES);
+    // whole tree in shared memory when it fits; otherwise only the top levels (every ray walks them) so that
+    // shared memory does not cost occupancy and L1 keeps the deeper, ray-dependent nodes
+    uint32_t staged = d.n_nodes <= RT_MAX_STAGED_NODES ? d.n_nodes : RT_TOP_STAGED_NODES;
     if (const char* sn = std::getenv("RT_B200_STAGED_NODES")) staged = std::min<uint32_t>(d.n_nodes, (uint32_t)std::max(0, std::atoi(sn)));
     d.n_staged_nodes = staged & ~1u;
     d.has_media = has_media ? 1u : 0u;
-    s->staged_bytes = (size_t)d.n_staged_nodes * 32;
+    d.n_rects = (uint32_t)(rects.size() / 4);
+    d.n_small = small ? n : 0u;
+    d.n_staged_prims = (n <= RT_MAX_STAGED_PRIMS && d.n_rects <= RT_MAX_STAGED_RECTS) ? n : 0u;
+    if (const char* sp = std::getenv("RT_B200_STAGE_PRIMS")) { if (sp[0] == '0') d.n_staged_prims = 0u; }
+    std::memcpy(d.always_k, always_k, sizeof(always_k));
+    s->staged_bytes = (size_t)d.n_staged_nodes * 32 + (size_t)d.n_staged_prims * 16 + (d.n_staged_prims ? (size_t)d.n_rects * 64 : 0);
     *out = s;
     return RT_OK;
 }
@@ -289,7 +325,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
 void rt_scene_destroy(RtScene* s) {
     if (!s) return;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->rects.release(); s->mats.release(); s->texs.release(); s->texels.release();
     delete s;
 }
 
@@ -304,7 +340,7 @@ int rt_scene_bvh_info(const RtScene* s, uint32_t* n_nodes, uint32_t* n_always, u
 uint64_t rt_scene_device_bytes(const RtScene* s) {
     if (!s) return 0;
     return (uint64_t)s->nodes.n * sizeof(float4) + (uint64_t)s->prim_head.n * sizeof(float4) + (uint64_t)s->prim_meta.n * sizeof(uint2) +
-           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
+           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)s->rects.n * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
            (uint64_t)s->texels.n * sizeof(float4);
 }
 
@@ -348,10 +384,20 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     RT_CUDA(ctx->counters.ensure(1));
     RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes));
 
-    const size_t fb_bytes = (size_t)rc.pixels_local * 3 * sizeof(float);
+    const size_t fb_elems = (size_t)rc.pixels_local * 3;
+    RT_CUDA(ctx->acc.ensure(fb_elems * 2));
+    double* acc_sum = ctx->acc.p;
+    double* acc_sumsq = d_sumsq ? ctx->acc.p + fb_elems : nullptr;
     RT_CUDA(cudaMemsetAsync(ctx->counters.p, 0, sizeof(WaveCounters), st));
-    RT_CUDA(cudaMemsetAsync(d_sum, 0, fb_bytes, st));
-    if (d_sumsq) RT_CUDA(cudaMemsetAsync(d_sumsq, 0, fb_bytes, st));
+    RT_CUDA(cudaMemsetAsync(ctx->acc.p, 0, fb_elems * (d_sumsq ? 2 : 1) * sizeof(double), st));
+
+    if (prm->max_depth == 0) {  // color(ray, world, 0) is black without tracing (src/render.rs:6-8)
+        RT_CUDA(cudaMemsetAsync(d_sum, 0, fb_elems * sizeof(float), st));
+        if (d_sumsq) RT_CUDA(cudaMemsetAsync(d_sumsq, 0, fb_elems * sizeof(float), st));
+        RT_CUDA(cudaStreamSynchronize(st));
+        if (stats) { std::memset(stats, 0, sizeof(*stats)); stats->paths = rc.paths_total; stats->bvh_nodes = scene->d.n_nodes; stats->bvh_always = scene->d.n_always; }
+        return RT_OK;
+    }
 
     const RayQueue q[2] = {{ctx->qa[0].p, ctx->qb[0].p, ctx->qc[0].p}, {ctx->qa[1].p, ctx->qb[1].p, ctx->qc[1].p}};
     WaveCounters* wc = ctx->counters.p;
@@ -390,7 +436,7 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
         if (timing) RT_CUDA(stage_event(k, 2));
         launch_shade(scene->d, rc, qin, qout, ctx->hits.p, ctx->done.p, wc, ku, st);
         if (timing) RT_CUDA(stage_event(k, 3));
-        launch_accumulate(rc, ctx->done.p, wc, ku, d_sum, d_sumsq, st);
+        launch_accumulate(rc, ctx->done.p, wc, ku, acc_sum, acc_sumsq, st);
         if (timing) RT_CUDA(stage_event(k, 4));
         launches += 4;
         ++k;
@@ -401,6 +447,9 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
             else if (k > iter_limit) return fail(RT_ERR_CUDA, "wavefront did not terminate after %llu iterations", (unsigned long long)k);
         }
     }
+    launch_finish(acc_sum, fb_elems, d_sum, st);
+    if (d_sumsq) launch_finish(acc_sumsq, fb_elems, d_sumsq, st);
+    launches += d_sumsq ? 2 : 1;
     RT_CUDA(cudaEventRecord(ctx->ev1, st));
     RT_CUDA(cudaEventSynchronize(ctx->ev1));
     RT_CUDA(cudaGetLastError());

@@ -6,7 +6,11 @@
 //    levels form a prefix that the extend kernel stages into shared memory.
 //  * Primitives are reordered into leaf order.  `prim_head[i]` (float4) is all the extend kernel needs
 //    for the common case — a translation-only sphere (cx, cy, cz, r>0).  Anything else (rectangles,
-//    rotated / scaled spheres, media) stores w = -1 and the index of a 128-byte general record in x.
+//    rotated / scaled spheres, media) stores w = -1, its kind in y and the index of its 128-byte general
+//    record in x; rectangles also carry in z the index of a compact 64-byte record in `rects` (rows z, x, y of
+//    the object<-world matrix + half extents) which is what the extend kernel tests.
+//  * Scenes of at most RT_SMALL_SCENE primitives have no tree (n_small = n_prims, primitives stay in the
+//    reference's DFS order) and are tested as a warp-uniform list out of shared memory.
 //  * `prim_meta[i]` = {order (reference DFS rank), material index} is read by shade / on exact t ties.
 //  * Materials are 32-byte records with the solid colour inlined (no texture hop for SolidColor).
 #pragma once
@@ -20,9 +24,18 @@ namespace rtb {
 
 constexpr uint32_t RT_NO_PRIM = 0xFFFFFFFFu;
 constexpr int RT_STACK_DEPTH = 64;       // traversal stack entries (builder caps tree depth below this)
+#ifndef RT_SMEM_STACK_N
+#define RT_SMEM_STACK_N 24
+#endif
+constexpr uint32_t RT_SMEM_STACK = RT_SMEM_STACK_N;   // of which this many per thread live in shared memory (96 B/thread)
 constexpr uint32_t RT_RING = 4;          // ring length of the per-iteration queue counters
-constexpr uint32_t RT_MAX_STAGED_NODES = 2048;  // 64 KB of BVH prefix staged in shared memory by extend
+constexpr uint32_t RT_MAX_STAGED_NODES = 2048;  // a BVH of at most this many nodes (64 KB) is staged whole in shared memory by extend
+constexpr uint32_t RT_TOP_STAGED_NODES = 256;   // larger trees: only this breadth-first prefix (top 8 levels, 8 KB)
 constexpr uint32_t RT_MAX_STAGED_MATS = 512;    // 16 KB of material records staged in shared memory by shade
+constexpr uint32_t RT_MAX_STAGED_PRIMS = 1024;  // primitive heads (16 KB) staged by extend when the whole table fits
+constexpr uint32_t RT_MAX_STAGED_RECTS = 256;   // compact rectangle records (16 KB) staged together with the heads
+constexpr uint32_t RT_SMALL_SCENE = 32;         // at most this many primitives: linear list instead of a BVH
+constexpr uint32_t RT_MAX_ALWAYS = 8;           // always-tested list (sky / ground / fog)
 
 struct DMaterial {       // 32 B, read as two float4
     uint32_t kind;       // RtMaterialKind
@@ -35,6 +48,7 @@ struct DScene {
     const float4* nodes;       // 2 float4 per node
     const float4* prim_head;   // per device primitive
     const uint2* prim_meta;    // {order, material (int32 bits)}
+    const float4* rects;       // 4 float4 per rectangle: row z, row x, row y of object<-world (xyz, translation), (hx, hy, 0, 0)
     const RtPrim* gen;         // general records (non translation-only-sphere primitives)
     const DMaterial* mats;
     const RtTexture* texs;
@@ -43,6 +57,10 @@ struct DScene {
     uint32_t root_is_leaf;     // BVH over < 2 primitives: node 0 is a leaf
     uint32_t n_staged_nodes;   // prefix of `nodes` staged in shared memory
     uint32_t has_media;
+    uint32_t n_rects;
+    uint32_t n_staged_prims;   // n_prims when heads (and all rects) are staged in shared memory, else 0
+    uint32_t n_small;          // > 0: no tree, test primitives [0, n_small) in order
+    float always_k[RT_MAX_ALWAYS];  // |centre|^2 - r^2 of the always-list spheres, rounded from f64 (big_sphere_hit)
 };
 
 // One queue buffer of live rays, SoA of three float4 streams (48 B per ray):

@@ -8,8 +8,12 @@
 //   Rectangle::hit                src/geometry.rs:152-181   (t >= 1e-6, inclusive bounds)
 //   Sprite::hit                   src/sprite.rs:94-138      (object-space ray, direction not renormalised)
 //   ConstantMedium::hit           src/volume.rs:46-100      (free-flight sampling inside hit())
+//   Hit for Vec<...>              src/geometry.rs:76-116    (linear list, strict <)
 // The traversal itself is NOT the reference's (which visits both children unconditionally): it is
 // ordered, t-pruned and runs over a rebuilt SAH tree; closest-hit results are topology independent.
+// Scenes of at most RT_SMALL_SCENE primitives skip the tree: every lane of a warp walks the same
+// shared-memory primitive list in DFS order (the reference's own linear-list Hit), which costs fewer
+// instructions than any traversal and keeps all 32 lanes converged.
 //
 // f32 policy (DESIGN.md "Precision"): the reference relies on f64 and `t > 1e-6` to reject the hit
 // at a scattered ray's own origin.  In f32 a hit point on the r = 1000 ground sphere carries ~6e-5 of
@@ -24,6 +28,13 @@
 #include "device_scene.h"
 #include "philox.h"
 
+#ifndef RT_OPT_STACK_T
+#define RT_OPT_STACK_T 0   // keep the entry distance of pushed subtrees and skip them at pop time once a closer hit exists
+#endif
+#ifndef RT_OPT_MERGE_LEAF
+#define RT_OPT_MERGE_LEAF 1  // test sibling leaves as one contiguous primitive range (one loop site)
+#endif
+
 namespace rtb {
 
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
@@ -34,6 +45,7 @@ __device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x *
 __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
 __device__ __forceinline__ float dot3(float3 a, float3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ float dot3(float4 a, float3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
 __device__ __forceinline__ float3 fma3(float s, float3 a, float3 b) { return f3(fmaf(s, a.x, b.x), fmaf(s, a.y, b.y), fmaf(s, a.z, b.z)); }
 __device__ __forceinline__ float3 normalize3(float3 a) {
     const float inv = rsqrtf(dot3(a, a));
@@ -48,69 +60,84 @@ __device__ __forceinline__ float3 xform_vector(const float* __restrict__ m, floa
     return f3(fmaf(m[0], v.x, fmaf(m[1], v.y, m[2] * v.z)), fmaf(m[4], v.x, fmaf(m[5], v.y, m[6] * v.z)),
               fmaf(m[8], v.x, fmaf(m[9], v.y, m[10] * v.z)));
 }
+// 1-ulp-class hardware approximations (MUFU.RCP / MUFU.SQRT + one multiply); the precise sequences cost ~8
+// instructions each and sit in the innermost loops.  Errors of a few ulp in t are far inside the 1e-4 budget.
+#ifdef RT_PRECISE_RCP
+__device__ __forceinline__ float fast_rcp(float x) { return 1.0f / x; }
+#else
+__device__ __forceinline__ float fast_rcp(float x) { return __fdividef(1.0f, x); }
+#endif
+__device__ __forceinline__ float fast_sqrt(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 
 constexpr float RT_T_EPS = 1e-6f;  // geometry.rs:57-66,159
 
+// Per-ray constants shared by every primitive / box test.
+struct RayCtx {
+    float3 o, d;
+    float a, inv_a;    // d.d and its reciprocal
+    float3 inv, oinv;  // 1/d and o/d for the slab test
+};
+
 // Both roots of |oc + t d|^2 = r^2 (tn <= tf); false when the ray misses.  Discriminant from the
 // perpendicular offset l = oc - (b/a) d (no b^2 - a c cancellation), roots from the stable q form.
-__device__ __forceinline__ bool sphere_roots(float3 oc, float3 d, float r, float& tn, float& tf) {
-    const float a = dot3(d, d);
+__device__ __forceinline__ bool sphere_roots(float3 oc, float3 d, float a, float inv_a, float r, float& tn, float& tf) {
     const float b = dot3(oc, d);  // half-b
-    const float inv_a = 1.0f / a;
     const float3 l = fma3(-b * inv_a, d, oc);
     const float disc = a * fmaf(r, r, -dot3(l, l));  // = b^2 - a c
     if (!(disc >= 0.0f)) return false;
-    const float sq = sqrtf(disc);
+    const float sq = fast_sqrt(disc);
     const float c = fmaf(-r, r, dot3(oc, oc));
-    if (b > 0.0f) {
-        const float q = -b - sq;
-        tn = q * inv_a;
-        tf = c / q;
-    } else {
-        const float q = sq - b;
-        tf = q * inv_a;
-        tn = (q != 0.0f) ? c / q : 0.0f;
-    }
-    if (tn > tf) { const float s = tn; tn = tf; tf = s; }
+    const float q = (b > 0.0f) ? (-b - sq) : (sq - b);
+    const float t0 = q * inv_a;
+    const float t1 = (q != 0.0f) ? __fdividef(c, q) : 0.0f;
+    tn = fminf(t0, t1);
+    tf = fmaxf(t0, t1);
     return true;
+}
+__device__ __forceinline__ bool sphere_roots(float3 oc, float3 d, float r, float& tn, float& tf) {
+    const float a = dot3(d, d);
+    return sphere_roots(oc, d, a, 1.0f / a, r, tn, tf);
 }
 
 // Sphere::hit with the self-origin rule.  Returns t or +inf.
-__device__ __forceinline__ float sphere_hit(float3 oc, float3 d, float r, bool is_self) {
+__device__ __forceinline__ float sphere_hit(const RayCtx& R, float3 ctr, float r, bool is_self) {
+    const float3 oc = R.o - ctr;
     if (is_self) {
-        const float b = dot3(oc, d);
-        if (b >= 0.0f) return CUDART_INF_F;         // leaving outward: cannot re-hit a convex surface
-        const float t = -2.0f * b / dot3(d, d);     // far root with the origin on the surface
+        const float b = dot3(oc, R.d);
+        if (b >= 0.0f) return CUDART_INF_F;    // leaving outward: cannot re-hit a convex surface
+        const float t = -2.0f * b * R.inv_a;   // far root with the origin on the surface
         return t > RT_T_EPS ? t : CUDART_INF_F;
     }
     float tn, tf;
-    if (!sphere_roots(oc, d, r, tn, tf)) return CUDART_INF_F;
+    if (!sphere_roots(oc, R.d, R.a, R.inv_a, r, tn, tf)) return CUDART_INF_F;
     if (tn > RT_T_EPS) return tn;
     if (tf > RT_T_EPS) return tf;
     return CUDART_INF_F;
 }
 
-// Same test in f64 for the primitives of the always-tested list (sky / ground spheres of radius 1e3):
-// a ray that starts 1e-3 above the r = 1000 ground and grazes it has c = |oc|^2 - r^2 ~ 2 against an f32
-// rounding error of |oc|^2 ~ 0.1, i.e. t would be off by percents.  o - c is exact in f64 for f32 inputs.
-__device__ __forceinline__ float sphere_hit_f64(float3 o, float3 ctr, float3 d, float r, bool is_self) {
-    const double ox = (double)o.x - (double)ctr.x, oy = (double)o.y - (double)ctr.y, oz = (double)o.z - (double)ctr.z;
-    const double dx = d.x, dy = d.y, dz = d.z;
-    const double a = dx * dx + dy * dy + dz * dz;
-    const double b = ox * dx + oy * dy + oz * dz;  // half-b
+// The same test for the huge spheres of the always-tested list (ground r = 1000, sky r = 2000, fog r = 5000),
+// expanded around the WORLD origin: c = |o|^2 - 2 o.ctr + K with K = |ctr|^2 - r^2 rounded once from f64 on the
+// host, b = o.d - ctr.d.  For a ray 1e-3 above the r = 1000 ground the centre-relative form has c ~ 2 with an f32
+// error of 2 |oc| ulp(|oc|) ~ 0.1 (t off by percents); this form has an error of ~ulp(2 o.ctr) ~ 1e-5.
+__device__ __forceinline__ float big_sphere_hit(const RayCtx& R, float3 ctr, float r, float K, bool is_self) {
+    const float b = dot3(R.o, R.d) - dot3(ctr, R.d);
     if (is_self) {
-        if (b >= 0.0) return CUDART_INF_F;
-        const float t = (float)(-2.0 * b / a);
+        if (b >= 0.0f) return CUDART_INF_F;
+        const float t = -2.0f * b * R.inv_a;
         return t > RT_T_EPS ? t : CUDART_INF_F;
     }
-    const double c = ox * ox + oy * oy + oz * oz - (double)r * (double)r;
-    const double disc = b * b - a * c;
-    if (!(disc >= 0.0)) return CUDART_INF_F;
-    const double sq = sqrt(disc);
-    const double q = (b > 0.0) ? (-b - sq) : (sq - b);  // stable: no cancellation in q
-    double t0 = q / a, t1 = (q != 0.0) ? c / q : 0.0;
-    if (t0 > t1) { const double s = t0; t0 = t1; t1 = s; }
-    const float tn = (float)t0, tf = (float)t1;
+    const float c = fmaf(-2.0f, dot3(R.o, ctr), dot3(R.o, R.o)) + K;
+    const float disc = fmaf(b, b, -R.a * c);
+    if (!(disc >= 0.0f)) return CUDART_INF_F;
+    const float sq = fast_sqrt(disc);
+    const float q = (b > 0.0f) ? (-b - sq) : (sq - b);
+    const float t0 = q * R.inv_a;
+    const float t1 = (q != 0.0f) ? __fdividef(c, q) : 0.0f;
+    const float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
     if (tn > RT_T_EPS) return tn;
     if (tf > RT_T_EPS) return tf;
     return CUDART_INF_F;
@@ -123,6 +150,20 @@ __device__ __forceinline__ float rect_hit(float3 o, float3 d, float w, float h) 
     const float x = fmaf(d.x, t, o.x), y = fmaf(d.y, t, o.y);
     const float hx = 0.5f * w, hy = 0.5f * h;
     if (x < -hx || x > hx || y < -hy || y > hy) return CUDART_INF_F;
+    return t;
+}
+
+// The same test on the compact 64-byte record the extend kernel reads (device_scene.h "rects"): rows of the
+// object<-world matrix, so t = -(row_z . o + tz) / (row_z . d) is the reference's (0 - o'.z) / d'.z, and the
+// object-space x, y come from the world-space hit point.
+__device__ __forceinline__ float rect_hit(const RayCtx& R, const float4 rz, const float4 rx, const float4 ry, const float4 ext) {
+    const float den = dot3(rz, R.d);
+    const float num = -(dot3(rz, R.o) + rz.w);
+    const float t = __fdividef(num, den);
+    if (!(t >= RT_T_EPS) || !(t < CUDART_INF_F)) return CUDART_INF_F;  // rejects NaN, inf, t < 1e-6
+    const float3 p = fma3(t, R.d, R.o);
+    const float x = dot3(rx, p) + rx.w, y = dot3(ry, p) + ry.w;
+    if (fabsf(x) > ext.x || fabsf(y) > ext.y) return CUDART_INF_F;
     return t;
 }
 
@@ -161,46 +202,30 @@ __device__ __forceinline__ float medium_sphere_hit(float3 o, float3 d, float r, 
     return entering ? t1 + distance : distance;
 }
 
-// Test device primitive `i`.  Returns t or +inf.  BIG = primitive of the always-tested list (f64 sphere test).
-template <bool BIG = false>
-__device__ __forceinline__ float prim_hit(const DScene& S, uint32_t i, float3 o, float3 d, uint32_t self_prim, const MediumKey& key) {
-    const float4 h = __ldg(&S.prim_head[i]);
-    if (h.w > 0.0f) {
-        if (BIG) return sphere_hit_f64(o, f3(h.x, h.y, h.z), d, h.w, i == self_prim);
-        return sphere_hit(o - f3(h.x, h.y, h.z), d, h.w, i == self_prim);
-    }
-    const RtPrim* __restrict__ g = &S.gen[__float_as_uint(h.x)];
+// Primitive of a 128-byte general record (rotated / scaled sphere, negative radius, medium).  Returns t or +inf.
+// Kept out of line: it is the rare path and would otherwise triple the size of the traversal loop.
+#ifndef RT_GENERAL_INLINE
+#define RT_GENERAL_INLINE __noinline__
+#endif
+__device__ RT_GENERAL_INLINE float general_hit(const RtPrim* __restrict__ g, float3 o, float3 d, bool is_self, const MediumKey key) {
     const float3 lo = xform_point(g->local_from_world, o);
     const float3 ld = xform_vector(g->local_from_world, d);
     const uint32_t kind = g->kind;
-    if (kind == RT_PRIM_RECT) return (i == self_prim) ? CUDART_INF_F : rect_hit(lo, ld, g->param[0], g->param[1]);
+    if (kind == RT_PRIM_RECT) return is_self ? CUDART_INF_F : rect_hit(lo, ld, g->param[0], g->param[1]);
     if (kind == RT_PRIM_SPHERE) {
         const float r = g->param[0];
-        if (r > 0.0f) return sphere_hit(lo, ld, r, i == self_prim);
-        // negative radius (normal flipped by geometry.rs:68): plain roots, no self rule
         float tn, tf;
+        if (r > 0.0f && is_self) {
+            const float b = dot3(lo, ld);
+            if (b >= 0.0f) return CUDART_INF_F;
+            const float t = -2.0f * b / dot3(ld, ld);
+            return t > RT_T_EPS ? t : CUDART_INF_F;
+        }
+        // (a negative radius flips the normal, geometry.rs:68: plain roots, no self rule)
         if (!sphere_roots(lo, ld, r, tn, tf)) return CUDART_INF_F;
         return tn > RT_T_EPS ? tn : (tf > RT_T_EPS ? tf : CUDART_INF_F);
     }
     return medium_sphere_hit(lo, ld, g->param[0], g->param[1], g->order, key);
-}
-
-// ---- BVH traversal -----------------------------------------------------------------------------
-
-struct RayBox {  // per-ray constants of the slab test
-    float3 inv, oinv;  // 1/d and o/d
-};
-
-// Slab test against [0, tmax]; returns entry distance or +inf.  fminf/fmaxf drop NaNs (0 * inf when the
-// origin lies on a slab of a zero direction component), which errs on the side of "hit" like the
-// reference's `if t0 > tmin` form.  The far distance is widened by 2 ulp (Ize, robust BVH traversal).
-__device__ __forceinline__ float slab(const float4 lo, const float4 hi, const RayBox& rb, float tmax) {
-    const float x0 = fmaf(lo.x, rb.inv.x, -rb.oinv.x), x1 = fmaf(hi.x, rb.inv.x, -rb.oinv.x);
-    const float y0 = fmaf(lo.y, rb.inv.y, -rb.oinv.y), y1 = fmaf(hi.y, rb.inv.y, -rb.oinv.y);
-    const float z0 = fmaf(lo.z, rb.inv.z, -rb.oinv.z), z1 = fmaf(hi.z, rb.inv.z, -rb.oinv.z);
-    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
-    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax)) * 1.0000004f;
-    return tn <= tf ? tn : CUDART_INF_F;
 }
 
 struct ClosestHit {
@@ -214,85 +239,210 @@ struct TraversalWork {
     uint32_t prim_tests;  // primitive intersection tests
 };
 
-template <bool BIG = false>
-__device__ __forceinline__ void consider(const DScene& S, uint32_t i, float3 o, float3 d, uint32_t self_prim, const MediumKey& key, ClosestHit& best) {
-    const float t = prim_hit<BIG>(S, i, o, d, self_prim, key);
-    if (t < best.t) { best.t = t; best.prim = i; }
-    else if (t == best.t && t < CUDART_INF_F && best.prim != RT_NO_PRIM) {
-        // exact tie: the reference keeps the DFS-earlier leaf (optimize.rs:475,484)
+// Shared-memory staging of the scene prefix (see k_extend): `nodes` = copy of S.nodes[0 .. 2*n_staged_nodes),
+// `heads` / `rects` = copies of the primitive tables when the whole scene is small enough (S.n_staged_prims).
+// All four are 32-bit SHARED-WINDOW byte addresses, read with explicit ld.shared / st.shared: handing the compiler
+// generic pointers made it merge the shared and global paths into address-space-agnostic LD (ncu/SASS: 16 generic LD,
+// no LDS, no LDG.CONSTANT) and cost 25-40 % on scenes whose nodes live in global memory.
+struct Staged {
+    uint32_t nodes;
+    uint32_t heads;
+    uint32_t rects;
+    uint32_t stack;  // this thread's column of the shared-memory traversal stack: entry k at stack + k * 4 * blockDim.x
+};
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+
+// Test device primitive `i`.  Returns t or +inf.  BIG = primitive of the always-tested list.
+template <bool BIG>
+__device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uint32_t i, const RayCtx& R, uint32_t self_prim, const MediumKey& key) {
+    const bool staged = i < S.n_staged_prims;
+    float4 h;
+    if (staged) h = lds128(sm.heads + 16u * i);
+    else h = __ldg(&S.prim_head[i]);
+    if (h.w > 0.0f) {
+        if (BIG) return big_sphere_hit(R, f3(h.x, h.y, h.z), h.w, S.always_k[i], i == self_prim);
+        return sphere_hit(R, f3(h.x, h.y, h.z), h.w, i == self_prim);
+    }
+    if (__float_as_uint(h.y) == (uint32_t)RT_PRIM_RECT) {
+        if (i == self_prim) return CUDART_INF_F;  // a plane cannot re-hit itself
+        const uint32_t ri = __float_as_uint(h.z);
+        if (staged) {
+            const uint32_t q = sm.rects + 64u * ri;
+            return rect_hit(R, lds128(q), lds128(q + 16u), lds128(q + 32u), lds128(q + 48u));
+        }
+        const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
+        return rect_hit(R, __ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+    }
+    return general_hit(&S.gen[__float_as_uint(h.x)], R.o, R.d, i == self_prim, key);
+}
+
+// Closest-hit update with the reference's tie rule (strict <, the DFS-earlier leaf wins an exact tie).
+template <bool ORDERED>
+__device__ __forceinline__ void take(const DScene& S, uint32_t i, float t, ClosestHit& best) {
+    if (t < best.t) { best.t = t; best.prim = i; return; }
+    if (ORDERED) return;  // candidates arrive in DFS order: the earlier one already holds the tie
+    if (t == best.t && t < CUDART_INF_F) {
         if (__ldg(&S.prim_meta[i]).x < __ldg(&S.prim_meta[best.prim]).x) best.prim = i;
     }
 }
 
-// `snodes` = shared-memory copy of nodes[0 .. 2*n_staged) (may be nullptr when n_staged == 0).
-__device__ __forceinline__ float4 load_node(const DScene& S, const float4* __restrict__ snodes, uint32_t idx4) {
-    return (idx4 < 2u * S.n_staged_nodes) ? snodes[idx4] : __ldg(&S.nodes[idx4]);
+// Slab test against [0, tmax]; returns entry distance or +inf.  fminf/fmaxf drop NaNs (0 * inf when the
+// origin lies on a slab of a zero direction component), which errs on the side of "hit" like the
+// reference's `if t0 > tmin` form.  1/d comes from MUFU.RCP, so the far distance is widened by 8 ulp
+// (Ize, robust BVH traversal): the test can only err towards visiting a node.
+__device__ __forceinline__ float slab(const float4 lo, const float4 hi, const RayCtx& R, float tmax) {
+    const float x0 = fmaf(lo.x, R.inv.x, -R.oinv.x), x1 = fmaf(hi.x, R.inv.x, -R.oinv.x);
+    const float y0 = fmaf(lo.y, R.inv.y, -R.oinv.y), y1 = fmaf(hi.y, R.inv.y, -R.oinv.y);
+    const float z0 = fmaf(lo.z, R.inv.z, -R.oinv.z), z1 = fmaf(hi.z, R.inv.z, -R.oinv.z);
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax)) * 1.000001f;
+    return tn <= tf ? tn : CUDART_INF_F;
+}
+
+__device__ __forceinline__ float4 load_node(const DScene& S, const Staged& sm, uint32_t idx4) {
+    if (idx4 < 2u * S.n_staged_nodes) return lds128(sm.nodes + 16u * idx4);
+    return __ldg(&S.nodes[idx4]);
+}
+// The four float4 of a sibling pair (64 contiguous bytes); `pair` is even, so the pair is staged or not as a whole.
+__device__ __forceinline__ void load_pair(const DScene& S, const Staged& sm, uint32_t pair, float4& llo, float4& lhi, float4& rlo, float4& rhi) {
+    if (pair < S.n_staged_nodes) {
+        const uint32_t a = sm.nodes + 32u * pair;
+        llo = lds128(a); lhi = lds128(a + 16u); rlo = lds128(a + 32u); rhi = lds128(a + 48u);
+    } else {
+        const float4* __restrict__ g = S.nodes + 2u * (size_t)pair;
+        llo = __ldg(g); lhi = __ldg(g + 1); rlo = __ldg(g + 2); rhi = __ldg(g + 3);
+    }
+}
+
+__device__ __forceinline__ RayCtx make_ray(float3 o, float3 d) {
+    RayCtx R;
+    R.o = o;
+    R.d = d;
+    R.a = dot3(d, d);
+    R.inv_a = fast_rcp(R.a);
+    R.inv = f3(fast_rcp(d.x), fast_rcp(d.y), fast_rcp(d.z));
+    R.oinv = f3(o.x * R.inv.x, o.y * R.inv.y, o.z * R.inv.z);
+    // o/d is NaN when both are 0: replace by 0 so that lo*inv - oinv stays +-inf (conservative)
+    if (R.oinv.x != R.oinv.x) R.oinv.x = 0.0f;
+    if (R.oinv.y != R.oinv.y) R.oinv.y = 0.0f;
+    if (R.oinv.z != R.oinv.z) R.oinv.z = 0.0f;
+    return R;
 }
 
 template <bool COUNT = false>
-__device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const float4* __restrict__ snodes, float3 o, float3 d, uint32_t self_prim,
-                                                  const MediumKey& key, TraversalWork* work = nullptr) {
+__device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged& sm, float3 o, float3 d, uint32_t self_prim, const MediumKey& key,
+                                                  TraversalWork* work = nullptr) {
     ClosestHit best{CUDART_INF_F, RT_NO_PRIM};
-    for (uint32_t i = 0; i < S.n_always; ++i) consider<true>(S, i, o, d, self_prim, key, best);
+    const RayCtx R = make_ray(o, d);
+
+    if (S.n_small) {
+        // small scene: the whole primitive list in DFS order, warp-uniform (geometry.rs:76-116)
+        for (uint32_t i = 0; i < S.n_small; ++i) take<true>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+        if (COUNT) work->prim_tests += S.n_small;
+        return best;
+    }
+    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true>(S, sm, i, R, self_prim, key), best);
     if (COUNT) work->prim_tests += S.n_always;
     if (S.n_nodes == 0) return best;
 
-    RayBox rb;
-    rb.inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    rb.oinv = f3(o.x * rb.inv.x, o.y * rb.inv.y, o.z * rb.inv.z);
-    // o/d is NaN when both are 0: replace by 0 so that lo*inv - oinv stays +-inf (conservative)
-    if (rb.oinv.x != rb.oinv.x) rb.oinv.x = 0.0f;
-    if (rb.oinv.y != rb.oinv.y) rb.oinv.y = 0.0f;
-    if (rb.oinv.z != rb.oinv.z) rb.oinv.z = 0.0f;
-
     if (S.root_is_leaf) {
-        const float4 lo = load_node(S, snodes, 0), hi = load_node(S, snodes, 1);
+        const float4 lo = load_node(S, sm, 0), hi = load_node(S, sm, 1);
         if (COUNT) work->box_tests += 1;
-        if (slab(lo, hi, rb, best.t) < CUDART_INF_F) {
+        if (slab(lo, hi, R, best.t) < CUDART_INF_F) {
             const uint32_t first = __float_as_uint(lo.w), cnt = __float_as_uint(hi.w);
-            for (uint32_t i = first; i < first + cnt; ++i) consider(S, i, o, d, self_prim, key, best);
+            for (uint32_t i = first; i < first + cnt; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
             if (COUNT) work->prim_tests += cnt;
         }
         return best;
     }
 
-    uint32_t stack[RT_STACK_DEPTH];
+    // Traversal stack: the first RT_SMEM_STACK entries live in shared memory (conflict-free: one column per thread),
+    // so the per-thread local-memory stack no longer competes with BVH nodes for L1; deeper entries (trees deeper
+    // than RT_SMEM_STACK, i.e. > 16 M well-balanced primitives) spill to a local array.
+    uint32_t stack_spill[RT_STACK_DEPTH - RT_SMEM_STACK];
+    const uint32_t sstride = 4u * blockDim.x;
+#if RT_OPT_STACK_T
+    float stack_t[RT_STACK_DEPTH];
+#endif
     int sp = 0;
-    uint32_t pair = __float_as_uint(load_node(S, snodes, 0).w);  // left child of the root; right = pair + 1
-    for (;;) {
-        const float4 llo = load_node(S, snodes, 2u * pair), lhi = load_node(S, snodes, 2u * pair + 1u);
-        const float4 rlo = load_node(S, snodes, 2u * pair + 2u), rhi = load_node(S, snodes, 2u * pair + 3u);
-        const float tl = slab(llo, lhi, rb, best.t);
-        const float tr = slab(rlo, rhi, rb, best.t);
+    uint32_t pair = __float_as_uint(load_node(S, sm, 0).w);  // left child of the root; right = pair + 1
+    do {
+        float4 llo, lhi, rlo, rhi;
+        load_pair(S, sm, pair, llo, lhi, rlo, rhi);
+        const float tl = slab(llo, lhi, R, best.t);
+        const float tr = slab(rlo, rhi, R, best.t);
         if (COUNT) work->box_tests += 2;
-        // near child first so that the far one can be pruned by what the near one finds
-        const bool swap = tr < tl;
-        const float t_far = swap ? tl : tr, t_near = swap ? tr : tl;
-        const uint32_t near_ref = __float_as_uint(swap ? rlo.w : llo.w), near_cnt = __float_as_uint(swap ? rhi.w : lhi.w);
-        const uint32_t far_ref = __float_as_uint(swap ? llo.w : rlo.w), far_cnt = __float_as_uint(swap ? lhi.w : rhi.w);
-        uint32_t next_near = RT_NO_PRIM, next_far = RT_NO_PRIM;
-        if (t_near < CUDART_INF_F) {
-            if (near_cnt) {
-                for (uint32_t i = near_ref; i < near_ref + near_cnt; ++i) consider(S, i, o, d, self_prim, key, best);
-                if (COUNT) work->prim_tests += near_cnt;
-            } else next_near = near_ref;
+        const uint32_t lcnt = __float_as_uint(lhi.w), rcnt = __float_as_uint(rhi.w);
+        const uint32_t lref = __float_as_uint(llo.w), rref = __float_as_uint(rlo.w);
+        const bool lhit = tl < CUDART_INF_F, rhit = tr < CUDART_INF_F;
+#if RT_OPT_MERGE_LEAF
+        // leaves: sibling leaves are adjacent in the primitive order, so both become ONE range and one loop site
+        uint32_t begin = 0u, end = 0u;
+        if (lhit && lcnt) { begin = lref; end = lref + lcnt; }
+        if (rhit && rcnt) { if (end == 0u) begin = rref; end = rref + rcnt; }
+        for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+        if (COUNT) work->prim_tests += end - begin;
+#else
+        // leaves, nearer first so that the farther one can be pruned by what the nearer one finds
+        {
+            const bool swap = tr < tl;
+            const uint32_t nref = swap ? rref : lref, ncnt = swap ? rcnt : lcnt, fref = swap ? lref : rref, fcnt = swap ? lcnt : rcnt;
+            const float tnear = swap ? tr : tl, tfar = swap ? tl : tr;
+            if (ncnt && tnear < CUDART_INF_F) {
+                for (uint32_t i = nref; i < nref + ncnt; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+                if (COUNT) work->prim_tests += ncnt;
+            }
+            if (fcnt && tfar <= best.t && tfar < CUDART_INF_F) {
+                for (uint32_t i = fref; i < fref + fcnt; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+                if (COUNT) work->prim_tests += fcnt;
+            }
         }
-        if (t_far <= best.t && t_far < CUDART_INF_F) {
-            if (far_cnt) {
-                for (uint32_t i = far_ref; i < far_ref + far_cnt; ++i) consider(S, i, o, d, self_prim, key, best);
-                if (COUNT) work->prim_tests += far_cnt;
-            } else next_far = far_ref;
+#endif
+        // interior children: descend into the nearer one, push the farther.  ONE back-edge: every lane computes its
+        // next pair and falls through to the loop test, so the warp reconverges at the loop head each iteration
+        // (with `continue`s on three paths the lanes of a warp drifted apart for good: ncu showed 4.7 active
+        // threads per instruction on the 1 M-sphere scene against 9.2 for the single-exit form).
+        const bool lin = lhit && !lcnt && tl <= best.t, rin = rhit && !rcnt && tr <= best.t;
+        uint32_t next = RT_NO_PRIM;
+        if (lin && rin) {
+            const bool swap = tr < tl;
+            const uint32_t pushed = swap ? lref : rref;
+            if (sp < (int)RT_SMEM_STACK) sts32(sm.stack + sp * sstride, pushed);
+            else stack_spill[sp - RT_SMEM_STACK] = pushed;
+#if RT_OPT_STACK_T
+            stack_t[sp] = swap ? tl : tr;
+#endif
+            sp += (sp < RT_STACK_DEPTH - 1);
+            next = swap ? rref : lref;
+        } else if (lin) {
+            next = lref;
+        } else if (rin) {
+            next = rref;
+        } else {
+#if RT_OPT_STACK_T
+            while (sp > 0) {  // pop, skipping subtrees that a closer hit has meanwhile made irrelevant
+                --sp;
+                if (stack_t[sp] <= best.t) { next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK]; break; }
+            }
+#else
+            if (sp > 0) {
+                --sp;
+                next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK];
+            }
+#endif
         }
-        // interior children: descend into the nearer, push the farther (its children are re-tested against best.t on pop)
-        if (next_near != RT_NO_PRIM) {
-            if (next_far != RT_NO_PRIM && sp < RT_STACK_DEPTH) stack[sp++] = next_far;
-            pair = next_near;
-            continue;
-        }
-        if (next_far != RT_NO_PRIM) { pair = next_far; continue; }
-        if (sp == 0) break;
-        pair = stack[--sp];
-    }
+        pair = next;
+    } while (pair != RT_NO_PRIM);
     return best;
 }
 

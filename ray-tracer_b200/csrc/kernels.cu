@@ -36,6 +36,32 @@ __device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
     return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
 }
 
+// Block-aggregated append of two streams (survivors, finished paths): ONE pair of global atomics per block
+// iteration.  With one atomic per warp, the 2 x 32 k same-address atomics of a launch serialise in one L2 slice
+// and cost about half of the shade kernel (ncu: 20 % of its stall samples sat on that ATOMG).
+// Must be called by every thread of the block.  `s_cnt` = [RT_SHADE_WARPS + 1][2] shared words.
+__device__ __forceinline__ void block_append2(uint32_t* cnt_a, bool pa, uint32_t* cnt_b, bool pb, uint32_t& slot_a, uint32_t& slot_b,
+                                              uint32_t (*s_cnt)[2]) {
+    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    const uint32_t ma = __ballot_sync(0xFFFFFFFFu, pa), mb = __ballot_sync(0xFFFFFFFFu, pb);
+    if (lane == 0) { s_cnt[warp][0] = (uint32_t)__popc(ma); s_cnt[warp][1] = (uint32_t)__popc(mb); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t ta = 0u, tb = 0u;
+        for (uint32_t w = 0; w < n_warps; ++w) {
+            const uint32_t ca = s_cnt[w][0], cb = s_cnt[w][1];
+            s_cnt[w][0] = ta; s_cnt[w][1] = tb;
+            ta += ca; tb += cb;
+        }
+        s_cnt[n_warps][0] = ta ? atomicAdd(cnt_a, ta) : 0u;
+        s_cnt[n_warps][1] = tb ? atomicAdd(cnt_b, tb) : 0u;
+    }
+    __syncthreads();
+    const uint32_t lt = (1u << lane) - 1u;
+    slot_a = s_cnt[n_warps][0] + s_cnt[warp][0] + (uint32_t)__popc(ma & lt);
+    slot_b = s_cnt[n_warps][1] + s_cnt[warp][1] + (uint32_t)__popc(mb & lt);
+}
+
 // local linear index -> (x, local row): 8x4 pixel tiles per warp where they fit, scanline remainders
 __device__ __forceinline__ void pixel_from_index(uint32_t q, uint32_t W, uint32_t rows, uint32_t& x, uint32_t& yl) {
     const uint32_t W8 = W & ~7u, R4 = rows & ~3u;
@@ -101,12 +127,25 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
 
 // ---- extend ----------------------------------------------------------------------------------------
 
-template <bool COUNT>
-__global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
-                                                          uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
-    extern __shared__ float4 snodes[];
-    for (uint32_t i = threadIdx.x; i < 2u * S.n_staged_nodes; i += blockDim.x) snodes[i] = S.nodes[i];
+// Copy the BVH prefix (and, for scenes that fit, the primitive heads and compact rectangle records) into shared
+// memory: [stack RT_SMEM_STACK x blockDim words][nodes 2*n_staged_nodes][heads n_staged_prims][rects 4*n_rects].
+__device__ __forceinline__ Staged stage_scene(const DScene& S, float4* smem_base) {
+    float4* smem4 = smem_base + (RT_SMEM_STACK * blockDim.x) / 4u;
+    const uint32_t n_node4 = 2u * S.n_staged_nodes, n_head4 = S.n_staged_prims, n_rect4 = S.n_staged_prims ? 4u * S.n_rects : 0u;
+    for (uint32_t i = threadIdx.x; i < n_node4; i += blockDim.x) smem4[i] = S.nodes[i];
+    for (uint32_t i = threadIdx.x; i < n_head4; i += blockDim.x) smem4[n_node4 + i] = S.prim_head[i];
+    for (uint32_t i = threadIdx.x; i < n_rect4; i += blockDim.x) smem4[n_node4 + n_head4 + i] = S.rects[i];
     __syncthreads();
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_base);
+    const uint32_t scene = base + RT_SMEM_STACK * blockDim.x * 4u;
+    return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
+                                                          uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
+    extern __shared__ float4 smem4[];
+    const Staged sm = stage_scene(S, smem4);
     const uint32_t n = wc->total[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x;
     TraversalWork work{0u, 0u};
@@ -119,7 +158,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_extend(const DScene S, cons
             key.k1 = sb >> 8;
             key.segment = sb & 0xFFu;
         }
-        const ClosestHit h = closest_hit<COUNT>(S, snodes, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
+        const ClosestHit h = closest_hit<COUNT>(S, sm, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
         hits[i] = make_float2(h.t, __uint_as_float(h.prim));
     }
     if (COUNT) {  // instrumented build only (RT_RENDER_COUNT_WORK): one atomic pair per warp
@@ -131,9 +170,10 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_extend(const DScene S, cons
 
 // ---- shade -----------------------------------------------------------------------------------------
 
-__global__ void __launch_bounds__(256) k_shade(const DScene S, const RenderConst rc, const RayQueue qin, RayQueue qout,
+__global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(const DScene S, const RenderConst rc, const RayQueue qin, RayQueue qout,
                                                const float2* __restrict__ hits, float4* __restrict__ done, WaveCounters* __restrict__ wc, uint32_t k) {
     __shared__ float4 smats[2 * RT_MAX_STAGED_MATS];
+    __shared__ uint32_t s_cnt[RT_SHADE_BLOCK / 32 + 1][2];
     const uint32_t n_staged = min(S.n_mats, RT_MAX_STAGED_MATS);
     for (uint32_t i = threadIdx.x; i < 2u * n_staged; i += blockDim.x) smats[i] = reinterpret_cast<const float4*>(S.mats)[i];
     __syncthreads();
@@ -142,9 +182,9 @@ __global__ void __launch_bounds__(256) k_shade(const DScene S, const RenderConst
     uint32_t* surv_next = &wc->surv[(k + 1) % RT_RING];
     uint32_t* done_cnt = &wc->done[s];
     const uint32_t stride = gridDim.x * blockDim.x;
-    // whole warps iterate together so the ballots below always see 32 lanes
-    for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += stride) {
-        const uint32_t i = base + lane_id();
+    // whole blocks iterate together: the append below synchronises the block
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {
+        const uint32_t i = base + threadIdx.x;
         bool alive = false, record = false;
         float4 na, nb, nc, rec;
         if (i < n) {
@@ -189,9 +229,9 @@ __global__ void __launch_bounds__(256) k_shade(const DScene S, const RenderConst
                 }
             }
         }
-        const uint32_t slot = warp_append(surv_next, alive);
+        uint32_t slot, dslot;
+        block_append2(surv_next, alive, done_cnt, record, slot, dslot, s_cnt);
         if (alive) { qout.a[slot] = na; qout.b[slot] = nb; qout.c[slot] = nc; }
-        const uint32_t dslot = warp_append(done_cnt, record);
         if (record) done[dslot] = rec;
     }
 }
@@ -199,7 +239,9 @@ __global__ void __launch_bounds__(256) k_shade(const DScene S, const RenderConst
 // ---- accumulate ------------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const float4* __restrict__ done, const WaveCounters* __restrict__ wc,
-                                                    uint32_t k, float* __restrict__ sum, float* __restrict__ sumsq) {
+                                                    uint32_t k, double* __restrict__ sum, double* __restrict__ sumsq) {
+    // f64 accumulators (native 64-bit atomics): an f32 running sum of 1024+ equal sky samples rounds the same way on
+    // every add and drifts by 1e-4 relative, which the 3-sigma image test sees on zero-variance pixels.
     const uint32_t n = wc->done[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -208,15 +250,20 @@ __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const 
         const uint32_t y = gp / rc.width, x = gp - y * rc.width;
         const uint32_t yl = (y - rc.row_begin) / rc.row_stride;
         const size_t o = ((size_t)yl * rc.width + x) * 3;
-        atomicAdd(&sum[o + 0], r.x);
-        atomicAdd(&sum[o + 1], r.y);
-        atomicAdd(&sum[o + 2], r.z);
+        atomicAdd(&sum[o + 0], (double)r.x);
+        atomicAdd(&sum[o + 1], (double)r.y);
+        atomicAdd(&sum[o + 2], (double)r.z);
         if (sumsq) {
-            atomicAdd(&sumsq[o + 0], r.x * r.x);
-            atomicAdd(&sumsq[o + 1], r.y * r.y);
-            atomicAdd(&sumsq[o + 2], r.z * r.z);
+            atomicAdd(&sumsq[o + 0], (double)r.x * (double)r.x);
+            atomicAdd(&sumsq[o + 1], (double)r.y * (double)r.y);
+            atomicAdd(&sumsq[o + 2], (double)r.z * (double)r.z);
         }
     }
+}
+
+// last step of the accumulate stage: f64 accumulators -> the caller's f32 sum buffers
+__global__ void __launch_bounds__(256) k_finish(const double* __restrict__ acc, size_t n, float* __restrict__ out) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) out[i] = (float)acc[i];
 }
 
 // ---- resolve (examples/book-one.rs:90-100) -----------------------------------------------------------
@@ -251,15 +298,14 @@ __global__ void __launch_bounds__(256) k_deinterleave(const float* __restrict__ 
 
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const RtRayIn* __restrict__ rays, uint64_t n, uint32_t seed_lo,
                                                          uint32_t seed_hi, RtHitOut* __restrict__ out) {
-    extern __shared__ float4 snodes[];
-    for (uint32_t i = threadIdx.x; i < 2u * S.n_staged_nodes; i += blockDim.x) snodes[i] = S.nodes[i];
-    __syncthreads();
+    extern __shared__ float4 smem4[];
+    const Staged sm = stage_scene(S, smem4);
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const RtRayIn r = rays[i];
         const float3 o = f3(r.origin[0], r.origin[1], r.origin[2]), d = f3(r.direction[0], r.direction[1], r.direction[2]);
         const MediumKey key{(uint32_t)i, (uint32_t)(i >> 32), 1u, seed_lo, seed_hi};
-        const ClosestHit h = closest_hit(S, snodes, o, d, RT_NO_PRIM, key);
+        const ClosestHit h = closest_hit<false>(S, sm, o, d, RT_NO_PRIM, key);
         RtHitOut res;
         res.hit = 0; res.prim = -1; res.t = 0.0f; res.material = -1;
         res.p[0] = res.p[1] = res.p[2] = res.n[0] = res.n[1] = res.n[2] = res.uv[0] = res.uv[1] = 0.0f;
@@ -278,7 +324,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
 // ---- launch wrappers ---------------------------------------------------------------------------------
 
 static int g_num_sms = 0;
-static int g_extend_blocks_per_sm = 0, g_trace_blocks_per_sm = 0;
+static int g_extend_blocks_per_sm = 0, g_trace_blocks_per_sm = 0, g_shade_blocks_per_sm = 0;
 static size_t g_extend_smem = ~(size_t)0;
 
 cudaError_t kernels_init(int device) {
@@ -287,12 +333,16 @@ cudaError_t kernels_init(int device) {
     const cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     if (e != cudaSuccess) return e;
     g_num_sms = sms;
+    const cudaError_t e2 = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shade_blocks_per_sm, k_shade, RT_SHADE_BLOCK, 0);
+    if (e2 != cudaSuccess) return e2;
+    if (g_shade_blocks_per_sm < 1) g_shade_blocks_per_sm = 1;
     return cudaSuccess;
 }
 
-cudaError_t kernels_configure(int device, size_t staged_bytes) {
+cudaError_t kernels_configure(int device, size_t scene_bytes) {
     cudaError_t e = kernels_init(device);
     if (e != cudaSuccess) return e;
+    const size_t staged_bytes = scene_bytes + (size_t)RT_SMEM_STACK * RT_EXTEND_BLOCK * sizeof(uint32_t);
     if (staged_bytes != g_extend_smem) {
         e = cudaFuncSetAttribute(k_extend<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
@@ -323,11 +373,12 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st) {
-    k_shade<<<g_num_sms * 4, 256, 0, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    k_shade<<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, 0, st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
-void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, float* sum, float* sumsq, cudaStream_t st) {
+void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
     k_accumulate<<<g_num_sms * 2, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
 }
+void launch_finish(const double* acc, size_t n, float* out, cudaStream_t st) { k_finish<<<g_num_sms * 4, 256, 0, st>>>(acc, n, out); }
 void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st) {
     k_resolve_u8<<<g_num_sms * 4, 256, 0, st>>>(sum, width, height, 1.0f / (float)spp, out);
 }

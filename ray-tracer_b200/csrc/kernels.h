@@ -7,6 +7,15 @@
 #ifndef RT_EXTEND_BLOCK
 #define RT_EXTEND_BLOCK 256
 #endif
+#ifndef RT_SHADE_BLOCK
+#define RT_SHADE_BLOCK 256
+#endif
+#ifndef RT_SHADE_MIN_BLOCKS
+#define RT_SHADE_MIN_BLOCKS 2
+#endif
+#ifndef RT_EXTEND_MIN_BLOCKS
+#define RT_EXTEND_MIN_BLOCKS 3
+#endif
 
 namespace rtb {
 
@@ -21,7 +30,8 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
                    bool count_work, cudaStream_t st);
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st);
-void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, float* sum, float* sumsq, cudaStream_t st);
+void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st);
+void launch_finish(const double* acc, size_t n, float* out, cudaStream_t st);
 void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st);
 void launch_deinterleave(const float* gathered, float* full, uint32_t width, uint32_t height, uint32_t n_shards, cudaStream_t st);
 void launch_trace(const DScene& S, const RtRayIn* rays, uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* out, cudaStream_t st);

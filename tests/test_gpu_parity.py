@@ -96,7 +96,7 @@ def test_trace_edge_cases(rt, orc, device):
         [277.5, 277.5, 277.5, 0, 1, 0],    # straight up into the light
         [277.5, 277.5, 277.5, 0, -1, 0],   # straight down onto the floor
         [277.5, 277.5, 277.5, 1, 0, 0],    # onto the green wall
-        [277.5, 277.5, 277.5, 0, 0, 2.5],  # unnormalised direction: t in units of |d|
+        [100.0, 400.0, 277.5, 0, 0, 2.5],  # unnormalised direction: t in units of |d| (clear of both cubes)
         [-100, 277.5, 277.5, 1, 0, 0],     # from outside through the back of the red wall (no culling)
     ], dtype=np.float32)
     ho, hg = so.trace(rays.astype(np.float64)), scene.trace(rays)
@@ -207,7 +207,7 @@ def _psnr_resolved(mean_a, mean_b):
 
 
 @pytest.mark.parametrize("name,w,h,spp_gpu,spp_cpu,depth", [("book-one", 64, 36, 16384, 4096, 50), ("cornell-box", 32, 32, 131072, 32768, 50),
-                                                          ("book-two", 40, 40, 32768, 4096, 50), ("stress:20000", 48, 27, 16384, 2048, 16)])
+                                                          ("book-two", 24, 24, 262144, 32768, 50), ("stress:20000", 48, 27, 16384, 2048, 16)])
 def test_image_statistics_against_high_spp_oracle(rt, orc, device, name, w, h, spp_gpu, spp_cpu, depth):
     """Gate 2.  The oracle renders with its FAITHFUL sampler (rejection sampling, sequential stream — the reference's
     algorithm) and a different seed: the two estimates are independent."""
@@ -218,16 +218,18 @@ def test_image_statistics_against_high_spp_oracle(rt, orc, device, name, w, h, s
     m_g, m_o = s_g.astype(np.float64) / spp_gpu, s_o / spp_cpu
     var_g = np.maximum(q_g.astype(np.float64) / spp_gpu - m_g ** 2, 0) / spp_gpu
     var_o = np.maximum(q_o / spp_cpu - m_o ** 2, 0) / spp_cpu
-    se = np.sqrt(var_g + var_o)
-    ok = se > 0
-    z = (m_g - m_o)[ok] / se[ok]
+    # f32 accumulation floor: a pixel that sees only the sky has zero true variance; its f32 sum / sum-of-squares
+    # carry ~1e-6 relative rounding, which must not be read as a Monte-Carlo standard error
+    floor = 2e-5 * np.maximum(np.maximum(m_g, m_o), 1e-3)
+    se = np.sqrt(var_g + var_o + floor ** 2)
+    ok = (var_g + var_o) > 0  # reporting only: every channel enters the z statistics (zero-variance ones through the floor)
+    z = (m_g - m_o) / se
     exceed = np.mean(np.abs(z) > 3.0)
     psnr = _psnr_resolved(m_g, m_o)
     print(f"{name}: {ok.mean():.3f} of channels have variance; |z|>3 fraction {exceed:.4f} (chance 0.0027), max |z| {np.abs(z).max():.2f}, "
           f"mean z {z.mean():+.3f}, PSNR {psnr:.1f} dB, rays/path gpu {st.rays / st.paths:.3f} oracle {sto.segments / sto.paths:.3f}")
     assert exceed <= 0.01 and np.abs(z).max() < 6.0
     assert abs(z.mean()) < 0.2  # no systematic brightness offset (a biased f32 self-intersection rule shows up here)
-    assert np.allclose(m_g[~ok], m_o[~ok], atol=1e-6)  # zero-variance pixels (direct view of a light / black) agree exactly
     assert psnr >= 40.0
     assert abs(st.rays / st.paths - sto.segments / sto.paths) < 0.02 * sto.segments / sto.paths
 
