@@ -32,7 +32,7 @@ def gather_rows(local, height, world, device_ctx=None, group=None):
     assert rows_padded == padded_rows(height, world) and local.shape[2] == 3 and local.is_contiguous()
     if world == 1:
         return local[:height]
-    gathered = torch.empty((world, rows_padded, width, 3), dtype=local.dtype, device=local.device)
+    gathered = torch.empty((world * rows_padded, width, 3), dtype=local.dtype, device=local.device)  # shards back to back
     dist.all_gather_into_tensor(gathered, local, group=group)
     if local.is_cuda:
         if device_ctx is None:
@@ -40,7 +40,7 @@ def gather_rows(local, height, world, device_ctx=None, group=None):
         full = torch.empty((height, width, 3), dtype=local.dtype, device=local.device)
         device_ctx.deinterleave_rows(gathered.data_ptr(), full.data_ptr(), width, height, world, torch.cuda.current_stream().cuda_stream)
         return full
-    return gathered.permute(1, 0, 2, 3).reshape(rows_padded * world, width, 3)[:height].contiguous()
+    return gathered.view(world, rows_padded, width, 3).permute(1, 0, 2, 3).reshape(rows_padded * world, width, 3)[:height].contiguous()
 
 
 def render_sharded(scene, cam, width, height, spp, max_depth, seed, rank, world, queue_capacity=0, flags=0, group=None):

@@ -284,3 +284,31 @@ def test_full_size_config1_properties(rt, orc, device):
     assert np.all(q <= s * 1.0 + 1e-3)  # per-path radiance <= 1 -> sum of squares <= sum
     sub, _, _ = orc.Scene("book-one", 1).render(w, h, 4, 50, seed=5, mode=orc.FAITHFUL, row_begin=0, row_stride=9)
     assert abs(s[0::9].mean() / spp - sub.mean() / 4) < 0.01
+
+
+def test_deinterleave_kernel_matches_index_arithmetic(rt, device):
+    """rt_deinterleave_rows (the kernel behind the NCCL gather) against the pure index arithmetic the gloo tests use."""
+    import torch
+
+    for height, width, shards in [(12, 9, 2), (10, 5, 3), (2160, 64, 8), (7, 3, 2)]:
+        rows = -(-height // shards)
+        gathered = torch.rand((shards * rows, width, 3), device="cuda")
+        full = torch.empty((height, width, 3), device="cuda")
+        device.deinterleave_rows(gathered.data_ptr(), full.data_ptr(), width, height, shards, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        want = gathered.view(shards, rows, width, 3).permute(1, 0, 2, 3).reshape(rows * shards, width, 3)[:height]
+        assert torch.equal(full, want)
+
+
+def test_render_sharded_single_rank_matches_render(rt, device):
+    import importlib
+
+    import torch
+
+    rtdist = importlib.import_module("ray-tracer_b200.dist")
+    scene = rt.Scene.example(device, "book-one", 1)
+    cam = scene.flat.camera(64 / 36)
+    full, st = rtdist.render_sharded(scene, cam, 64, 36, 8, 50, 3, 0, 1)
+    ref, _, _ = scene.render(cam, 64, 36, 8, 50, seed=3, want_sumsq=False)
+    torch.cuda.synchronize()
+    assert np.allclose(full.cpu().numpy(), ref, rtol=1e-6, atol=1e-6)
