@@ -59,10 +59,12 @@ struct DevBuf {
 struct RtContext {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    std::vector<cudaEvent_t> stage_events;  // 5 per wavefront iteration when stage timing is on (no sync until the render ends)
+    cudaStream_t side = nullptr;  // accumulate_k runs here, overlapped with generate/extend of iteration k+1
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_shaded[2] = {nullptr, nullptr}, ev_accumulated[2] = {nullptr, nullptr};
+    std::vector<cudaEvent_t> stage_events;  // 6 per wavefront iteration when stage timing is on (no sync until the render ends)
+    bool overlap_accumulate = true;
     // wavefront state (sized on demand for the requested queue capacity)
-    DevBuf<float4> qa[2], qb[2], qc[2], done;
+    DevBuf<float4> qa[2], qb[2], qc[2], done[2];
     DevBuf<float2> hits;
     DevBuf<WaveCounters> counters;
     DevBuf<float> fb_sum, fb_sumsq;
@@ -76,7 +78,7 @@ struct RtContext {
 struct RtScene {
     RtContext* ctx = nullptr;
     DScene d{};
-    DevBuf<float4> nodes, prim_head, texels, rects;
+    DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm;
     DevBuf<uint2> prim_meta;
     DevBuf<RtPrim> gen;
     DevBuf<DMaterial> mats;
@@ -181,8 +183,14 @@ int rt_init(int device_id, RtContext** out) {
     if (!ctx) return fail(RT_ERR_OOM, "out of host memory");
     ctx->device = device_id;
     RT_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    RT_CUDA(cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking));
     RT_CUDA(cudaEventCreate(&ctx->ev0));
     RT_CUDA(cudaEventCreate(&ctx->ev1));
+    for (int i = 0; i < 2; ++i) {
+        RT_CUDA(cudaEventCreateWithFlags(&ctx->ev_shaded[i], cudaEventDisableTiming));
+        RT_CUDA(cudaEventCreateWithFlags(&ctx->ev_accumulated[i], cudaEventDisableTiming));
+    }
+    if (const char* ov = std::getenv("RT_B200_OVERLAP_ACCUMULATE")) ctx->overlap_accumulate = ov[0] != '0';
     RT_CUDA(cudaMallocHost(&ctx->h_status, sizeof(WaveCounters)));
     const char* st = std::getenv("RT_B200_STAGE_TIMING");
     ctx->stage_timing = st && st[0] == '1';
@@ -198,11 +206,13 @@ void rt_shutdown(RtContext* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     for (int i = 0; i < 2; ++i) { ctx->qa[i].release(); ctx->qb[i].release(); ctx->qc[i].release(); }
-    ctx->done.release(); ctx->hits.release(); ctx->counters.release(); ctx->fb_sum.release(); ctx->fb_sumsq.release(); ctx->acc.release(); ctx->scratch.release();
+    ctx->done[0].release(); ctx->done[1].release(); ctx->hits.release(); ctx->counters.release(); ctx->fb_sum.release(); ctx->fb_sumsq.release(); ctx->acc.release(); ctx->scratch.release();
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     for (auto& ev : ctx->stage_events) if (ev) cudaEventDestroy(ev);
+    for (int i = 0; i < 2; ++i) { if (ctx->ev_shaded[i]) cudaEventDestroy(ctx->ev_shaded[i]); if (ctx->ev_accumulated[i]) cudaEventDestroy(ctx->ev_accumulated[i]); }
+    if (ctx->side) cudaStreamDestroy(ctx->side);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -237,7 +247,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     std::vector<float4> head(n);
     std::vector<uint2> meta(n);
     std::vector<RtPrim> gen;
-    std::vector<float4> rects;
+    std::vector<float4> rects, rect_nrm;
     bool has_media = false;
     float always_k[RT_MAX_ALWAYS] = {0};
     for (uint32_t i = 0; i < n; ++i) {
@@ -258,6 +268,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
                 rects.push_back(make_float4(m[0], m[1], m[2], m[3]));
                 rects.push_back(make_float4(m[4], m[5], m[6], m[7]));
                 rects.push_back(make_float4(0.5f * p.param[0], 0.5f * p.param[1], 0.0f, 0.0f));
+                rect_nrm.push_back(make_float4(p.world_from_local[2], p.world_from_local[6], p.world_from_local[10], 0.0f));
             }
             float fx, fy, fz;
             std::memcpy(&fx, &gi, 4);
@@ -293,6 +304,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     if (e == cudaSuccess) e = upload(s->prim_meta, meta.data(), meta.size());
     if (e == cudaSuccess) e = upload(s->gen, gen.data(), gen.size());
     if (e == cudaSuccess) e = upload(s->rects, rects.data(), rects.size());
+    if (e == cudaSuccess) e = upload(s->rect_nrm, rect_nrm.data(), rect_nrm.size());
     if (e == cudaSuccess) e = upload(s->mats, mats.data(), mats.size());
     if (e == cudaSuccess) e = upload(s->texs, desc->textures, (size_t)desc->n_textures);
     if (e == cudaSuccess) e = upload(s->texels, reinterpret_cast<const float4*>(desc->texels), (size_t)desc->n_texels);
@@ -301,7 +313,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
         return fail(e == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(e));
     }
     DScene& d = s->d;
-    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.rects = s->rects.p;
+    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.rects = s->rects.p; d.rect_nrm = s->rect_nrm.p;
     d.mats = s->mats.p; d.texs = s->texs.p; d.texels = s->texels.p;
     d.n_nodes = (uint32_t)bvh.nodes.size(); d.n_prims = n; d.n_always = bvh.n_always; d.n_gen = (uint32_t)gen.size();
     d.n_mats = desc->n_materials; d.n_texs = desc->n_textures;
@@ -317,6 +329,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     d.n_staged_prims = (n <= RT_MAX_STAGED_PRIMS && d.n_rects <= RT_MAX_STAGED_RECTS) ? n : 0u;
     if (const char* sp = std::getenv("RT_B200_STAGE_PRIMS")) { if (sp[0] == '0') d.n_staged_prims = 0u; }
     std::memcpy(d.always_k, always_k, sizeof(always_k));
+    d.small_all_rects = (small && d.n_staged_prims == n && d.n_rects == n) ? 1u : 0u;
     s->staged_bytes = (size_t)d.n_staged_nodes * 32 + (size_t)d.n_staged_prims * 16 + (d.n_staged_prims ? (size_t)d.n_rects * 64 : 0);
     *out = s;
     return RT_OK;
@@ -325,7 +338,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
 void rt_scene_destroy(RtScene* s) {
     if (!s) return;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->rects.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->mats.release(); s->texs.release(); s->texels.release();
     delete s;
 }
 
@@ -340,7 +353,7 @@ int rt_scene_bvh_info(const RtScene* s, uint32_t* n_nodes, uint32_t* n_always, u
 uint64_t rt_scene_device_bytes(const RtScene* s) {
     if (!s) return 0;
     return (uint64_t)s->nodes.n * sizeof(float4) + (uint64_t)s->prim_head.n * sizeof(float4) + (uint64_t)s->prim_meta.n * sizeof(uint2) +
-           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)s->rects.n * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
+           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)(s->rects.n + s->rect_nrm.n) * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
            (uint64_t)s->texels.n * sizeof(float4);
 }
 
@@ -380,7 +393,8 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
 
     for (int i = 0; i < 2; ++i) { RT_CUDA(ctx->qa[i].ensure(cap)); RT_CUDA(ctx->qb[i].ensure(cap)); RT_CUDA(ctx->qc[i].ensure(cap)); }
     RT_CUDA(ctx->hits.ensure(cap));
-    RT_CUDA(ctx->done.ensure(cap));
+    RT_CUDA(ctx->done[0].ensure(cap));
+    RT_CUDA(ctx->done[1].ensure(cap));
     RT_CUDA(ctx->counters.ensure(1));
     RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes));
 
@@ -411,15 +425,17 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
 
     const bool timing = ctx->stage_timing || (prm->flags & RT_RENDER_STAGE_TIMING);
     const bool count_work = (prm->flags & RT_RENDER_COUNT_WORK) != 0;
-    auto stage_event = [&](uint64_t iter, int which) -> cudaError_t {
-        const size_t idx = (size_t)iter * 5 + (size_t)which;
+    const bool overlap = ctx->overlap_accumulate;
+    cudaStream_t acc_st = overlap ? ctx->side : st;
+    auto stage_event = [&](uint64_t iter, int which, cudaStream_t on) -> cudaError_t {
+        const size_t idx = (size_t)iter * 6 + (size_t)which;
         while (ctx->stage_events.size() <= idx) {
             cudaEvent_t ev = nullptr;
             const cudaError_t e = cudaEventCreate(&ev);
             if (e != cudaSuccess) return e;
             ctx->stage_events.push_back(ev);
         }
-        return cudaEventRecord(ctx->stage_events[idx], st);
+        return cudaEventRecord(ctx->stage_events[idx], on);
     };
 
     RT_CUDA(cudaEventRecord(ctx->ev0, st));
@@ -429,15 +445,23 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
         const uint32_t ku = (uint32_t)k;
         const RayQueue& qin = q[k & 1];
         const RayQueue& qout = q[(k + 1) & 1];
-        if (timing) RT_CUDA(stage_event(k, 0));
+        if (timing) RT_CUDA(stage_event(k, 0, st));
         launch_generate(rc, qin, wc, ku, st);
-        if (timing) RT_CUDA(stage_event(k, 1));
+        if (timing) RT_CUDA(stage_event(k, 1, st));
         launch_extend(scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, count_work, st);
-        if (timing) RT_CUDA(stage_event(k, 2));
-        launch_shade(scene->d, rc, qin, qout, ctx->hits.p, ctx->done.p, wc, ku, st);
-        if (timing) RT_CUDA(stage_event(k, 3));
-        launch_accumulate(rc, ctx->done.p, wc, ku, acc_sum, acc_sumsq, st);
-        if (timing) RT_CUDA(stage_event(k, 4));
+        if (timing) RT_CUDA(stage_event(k, 2, st));
+        // shade_k refills done[k & 1]: accumulate_{k-2} must be through with it
+        if (overlap && k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[k & 1], 0));
+        launch_shade(scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, ku, st);
+        if (timing) RT_CUDA(stage_event(k, 3, st));
+        if (overlap) {
+            RT_CUDA(cudaEventRecord(ctx->ev_shaded[k & 1], st));
+            RT_CUDA(cudaStreamWaitEvent(acc_st, ctx->ev_shaded[k & 1], 0));
+        }
+        if (timing) RT_CUDA(stage_event(k, 4, acc_st));
+        launch_accumulate(rc, ctx->done[k & 1].p, wc, ku, acc_sum, acc_sumsq, acc_st);
+        if (timing) RT_CUDA(stage_event(k, 5, acc_st));
+        if (overlap) RT_CUDA(cudaEventRecord(ctx->ev_accumulated[k & 1], acc_st));
         launches += 4;
         ++k;
         if (k >= min_iters && ((k - min_iters) % poll == 0)) {
@@ -447,6 +471,10 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
             else if (k > iter_limit) return fail(RT_ERR_CUDA, "wavefront did not terminate after %llu iterations", (unsigned long long)k);
         }
     }
+    if (overlap) {  // the last two accumulates join the render stream before the accumulators are read
+        RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[0], 0));
+        if (k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[1], 0));
+    }
     launch_finish(acc_sum, fb_elems, d_sum, st);
     if (d_sumsq) launch_finish(acc_sumsq, fb_elems, d_sumsq, st);
     launches += d_sumsq ? 2 : 1;
@@ -454,12 +482,14 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     RT_CUDA(cudaEventSynchronize(ctx->ev1));
     RT_CUDA(cudaGetLastError());
     if (timing) {
-        for (uint64_t it = 0; it < k; ++it)
+        for (uint64_t it = 0; it < k; ++it) {
+            const int from[4] = {0, 1, 2, 4}, to[4] = {1, 2, 3, 5};  // generate, extend, shade on the render stream; accumulate on its own
             for (int i = 0; i < 4; ++i) {
                 float ms = 0;
-                RT_CUDA(cudaEventElapsedTime(&ms, ctx->stage_events[it * 5 + i], ctx->stage_events[it * 5 + i + 1]));
+                RT_CUDA(cudaEventElapsedTime(&ms, ctx->stage_events[it * 6 + from[i]], ctx->stage_events[it * 6 + to[i]]));
                 ms_stage[i] += ms;
             }
+        }
     }
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));

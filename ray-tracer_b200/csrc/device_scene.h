@@ -49,6 +49,7 @@ struct DScene {
     const float4* prim_head;   // per device primitive
     const uint2* prim_meta;    // {order, material (int32 bits)}
     const float4* rects;       // 4 float4 per rectangle: row z, row x, row y of object<-world (xyz, translation), (hx, hy, 0, 0)
+    const float4* rect_nrm;    // per rectangle: world-space normal M (0,0,1) (forward matrix, not renormalised: SURVEY A.5)
     const RtPrim* gen;         // general records (non translation-only-sphere primitives)
     const DMaterial* mats;
     const RtTexture* texs;
@@ -60,6 +61,7 @@ struct DScene {
     uint32_t n_rects;
     uint32_t n_staged_prims;   // n_prims when heads (and all rects) are staged in shared memory, else 0
     uint32_t n_small;          // > 0: no tree, test primitives [0, n_small) in order
+    uint32_t small_all_rects;  // n_small > 0, every primitive is a rectangle and the records are staged: specialised loop
     float always_k[RT_MAX_ALWAYS];  // |centre|^2 - r^2 of the always-list spheres, rounded from f64 (big_sphere_hit)
 };
 

@@ -345,6 +345,24 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     ClosestHit best{CUDART_INF_F, RT_NO_PRIM};
     const RayCtx R = make_ray(o, d);
 
+    if (S.small_all_rects) {
+        // small scene made of rectangles only (cornell-box: 18): rectangle i IS primitive i, records in shared memory.
+        // Branch-free body (every reject is a predicate on the final select) so that ptxas can unroll and overlap the
+        // LDS of the next rectangle with the arithmetic of this one; strict `<` in DFS order = the reference's tie rule.
+#pragma unroll 3
+        for (uint32_t i = 0; i < S.n_small; ++i) {
+            const uint32_t q = sm.rects + 64u * i;
+            const float4 rz = lds128(q), rx = lds128(q + 16u), ry = lds128(q + 32u), ext = lds128(q + 48u);
+            const float t = __fdividef(-(dot3(rz, R.o) + rz.w), dot3(rz, R.d));
+            const float3 p = fma3(t, R.d, R.o);
+            const float x = dot3(rx, p) + rx.w, y = dot3(ry, p) + ry.w;
+            const bool ok = (t >= RT_T_EPS) & (t < best.t) & (fabsf(x) <= ext.x) & (fabsf(y) <= ext.y) & (i != self_prim);
+            best.t = ok ? t : best.t;
+            best.prim = ok ? i : best.prim;
+        }
+        if (COUNT) work->prim_tests += S.n_small;
+        return best;
+    }
     if (S.n_small) {
         // small scene: the whole primitive list in DFS order, warp-uniform (geometry.rs:76-116)
         for (uint32_t i = 0; i < S.n_small; ++i) take<true>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);

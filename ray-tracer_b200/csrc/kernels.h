@@ -11,7 +11,7 @@
 #define RT_SHADE_BLOCK 256
 #endif
 #ifndef RT_SHADE_MIN_BLOCKS
-#define RT_SHADE_MIN_BLOCKS 2
+#define RT_SHADE_MIN_BLOCKS 4
 #endif
 #ifndef RT_EXTEND_MIN_BLOCKS
 #define RT_EXTEND_MIN_BLOCKS 3

@@ -64,19 +64,25 @@ __device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, flo
         if (want_uv) sphere_uv(h.n, h.u, h.v);
         return h;
     }
+    if (__float_as_uint(head.y) == (uint32_t)RT_PRIM_RECT) {
+        // Sprite::hit returns M (o' + t d') = o + t d and M (0,0,1) (sprite.rs:108-115): the world-space point needs no
+        // matrix at all and the normal is one precomputed column — 16 B instead of the 128-byte record
+        const uint32_t ri = __float_as_uint(head.z);
+        const float4 nrm = __ldg(&S.rect_nrm[ri]);
+        h.p = fma3(t, d, o);
+        h.n = f3(nrm.x, nrm.y, nrm.z);
+        if (want_uv) {  // geometry.rs:170-171
+            const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
+            const float4 rx = __ldg(q + 1), ry = __ldg(q + 2), ext = __ldg(q + 3);
+            h.u = (dot3(rx, h.p) + rx.w + ext.x) / (2.0f * ext.x);
+            h.v = (dot3(ry, h.p) + ry.w + ext.y) / (2.0f * ext.y);
+        }
+        return h;
+    }
     const RtPrim* __restrict__ g = &S.gen[__float_as_uint(head.x)];
     const float3 lo = xform_point(g->local_from_world, o);
     const float3 ld = xform_vector(g->local_from_world, d);
     const uint32_t kind = g->kind;
-    if (kind == RT_PRIM_RECT) {
-        float3 lp = fma3(t, ld, lo);
-        lp.z = 0.0f;  // on the plane by construction
-        h.p = xform_point(g->world_from_local, lp);
-        h.n = xform_vector(g->world_from_local, f3(0.0f, 0.0f, 1.0f));  // forward matrix (A.5)
-        h.u = (lp.x + 0.5f * g->param[0]) / g->param[0];                  // geometry.rs:170-171
-        h.v = (lp.y + 0.5f * g->param[1]) / g->param[1];
-        return h;
-    }
     if (kind == RT_PRIM_SPHERE) {
         const float r = g->param[0];
         const float3 q = fma3(t, ld, lo) * (1.0f / r);
