@@ -114,7 +114,8 @@ typedef struct RtRenderParams {
 } RtRenderParams;
 
 typedef enum RtRenderFlags {
-    RT_RENDER_STAGE_TIMING = 1u, /* bracket every stage launch with CUDA events (no extra syncs) and fill RtStats.ms_<stage> */
+    RT_RENDER_STAGE_TIMING = 1u, /* bracket the stage launches of every 8th wavefront iteration with CUDA events (no extra syncs)
+                                    and fill RtStats.ms_<stage> with sum over the timed iterations * iterations / timed_iterations */
     RT_RENDER_COUNT_WORK = 2u    /* run the instrumented extend kernel and fill RtStats.box_tests / prim_tests (slower; not for timing) */
 } RtRenderFlags;
 
@@ -124,9 +125,11 @@ typedef struct RtStats {
     uint64_t iterations; /* wavefront iterations */
     uint64_t launches;   /* kernels launched */
     float ms_total;      /* device time of the whole render (CUDA events on the render stream) */
-    float ms_generate, ms_extend, ms_shade, ms_accumulate; /* summed over iterations; filled with RT_RENDER_STAGE_TIMING, else 0 */
+    float ms_generate, ms_extend, ms_shade, ms_accumulate; /* whole-render stage times estimated from the timed iterations
+                                                              (RT_RENDER_STAGE_TIMING), else 0 */
     uint32_t bvh_nodes, bvh_always; /* device BVH size / primitives in the always-tested list */
     uint64_t box_tests, prim_tests; /* ray/AABB and ray/primitive tests of the whole render (RT_RENDER_COUNT_WORK), else 0 */
+    uint64_t timed_iterations;      /* iterations whose launches were bracketed by events (RT_RENDER_STAGE_TIMING), else 0 */
 } RtStats;
 
 typedef struct RtRayIn {

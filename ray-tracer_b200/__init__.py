@@ -50,7 +50,8 @@ class RtRenderParams(C.Structure):
 class RtStats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("iterations", C.c_uint64), ("launches", C.c_uint64), ("ms_total", C.c_float),
                 ("ms_generate", C.c_float), ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_accumulate", C.c_float),
-                ("bvh_nodes", C.c_uint32), ("bvh_always", C.c_uint32), ("box_tests", C.c_uint64), ("prim_tests", C.c_uint64)]
+                ("bvh_nodes", C.c_uint32), ("bvh_always", C.c_uint32), ("box_tests", C.c_uint64), ("prim_tests", C.c_uint64),
+                ("timed_iterations", C.c_uint64)]
 
 
 class RthCameraArgs(C.Structure):

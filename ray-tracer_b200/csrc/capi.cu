@@ -72,19 +72,21 @@ struct RtContext {
     DevBuf<uint8_t> scratch;
     WaveCounters* h_status = nullptr;  // pinned
     bool stage_timing = false;
-    uint32_t default_capacity = 1u << 20;
+    uint32_t default_capacity = 1u << 22;  // 4 M live rays (570 MB of wavefront state): per-launch fixed costs amortise, +20 % over 1 M (r1c)
 };
 
 struct RtScene {
     RtContext* ctx = nullptr;
     DScene d{};
-    DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm;
+    DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm, fr_blob;
     DevBuf<uint2> prim_meta;
     DevBuf<RtPrim> gen;
     DevBuf<DMaterial> mats;
     DevBuf<RtTexture> texs;
     uint32_t bvh_depth = 0;
     size_t staged_bytes = 0;
+    size_t fr_bytes = 0;     // k_extend_rects' staged frame-rect table (0: the scene has none)
+    size_t shade_bytes = 0;  // k_shade's staged tables: materials, and for small scenes heads / meta / rect normals
 };
 
 namespace {
@@ -152,6 +154,99 @@ int validateDesc(const RtSceneDesc* d) {
             return fail(RT_ERR_INVALID, "texture %u: texel range out of bounds", i);
     }
     return RT_OK;
+}
+
+// Frame-rect table of a small all-rectangle scene (device_scene.h "fr_*").  Rigid transforms only: every row of the
+// object<-world matrix must be +-(a row of the frame) to 1e-6, else the scene keeps the general 64-byte rectangle records.
+// With local = s * (U_k . p) + t for a frame row U_k and sign s:  plane z = 0  <=>  U_kz . p = -s_z t_z;
+// |local x| <= hx  <=>  |U_ka . p - (-s_x t_x)| <= hx.
+struct FrameRects {
+    std::vector<float4> blob;
+    uint32_t n = 0, frames = 0, identity = 0;
+    uint32_t range[RT_MAX_FRAMES * 3 + 1] = {0};
+};
+bool buildFrameRects(const RtPrim* prims, const std::vector<uint32_t>& order, FrameRects& out) {
+    struct Rec { uint32_t frame, axis, prim; float w, ca, cb, ha, hb; };
+    struct Frame { double u[3][3]; bool identity; };
+    std::vector<Frame> frames;
+    std::vector<Rec> recs;
+    const uint32_t n = (uint32_t)order.size();
+    auto rowOf = [](const float* m, int r, double v[3]) { v[0] = m[4 * r]; v[1] = m[4 * r + 1]; v[2] = m[4 * r + 2]; };
+    // match row v against the rows of frame F: returns axis and sign, or -1
+    auto matchRow = [](const Frame& F, const double v[3], double& sign) -> int {
+        for (int k = 0; k < 3; ++k) {
+            for (double sg : {1.0, -1.0}) {
+                double err = 0;
+                for (int c = 0; c < 3; ++c) err = std::max(err, std::fabs(v[c] - sg * F.u[k][c]));
+                if (err <= 1e-6) { sign = sg; return k; }
+            }
+        }
+        return -1;
+    };
+    for (uint32_t i = 0; i < n; ++i) {
+        const RtPrim& p = prims[order[i]];
+        if (p.kind != RT_PRIM_RECT) return false;
+        double rx[3], ry[3], rz[3];
+        rowOf(p.local_from_world, 0, rx); rowOf(p.local_from_world, 1, ry); rowOf(p.local_from_world, 2, rz);
+        const double* rows[3] = {rx, ry, rz};
+        for (int a = 0; a < 3; ++a)
+            for (int b = a; b < 3; ++b) {
+                double dot = rows[a][0] * rows[b][0] + rows[a][1] * rows[b][1] + rows[a][2] * rows[b][2];
+                if (std::fabs(dot - (a == b ? 1.0 : 0.0)) > 1e-6) return false;  // not rigid
+            }
+        int f = -1, kx = -1, ky = -1, kz = -1;
+        double sx = 1, sy = 1, sz = 1;
+        for (uint32_t j = 0; j < frames.size() && f < 0; ++j) {
+            kx = matchRow(frames[j], rx, sx); ky = matchRow(frames[j], ry, sy); kz = matchRow(frames[j], rz, sz);
+            if (kx >= 0 && ky >= 0 && kz >= 0 && kx != ky && kx != kz && ky != kz) f = (int)j;
+        }
+        if (f < 0) {
+            Frame F{};
+            Frame I{{{1, 0, 0}, {0, 1, 0}, {0, 0, 1}}, true};
+            double t;
+            const bool world = matchRow(I, rx, t) >= 0 && matchRow(I, ry, t) >= 0 && matchRow(I, rz, t) >= 0;
+            if (world) F = I;
+            else { for (int c = 0; c < 3; ++c) { F.u[0][c] = rx[c]; F.u[1][c] = ry[c]; F.u[2][c] = rz[c]; } F.identity = false; }
+            if (frames.size() >= RT_MAX_FRAMES) return false;
+            frames.push_back(F);
+            f = (int)frames.size() - 1;
+            kx = matchRow(frames[f], rx, sx); ky = matchRow(frames[f], ry, sy); kz = matchRow(frames[f], rz, sz);
+            if (kx < 0 || ky < 0 || kz < 0 || kx == ky || kx == kz || ky == kz) return false;
+        }
+        const float* m = p.local_from_world;
+        const double hx = 0.5 * (double)p.param[0], hy = 0.5 * (double)p.param[1];
+        const double cx = -sx * (double)m[3], cy = -sy * (double)m[7];
+        Rec r{};
+        r.frame = (uint32_t)f; r.axis = (uint32_t)kz; r.prim = i;
+        r.w = (float)(-sz * (double)m[11]);
+        if (kx < ky) { r.ca = (float)cx; r.ha = (float)hx; r.cb = (float)cy; r.hb = (float)hy; }
+        else { r.ca = (float)cy; r.ha = (float)hy; r.cb = (float)cx; r.hb = (float)hx; }
+        recs.push_back(r);
+    }
+    // the world frame first (its rays need no rotation), then groups by (frame, axis), DFS order inside a group
+    int world = -1;
+    for (uint32_t j = 0; j < frames.size(); ++j) if (frames[j].identity) world = (int)j;
+    std::vector<uint32_t> slot(frames.size());
+    uint32_t next = world >= 0 ? 1u : 0u;
+    for (uint32_t j = 0; j < frames.size(); ++j) slot[j] = ((int)j == world) ? 0u : next++;
+    for (auto& r : recs) r.frame = slot[r.frame];
+    std::stable_sort(recs.begin(), recs.end(), [](const Rec& a, const Rec& b) { return a.frame != b.frame ? a.frame < b.frame : a.axis < b.axis; });
+    out.n = n; out.frames = (uint32_t)frames.size(); out.identity = world >= 0 ? 1u : 0u;
+    out.blob.assign(3 * frames.size() + n + (n + 1) / 2, make_float4(0, 0, 0, 0));
+    for (uint32_t j = 0; j < frames.size(); ++j)
+        for (int k = 0; k < 3; ++k) out.blob[3 * slot[j] + k] = make_float4((float)frames[j].u[k][0], (float)frames[j].u[k][1], (float)frames[j].u[k][2], 0.0f);
+    float2* ext = reinterpret_cast<float2*>(out.blob.data() + 3 * frames.size() + n);
+    uint32_t g = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const Rec& r = recs[i];
+        while (g <= r.frame * 3 + r.axis) out.range[g++] = i;
+        float fi;
+        std::memcpy(&fi, &r.prim, 4);
+        out.blob[3 * frames.size() + i] = make_float4(r.w, r.ca, r.cb, fi);
+        ext[i] = make_float2(r.ha, r.hb);
+    }
+    while (g <= RT_MAX_FRAMES * 3) out.range[g++] = n;
+    return true;
 }
 
 template <class T>
@@ -305,6 +400,10 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     if (e == cudaSuccess) e = upload(s->gen, gen.data(), gen.size());
     if (e == cudaSuccess) e = upload(s->rects, rects.data(), rects.size());
     if (e == cudaSuccess) e = upload(s->rect_nrm, rect_nrm.data(), rect_nrm.size());
+    FrameRects fr;
+    bool use_fr = small && rects.size() / 4 == n && buildFrameRects(desc->prims, bvh.order, fr);
+    if (const char* ef = std::getenv("RT_B200_RECT_FRAMES")) { if (ef[0] == '0') use_fr = false; }
+    if (e == cudaSuccess && use_fr) e = upload(s->fr_blob, fr.blob.data(), fr.blob.size());
     if (e == cudaSuccess) e = upload(s->mats, mats.data(), mats.size());
     if (e == cudaSuccess) e = upload(s->texs, desc->textures, (size_t)desc->n_textures);
     if (e == cudaSuccess) e = upload(s->texels, reinterpret_cast<const float4*>(desc->texels), (size_t)desc->n_texels);
@@ -331,6 +430,13 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     std::memcpy(d.always_k, always_k, sizeof(always_k));
     d.small_all_rects = (small && d.n_staged_prims == n && d.n_rects == n) ? 1u : 0u;
     s->staged_bytes = (size_t)d.n_staged_nodes * 32 + (size_t)d.n_staged_prims * 16 + (d.n_staged_prims ? (size_t)d.n_rects * 64 : 0);
+    if (use_fr) {
+        d.fr_blob = s->fr_blob.p; d.fr_n = fr.n; d.fr_frames = fr.frames; d.fr_identity = fr.identity;
+        std::memcpy(d.fr_range, fr.range, sizeof(fr.range));
+        s->fr_bytes = fr.blob.size() * sizeof(float4);
+    }
+    s->shade_bytes = (size_t)std::min<uint32_t>(d.n_mats, RT_MAX_STAGED_MATS) * 32 + (size_t)d.n_staged_prims * (16 + 8) +
+                     (d.n_staged_prims ? (size_t)d.n_rects * 16 : 0);
     *out = s;
     return RT_OK;
 }
@@ -338,7 +444,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
 void rt_scene_destroy(RtScene* s) {
     if (!s) return;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
     delete s;
 }
 
@@ -396,7 +502,7 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     RT_CUDA(ctx->done[0].ensure(cap));
     RT_CUDA(ctx->done[1].ensure(cap));
     RT_CUDA(ctx->counters.ensure(1));
-    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes));
+    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes, scene->shade_bytes, scene->fr_bytes));
 
     const size_t fb_elems = (size_t)rc.pixels_local * 3;
     RT_CUDA(ctx->acc.ensure(fb_elems * 2));
@@ -427,8 +533,13 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     const bool count_work = (prm->flags & RT_RENDER_COUNT_WORK) != 0;
     const bool overlap = ctx->overlap_accumulate;
     cudaStream_t acc_st = overlap ? ctx->side : st;
-    auto stage_event = [&](uint64_t iter, int which, cudaStream_t on) -> cudaError_t {
-        const size_t idx = (size_t)iter * 6 + (size_t)which;
+    // stage timing brackets every `tstride`-th iteration only: six event records per iteration cost ~20 % of a
+    // cornell-box render, which would handicap the very step that is being measured
+    uint64_t tstride = 8;
+    if (const char* ts = std::getenv("RT_B200_STAGE_TIMING_STRIDE")) { const long v = std::atol(ts); if (v >= 1) tstride = (uint64_t)v; }
+    uint64_t n_timed = 0;
+    auto stage_event = [&](uint64_t slot, int which, cudaStream_t on) -> cudaError_t {
+        const size_t idx = (size_t)slot * 6 + (size_t)which;
         while (ctx->stage_events.size() <= idx) {
             cudaEvent_t ev = nullptr;
             const cudaError_t e = cudaEventCreate(&ev);
@@ -445,22 +556,24 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
         const uint32_t ku = (uint32_t)k;
         const RayQueue& qin = q[k & 1];
         const RayQueue& qout = q[(k + 1) & 1];
-        if (timing) RT_CUDA(stage_event(k, 0, st));
+        const bool timed = timing && (k % tstride == 0);
+        const uint64_t ts = n_timed;
+        if (timed) RT_CUDA(stage_event(ts, 0, st));
         launch_generate(rc, qin, wc, ku, st);
-        if (timing) RT_CUDA(stage_event(k, 1, st));
+        if (timed) RT_CUDA(stage_event(ts, 1, st));
         launch_extend(scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, count_work, st);
-        if (timing) RT_CUDA(stage_event(k, 2, st));
+        if (timed) RT_CUDA(stage_event(ts, 2, st));
         // shade_k refills done[k & 1]: accumulate_{k-2} must be through with it
         if (overlap && k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[k & 1], 0));
         launch_shade(scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, ku, st);
-        if (timing) RT_CUDA(stage_event(k, 3, st));
+        if (timed) RT_CUDA(stage_event(ts, 3, st));
         if (overlap) {
             RT_CUDA(cudaEventRecord(ctx->ev_shaded[k & 1], st));
             RT_CUDA(cudaStreamWaitEvent(acc_st, ctx->ev_shaded[k & 1], 0));
         }
-        if (timing) RT_CUDA(stage_event(k, 4, acc_st));
+        if (timed) RT_CUDA(stage_event(ts, 4, acc_st));
         launch_accumulate(rc, ctx->done[k & 1].p, wc, ku, acc_sum, acc_sumsq, acc_st);
-        if (timing) RT_CUDA(stage_event(k, 5, acc_st));
+        if (timed) { RT_CUDA(stage_event(ts, 5, acc_st)); ++n_timed; }
         if (overlap) RT_CUDA(cudaEventRecord(ctx->ev_accumulated[k & 1], acc_st));
         launches += 4;
         ++k;
@@ -482,7 +595,7 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     RT_CUDA(cudaEventSynchronize(ctx->ev1));
     RT_CUDA(cudaGetLastError());
     if (timing) {
-        for (uint64_t it = 0; it < k; ++it) {
+        for (uint64_t it = 0; it < n_timed; ++it) {
             const int from[4] = {0, 1, 2, 4}, to[4] = {1, 2, 3, 5};  // generate, extend, shade on the render stream; accumulate on its own
             for (int i = 0; i < 4; ++i) {
                 float ms = 0;
@@ -490,6 +603,8 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
                 ms_stage[i] += ms;
             }
         }
+        // estimate of the whole render: the timed iterations are a uniform 1-in-tstride sample
+        if (n_timed) for (int i = 0; i < 4; ++i) ms_stage[i] *= (float)((double)k / (double)n_timed);
     }
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
@@ -503,6 +618,7 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
         stats->ms_generate = ms_stage[0]; stats->ms_extend = ms_stage[1]; stats->ms_shade = ms_stage[2]; stats->ms_accumulate = ms_stage[3];
         stats->bvh_nodes = scene->d.n_nodes; stats->bvh_always = scene->d.n_always;
         stats->box_tests = ctx->h_status->st_box_tests; stats->prim_tests = ctx->h_status->st_prim_tests;
+        stats->timed_iterations = n_timed;
     }
     return RT_OK;
 }
@@ -528,7 +644,7 @@ int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtH
     if (n == 0) return RT_OK;
     RtContext* ctx = scene->ctx;
     RT_CUDA(cudaSetDevice(ctx->device));
-    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes));
+    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes, scene->shade_bytes, scene->fr_bytes));
     const size_t in_bytes = n * sizeof(RtRayIn), out_bytes = n * sizeof(RtHitOut);
     RT_CUDA(ctx->scratch.ensure(in_bytes + out_bytes + 256));
     RtRayIn* d_rays = reinterpret_cast<RtRayIn*>(ctx->scratch.p);

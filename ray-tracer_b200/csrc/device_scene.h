@@ -36,6 +36,7 @@ constexpr uint32_t RT_MAX_STAGED_PRIMS = 1024;  // primitive heads (16 KB) stage
 constexpr uint32_t RT_MAX_STAGED_RECTS = 256;   // compact rectangle records (16 KB) staged together with the heads
 constexpr uint32_t RT_SMALL_SCENE = 32;         // at most this many primitives: linear list instead of a BVH
 constexpr uint32_t RT_MAX_ALWAYS = 8;           // always-tested list (sky / ground / fog)
+constexpr uint32_t RT_MAX_FRAMES = 8;           // frame-rect list: distinct orthonormal frames the rectangles of a small scene are aligned to
 
 struct DMaterial {       // 32 B, read as two float4
     uint32_t kind;       // RtMaterialKind
@@ -63,6 +64,15 @@ struct DScene {
     uint32_t n_small;          // > 0: no tree, test primitives [0, n_small) in order
     uint32_t small_all_rects;  // n_small > 0, every primitive is a rectangle and the records are staged: specialised loop
     float always_k[RT_MAX_ALWAYS];  // |centre|^2 - r^2 of the always-list spheres, rounded from f64 (big_sphere_hit)
+    // Frame-rect list (k_extend_rects; small all-rectangle scenes whose transforms are rigid): the rectangles are grouped
+    // by the orthonormal frame they are axis-aligned in (cornell-box: world + one frame per rotated cube) and, inside a
+    // frame, by normal axis.  fr_blob = [3 float4 rows per frame][fr_n x float4 (plane w, centre a, centre b, primitive)]
+    // [fr_n x float2 (half extent a, half extent b)]; group (f, k) = records fr_range[3f+k] .. fr_range[3f+k+1].
+    const float4* fr_blob;
+    uint32_t fr_n;         // > 0: extend uses the frame-rect list
+    uint32_t fr_frames;
+    uint32_t fr_identity;  // frame 0 is the world frame: no rotation of the ray
+    uint32_t fr_range[RT_MAX_FRAMES * 3 + 1];
 };
 
 // One queue buffer of live rays, SoA of three float4 streams (48 B per ray):
@@ -81,6 +91,7 @@ struct WaveCounters {
     uint32_t total[RT_RING];   // surv + regenerated camera rays = size of queue k
     uint32_t done[RT_RING];    // finished-path records produced by shade k
     uint64_t issued[RT_RING];  // camera samples issued before iteration k
+    uint32_t cursor[RT_RING];  // ray-index allocator of the persistent extend kernel of iteration k (chunks of RT_FEED_RANGE)
     // status block copied to the host when polling for termination
     uint64_t st_issued;
     uint64_t st_rays;

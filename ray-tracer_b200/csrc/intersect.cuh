@@ -28,12 +28,6 @@
 #include "device_scene.h"
 #include "philox.h"
 
-#ifndef RT_OPT_STACK_T
-#define RT_OPT_STACK_T 0   // keep the entry distance of pushed subtrees and skip them at pop time once a closer hit exists
-#endif
-#ifndef RT_OPT_MERGE_LEAF
-#define RT_OPT_MERGE_LEAF 1  // test sibling leaves as one contiguous primitive range (one loop site)
-#endif
 
 namespace rtb {
 
@@ -339,6 +333,49 @@ __device__ __forceinline__ RayCtx make_ray(float3 o, float3 d) {
     return R;
 }
 
+// One step of the ordered, t-pruned traversal: test the two children of `pair`, intersect the primitives of the
+// children that are leaves, descend into the nearer interior child (pushing the farther) or pop.  Returns the next
+// pair, RT_NO_PRIM when the traversal is over.  Shared by closest_hit (one ray per thread until done) and the
+// persistent extend kernel (lanes refill with new rays while their neighbours keep stepping).
+template <bool COUNT>
+__device__ __forceinline__ uint32_t traverse_step(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key,
+                                                  ClosestHit& best, uint32_t pair, int& sp, uint32_t* stack_spill, TraversalWork* work) {
+    const uint32_t sstride = 4u * blockDim.x;
+    float4 llo, lhi, rlo, rhi;
+    load_pair(S, sm, pair, llo, lhi, rlo, rhi);
+    const float tl = slab(llo, lhi, R, best.t);
+    const float tr = slab(rlo, rhi, R, best.t);
+    if (COUNT) work->box_tests += 2;
+    const uint32_t lcnt = __float_as_uint(lhi.w), rcnt = __float_as_uint(rhi.w);
+    const uint32_t lref = __float_as_uint(llo.w), rref = __float_as_uint(rlo.w);
+    const bool lhit = tl < CUDART_INF_F, rhit = tr < CUDART_INF_F;
+    // leaves: sibling leaves are adjacent in the primitive order, so both become ONE range and one loop site
+    uint32_t begin = 0u, end = 0u;
+    if (lhit && lcnt) { begin = lref; end = lref + lcnt; }
+    if (rhit && rcnt) { if (end == 0u) begin = rref; end = rref + rcnt; }
+    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+    if (COUNT) work->prim_tests += end - begin;
+    // interior children: descend into the nearer one, push the farther
+    const bool lin = lhit && !lcnt && tl <= best.t, rin = rhit && !rcnt && tr <= best.t;
+    uint32_t next = RT_NO_PRIM;
+    if (lin && rin) {
+        const bool swap = tr < tl;
+        const uint32_t pushed = swap ? lref : rref;
+        if (sp < (int)RT_SMEM_STACK) sts32(sm.stack + sp * sstride, pushed);
+        else stack_spill[sp - RT_SMEM_STACK] = pushed;
+        sp += (sp < RT_STACK_DEPTH - 1);
+        next = swap ? rref : lref;
+    } else if (lin) {
+        next = lref;
+    } else if (rin) {
+        next = rref;
+    } else if (sp > 0) {
+        --sp;
+        next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK];
+    }
+    return next;
+}
+
 template <bool COUNT = false>
 __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged& sm, float3 o, float3 d, uint32_t self_prim, const MediumKey& key,
                                                   TraversalWork* work = nullptr) {
@@ -388,78 +425,13 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     // so the per-thread local-memory stack no longer competes with BVH nodes for L1; deeper entries (trees deeper
     // than RT_SMEM_STACK, i.e. > 16 M well-balanced primitives) spill to a local array.
     uint32_t stack_spill[RT_STACK_DEPTH - RT_SMEM_STACK];
-    const uint32_t sstride = 4u * blockDim.x;
-#if RT_OPT_STACK_T
-    float stack_t[RT_STACK_DEPTH];
-#endif
     int sp = 0;
     uint32_t pair = __float_as_uint(load_node(S, sm, 0).w);  // left child of the root; right = pair + 1
+    // ONE back-edge: every lane computes its next pair and falls through to the loop test, so the warp reconverges at
+    // the loop head each iteration (with `continue`s on three paths the lanes of a warp drifted apart for good: ncu
+    // showed 4.7 active threads per instruction on the 1 M-sphere scene against 9.2 for the single-exit form).
     do {
-        float4 llo, lhi, rlo, rhi;
-        load_pair(S, sm, pair, llo, lhi, rlo, rhi);
-        const float tl = slab(llo, lhi, R, best.t);
-        const float tr = slab(rlo, rhi, R, best.t);
-        if (COUNT) work->box_tests += 2;
-        const uint32_t lcnt = __float_as_uint(lhi.w), rcnt = __float_as_uint(rhi.w);
-        const uint32_t lref = __float_as_uint(llo.w), rref = __float_as_uint(rlo.w);
-        const bool lhit = tl < CUDART_INF_F, rhit = tr < CUDART_INF_F;
-#if RT_OPT_MERGE_LEAF
-        // leaves: sibling leaves are adjacent in the primitive order, so both become ONE range and one loop site
-        uint32_t begin = 0u, end = 0u;
-        if (lhit && lcnt) { begin = lref; end = lref + lcnt; }
-        if (rhit && rcnt) { if (end == 0u) begin = rref; end = rref + rcnt; }
-        for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
-        if (COUNT) work->prim_tests += end - begin;
-#else
-        // leaves, nearer first so that the farther one can be pruned by what the nearer one finds
-        {
-            const bool swap = tr < tl;
-            const uint32_t nref = swap ? rref : lref, ncnt = swap ? rcnt : lcnt, fref = swap ? lref : rref, fcnt = swap ? lcnt : rcnt;
-            const float tnear = swap ? tr : tl, tfar = swap ? tl : tr;
-            if (ncnt && tnear < CUDART_INF_F) {
-                for (uint32_t i = nref; i < nref + ncnt; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
-                if (COUNT) work->prim_tests += ncnt;
-            }
-            if (fcnt && tfar <= best.t && tfar < CUDART_INF_F) {
-                for (uint32_t i = fref; i < fref + fcnt; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
-                if (COUNT) work->prim_tests += fcnt;
-            }
-        }
-#endif
-        // interior children: descend into the nearer one, push the farther.  ONE back-edge: every lane computes its
-        // next pair and falls through to the loop test, so the warp reconverges at the loop head each iteration
-        // (with `continue`s on three paths the lanes of a warp drifted apart for good: ncu showed 4.7 active
-        // threads per instruction on the 1 M-sphere scene against 9.2 for the single-exit form).
-        const bool lin = lhit && !lcnt && tl <= best.t, rin = rhit && !rcnt && tr <= best.t;
-        uint32_t next = RT_NO_PRIM;
-        if (lin && rin) {
-            const bool swap = tr < tl;
-            const uint32_t pushed = swap ? lref : rref;
-            if (sp < (int)RT_SMEM_STACK) sts32(sm.stack + sp * sstride, pushed);
-            else stack_spill[sp - RT_SMEM_STACK] = pushed;
-#if RT_OPT_STACK_T
-            stack_t[sp] = swap ? tl : tr;
-#endif
-            sp += (sp < RT_STACK_DEPTH - 1);
-            next = swap ? rref : lref;
-        } else if (lin) {
-            next = lref;
-        } else if (rin) {
-            next = rref;
-        } else {
-#if RT_OPT_STACK_T
-            while (sp > 0) {  // pop, skipping subtrees that a closer hit has meanwhile made irrelevant
-                --sp;
-                if (stack_t[sp] <= best.t) { next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK]; break; }
-            }
-#else
-            if (sp > 0) {
-                --sp;
-                next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK];
-            }
-#endif
-        }
-        pair = next;
+        pair = traverse_step<COUNT>(S, sm, R, self_prim, key, best, pair, sp, stack_spill, work);
     } while (pair != RT_NO_PRIM);
     return best;
 }

@@ -15,6 +15,8 @@
 // host never has to know queue sizes; it polls a status block every few iterations to detect the end.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include "device_scene.h"
 #include "intersect.cuh"
 #include "kernels.h"
@@ -34,32 +36,6 @@ __device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
     if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
     base = __shfl_sync(0xFFFFFFFFu, base, leader);
     return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
-}
-
-// Block-aggregated append of two streams (survivors, finished paths): ONE pair of global atomics per block
-// iteration.  With one atomic per warp, the 2 x 32 k same-address atomics of a launch serialise in one L2 slice
-// and cost about half of the shade kernel (ncu: 20 % of its stall samples sat on that ATOMG).
-// Must be called by every thread of the block.  `s_cnt` = [RT_SHADE_WARPS + 1][2] shared words.
-__device__ __forceinline__ void block_append2(uint32_t* cnt_a, bool pa, uint32_t* cnt_b, bool pb, uint32_t& slot_a, uint32_t& slot_b,
-                                              uint32_t (*s_cnt)[2]) {
-    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
-    const uint32_t ma = __ballot_sync(0xFFFFFFFFu, pa), mb = __ballot_sync(0xFFFFFFFFu, pb);
-    if (lane == 0) { s_cnt[warp][0] = (uint32_t)__popc(ma); s_cnt[warp][1] = (uint32_t)__popc(mb); }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t ta = 0u, tb = 0u;
-        for (uint32_t w = 0; w < n_warps; ++w) {
-            const uint32_t ca = s_cnt[w][0], cb = s_cnt[w][1];
-            s_cnt[w][0] = ta; s_cnt[w][1] = tb;
-            ta += ca; tb += cb;
-        }
-        s_cnt[n_warps][0] = ta ? atomicAdd(cnt_a, ta) : 0u;
-        s_cnt[n_warps][1] = tb ? atomicAdd(cnt_b, tb) : 0u;
-    }
-    __syncthreads();
-    const uint32_t lt = (1u << lane) - 1u;
-    slot_a = s_cnt[n_warps][0] + s_cnt[warp][0] + (uint32_t)__popc(ma & lt);
-    slot_b = s_cnt[n_warps][1] + s_cnt[warp][1] + (uint32_t)__popc(mb & lt);
 }
 
 // local linear index -> (x, local row): 8x4 pixel tiles per warp where they fit, scanline remainders
@@ -118,6 +94,7 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
         wc->issued[(k + 1) % RT_RING] = issued + n_new;
         wc->surv[(k + 2) % RT_RING] = 0u;
         wc->done[(k + 1) % RT_RING] = 0u;
+        wc->cursor[(k + 1) % RT_RING] = 0u;
         wc->st_issued = issued + n_new;
         wc->st_rays += total;
         wc->st_total = total;
@@ -168,71 +145,349 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_EXTEND_MIN_BLOCKS) k_exten
     }
 }
 
+// ---- extend, persistent form for BVH scenes ------------------------------------------------------------------
+//
+// k_extend gives every thread one ray at a time, so a warp is as slow as its longest ray: the r1 profiles show 20.8
+// (book-one) and 9.2 (1 M spheres) active threads per instruction.  Here the warps are persistent and their lanes are
+// refilled: as soon as RT_REFILL_MIN lanes have finished their rays, those lanes store their hits and take the next
+// rays, while the other lanes keep their traversal state (Aila & Laine's persistent threads with dynamic fetch, done
+// per lane with __ballot_sync / popc ranks).  Rays are not read from HBM by the idle lanes — that would stall the
+// whole warp for a DRAM round trip at every refill — but from a per-warp shared-memory double buffer that cp.async
+// fills one 32-ray chunk ahead; chunks come from a per-launch cursor in ranges of RT_FEED_RANGE (one global atomic per
+// 128 rays), so a warp's first 32 rays are consecutive queue entries (a coherent 8x4 camera tile).
+__device__ __forceinline__ void cp_async16(uint32_t smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+constexpr uint32_t RT_FEED_BUF_BYTES = 32u * (16u + 16u + 4u);  // a, b, c.w of 32 rays
+constexpr uint32_t RT_FEED_WARP_BYTES = 2u * RT_FEED_BUF_BYTES;
+
+struct WarpFeed {  // warp-uniform
+    uint32_t buf;                  // shared-window address of this warp's two buffers
+    uint32_t cur, cur_base, cur_cnt, cur_pos;
+    uint32_t nxt_base, nxt_cnt;    // chunk in flight into buffer cur ^ 1 (nxt_cnt = 0: none)
+    uint32_t r_next, r_end;        // claimed ray indices not yet requested
+    bool more;                     // the cursor may still hold rays
+};
+
+// claim the next chunk of up to 32 rays; cnt = 0 when the queue is exhausted
+__device__ __forceinline__ void feed_claim(WarpFeed& F, uint32_t* cursor, uint32_t n, uint32_t& base, uint32_t& cnt) {
+    if (F.r_next >= F.r_end) {
+        if (F.more) {
+            uint32_t b = 0u;
+            if (lane_id() == 0) b = atomicAdd(cursor, (uint32_t)RT_FEED_RANGE);
+            b = __shfl_sync(0xFFFFFFFFu, b, 0);
+            if (b >= n) { F.more = false; }
+            else { F.r_next = b; F.r_end = min(b + (uint32_t)RT_FEED_RANGE, n); }
+        }
+        if (!F.more) { base = 0u; cnt = 0u; return; }
+    }
+    base = F.r_next;
+    cnt = min(32u, F.r_end - F.r_next);
+    F.r_next += cnt;
+}
+
+__device__ __forceinline__ void feed_prefetch(const WarpFeed& F, uint32_t which, const RayQueue& q, bool has_media, uint32_t base, uint32_t cnt) {
+    const uint32_t lane = lane_id();
+    if (lane < cnt) {
+        const uint32_t b = F.buf + which * RT_FEED_BUF_BYTES;
+        cp_async16(b + 16u * lane, &q.a[base + lane]);
+        cp_async16(b + 512u + 16u * lane, &q.b[base + lane]);
+        if (has_media) cp_async4(b + 1024u + 4u * lane, &q.c[base + lane].w);
+    }
+    cp_async_commit();
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_bvh(const DScene S, const RayQueue q, float2* __restrict__ hits,
+                                                                                  WaveCounters* __restrict__ wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
+                                                                                  uint32_t staged_bytes) {
+    extern __shared__ float4 smem4[];
+    const Staged sm = stage_scene(S, smem4);
+    const uint32_t n = wc->total[k % RT_RING];
+    uint32_t* cursor = &wc->cursor[k % RT_RING];
+    const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
+    const bool has_media = S.has_media != 0u;
+    TraversalWork work{0u, 0u};
+
+    WarpFeed F;
+    F.buf = (uint32_t)__cvta_generic_to_shared(smem4) + RT_SMEM_STACK * blockDim.x * 4u + staged_bytes + (threadIdx.x >> 5) * RT_FEED_WARP_BYTES;
+    F.cur = 0u; F.cur_pos = 0u; F.r_next = F.r_end = 0u; F.more = true;
+    feed_claim(F, cursor, n, F.cur_base, F.cur_cnt);
+    if (F.cur_cnt) feed_prefetch(F, 0u, q, has_media, F.cur_base, F.cur_cnt);
+    feed_claim(F, cursor, n, F.nxt_base, F.nxt_cnt);
+    if (F.nxt_cnt) feed_prefetch(F, 1u, q, has_media, F.nxt_base, F.nxt_cnt);
+    cp_async_wait_all();  // (the first refill needs buffer 0; waiting for both keeps the code simple)
+    __syncwarp();
+
+    // per-lane traversal state
+    RayCtx R = make_ray(f3(0.f, 0.f, 0.f), f3(1.f, 0.f, 0.f));
+    ClosestHit best{CUDART_INF_F, RT_NO_PRIM};
+    MediumKey key{0u, 0u, 0u, seed_lo, seed_hi};
+    uint32_t stack_spill[RT_STACK_DEPTH - RT_SMEM_STACK];
+    uint32_t ray_i = RT_NO_PRIM, self_prim = RT_NO_PRIM, pair = RT_NO_PRIM;
+    int sp = 0;
+    const uint32_t root_pair = __float_as_uint(load_node(S, sm, 0).w);
+
+    for (;;) {
+        const bool idle = pair == RT_NO_PRIM;
+        const uint32_t m_idle = __ballot_sync(0xFFFFFFFFu, idle);
+        if (m_idle == 0xFFFFFFFFu || (uint32_t)__popc(m_idle) >= (uint32_t)RT_REFILL_MIN) {
+            if (idle && ray_i != RT_NO_PRIM) {
+                hits[ray_i] = make_float2(best.t, __uint_as_float(best.prim));
+                ray_i = RT_NO_PRIM;
+            }
+            uint32_t want = m_idle;  // lanes still without a ray
+            while (want != 0u) {
+                if (F.cur_pos == F.cur_cnt) {  // current buffer drained: switch to the chunk in flight, request the one after
+                    if (F.nxt_cnt == 0u) break;  // queue exhausted
+                    cp_async_wait_all();
+                    __syncwarp();
+                    F.cur ^= 1u; F.cur_base = F.nxt_base; F.cur_cnt = F.nxt_cnt; F.cur_pos = 0u;
+                    feed_claim(F, cursor, n, F.nxt_base, F.nxt_cnt);
+                    if (F.nxt_cnt) feed_prefetch(F, F.cur ^ 1u, q, has_media, F.nxt_base, F.nxt_cnt);
+                }
+                const uint32_t avail = F.cur_cnt - F.cur_pos;
+                const uint32_t rank = (uint32_t)__popc(want & lt);
+                const bool mine = ((want >> lane) & 1u) && rank < avail;
+                if (mine) {
+                    const uint32_t slot = F.cur_pos + rank;
+                    const uint32_t b = F.buf + F.cur * RT_FEED_BUF_BYTES;
+                    const float4 ra = lds128(b + 16u * slot), rb = lds128(b + 512u + 16u * slot);
+                    ray_i = F.cur_base + slot;
+                    self_prim = __float_as_uint(ra.w);
+                    if (has_media) {
+                        const uint32_t sb = lds32(b + 1024u + 4u * slot);
+                        key.k0 = __float_as_uint(rb.w);
+                        key.k1 = sb >> 8;
+                        key.segment = sb & 0xFFu;
+                    }
+                    R = make_ray(f3(ra.x, ra.y, ra.z), f3(rb.x, rb.y, rb.z));
+                    best.t = CUDART_INF_F;
+                    best.prim = RT_NO_PRIM;
+                    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true>(S, sm, i, R, self_prim, key), best);
+                    if (COUNT) work.prim_tests += S.n_always;
+                    sp = 0;
+                    pair = root_pair;
+                }
+                const uint32_t got = __ballot_sync(0xFFFFFFFFu, mine);
+                want &= ~got;
+                F.cur_pos += (uint32_t)__popc(got);
+                __syncwarp();  // every lane has read its slot before the buffer can be refilled
+            }
+            if (__ballot_sync(0xFFFFFFFFu, pair != RT_NO_PRIM) == 0u) break;  // no lane has work and the queue is exhausted
+        }
+        if (pair != RT_NO_PRIM) pair = traverse_step<COUNT>(S, sm, R, self_prim, key, best, pair, sp, stack_spill, &work);
+    }
+    if (COUNT) {
+        uint32_t bt = work.box_tests, pt = work.prim_tests;
+        for (int off = 16; off > 0; off >>= 1) { bt += __shfl_down_sync(0xFFFFFFFFu, bt, off); pt += __shfl_down_sync(0xFFFFFFFFu, pt, off); }
+        if (lane == 0) { atomicAdd(&wc->st_box_tests, (unsigned long long)bt); atomicAdd(&wc->st_prim_tests, (unsigned long long)pt); }
+    }
+}
+
+// Extend for small all-rectangle scenes (cornell-box): the frame-rect list of device_scene.h.  Per ray: one rotation
+// into each frame (none for the world frame) and three reciprocals, then ~15 instructions per rectangle
+// (t = (w - o_k) / d_k, two in-plane coordinates against their extents) instead of the ~37 of the general record
+// (r1b profile: 111 SASS instructions per 3 rectangles, 68 % issue-active -> issue bound).  No traversal stack and
+// few registers: twice the resident warps of k_extend.  Rectangle::hit semantics as in rect_hit (geometry.rs:152-181:
+// t >= 1e-6, inclusive extents); closest hit with the reference's tie rule (strict <, DFS-earlier wins: the groups
+// are not in DFS order, so an exact tie compares primitive indices, which ARE DFS ranks in a small scene).
+template <int K>
+__device__ __forceinline__ void frame_axis_rects(const DScene& S, uint32_t recs, uint32_t exts, uint32_t f, const float3 o, const float3 d, const float3 inv,
+                                                 uint32_t self_prim, float& best_t, uint32_t& best_i) {
+    const float ok = K == 0 ? o.x : (K == 1 ? o.y : o.z), ik = K == 0 ? inv.x : (K == 1 ? inv.y : inv.z);
+    const float oa = K == 0 ? o.y : o.x, da = K == 0 ? d.y : d.x;
+    const float ob = K == 2 ? o.y : o.z, db = K == 2 ? d.y : d.z;
+    const uint32_t j0 = S.fr_range[3u * f + K], j1 = S.fr_range[3u * f + K + 1];
+    // groups hold one to three rectangles: a rolled loop (3 uniform instructions per trip) beats ptxas' unroll-by-4
+    // with its remainder ladder, which cost ~25 instructions per group (r1d profile: 689 lane-instructions per ray)
+#pragma unroll 1
+    for (uint32_t j = j0; j < j1; ++j) {
+        const float4 A = lds128(recs + 16u * j);
+        float2 B;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(B.x), "=f"(B.y) : "r"(exts + 8u * j));
+        const float t = (A.x - ok) * ik;
+        const float pa = fmaf(t, da, oa) - A.y, pb = fmaf(t, db, ob) - A.z;
+        const uint32_t idx = __float_as_uint(A.w);
+        // best_t starts at FLT_MAX, not +inf, so t = +inf (d_k = 0) can neither be closer nor tie; NaN fails t >= eps
+        const bool closer = (t < best_t) | ((t == best_t) & (idx < best_i));
+        const bool hit = (t >= RT_T_EPS) & (fabsf(pa) <= B.x) & (fabsf(pb) <= B.y) & (idx != self_prim) & closer;
+        best_t = hit ? t : best_t;
+        best_i = hit ? idx : best_i;
+    }
+}
+
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_RECTS_MIN_BLOCKS) k_extend_rects(const DScene S, const RayQueue q, float2* __restrict__ hits,
+                                                                                      WaveCounters* __restrict__ wc, uint32_t k) {
+    extern __shared__ float4 smem4[];
+    const uint32_t n_blob = 3u * S.fr_frames + S.fr_n + (S.fr_n + 1u) / 2u;
+    for (uint32_t i = threadIdx.x; i < n_blob; i += blockDim.x) smem4[i] = S.fr_blob[i];
+    __syncthreads();
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem4);
+    const uint32_t recs = base + 48u * S.fr_frames, exts = recs + 16u * S.fr_n;
+    const uint32_t n = wc->total[k % RT_RING];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float4 a = q.a[i], b = q.b[i];
+        const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z);
+        const uint32_t self_prim = __float_as_uint(a.w);
+        float best_t = 3.402823466e38f;  // a miss is prim == RT_NO_PRIM; its t is never read
+        uint32_t best_i = RT_NO_PRIM;
+#pragma unroll 1
+        for (uint32_t f = 0; f < S.fr_frames; ++f) {
+            float3 of = o, df = d;
+            if (f > 0u || !S.fr_identity) {
+                const float4 u0 = lds128(base + 48u * f), u1 = lds128(base + 48u * f + 16u), u2 = lds128(base + 48u * f + 32u);
+                of = f3(dot3(u0, o), dot3(u1, o), dot3(u2, o));
+                df = f3(dot3(u0, d), dot3(u1, d), dot3(u2, d));
+            }
+            const float3 inv = f3(rcp_approx(df.x), rcp_approx(df.y), rcp_approx(df.z));
+            frame_axis_rects<0>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
+            frame_axis_rects<1>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
+            frame_axis_rects<2>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
+        }
+        hits[i] = make_float2(best_i == RT_NO_PRIM ? CUDART_INF_F : best_t, __uint_as_float(best_i));
+    }
+}
+
 // ---- shade -----------------------------------------------------------------------------------------
 
-__global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(const DScene S, const RenderConst rc, const RayQueue qin, RayQueue qout,
+// Shared memory of k_shade (dynamic): [materials 2 float4 each][prim heads][rect normals][prim meta uint2].  The
+// primitive tables are staged when the scene is small (S.n_staged_prims): the r1b profile showed the dependent chain
+// hit -> prim_meta -> prim_head -> rect_nrm (three L1/L2 round trips) as ~30 % of the kernel's stall samples.
+struct ShadeOne {
+    bool alive, record;
+    float4 o0, o1, o2;  // alive: the three queue words of the scattered ray; record: o0 = (radiance, pixel)
+};
+
+__device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst& rc, const float4* smats, uint32_t n_staged_mats,
+                                              const float4 a, const float4 b, const float4 c, const float2 h) {
+    ShadeOne r;
+    r.alive = r.record = false;
+    r.o0 = r.o1 = r.o2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const uint32_t prim = __float_as_uint(h.y);
+    if (prim == RT_NO_PRIM) return r;  // miss -> black (render.rs:26)
+    const uint2 meta = S.prim_meta[prim];
+    const float4 head = S.prim_head[prim];
+    const int32_t mi = (int32_t)meta.y;
+    if (mi < 0) return r;  // no material -> black (render.rs:18-20)
+    DMaterial m;
+    {
+        const float4* src = ((uint32_t)mi < n_staged_mats) ? &smats[2 * mi] : reinterpret_cast<const float4*>(S.mats) + 2 * (size_t)mi;
+        const float4 m0 = src[0], m1 = src[1];
+        m.kind = __float_as_uint(m0.x); m.texture = (int32_t)__float_as_uint(m0.y); m.fuzz = m0.z; m.ior = m0.w;
+        m.r = m1.x; m.g = m1.y; m.b = m1.z; m.pad = 0.0f;
+    }
+    const uint32_t sb = __float_as_uint(c.w), gp = __float_as_uint(b.w);
+    const uint32_t sample = sb >> 8, segment = sb & 0xFFu;
+    const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z), thr = f3(c.x, c.y, c.z);
+    const MediumKey key{gp, sample, segment, rc.seed_lo, rc.seed_hi};
+    const HitDetail hd = hit_detail(S, prim, o, d, h.x, m.texture >= 0, key, head);
+    const Philox4 rnd = philox4x32_10(segment, RT_DIM_SHADE, rc.seed_lo, rc.seed_hi, gp, sample);
+    const ScatterResult sr = shade_material(S, m, d, hd, rnd);
+    if (sr.scattered) {
+        if (segment < rc.max_depth) {  // color(.., 0) returns black without tracing (render.rs:6-8)
+            const float3 t2 = thr * sr.attenuation;
+            const bool is_medium = head.w <= 0.0f && __float_as_uint(head.y) == (uint32_t)RT_PRIM_MEDIUM_SPHERE;  // general records carry their kind in .y
+            r.o0 = make_float4(hd.p.x, hd.p.y, hd.p.z, __uint_as_float(is_medium ? RT_NO_PRIM : prim));
+            r.o1 = make_float4(sr.dir.x, sr.dir.y, sr.dir.z, b.w);
+            r.o2 = make_float4(t2.x, t2.y, t2.z, __uint_as_float((sample << 8) | (segment + 1u)));
+            r.alive = true;
+        }
+    } else if (m.kind == RT_MAT_DIFFUSE_LIGHT) {
+        const float3 L = thr * sr.attenuation;
+        if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {
+            r.o0 = make_float4(L.x, L.y, L.z, b.w);
+            r.record = true;
+        }
+    }
+    return r;
+}
+
+// Each thread shades RT_SHADE_RAYS rays per block round (their queue words are all requested before the first is
+// used: RT_SHADE_RAYS x the memory-level parallelism) and the block allocates output slots for the whole round with
+// ONE barrier pair and ONE pair of global atomics (block_append2 generalised to RT_SHADE_RAYS ballots per warp).
+__global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
                                                const float2* __restrict__ hits, float4* __restrict__ done, WaveCounters* __restrict__ wc, uint32_t k) {
-    __shared__ float4 smats[2 * RT_MAX_STAGED_MATS];
+    extern __shared__ float4 shade_smem[];
     __shared__ uint32_t s_cnt[RT_SHADE_BLOCK / 32 + 1][2];
-    const uint32_t n_staged = min(S.n_mats, RT_MAX_STAGED_MATS);
-    for (uint32_t i = threadIdx.x; i < 2u * n_staged; i += blockDim.x) smats[i] = reinterpret_cast<const float4*>(S.mats)[i];
+    constexpr int R = RT_SHADE_RAYS;
+    const uint32_t n_staged = min(S0.n_mats, RT_MAX_STAGED_MATS);
+    const uint32_t n_sp = S0.n_staged_prims, n_sr = n_sp ? S0.n_rects : 0u;
+    float4* smats = shade_smem;
+    float4* s_head = smats + 2u * n_staged;
+    float4* s_nrm = s_head + n_sp;
+    uint2* s_meta = reinterpret_cast<uint2*>(s_nrm + n_sr);
+    for (uint32_t i = threadIdx.x; i < 2u * n_staged; i += blockDim.x) smats[i] = reinterpret_cast<const float4*>(S0.mats)[i];
+    for (uint32_t i = threadIdx.x; i < n_sp; i += blockDim.x) { s_head[i] = S0.prim_head[i]; s_meta[i] = S0.prim_meta[i]; }
+    for (uint32_t i = threadIdx.x; i < n_sr; i += blockDim.x) s_nrm[i] = S0.rect_nrm[i];
+    DScene S = S0;
+    if (n_sp) { S.prim_head = s_head; S.prim_meta = s_meta; S.rect_nrm = s_nrm; }
     __syncthreads();
     const uint32_t s = k % RT_RING;
     const uint32_t n = wc->total[s];
     uint32_t* surv_next = &wc->surv[(k + 1) % RT_RING];
     uint32_t* done_cnt = &wc->done[s];
-    const uint32_t stride = gridDim.x * blockDim.x;
-    // whole blocks iterate together: the append below synchronises the block
-    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {
-        const uint32_t i = base + threadIdx.x;
-        bool alive = false, record = false;
-        float4 na, nb, nc, rec;
-        if (i < n) {
-            const float4 a = qin.a[i], b = qin.b[i], c = qin.c[i];
-            const float2 h = hits[i];
-            const uint32_t prim = __float_as_uint(h.y);
-            if (prim != RT_NO_PRIM) {  // miss -> black (render.rs:26)
-                const uint2 meta = __ldg(&S.prim_meta[prim]);
-                const int32_t mi = (int32_t)meta.y;
-                if (mi >= 0) {  // no material -> black (render.rs:18-20)
-                    DMaterial m;
-                    {
-                        const float4* src = ((uint32_t)mi < n_staged) ? &smats[2 * mi] : reinterpret_cast<const float4*>(S.mats) + 2 * (size_t)mi;
-                        const float4 m0 = src[0], m1 = src[1];
-                        m.kind = __float_as_uint(m0.x); m.texture = (int32_t)__float_as_uint(m0.y); m.fuzz = m0.z; m.ior = m0.w;
-                        m.r = m1.x; m.g = m1.y; m.b = m1.z; m.pad = 0.0f;
-                    }
-                    const uint32_t sb = __float_as_uint(c.w), gp = __float_as_uint(b.w);
-                    const uint32_t sample = sb >> 8, segment = sb & 0xFFu;
-                    const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z), thr = f3(c.x, c.y, c.z);
-                    const MediumKey key{gp, sample, segment, rc.seed_lo, rc.seed_hi};
-                    const HitDetail hd = hit_detail(S, prim, o, d, h.x, m.texture >= 0, key);
-                    const Philox4 rnd = philox4x32_10(segment, RT_DIM_SHADE, rc.seed_lo, rc.seed_hi, gp, sample);
-                    const ScatterResult sr = shade_material(S, m, d, hd, rnd);
-                    if (sr.scattered) {
-                        if (segment < rc.max_depth) {  // color(.., 0) returns black without tracing (render.rs:6-8)
-                            const float3 t2 = thr * sr.attenuation;
-                            const float4 head = __ldg(&S.prim_head[prim]);  // general records carry their kind in .y
-                            const bool is_medium = head.w <= 0.0f && __float_as_uint(head.y) == (uint32_t)RT_PRIM_MEDIUM_SPHERE;
-                            na = make_float4(hd.p.x, hd.p.y, hd.p.z, __uint_as_float(is_medium ? RT_NO_PRIM : prim));
-                            nb = make_float4(sr.dir.x, sr.dir.y, sr.dir.z, b.w);
-                            nc = make_float4(t2.x, t2.y, t2.z, __uint_as_float((sample << 8) | (segment + 1u)));
-                            alive = true;
-                        }
-                    } else if (m.kind == RT_MAT_DIFFUSE_LIGHT) {
-                        const float3 L = thr * sr.attenuation;
-                        if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {
-                            rec = make_float4(L.x, L.y, L.z, b.w);
-                            record = true;
-                        }
-                    }
-                }
-            }
+    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    const uint32_t stride = gridDim.x * blockDim.x * R;
+    // whole blocks iterate together: the slot allocation below synchronises the block
+    for (uint32_t base = blockIdx.x * blockDim.x * R; base < n; base += stride) {
+        float4 a[R], b[R], c[R];
+        float2 h[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t i = base + r * blockDim.x + threadIdx.x;
+            if (i < n) { h[r] = hits[i]; a[r] = qin.a[i]; b[r] = qin.b[i]; c[r] = qin.c[i]; }
+            else { h[r] = make_float2(0.f, __uint_as_float(RT_NO_PRIM)); a[r] = b[r] = c[r] = make_float4(0.f, 0.f, 0.f, 0.f); }
         }
-        uint32_t slot, dslot;
-        block_append2(surv_next, alive, done_cnt, record, slot, dslot, s_cnt);
-        if (alive) { qout.a[slot] = na; qout.b[slot] = nb; qout.c[slot] = nc; }
-        if (record) done[dslot] = rec;
+        ShadeOne res[R];
+        uint32_t ma[R], mb[R], ca = 0u, cb = 0u;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            res[r] = shade_one(S, rc, smats, n_staged, a[r], b[r], c[r], h[r]);
+            ma[r] = __ballot_sync(0xFFFFFFFFu, res[r].alive);
+            mb[r] = __ballot_sync(0xFFFFFFFFu, res[r].record);
+            ca += (uint32_t)__popc(ma[r]);
+            cb += (uint32_t)__popc(mb[r]);
+        }
+        if (lane == 0) { s_cnt[warp][0] = ca; s_cnt[warp][1] = cb; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t ta = 0u, tb = 0u;
+            for (uint32_t w = 0; w < n_warps; ++w) {
+                const uint32_t wa = s_cnt[w][0], wb = s_cnt[w][1];
+                s_cnt[w][0] = ta; s_cnt[w][1] = tb;
+                ta += wa; tb += wb;
+            }
+            s_cnt[n_warps][0] = ta ? atomicAdd(surv_next, ta) : 0u;
+            s_cnt[n_warps][1] = tb ? atomicAdd(done_cnt, tb) : 0u;
+        }
+        __syncthreads();
+        uint32_t slot = s_cnt[n_warps][0] + s_cnt[warp][0], dslot = s_cnt[n_warps][1] + s_cnt[warp][1];
+        __syncwarp();
+        const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (res[r].alive) {
+                const uint32_t sl = slot + (uint32_t)__popc(ma[r] & lt);
+                qout.a[sl] = res[r].o0; qout.b[sl] = res[r].o1; qout.c[sl] = res[r].o2;
+            }
+            if (res[r].record) done[dslot + (uint32_t)__popc(mb[r] & lt)] = res[r].o0;
+            slot += (uint32_t)__popc(ma[r]);
+            dslot += (uint32_t)__popc(mb[r]);
+        }
     }
 }
 
@@ -311,7 +566,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
         res.p[0] = res.p[1] = res.p[2] = res.n[0] = res.n[1] = res.n[2] = res.uv[0] = res.uv[1] = 0.0f;
         if (h.prim != RT_NO_PRIM) {
             const uint2 meta = __ldg(&S.prim_meta[h.prim]);
-            const HitDetail hd = hit_detail(S, h.prim, o, d, h.t, true, key);
+            const HitDetail hd = hit_detail(S, h.prim, o, d, h.t, true, key, __ldg(&S.prim_head[h.prim]));
             res.hit = 1; res.prim = (int32_t)meta.x; res.t = hd.t; res.material = (int32_t)meta.y;
             res.p[0] = hd.p.x; res.p[1] = hd.p.y; res.p[2] = hd.p.z;
             res.n[0] = hd.n.x; res.n[1] = hd.n.y; res.n[2] = hd.n.z;
@@ -325,7 +580,10 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
 
 static int g_num_sms = 0;
 static int g_extend_blocks_per_sm = 0, g_trace_blocks_per_sm = 0, g_shade_blocks_per_sm = 0;
-static size_t g_extend_smem = ~(size_t)0;
+static size_t g_extend_smem = ~(size_t)0, g_shade_smem = ~(size_t)0, g_rects_smem = ~(size_t)0;
+static int g_rects_blocks_per_sm = 0, g_bvh_blocks_per_sm = 0;
+static size_t g_bvh_smem = 0, g_scene_smem = 0;
+static int g_persistent = -1;
 
 cudaError_t kernels_init(int device) {
     if (g_num_sms > 0) return cudaSuccess;
@@ -333,15 +591,28 @@ cudaError_t kernels_init(int device) {
     const cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     if (e != cudaSuccess) return e;
     g_num_sms = sms;
-    const cudaError_t e2 = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shade_blocks_per_sm, k_shade, RT_SHADE_BLOCK, 0);
-    if (e2 != cudaSuccess) return e2;
-    if (g_shade_blocks_per_sm < 1) g_shade_blocks_per_sm = 1;
     return cudaSuccess;
 }
 
-cudaError_t kernels_configure(int device, size_t scene_bytes) {
+cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes, size_t fr_bytes) {
     cudaError_t e = kernels_init(device);
     if (e != cudaSuccess) return e;
+    if (fr_bytes && fr_bytes != g_rects_smem) {
+        e = cudaFuncSetAttribute(k_extend_rects, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fr_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_rects_blocks_per_sm, k_extend_rects, RT_EXTEND_BLOCK, fr_bytes);
+        if (e != cudaSuccess) return e;
+        if (g_rects_blocks_per_sm < 1) g_rects_blocks_per_sm = 1;
+        g_rects_smem = fr_bytes;
+    }
+    if (shade_bytes != g_shade_smem) {
+        e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shade_blocks_per_sm, k_shade, RT_SHADE_BLOCK, shade_bytes);
+        if (e != cudaSuccess) return e;
+        if (g_shade_blocks_per_sm < 1) g_shade_blocks_per_sm = 1;
+        g_shade_smem = shade_bytes;
+    }
     const size_t staged_bytes = scene_bytes + (size_t)RT_SMEM_STACK * RT_EXTEND_BLOCK * sizeof(uint32_t);
     if (staged_bytes != g_extend_smem) {
         e = cudaFuncSetAttribute(k_extend<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
@@ -357,6 +628,20 @@ cudaError_t kernels_configure(int device, size_t scene_bytes) {
         if (g_extend_blocks_per_sm < 1) g_extend_blocks_per_sm = 1;
         if (g_trace_blocks_per_sm < 1) g_trace_blocks_per_sm = 1;
         g_extend_smem = staged_bytes;
+        // persistent form: + the per-warp ray double buffers
+        g_scene_smem = scene_bytes;
+        g_bvh_smem = staged_bytes + (size_t)(RT_EXTEND_BLOCK / 32) * RT_FEED_WARP_BYTES;
+        e = cudaFuncSetAttribute(k_extend_bvh<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_bvh_smem);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_extend_bvh<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_bvh_smem);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_bvh_blocks_per_sm, k_extend_bvh<false>, RT_EXTEND_BLOCK, g_bvh_smem);
+        if (e != cudaSuccess) return e;
+        if (g_bvh_blocks_per_sm < 1) g_bvh_blocks_per_sm = 1;
+    }
+    if (g_persistent < 0) {  // 0: never, 1: always (where a tree exists), 2 (default): trees that do not fit shared memory by far
+        const char* pe = getenv("RT_B200_PERSISTENT");
+        g_persistent = pe ? atoi(pe) : 2;
     }
     return cudaSuccess;
 }
@@ -368,12 +653,23 @@ void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc,
 }
 void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                    bool count_work, cudaStream_t st) {
+    if (S.fr_n && !count_work) { k_extend_rects<<<g_num_sms * g_rects_blocks_per_sm, RT_EXTEND_BLOCK, g_rects_smem, st>>>(S, q, hits, wc, k); return; }
+    // The persistent form pays where rays are long and uneven (1 M spheres: 69 box tests per ray, +20 %); on trees that
+    // live in shared memory (book-one: 18 box tests) the per-ray set-up at partial warp occupancy costs more than the
+    // idle lanes it saves (r1e: 7.1 vs 12.6 Grays/s), so those keep one ray per thread.
+    const bool persistent = g_persistent == 1 || (g_persistent == 2 && S.n_nodes >= RT_PERSISTENT_MIN_NODES);
+    if (persistent && S.n_small == 0u && !S.root_is_leaf && S.n_nodes > 0u) {
+        const int grid = g_num_sms * g_bvh_blocks_per_sm;
+        if (count_work) k_extend_bvh<true><<<grid, RT_EXTEND_BLOCK, g_bvh_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)g_scene_smem);
+        else k_extend_bvh<false><<<grid, RT_EXTEND_BLOCK, g_bvh_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)g_scene_smem);
+        return;
+    }
     if (count_work) k_extend<true><<<g_num_sms * g_extend_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
     else k_extend<false><<<g_num_sms * g_extend_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st) {
-    k_shade<<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, 0, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    k_shade<<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
 void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
     k_accumulate<<<g_num_sms * 2, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);

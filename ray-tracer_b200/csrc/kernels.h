@@ -13,14 +13,33 @@
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 4
 #endif
+#ifndef RT_SHADE_RAYS
+#define RT_SHADE_RAYS 1   // rays shaded per thread per block round (one barrier pair / atomic pair per round)
+#endif
+#ifndef RT_REFILL_MIN
+#define RT_REFILL_MIN 16     // persistent extend: idle lanes of a warp fetch new rays once at least this many are idle
+#endif
+#ifndef RT_PERSISTENT_MIN_NODES
+#define RT_PERSISTENT_MIN_NODES 65536u  // BVH size from which extend runs in its persistent, lane-refilling form
+#endif
+#ifndef RT_FEED_RANGE
+#define RT_FEED_RANGE 128    // ray indices a warp claims per global atomic (multiple of 32)
+#endif
+#ifndef RT_BVH_MIN_BLOCKS
+#define RT_BVH_MIN_BLOCKS 3
+#endif
+#ifndef RT_RECTS_MIN_BLOCKS
+#define RT_RECTS_MIN_BLOCKS 6
+#endif
 #ifndef RT_EXTEND_MIN_BLOCKS
 #define RT_EXTEND_MIN_BLOCKS 3
 #endif
 
 namespace rtb {
 
-// Must be called (per process) before any launch; `staged_bytes` = shared-memory bytes of BVH prefix.
-cudaError_t kernels_configure(int device, size_t staged_bytes);
+// Must be called before the launches of a scene; `staged_bytes` = shared-memory bytes of the scene prefix staged by
+// extend / trace, `fr_bytes` = bytes of the frame-rect table staged by k_extend_rects (0: none), `shade_bytes` = shared-memory bytes of the material / primitive tables staged by shade.
+cudaError_t kernels_configure(int device, size_t staged_bytes, size_t shade_bytes, size_t fr_bytes);
 // SM count only (kernels without dynamic shared memory).
 cudaError_t kernels_init(int device);
 int kernels_num_sms();

@@ -53,12 +53,14 @@ __device__ __forceinline__ void sphere_uv(float3 unit, float& u, float& v) {  //
 
 // Rebuild the reference's HitRecord for (ray, t, prim).  `want_uv` skips the atan2/acos when the
 // material's texture does not read uv.
-__device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, float3 o, float3 d, float t, bool want_uv, const MediumKey& key) {
+// S.prim_head / S.rect_nrm are read with plain (generic) loads: k_shade points them at its shared-memory copies when
+// the tables are small enough to be staged (ld.global.nc on a shared address would be illegal).
+__device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, float3 o, float3 d, float t, bool want_uv, const MediumKey& key,
+                                                const float4 head) {
     HitDetail h;
     h.u = h.v = 0.0f;
     h.t = t;
     h.uv_valid = want_uv;
-    const float4 head = __ldg(&S.prim_head[i]);
     if (head.w > 0.0f) {  // translation-only sphere
         sphere_record_f64(o, d, f3(head.x, head.y, head.z), head.w, t, h.p, h.n, h.t);
         if (want_uv) sphere_uv(h.n, h.u, h.v);
@@ -68,7 +70,7 @@ __device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, flo
         // Sprite::hit returns M (o' + t d') = o + t d and M (0,0,1) (sprite.rs:108-115): the world-space point needs no
         // matrix at all and the normal is one precomputed column — 16 B instead of the 128-byte record
         const uint32_t ri = __float_as_uint(head.z);
-        const float4 nrm = __ldg(&S.rect_nrm[ri]);
+        const float4 nrm = S.rect_nrm[ri];
         h.p = fma3(t, d, o);
         h.n = f3(nrm.x, nrm.y, nrm.z);
         if (want_uv) {  // geometry.rs:170-171

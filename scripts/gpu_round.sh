@@ -14,6 +14,15 @@ for s in $STEPS; do
     bench)  timeout 600 python bench.py > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?"; cat $OUT/bench.json ;;
     ref)    timeout 400 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "ref rc=$?"; cat $OUT/bench_ref.json ;;
     scenes) timeout 600 python scripts/time_scenes.py > $OUT/scenes.log 2>&1; echo "scenes rc=$?"; cat $OUT/scenes.log ;;
+    variants)
+      RT_B200_LIB=$PWD/ray-tracer_b200/librt_b200.so python scripts/time_scenes.py $VSCENES > $OUT/variants.log 2>&1
+      bash scripts/bench_variants.sh $VSCENES >> $OUT/variants.log 2>&1; echo "variants rc=$?"; cat $OUT/variants.log ;;
+    persist)
+      RT_B200_PERSISTENT=0 python scripts/time_scenes.py book-one book-two stress 2>&1 | sed "s/^/[non-persistent] /" > $OUT/persist.log
+      python scripts/time_scenes.py book-one book-two stress >> $OUT/persist.log 2>&1; cat $OUT/persist.log ;;
+    caps)
+      for cap in 524288 2097152 4194304; do RT_B200_QUEUE_CAPACITY=$cap python scripts/time_scenes.py cornell-box book-one 2>&1 | sed "s/^/[cap $cap] /"; done > $OUT/caps.log
+      RT_B200_RECT_FRAMES=0 python scripts/time_scenes.py cornell-box 2>&1 | sed "s/^/[no frame-rects] /" >> $OUT/caps.log; cat $OUT/caps.log ;;
     allbench)
       for wl in book-one book-two stress-1m book-one-4k; do
         timeout 900 python bench.py --workload $wl --steps 2 --warmup 3 --no-cpu-baseline > $OUT/bench_$wl.json 2> $OUT/bench_$wl.err; echo "bench $wl rc=$?"; cat $OUT/bench_$wl.json
@@ -24,7 +33,8 @@ for s in $STEPS; do
         python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $OUT/ncu_launches.log 2>&1
       echo "launches rc=$?" ;;
     full)
-      for sc in "cornell-box 600 600 16 50" "book-one 1920 1080 4 50"; do
+      IFS=';' read -ra SCS <<< "${FULLSCENES:-cornell-box 600 600 16 50;book-one 1920 1080 4 50}"
+      for sc in "${SCS[@]}"; do
         set -- $sc
         timeout 120 python scripts/profile_target.py $sc > $OUT/plain_$1.log 2>&1 &&
         timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_extend|k_shade' -s 40 -c 4 -o $OUT/full_$1 -f \
