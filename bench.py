@@ -103,6 +103,29 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(busy), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def measure_l2():
+    """L2 read-stream bandwidth measured on this box by ray-tracer_b200/tools/l2bw (no L2 figure in MEASURED_PEAKS.json)."""
+    tool = os.path.join(ROOT, "ray-tracer_b200", "tools", "l2bw")
+    if not os.path.exists(tool):
+        return None
+    try:
+        out = subprocess.run([tool], capture_output=True, text=True, timeout=120).stdout.strip().splitlines()[-1]
+        return json.loads(out)
+    except Exception:  # noqa: BLE001 - a missing figure is reported as null, never guessed
+        return None
+
+
+def ncu_traffic(workload, kernel):
+    """DRAM bytes per ray of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json)."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(path):
+        return None, None
+    t = json.load(open(path)).get(workload)
+    if not t or t.get("kernel") != kernel:
+        return None, None
+    return float(t["dram_bytes_per_ray"]), t.get("source")
+
+
 def run_reference(args, wl):
     """The reference's own CPU implementation of the path, restated (oracle FAITHFUL mode), all host threads."""
     rank = int(os.environ.get("RANK", "0"))
@@ -281,6 +304,7 @@ def main():
 
     if rank == 0:
         hbm_peak, peak_src, sm_max = load_peaks()
+        l2_peak = measure_l2()
         n_extend = float(counts[5])  # extend launches = wavefront iterations, summed over ranks
         rays_per_launch = tot_rays / max(n_extend, 1)
         # per-launch duration: summed extend time of the slowest rank / its launches (ranks have equal iteration counts to within a few)
@@ -289,34 +313,48 @@ def main():
         dur = extend_s / max(extend_launches_rank, 1)
         achieved = EXTEND_BYTES_PER_RAY * rays_per_launch / max(dur, 1e-12) / 1e9
         sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
+        kinds = flat.prims()["kind"]
+        rect_frac = float(np.mean(kinds == rt.PRIM_RECT))
+        info = scene.bvh_info()
+        kernel = "k_extend_rects" if (info["nodes"] == 0 and rect_frac == 1.0) else ("k_extend_bvh" if info["nodes"] >= 65536 else "k_extend")
+        bytes_per_ray, traffic_src = ncu_traffic(args.workload, kernel)
         line = {
             "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_all / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": cfg, "scene": scene_name, "width": W, "height": H, "spp": spp, "max_depth": depth, "seed_scene": 1,
                        "sharding": f"rows y % {world} == rank, NCCL all-gather + de-interleave" if world > 1 else "single GPU",
-                       "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": scene.bvh_info()},
+                       "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": info,
+                       "queue_capacity": args.queue_capacity or 1 << 22},
             "grays_per_s": tot_rays / (ms_all * 1e-3) / 1e9, "rays_per_path": tot_rays / tot_paths, "mean_radiance": mean_check,
             "gpu_launches": tot_launches,
             "stage_ms_per_step": {"generate": ms_stage[0] / args.steps, "extend": ms_stage[1] / args.steps, "shade": ms_stage[2] / args.steps,
                                   "accumulate": ms_stage[3] / args.steps},
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": scene_bytes + 64 + 40,
                     "d2h_bytes_per_step": W * H * 3 * 4, "ms_per_step": float(e2e_t[0]) / args.steps * 1e3},
-            "roofline": {"kernel": "k_extend", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": None, "peak_source": peak_src, "launch_us": dur * 1e6, "rays_per_launch": rays_per_launch,
+            "roofline": {"kernel": kernel, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "traffic": bytes_per_ray * rays_per_launch if bytes_per_ray else None, "traffic_source": traffic_src,
+                         "peak_source": peak_src, "launch_us": dur * 1e6, "rays_per_launch": rays_per_launch,
+                         "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY,
+                         "timing": "CUDA events around the kernel's launches of every 8th wavefront iteration inside the timed region",
                          "note": "extend is FP32-issue/latency bound, not HBM bound; see roofline_fp32 and DESIGN.md"},
             "clocks": clocks,
         }
-        kinds = flat.prims()["kind"]
-        rect_frac = float(np.mean(kinds == rt.PRIM_RECT))
         instr_per_ray = box_per_ray * FP32_PER_BOX + prim_per_ray * (rect_frac * FP32_PER_RECT + (1 - rect_frac) * FP32_PER_SPHERE)
         rays_per_s_kernel = tot_rays / world / max(extend_s, 1e-12)  # per GPU, inside k_extend
         fp32_peak = 148 * 128 * sm_mhz * 1e6
-        line["roofline_fp32"] = {"kernel": "k_extend", "bound": "fp32-issue", "box_tests_per_ray": box_per_ray, "prim_tests_per_ray": prim_per_ray,
+        l2_bytes_per_ray = box_per_ray * 32 + prim_per_ray * (rect_frac * 64 + (1 - rect_frac) * 16)
+        if l2_peak:
+            l2_gbs = l2_peak["l2_read_gbs_32MB"]
+            line["roofline_l2"] = {"kernel": kernel, "bound": "l2", "achieved": rays_per_s_kernel * l2_bytes_per_ray / 1e9, "peak": l2_gbs, "unit": "GB/s",
+                                   "frac": rays_per_s_kernel * l2_bytes_per_ray / 1e9 / l2_gbs, "bytes_per_ray": l2_bytes_per_ray,
+                                   "peak_source": "measured now by ray-tracer_b200/tools/l2bw (32 MB read stream, ld.global.cg)", "l2bw": l2_peak,
+                                   "note": "upper bound on node/primitive traffic: staged tables are read from shared memory, not L2"}
+        line["roofline_fp32"] = {"kernel": kernel, "bound": "fp32-issue", "box_tests_per_ray": box_per_ray, "prim_tests_per_ray": prim_per_ray,
                                  "algorithmic_lane_instr_per_ray": instr_per_ray, "grays_per_s_in_kernel": rays_per_s_kernel / 1e9,
                                  "achieved": rays_per_s_kernel * instr_per_ray / 1e12, "peak": fp32_peak / 1e12, "unit": "T lane-instr/s",
                                  "frac": rays_per_s_kernel * instr_per_ray / fp32_peak, "sm_mhz": sm_mhz,
-                                 "l2_bytes_per_ray": box_per_ray * 32 + prim_per_ray * (rect_frac * 128 + (1 - rect_frac) * 16)}
+                                 "l2_bytes_per_ray": l2_bytes_per_ray}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
         print(json.dumps(line), flush=True)
