@@ -639,7 +639,8 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
         if (e != cudaSuccess) return e;
         if (g_bvh_blocks_per_sm < 1) g_bvh_blocks_per_sm = 1;
     }
-    if (g_persistent < 0) {  // 0: never, 1: always (where a tree exists), 2 (default): trees that do not fit shared memory by far
+    {  // 0: never, 1: always (where a tree exists), 2 (default): trees that do not fit shared memory by far; re-read per
+       // scene so that tests can compare the two forms in one process
         const char* pe = getenv("RT_B200_PERSISTENT");
         g_persistent = pe ? atoi(pe) : 2;
     }

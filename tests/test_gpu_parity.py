@@ -312,3 +312,109 @@ def test_render_sharded_single_rank_matches_render(rt, device):
     ref, _, _ = scene.render(cam, 64, 36, 8, 50, seed=3, want_sumsq=False)
     torch.cuda.synchronize()
     assert np.allclose(full.cpu().numpy(), ref, rtol=1e-6, atol=1e-6)
+
+
+# ---- the specialised extend kernels against the general one (which the trace tests pin to the oracle) -------------
+
+def _render_with_env(rt, device, name, env, w, h, spp, depth=50, seed=3, tables=None, cam=None, queue_capacity=0):
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        scene = rt.Scene.from_tables(device, *tables) if tables else rt.Scene.example(device, name, 1)
+        cam = cam if cam is not None else scene.flat.camera(w / h)
+        s, q, st = scene.render(cam, w, h, spp, depth, seed=seed, queue_capacity=queue_capacity)
+        scene.close()
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    return s, q, st
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,w,h,spp", [("book-one", 128, 72, 8), ("book-two", 64, 64, 4), ("stress:20000", 96, 54, 4)])
+def test_persistent_extend_matches_one_ray_per_thread(rt, device, name, w, h, spp):
+    """k_extend_bvh (lane-refilling persistent warps, cp.async ray feed) and k_extend walk the same tree with the same
+    arithmetic: identical closest hits, so identical paths — only the order of the f64 accumulations differs."""
+    a, qa, sa = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "0"}, w, h, spp)
+    b, qb, sb = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "1"}, w, h, spp)
+    assert sa.rays == sb.rays and sa.paths == sb.paths
+    assert np.allclose(a, b, rtol=1e-5, atol=1e-5) and np.allclose(qa, qb, rtol=1e-5, atol=1e-5)
+    # a queue smaller than one feed range and one that is not a multiple of 32
+    c, _, sc = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "1"}, w, h, 1, queue_capacity=1056)
+    d, _, sd = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "0"}, w, h, 1, queue_capacity=1056)
+    assert sc.rays == sd.rays and np.allclose(c, d, rtol=1e-5, atol=1e-5)
+
+
+def _rect_tables(rt, rects, materials):
+    """Flat tables for rigidly placed rectangles: [(R 3x3 world<-local rotation, centre, width, height, material)]."""
+    prims = np.zeros(len(rects), dtype=rt.PRIM_DTYPE)
+    for i, (R, c, wd, ht, m) in enumerate(rects):
+        R, c = np.asarray(R, dtype=np.float64), np.asarray(c, dtype=np.float64)
+        prims[i]["kind"], prims[i]["material"], prims[i]["order"] = rt.PRIM_RECT, m, i
+        prims[i]["param"][0], prims[i]["param"][1] = wd, ht
+        prims[i]["world_from_local"] = np.concatenate([R, c[:, None]], axis=1).reshape(12).astype(np.float32)
+        prims[i]["local_from_world"] = np.concatenate([R.T, (-R.T @ c)[:, None]], axis=1).reshape(12).astype(np.float32)
+    mats = np.zeros(len(materials), dtype=rt.MATERIAL_DTYPE)
+    texs = np.zeros(len(materials), dtype=rt.TEXTURE_DTYPE)
+    for i, (kind, rgb, fuzz, ior) in enumerate(materials):
+        mats[i] = (kind, i, fuzz, ior)
+        texs[i]["kind"], texs[i]["a"], texs[i]["b"] = rt.TEX_SOLID, -1, -1
+        texs[i]["rgb"][:3] = rgb
+    return prims, mats, texs
+
+
+def _rot(axis, deg):
+    a = np.asarray(axis, dtype=np.float64)
+    a /= np.linalg.norm(a)
+    th = math.radians(deg)
+    K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    return np.eye(3) + math.sin(th) * K + (1 - math.cos(th)) * (K @ K)
+
+
+@pytest.mark.gpu
+def test_frame_rect_extend_matches_general_records(rt, device):
+    """k_extend_rects (rectangles grouped by the frame they are axis-aligned in) against the general 64-byte rectangle
+    records: cornell-box, and a random closed room with boxes in three tilted frames, face normals permuted and
+    flipped, a coplanar pair (exact tie -> the DFS-earlier rectangle) and one frame used by a single rectangle."""
+    a, qa, sa = _render_with_env(rt, device, "cornell-box", {"RT_B200_RECT_FRAMES": "0"}, 96, 96, 16)
+    b, qb, sb = _render_with_env(rt, device, "cornell-box", {}, 96, 96, 16)
+    assert sa.rays == sb.rays
+    assert np.allclose(a, b, rtol=2e-4, atol=2e-4) and np.allclose(qa, qb, rtol=5e-4, atol=5e-4)
+
+    rng = np.random.default_rng(11)
+    mats = [(rt.MAT_LAMBERTIAN, (0.7, 0.6, 0.5), 0, 0), (rt.MAT_DIFFUSE_LIGHT, (4, 4, 4), 0, 0), (rt.MAT_METAL, (0.8, 0.8, 0.9), 0.1, 0),
+            (rt.MAT_LAMBERTIAN, (0.2, 0.7, 0.3), 0, 0)]
+    I = np.eye(3)
+    face = {"+x": _rot([0, 1, 0], 90), "-x": _rot([0, 1, 0], -90), "+y": _rot([1, 0, 0], -90), "-y": _rot([1, 0, 0], 90), "+z": I, "-z": _rot([0, 1, 0], 180)}
+    rects = []
+    L = 10.0
+    for name, sgn, ax in [("+x", 1, 0), ("-x", -1, 0), ("+y", 1, 1), ("-y", -1, 1), ("+z", 1, 2)]:  # room, open towards -z (camera side)
+        c = np.zeros(3)
+        c[ax] = sgn * L / 2
+        rects.append((face[name], c, L, L, 1 if name == "+y" else (3 if name == "-x" else 0)))
+    for k in range(3):  # boxes, each in its own tilted frame, faces through all six permutations / signs
+        F = _rot(rng.normal(size=3), rng.uniform(10, 80))
+        centre = rng.uniform(-2.5, 2.5, size=3)
+        half = rng.uniform(0.6, 1.4, size=3)
+        for name, sgn, ax in [("+x", 1, 0), ("-x", -1, 0), ("+y", 1, 1), ("-y", -1, 1), ("+z", 1, 2), ("-z", -1, 2)]:
+            n_local = np.zeros(3)
+            n_local[ax] = sgn * half[ax]
+            Rf = face[name]
+            ext = np.abs(Rf.T @ (2 * half))  # extents of the face along its own x / y
+            rects.append((F @ Rf, centre + F @ n_local, ext[0], ext[1], 2 if k == 0 else 0))
+    rects.append((_rot([1, 2, 3], 33), [0.5, -3.0, 1.0], 1.5, 2.5, 3))  # a frame of its own
+    rects.append((I, [0, 0, L / 2], L / 2, L / 2, 3))                  # coplanar with the back wall: ties go to the earlier one
+    tables = _rect_tables(rt, rects, mats)
+    assert len(rects) <= 32
+    cam = rt.make_camera(rt.camera_args([0, 0, -22], [0, 0, 0], [0, 1, 0], math.radians(30), 1.0, 1.0, 0.0))
+    a, qa, sa = _render_with_env(rt, device, None, {"RT_B200_RECT_FRAMES": "0"}, 96, 96, 16, depth=12, tables=tables, cam=cam)
+    b, qb, sb = _render_with_env(rt, device, None, {}, 96, 96, 16, depth=12, tables=tables, cam=cam)
+    assert sa.rays > 96 * 96 * 16 * 2  # paths do bounce
+    # f32 rounding differs between the two formulations: a path may flip at a grazing edge, the image may not
+    assert abs(int(sa.rays) - int(sb.rays)) <= 2e-3 * sa.rays
+    close = np.abs(a - b).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(a).max(axis=2))
+    assert close.mean() >= 0.985, close.mean()
+    assert abs(a.mean() - b.mean()) <= 5e-3 * a.mean()
