@@ -394,7 +394,8 @@ def test_frame_rect_extend_matches_general_records(rt, device):
     for name, sgn, ax in [("+x", 1, 0), ("-x", -1, 0), ("+y", 1, 1), ("-y", -1, 1), ("+z", 1, 2)]:  # room, open towards -z (camera side)
         c = np.zeros(3)
         c[ax] = sgn * L / 2
-        rects.append((face[name], c, L, L, 1 if name == "+y" else (3 if name == "-x" else 0)))
+        inward = face[("-" if sgn > 0 else "+") + name[1]]  # normals face the room, so Lambertian walls scatter back into it
+        rects.append((inward, c, L, L, 1 if name == "+y" else (3 if name == "-x" else 0)))
     for k in range(3):  # boxes, each in its own tilted frame, faces through all six permutations / signs
         F = _rot(rng.normal(size=3), rng.uniform(10, 80))
         centre = rng.uniform(-2.5, 2.5, size=3)
