@@ -175,6 +175,13 @@ int rt_render(RtScene* scene, const RtCamera* cam, const RtRenderParams* params,
 int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* params, float* d_sum_rgb,
                      float* d_sumsq_rgb, void* cuda_stream, RtStats* stats);
 
+/* Batched `render::color(&ray, world, max_depth)` (src/render.rs:5-29) on caller-supplied rays — the literal per-ray entry point
+ * of the reference, fed through the same wavefront.  Ray i is evaluated `spp` times with independent
+ * random streams (Philox key = (i, sample)); out_sum_rgb[3 i ..] receives the SUM of the spp radiances (divide by spp for the
+ * mean), out_sumsq_rgb (nullable) the sum of their squares.  The direction is used as given (not normalised), like color(). */
+int rt_color_rays(RtScene* scene, const RtRayIn* rays, uint64_t n, uint32_t spp, uint32_t max_depth, uint64_t seed,
+                  float* out_sum_rgb, float* out_sumsq_rgb, RtStats* stats);
+
 /* Closest-hit query on caller-supplied rays (batched equivalent of `world.hit(&ray)`,
  * src/optimize.rs:469-498); medium free-flight draws are keyed by (ray index, prim order, seed). */
 int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtHitOut* out);

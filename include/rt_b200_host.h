@@ -34,6 +34,16 @@ int rth_scene_upload(RtContext* ctx, const RthFlatScene* flat, RtScene** out);
 /* PerspectiveCamera::new -> device camera constants (f64 math of src/camera.rs:34-45, rounded to f32). */
 int rth_camera(const RthCameraArgs* args, RtCamera* out);
 
+
+/* Encoders of the example drivers' output formats, fed with the top-down 8-bit image of
+ * rt_resolve_u8.  RTH_IMAGE_PPM_P3: "P3\n<w> <h>\n255\n" + one "r g b\n" line per pixel, rows top to bottom
+ * (examples/book-one.rs:28-30,90-100).  RTH_IMAGE_PNG_RGBA8: 8-bit RGBA PNG, alpha 255, row 0 = top
+ * (examples/main.rs:105-135).  Two-call pattern: *needed receives the encoded size; bytes are written when
+ * out != NULL and capacity >= *needed (else RT_ERR_INVALID with *needed set). */
+typedef enum RthImageFormat { RTH_IMAGE_PPM_P3 = 0, RTH_IMAGE_PNG_RGBA8 = 1 } RthImageFormat;
+int rth_encode_image(int format, const uint8_t* rgb_top_down, uint32_t width, uint32_t height, uint8_t* out, uint64_t capacity,
+                     uint64_t* needed);
+
 #ifdef __cplusplus
 }
 #endif

@@ -255,6 +255,32 @@ int orc_paths(const OrcScene* s, const OrcCameraArgs* camArgs, const OrcRenderPa
 //   * the ray is re-traced under 8 perturbations of relative size `rel_perturb` (a few f32 ulps of the
 //     inputs); hit/miss or primitive changes make it unstable, and the largest change of t / p / n is
 //     reported as the query's conditioning (`*_sens`).
+// render::color (src/render.rs:5-29) on caller rays: ray i evaluated spp times, random streams keyed (i, sample) like a pixel of
+// an n x 1 image; out_sum: n*3 sums, out_segments (nullable): n segment counts summed over the spp evaluations.
+int orc_color_rays(const OrcScene* s, const double* rays, uint64_t n, uint32_t spp, uint32_t max_depth, uint64_t seed, int sampler_mode,
+                   double* out_sum, uint64_t* out_segments) {
+    if (!s || !rays || !out_sum) return -1;
+    orc::PathRng g;
+    g.mode = (orc::SamplerMode)sampler_mode;
+    g.seed_lo = (uint32_t)seed; g.seed_hi = (uint32_t)(seed >> 32);
+    for (uint64_t i = 0; i < n; ++i) {
+        const double* r = rays + 6 * i;
+        const orc::Ray ray{{r[0], r[1], r[2]}, {r[3], r[4], r[5]}};
+        orc::Vec3 acc;
+        const uint64_t before = g.counters.segments;
+        for (uint32_t k = 0; k < spp; ++k) {
+            g.key0 = (uint32_t)i; g.key1 = k;
+            g.bounce = 0; g.seq = 0;
+            orc::tls_rng() = &g;
+            acc += orc::color(ray, *s->world, max_depth);
+            orc::tls_rng() = nullptr;
+        }
+        out_sum[3 * i] = acc.x; out_sum[3 * i + 1] = acc.y; out_sum[3 * i + 2] = acc.z;
+        if (out_segments) out_segments[i] = g.counters.segments - before;
+    }
+    return 0;
+}
+
 int orc_trace(const OrcScene* s, const double* rays, uint64_t n, uint64_t seed, double rel_perturb, double tie_rel, OrcHit* out) {
     if (!s || !rays || !out) return -1;
     orc::PathRng g;

@@ -156,6 +156,17 @@ class Scene:
         assert rc == 0
         return rgb, seg
 
+    def color_rays(self, rays, spp, max_depth, seed=1, mode=PAIRED):
+        """render::color on caller rays [n,6]: (sum[n,3] over spp evaluations keyed (ray, sample), segments[n])."""
+        rays = _f8(rays).reshape(-1, 6)
+        out = np.zeros((len(rays), 3), dtype=np.float64)
+        seg = np.zeros(len(rays), dtype=np.uint64)
+        L = lib()
+        L.orc_color_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
+        rc = L.orc_color_rays(self._h, _p(rays), len(rays), int(spp), int(max_depth), int(seed), int(mode), _p(out), _p(seg))
+        assert rc == 0
+        return out, seg
+
     def trace(self, rays, seed=1, rel_perturb=1e-6, tie_rel=1e-4):
         """Closest hit per ray plus the margin diagnostics (stable, t_second, *_sens) of orc_trace."""
         rays = _f8(rays).reshape(-1, 6)

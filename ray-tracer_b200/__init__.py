@@ -60,9 +60,9 @@ class RthCameraArgs(C.Structure):
 
 
 # every symbol include/rt_b200.h and include/rt_b200_host.h declare
-ABI_SYMBOLS = ["rt_init", "rt_shutdown", "rt_scene_create", "rt_scene_destroy", "rt_render", "rt_render_device", "rt_trace", "rt_resolve_u8",
+ABI_SYMBOLS = ["rt_init", "rt_shutdown", "rt_scene_create", "rt_scene_destroy", "rt_render", "rt_render_device", "rt_trace", "rt_color_rays", "rt_resolve_u8",
                "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
-               "rth_flat_desc", "rth_scene_upload", "rth_camera"]
+               "rth_flat_desc", "rth_scene_upload", "rth_camera", "rth_encode_image"]
 
 
 class BackendError(RuntimeError):
@@ -86,6 +86,7 @@ def _load():
     L.rt_render.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
     L.rt_render_device.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, vp, C.POINTER(RtStats)]
     L.rt_trace.argtypes = [vp, vp, u64, u64, vp]
+    L.rt_color_rays.argtypes = [vp, vp, u64, u32, u32, u64, vp, vp, C.POINTER(RtStats)]
     L.rt_resolve_u8.argtypes = [vp, vp, u32, u32, u32, vp]
     L.rt_deinterleave_rows.argtypes = [vp, vp, vp, u32, u32, u32, vp]
     L.rt_scene_device_bytes.argtypes = [vp]
@@ -100,6 +101,7 @@ def _load():
     L.rth_flat_desc.argtypes = [vp, C.POINTER(RtSceneDesc)]
     L.rth_scene_upload.argtypes = [vp, vp, C.POINTER(vp)]
     L.rth_camera.argtypes = [C.POINTER(RthCameraArgs), C.POINTER(RtCamera)]
+    L.rth_encode_image.argtypes = [C.c_int, vp, u32, u32, vp, u64, C.POINTER(u64)]
     return L
 
 
@@ -142,6 +144,23 @@ class Device:
         out = np.zeros((h, w, 3), dtype=np.uint8)
         _check(lib.rt_resolve_u8(self._h, _ptr(s), w, h, int(spp), _ptr(out)))
         return out
+
+
+IMAGE_PPM_P3, IMAGE_PNG_RGBA8 = 0, 1
+
+
+def encode_image(rgb_top_down, fmt):
+    """rth_encode_image: the example drivers' PPM P3 (examples/book-one.rs:28-30,90-100) or RGBA8 PNG (examples/main.rs:105-135)
+    bytes of a top-down [H, W, 3] uint8 image (the output of Device.resolve_u8).  Host-only: no GPU involved."""
+    img = np.ascontiguousarray(rgb_top_down, dtype=np.uint8)
+    if img.ndim != 3 or img.shape[2] != 3:
+        raise ValueError("expected [H, W, 3] uint8")
+    h, w = img.shape[:2]
+    need = C.c_uint64(0)
+    _check(lib.rth_encode_image(fmt, _ptr(img), w, h, None, 0, C.byref(need)))
+    out = np.empty(need.value, dtype=np.uint8)
+    _check(lib.rth_encode_image(fmt, _ptr(img), w, h, _ptr(out), need.value, C.byref(need)))
+    return out.tobytes()
 
 
 def camera_args(eye, center, up, fov, aspect, focus, lens):
@@ -277,3 +296,12 @@ class Scene:
         out = np.zeros(len(r), dtype=HIT_DTYPE)
         _check(lib.rt_trace(self._h, _ptr(r), len(r), int(seed), _ptr(out)))
         return out
+
+    def color_rays(self, rays, spp, max_depth, seed=1, want_sumsq=False):
+        """rt_color_rays: batched render::color on rays [n,6] f32 -> (sum[n,3], sumsq[n,3] or None, RtStats)."""
+        r = np.ascontiguousarray(np.asarray(rays, dtype=np.float32).reshape(-1, 6))
+        s = np.zeros((len(r), 3), dtype=np.float32)
+        q = np.zeros((len(r), 3), dtype=np.float32) if want_sumsq else None
+        st = RtStats()
+        _check(lib.rt_color_rays(self._h, _ptr(r), len(r), int(spp), int(max_depth), int(seed), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
+        return s, q, st

@@ -474,8 +474,40 @@ int rt_deinterleave_rows(RtContext* ctx, const float* d_gathered, float* d_full,
     return RT_OK;
 }
 
+static int render_core(RtScene* scene, const RtCamera* cam, const RtRayIn* d_user_rays, const RtRenderParams* prm, float* d_sum, float* d_sumsq,
+                       void* cuda_stream, RtStats* stats);
+
 int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
     if (!scene || !cam || !prm || !d_sum) return fail(RT_ERR_INVALID, "null argument");
+    return render_core(scene, cam, nullptr, prm, d_sum, d_sumsq, cuda_stream, stats);
+}
+
+// Batched `render::color(&ray, world, max_depth)` (src/render.rs:5-29) on caller rays: ray i is "pixel" i of an n x 1 image,
+// `spp` independent evaluations of color() per ray (Philox key = (i, sample)), sums returned like rt_render.
+int rt_color_rays(RtScene* scene, const RtRayIn* rays, uint64_t n, uint32_t spp, uint32_t max_depth, uint64_t seed, float* out_sum, float* out_sumsq,
+                  RtStats* stats) {
+    if (!scene || !rays || !out_sum) return fail(RT_ERR_INVALID, "null argument");
+    if (n == 0 || n >= (1ull << 32)) return fail(RT_ERR_INVALID, "ray count must be in [1, 2^32)");
+    RtContext* ctx = scene->ctx;
+    RT_CUDA(cudaSetDevice(ctx->device));
+    RT_CUDA(ctx->scratch.ensure(n * sizeof(RtRayIn)));
+    RT_CUDA(ctx->fb_sum.ensure(n * 3));
+    if (out_sumsq) RT_CUDA(ctx->fb_sumsq.ensure(n * 3));
+    RT_CUDA(cudaMemcpyAsync(ctx->scratch.p, rays, n * sizeof(RtRayIn), cudaMemcpyHostToDevice, ctx->stream));
+    RtRenderParams prm{};
+    prm.width = (uint32_t)n; prm.height = 1; prm.spp = spp; prm.max_depth = max_depth; prm.seed = seed; prm.row_begin = 0; prm.row_stride = 1;
+    RtCamera cam{};
+    const int rc = render_core(scene, &cam, reinterpret_cast<const RtRayIn*>(ctx->scratch.p), &prm, ctx->fb_sum.p, out_sumsq ? ctx->fb_sumsq.p : nullptr, nullptr, stats);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(cudaMemcpy(out_sum, ctx->fb_sum.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+    if (out_sumsq) RT_CUDA(cudaMemcpy(out_sumsq, ctx->fb_sumsq.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+}  // extern "C" (render_core is internal)
+
+static int render_core(RtScene* scene, const RtCamera* cam, const RtRayIn* d_user_rays, const RtRenderParams* prm, float* d_sum, float* d_sumsq,
+                       void* cuda_stream, RtStats* stats) {
     RtContext* ctx = scene->ctx;
     if (prm->width == 0 || prm->height == 0 || prm->spp == 0) return fail(RT_ERR_INVALID, "width/height/spp must be > 0");
     if (prm->row_stride == 0 || prm->row_begin >= prm->height) return fail(RT_ERR_INVALID, "bad row_begin/row_stride");
@@ -496,6 +528,7 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     rc.capacity = cap;
     rc.pixels_local = (uint64_t)rc.width * rc.rows_local;
     rc.paths_total = rc.pixels_local * rc.spp;
+    rc.user_rays = d_user_rays;
 
     for (int i = 0; i < 2; ++i) { RT_CUDA(ctx->qa[i].ensure(cap)); RT_CUDA(ctx->qb[i].ensure(cap)); RT_CUDA(ctx->qc[i].ensure(cap)); }
     RT_CUDA(ctx->hits.ensure(cap));
@@ -622,6 +655,8 @@ int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* 
     }
     return RT_OK;
 }
+
+extern "C" {
 
 int rt_render(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* out_sum, float* out_sumsq, RtStats* stats) {
     if (!scene || !prm || !out_sum) return fail(RT_ERR_INVALID, "null argument");

@@ -108,6 +108,7 @@ struct RenderConst {
     uint32_t capacity;
     uint64_t paths_total;   // width * rows_local * spp
     uint64_t pixels_local;  // width * rows_local
+    const RtRayIn* user_rays;  // rt_color_rays: path `pixel` starts from user_rays[pixel] instead of a camera ray (else null)
 };
 
 }  // namespace rtb

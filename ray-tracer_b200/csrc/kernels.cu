@@ -82,7 +82,13 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
         const uint32_t gp = y * rc.width + x;
         const Philox4 rnd = philox4x32_10(0u, RT_DIM_CAMERA, rc.seed_lo, rc.seed_hi, gp, sample);
         float3 o, d;
-        camera_ray(rc.cam, x, y, rc.width, rc.height, rnd, o, d);
+        if (rc.user_rays) {  // batched render::color(&ray, ..): the caller's ray as it is (direction not normalised, src/render.rs:5)
+            const RtRayIn r = rc.user_rays[gp];
+            o = f3(r.origin[0], r.origin[1], r.origin[2]);
+            d = f3(r.direction[0], r.direction[1], r.direction[2]);
+        } else {
+            camera_ray(rc.cam, x, y, rc.width, rc.height, rnd, o, d);
+        }
         const uint32_t slot = surv + i;
         q.a[slot] = make_float4(o.x, o.y, o.z, __uint_as_float(RT_NO_PRIM));
         q.b[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(gp));

@@ -109,6 +109,20 @@ inline std::vector<std::optional<TraceHit>> trace_rays(World& world, const std::
     return res;
 }
 
+// render::color(&ray, world, maxDepth) (src/render.rs:5) for a batch of rays: the mean of `spp` evaluations per ray.
+inline std::vector<Vec3> color(World& world, const std::vector<Ray>& rays, uint32_t maxDepth, uint32_t spp = 1, uint64_t seed = 1) {
+    std::vector<RtRayIn> in(rays.size());
+    for (size_t i = 0; i < rays.size(); ++i) {
+        const Ray& r = rays[i];
+        in[i] = RtRayIn{{(float)r.origin.x, (float)r.origin.y, (float)r.origin.z}, {(float)r.direction.x, (float)r.direction.y, (float)r.direction.z}};
+    }
+    std::vector<float> sum(rays.size() * 3);
+    check(rt_color_rays(world.handle(), in.data(), in.size(), spp, maxDepth, seed, sum.data(), nullptr, nullptr));
+    std::vector<Vec3> out(rays.size());
+    for (size_t i = 0; i < out.size(); ++i) out[i] = Vec3(sum[3 * i] / spp, sum[3 * i + 1] / spp, sum[3 * i + 2] / spp);
+    return out;
+}
+
 }  // namespace gpu
 }  // namespace host
 }  // namespace rtb

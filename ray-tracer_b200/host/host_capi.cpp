@@ -3,11 +3,13 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <vector>
 
 #include "../../include/rt_b200_host.h"
 #include "../examples/scenes.hpp"
 #include "flatten.hpp"
 #include "gpu.hpp"
+#include "image_io.hpp"
 
 namespace {
 
@@ -96,6 +98,24 @@ int rth_camera(const RthCameraArgs* a, RtCamera* out) {
     const rtb::host::PerspectiveCamera cam({a->eye[0], a->eye[1], a->eye[2]}, {a->center[0], a->center[1], a->center[2]}, {a->up[0], a->up[1], a->up[2]},
                                            a->fov, a->aspect, a->focus_distance, a->lens_radius);
     *out = rtb::host::flattenCamera(cam);
+    return RT_OK;
+}
+
+int rth_encode_image(int format, const uint8_t* rgb, uint32_t width, uint32_t height, uint8_t* out, uint64_t capacity, uint64_t* needed) {
+    if (!rgb || !needed || width == 0 || height == 0) return RT_ERR_INVALID;
+    std::vector<uint8_t> bytes;
+    if (format == RTH_IMAGE_PPM_P3) {
+        const std::string text = rth::encode_ppm_p3(rgb, width, height);
+        bytes.assign(text.begin(), text.end());
+    } else if (format == RTH_IMAGE_PNG_RGBA8) {
+        bytes = rth::encode_png_rgba8(rgb, width, height);
+    } else {
+        return RT_ERR_UNSUPPORTED;
+    }
+    *needed = bytes.size();
+    if (!out) return RT_OK;
+    if (capacity < bytes.size()) return RT_ERR_INVALID;
+    std::memcpy(out, bytes.data(), bytes.size());
     return RT_OK;
 }
 

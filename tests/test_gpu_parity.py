@@ -419,3 +419,35 @@ def test_frame_rect_extend_matches_general_records(rt, device):
     close = np.abs(a - b).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(a).max(axis=2))
     assert close.mean() >= 0.985, close.mean()
     assert abs(a.mean() - b.mean()) <= 5e-3 * a.mean()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["book-one", "cornell-box", "book-two"])
+def test_color_rays_matches_oracle_color(rt, orc, device, name):
+    """rt_color_rays — the reference's per-ray entry point render::color (src/render.rs:5) batched through the wavefront
+     — against the oracle's color() on the same rays with the same Philox keys (ray, sample, segment)."""
+    so = orc.Scene(name, 1)
+    sg = rt.Scene.example(device, name, 1)
+    cam_rays = orc.camera_rays(so.camera(16 / 9), 48, 27)
+    hits = so.trace(cam_rays, rel_perturb=0.0)
+    pts = hits["p"][hits["hit"] == 1]
+    rng = np.random.default_rng(3)
+    d = rng.normal(size=(1500, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = pts[rng.integers(0, len(pts), len(d))]
+    o = o + 1e-3 * d * np.maximum(1.0, np.abs(o).max(axis=1, keepdims=True))
+    bounce = np.concatenate([o, d * rng.uniform(0.5, 3.0, size=(len(d), 1))], axis=1)  # color() takes un-normalised directions
+    rays = np.concatenate([cam_rays, bounce]).astype(np.float32)
+    spp = 4
+    s_g, q_g, st = sg.color_rays(rays, spp, 50, seed=9, want_sumsq=True)
+    s_o, seg = so.color_rays(rays.astype(np.float64), spp, 50, seed=9)
+    assert st.paths == len(rays) * spp
+    assert abs(int(st.rays) - int(seg.sum())) <= 0.005 * seg.sum()
+    ok = np.abs(s_g - s_o).max(axis=1) <= 2e-3 * np.maximum(1.0, np.abs(s_o).max(axis=1))
+    print(f"{name}: color_rays agreement {ok.mean():.4f} over {len(rays)} rays x {spp}")
+    assert ok.mean() >= 0.985
+    assert np.all(q_g >= 0.0)
+    zero, _, _ = sg.color_rays(rays[:64], 2, 0)
+    assert np.all(zero == 0.0)
+    with pytest.raises(rt.BackendError):
+        sg.color_rays(np.zeros((0, 6), dtype=np.float32), 1, 5)

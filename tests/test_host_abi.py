@@ -207,3 +207,42 @@ def test_oracle_bvh_agrees_with_bruteforce_over_flat_tables(rt, orc, name):
     both = st & np.isfinite(t)
     tol = 1e-4 * np.maximum(hits["t"][both], 1e-3) + 64 * hits["t_sens"][both]  # f32 matrices in the flat tables
     assert np.all(np.abs(t[both] - hits["t"][both]) <= tol)
+
+
+def test_image_encoders_match_the_example_drivers_formats(rt):
+    """rth_encode_image: PPM P3 text exactly as examples/book-one.rs:28-30,90-100 prints it, and a PNG that
+    decodes (zlib + chunk CRCs checked here, PIL when present) to the RGBA pixels examples/main.rs:105-135 puts."""
+    import struct
+    import zlib
+
+    rng = np.random.default_rng(5)
+    for w, h in [(1, 1), (7, 3), (300, 250)]:  # 300x250 RGBA rows exceed one 65535-byte stored block
+        img = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+        img[0, 0] = (0, 255, 7)
+        ppm = rt.encode_image(img, rt.IMAGE_PPM_P3).decode()
+        expect = f"P3\n{w} {h}\n255\n" + "".join(f"{int(p[0])} {int(p[1])} {int(p[2])}\n" for p in img.reshape(-1, 3))  # println!("{:?} {:?} {:?}")
+        assert ppm == expect
+        png = rt.encode_image(img, rt.IMAGE_PNG_RGBA8)
+        assert png[:8] == b"\x89PNG\r\n\x1a\n"
+        pos, chunks = 8, []
+        while pos < len(png):
+            (n,) = struct.unpack(">I", png[pos:pos + 4])
+            kind, data = png[pos + 4:pos + 8], png[pos + 8:pos + 8 + n]
+            (crc,) = struct.unpack(">I", png[pos + 8 + n:pos + 12 + n])
+            assert crc == zlib.crc32(kind + data)
+            chunks.append((kind, data))
+            pos += 12 + n
+        assert [k for k, _ in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+        assert struct.unpack(">IIBBBBB", chunks[0][1]) == (w, h, 8, 6, 0, 0, 0)
+        raw = np.frombuffer(zlib.decompress(chunks[1][1]), dtype=np.uint8).reshape(h, 1 + 4 * w)
+        assert np.all(raw[:, 0] == 0)
+        rgba = raw[:, 1:].reshape(h, w, 4)
+        assert np.array_equal(rgba[..., :3], img) and np.all(rgba[..., 3] == 255)
+        try:
+            import io
+            from PIL import Image
+            assert np.array_equal(np.asarray(Image.open(io.BytesIO(png)).convert("RGBA"))[..., :3], img)
+        except ImportError:
+            pass
+    with pytest.raises(rt.BackendError):
+        rt.encode_image(np.zeros((2, 2, 3), dtype=np.uint8), 9)

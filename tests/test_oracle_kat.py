@@ -325,3 +325,23 @@ def test_resolve_u8(orc):  # examples/book-one.rs:90-100, A.12
     out = orc.resolve_u8(s, 4)
     assert list(out[1, 0]) == [127, 255, 255]  # rows top -> bottom: y = 0 is the LAST row
     assert out[0, 1, 0] == 255 and out[0, 1, 1] == 255 and out[0, 1, 2] == int(math.sqrt(0.999) * 255)
+
+
+def test_color_on_caller_rays_known_answers(orc):
+    """orc_color_rays = render::color (src/render.rs:5-29) on given rays: a ray that sees the cornell light returns its emission on
+    every evaluation (DiffuseLight never scatters, material.rs:290-297), depth 0 is black (render.rs:6-8), a ray leaving through the
+    open front is black (render.rs:26), and a diffuse bounce needs more than one segment."""
+    s = orc.Scene("cornell-box", 1)
+    rays = np.array([[277.5, 277.5, 277.5, 0, 1, 0],      # straight up into the light (y = 554, emission 15)
+                     [277.5, 277.5, 277.5, 0, 2.5, 0],    # same, direction not normalised
+                     [277.5, 277.5, 277.5, 0, 0, -1],     # out of the open front
+                     [277.5, 277.5, 277.5, 0, -1, 0]],    # floor: scatters
+                    dtype=np.float64)
+    out, seg = s.color_rays(rays, 8, 50, seed=3)
+    assert np.allclose(out[0], 15.0 * 8) and np.allclose(out[1], 15.0 * 8) and list(seg[:2]) == [8, 8]
+    assert np.all(out[2] == 0.0) and seg[2] == 8
+    assert seg[3] > 8 and np.all(out[3] >= 0.0)
+    zero, seg0 = s.color_rays(rays, 4, 0, seed=3)
+    assert np.all(zero == 0.0) and np.all(seg0 == 0)
+    again, _ = s.color_rays(rays, 8, 50, seed=3)
+    assert np.array_equal(out, again)  # dimensioned Philox draws: a function of (ray, sample, segment, seed) only
