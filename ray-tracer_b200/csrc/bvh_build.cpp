@@ -3,9 +3,12 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <atomic>
 #include <numeric>
+#include <thread>
 
 namespace rtb {
 namespace {
@@ -42,15 +45,25 @@ struct Builder {
     std::vector<float> cx, cy, cz;   // centroids by input id
     std::vector<TmpNode> tmp;
     uint32_t depth_seen = 0;
+    // Subtrees of at most `defer_below` primitives are not built by the top-level recursion but recorded as tasks and built
+    // concurrently afterwards (disjoint ranges of idx, thread-local node vectors spliced in task order: the tree is the same
+    // for every thread count).  1 M spheres: 1.2 s -> a fraction of that on the box's 16 threads.
+    struct Task { int32_t node; uint32_t first, count, depth; };
+    std::vector<Task> tasks;
+    uint32_t defer_below = 0;
 
     Builder(const std::vector<Box3>& b, const BvhOptions& o) : boxes(b), opt(o) {}
 
     const float* centroidAxis(int a) const { return a == 0 ? cx.data() : (a == 1 ? cy.data() : cz.data()); }
 
-    int32_t build(uint32_t first, uint32_t count, uint32_t depth) {
+    int32_t build(std::vector<TmpNode>& tmp, uint32_t& depth_seen, uint32_t first, uint32_t count, uint32_t depth, bool may_defer) {
         depth_seen = std::max(depth_seen, depth);
         const int32_t me = (int32_t)tmp.size();
         tmp.emplace_back();
+        if (may_defer && count <= defer_below && count > 1) {
+            tasks.push_back(Task{me, first, count, depth});
+            return me;
+        }
         Grow box, cbox;
         for (uint32_t i = first; i < first + count; ++i) {
             const uint32_t p = idx[i];
@@ -116,8 +129,8 @@ struct Builder {
             mid = (uint32_t)(it - idx.begin());
             if (mid == first || mid == first + count) mid = first + count / 2;
         }
-        const int32_t l = build(first, mid - first, depth + 1);
-        const int32_t r = build(mid, first + count - mid, depth + 1);
+        const int32_t l = build(tmp, depth_seen, first, mid - first, depth + 1, may_defer);
+        const int32_t r = build(tmp, depth_seen, mid, first + count - mid, depth + 1, may_defer);
         tmp[me].left = l;
         tmp[me].right = r;
         return me;
@@ -171,7 +184,35 @@ BvhResult build_bvh(const std::vector<Box3>& boxes, const BvhOptions& opt) {
     const uint32_t m = (uint32_t)b.idx.size();
     if (m == 0) return res;
     b.tmp.reserve(2 * (size_t)m);
-    const int32_t root = b.build(0, m, 0);
+    unsigned hw = std::thread::hardware_concurrency();
+    unsigned n_threads = std::max(1u, std::min(hw ? hw : 1u, 32u));
+    if (const char* e = std::getenv("RT_B200_BVH_THREADS")) { const int v = std::atoi(e); if (v >= 1) n_threads = (unsigned)std::min(v, 64); }
+    b.defer_below = (n_threads > 1 && m >= 65536u) ? m / (8u * n_threads) : 0u;
+    const int32_t root = b.build(b.tmp, b.depth_seen, 0, m, 0, b.defer_below > 0);
+    if (!b.tasks.empty()) {
+        std::vector<std::vector<TmpNode>> local(b.tasks.size());
+        std::vector<uint32_t> local_depth(b.tasks.size(), 0u);
+        std::atomic<size_t> next{0};
+        auto worker = [&]() {
+            for (size_t t = next.fetch_add(1); t < b.tasks.size(); t = next.fetch_add(1)) {
+                const Builder::Task& k = b.tasks[t];
+                local[t].reserve(2 * (size_t)k.count);
+                b.build(local[t], local_depth[t], k.first, k.count, k.depth, false);
+            }
+        };
+        std::vector<std::thread> pool;
+        for (unsigned i = 1; i < n_threads; ++i) pool.emplace_back(worker);
+        worker();
+        for (auto& th : pool) th.join();
+        for (size_t t = 0; t < b.tasks.size(); ++t) {  // splice: local node 0 replaces the placeholder, local k >= 1 lands at off + k
+            const int32_t off = (int32_t)b.tmp.size() - 1;
+            std::vector<TmpNode>& loc = local[t];
+            for (TmpNode& nd : loc) { if (nd.left >= 0) { nd.left += off; nd.right += off; } }
+            b.tmp[b.tasks[t].node] = loc[0];
+            b.tmp.insert(b.tmp.end(), loc.begin() + 1, loc.end());
+            b.depth_seen = std::max(b.depth_seen, local_depth[t]);
+        }
+    }
     res.depth = b.depth_seen;
 
     // 3. breadth-first emission with adjacent sibling pairs; leaf ranges are offset by the always-list
@@ -185,21 +226,38 @@ BvhResult build_bvh(const std::vector<Box3>& boxes, const BvhOptions& opt) {
         emitNode(res.nodes[0], rt, base + rt.first, rt.count);
         return res;
     }
-    std::vector<std::pair<int32_t, uint32_t>> queue;  // (tmp node, emitted slot)
-    queue.emplace_back(root, 0u);
-    for (size_t head = 0; head < queue.size(); ++head) {
-        const int32_t t = queue[head].first;
-        const uint32_t slot = queue[head].second;
-        const TmpNode& node = b.tmp[t];
-        const uint32_t pairAt = (uint32_t)res.nodes.size();
-        res.nodes.resize(res.nodes.size() + 2);
-        emitNode(res.nodes[slot], node, pairAt, 0u);
-        const int32_t kids[2] = {node.left, node.right};
-        for (int c = 0; c < 2; ++c) {
-            const TmpNode& kid = b.tmp[kids[c]];
-            if (kid.left < 0) emitNode(res.nodes[pairAt + c], kid, base + kid.first, kid.count);
-            else queue.emplace_back(kids[c], pairAt + c);
+    // Emission order.  The first treelet is the top of the tree, breadth-first (extend stages that prefix in shared memory);
+    // below it the tree is cut into treelets of `treelet_pairs` sibling pairs (2 KB), each stored contiguously and visited
+    // depth-first, so that the node fetches of one ray's descent fall into a few cache lines instead of one line per level
+    // (plain breadth-first order: 65 % L1 / 75 % L2 hit rate on the 1 M-sphere tree, r1j).
+    const uint32_t top_pairs = std::max<uint32_t>(1u, opt.top_nodes / 2u), treelet_pairs = std::max<uint32_t>(1u, opt.treelet_nodes / 2u);
+    std::vector<std::pair<int32_t, uint32_t>> roots;  // treelet roots still to emit (tmp node, emitted slot), LIFO
+    roots.emplace_back(root, 0u);
+    std::vector<std::pair<int32_t, uint32_t>> queue;
+    bool first_treelet = true;
+    while (!roots.empty()) {
+        queue.clear();
+        queue.push_back(roots.back());
+        roots.pop_back();
+        const uint32_t budget = first_treelet ? top_pairs : treelet_pairs;
+        first_treelet = false;
+        uint32_t used = 0;
+        size_t head = 0;
+        for (; head < queue.size() && used < budget; ++head, ++used) {
+            const int32_t t = queue[head].first;
+            const uint32_t slot = queue[head].second;
+            const TmpNode& node = b.tmp[t];
+            const uint32_t pairAt = (uint32_t)res.nodes.size();
+            res.nodes.resize(res.nodes.size() + 2);
+            emitNode(res.nodes[slot], node, pairAt, 0u);
+            const int32_t kids[2] = {node.left, node.right};
+            for (int c = 0; c < 2; ++c) {
+                const TmpNode& kid = b.tmp[kids[c]];
+                if (kid.left < 0) emitNode(res.nodes[pairAt + c], kid, base + kid.first, kid.count);
+                else queue.emplace_back(kids[c], pairAt + c);
+            }
         }
+        for (size_t i = queue.size(); i-- > head;) roots.push_back(queue[i]);  // the frontier becomes new treelet roots (left subtree first)
     }
     return res;
 }

@@ -1,5 +1,5 @@
 // Host-side builder of the device BVH: binned-SAH tree over the world-space boxes of the flattened
-// primitives, emitted breadth-first as 32-byte {lo, leftOrFirst}{hi, count} nodes with sibling pairs
+// primitives, emitted (top breadth-first, then in depth-first treelets) as 32-byte {lo, leftOrFirst}{hi, count} nodes with sibling pairs
 // adjacent.  The reference builds a random-axis median-split tree (src/optimize.rs:363-440) whose
 // closest-hit answers do not depend on topology, so the device tree is rebuilt for quality
 // (SURVEY §7.2-4); primitives whose box spans most of the scene (sky / ground / fog spheres) are
@@ -37,6 +37,8 @@ struct BvhOptions {
     float always_area_fraction = 0.5f;
     uint32_t max_always = 8;
     uint32_t max_depth = 56;
+    uint32_t top_nodes = 256;      // breadth-first prefix (what extend stages in shared memory for large trees)
+    uint32_t treelet_nodes = 64;   // below the prefix: nodes per contiguously stored treelet (2 KB)
 };
 
 BvhResult build_bvh(const std::vector<Box3>& boxes, const BvhOptions& opt = BvhOptions());

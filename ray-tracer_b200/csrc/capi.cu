@@ -324,6 +324,8 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     BvhOptions opt;
     if (const char* ml = std::getenv("RT_B200_BVH_MAX_LEAF")) { const int v = std::atoi(ml); if (v >= 1 && v <= 16) opt.max_leaf = (uint32_t)v; }
     opt.max_always = RT_MAX_ALWAYS;
+    if (const char* tn = std::getenv("RT_B200_BVH_TREELET")) { const int v = std::atoi(tn); if (v >= 2) opt.treelet_nodes = (uint32_t)v; }
+    opt.top_nodes = RT_TOP_STAGED_NODES;
     uint32_t small_limit = RT_SMALL_SCENE;
     if (const char* sl = std::getenv("RT_B200_SMALL_SCENE")) small_limit = (uint32_t)std::max(0, std::min(std::atoi(sl), (int)RT_SMALL_SCENE));
     const bool small = n <= small_limit;

@@ -313,8 +313,13 @@ __device__ __forceinline__ void load_pair(const DScene& S, const Staged& sm, uin
         const uint32_t a = sm.nodes + 32u * pair;
         llo = lds128(a); lhi = lds128(a + 16u); rlo = lds128(a + 32u); rhi = lds128(a + 48u);
     } else {
+        // one 32-byte node per 256-bit load (sm_100: LDG.E.256): two L1 requests per pair instead of four — the r1k profile of
+        // the 1 M-sphere scene has the kernel at 70 % of L1 (l1tex) throughput with four divergent LDG.128 per visit
         const float4* __restrict__ g = S.nodes + 2u * (size_t)pair;
-        llo = __ldg(g); lhi = __ldg(g + 1); rlo = __ldg(g + 2); rhi = __ldg(g + 3);
+        asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=f"(llo.x), "=f"(llo.y), "=f"(llo.z), "=f"(llo.w), "=f"(lhi.x), "=f"(lhi.y), "=f"(lhi.z), "=f"(lhi.w) : "l"(g));
+        asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=f"(rlo.x), "=f"(rlo.y), "=f"(rlo.z), "=f"(rlo.w), "=f"(rhi.x), "=f"(rhi.y), "=f"(rhi.z), "=f"(rhi.w) : "l"(g + 2));
     }
 }
 
@@ -333,13 +338,16 @@ __device__ __forceinline__ RayCtx make_ray(float3 o, float3 d) {
     return R;
 }
 
-// One step of the ordered, t-pruned traversal: test the two children of `pair`, intersect the primitives of the
-// children that are leaves, descend into the nearer interior child (pushing the farther) or pop.  Returns the next
-// pair, RT_NO_PRIM when the traversal is over.  Shared by closest_hit (one ray per thread until done) and the
-// persistent extend kernel (lanes refill with new rays while their neighbours keep stepping).
+// One NODE step of the ordered, t-pruned traversal: test the two children of `pair`; children that are leaves are not
+// intersected here but returned as ONE pending primitive range [leaf_begin, leaf_end) (sibling leaves are adjacent in
+// the primitive order); descend into the nearer interior child (pushing the farther) or pop.  Returns the next pair,
+// RT_NO_PRIM when the traversal is over.  Primitive tests are deferred so that the lanes of a warp run them together
+// ("while-while" traversal, Aila & Laine): in the if-if form the ~140-instruction leaf loop ran on nearly every warp
+// iteration for ~2 of 32 lanes (r1k profile of the 1 M-sphere scene: 192 warp-instructions per iteration, of which the
+// node step is ~60).
 template <bool COUNT>
-__device__ __forceinline__ uint32_t traverse_step(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key,
-                                                  ClosestHit& best, uint32_t pair, int& sp, uint32_t* stack_spill, TraversalWork* work) {
+__device__ __forceinline__ uint32_t node_step(const DScene& S, const Staged& sm, const RayCtx& R, const ClosestHit& best, uint32_t pair, int& sp,
+                                              uint32_t* stack_spill, uint32_t& leaf_begin, uint32_t& leaf_end, TraversalWork* work) {
     const uint32_t sstride = 4u * blockDim.x;
     float4 llo, lhi, rlo, rhi;
     load_pair(S, sm, pair, llo, lhi, rlo, rhi);
@@ -349,14 +357,13 @@ __device__ __forceinline__ uint32_t traverse_step(const DScene& S, const Staged&
     const uint32_t lcnt = __float_as_uint(lhi.w), rcnt = __float_as_uint(rhi.w);
     const uint32_t lref = __float_as_uint(llo.w), rref = __float_as_uint(rlo.w);
     const bool lhit = tl < CUDART_INF_F, rhit = tr < CUDART_INF_F;
-    // leaves: sibling leaves are adjacent in the primitive order, so both become ONE range and one loop site
     uint32_t begin = 0u, end = 0u;
     if (lhit && lcnt) { begin = lref; end = lref + lcnt; }
     if (rhit && rcnt) { if (end == 0u) begin = rref; end = rref + rcnt; }
-    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
-    if (COUNT) work->prim_tests += end - begin;
+    leaf_begin = begin;
+    leaf_end = end;
     // interior children: descend into the nearer one, push the farther
-    const bool lin = lhit && !lcnt && tl <= best.t, rin = rhit && !rcnt && tr <= best.t;
+    const bool lin = lhit && !lcnt, rin = rhit && !rcnt;
     uint32_t next = RT_NO_PRIM;
     if (lin && rin) {
         const bool swap = tr < tl;
@@ -374,6 +381,13 @@ __device__ __forceinline__ uint32_t traverse_step(const DScene& S, const Staged&
         next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK];
     }
     return next;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void leaf_tests(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key, ClosestHit& best,
+                                           uint32_t begin, uint32_t end, TraversalWork* work) {
+    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+    if (COUNT) work->prim_tests += end - begin;
 }
 
 template <bool COUNT = false>
@@ -427,11 +441,13 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     uint32_t stack_spill[RT_STACK_DEPTH - RT_SMEM_STACK];
     int sp = 0;
     uint32_t pair = __float_as_uint(load_node(S, sm, 0).w);  // left child of the root; right = pair + 1
-    // ONE back-edge: every lane computes its next pair and falls through to the loop test, so the warp reconverges at
-    // the loop head each iteration (with `continue`s on three paths the lanes of a warp drifted apart for good: ncu
-    // showed 4.7 active threads per instruction on the 1 M-sphere scene against 9.2 for the single-exit form).
+    // while-while: lanes walk nodes until each has found a leaf range (or finished), then the warp intersects the pending
+    // ranges together.  One back-edge per loop, so the warp reconverges at both loop heads.
+    uint32_t leaf_begin = 0u, leaf_end = 0u;
     do {
-        pair = traverse_step<COUNT>(S, sm, R, self_prim, key, best, pair, sp, stack_spill, work);
+        while (pair != RT_NO_PRIM && leaf_end == leaf_begin) pair = node_step<COUNT>(S, sm, R, best, pair, sp, stack_spill, leaf_begin, leaf_end, work);
+        leaf_tests<COUNT>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
+        leaf_begin = leaf_end = 0u;
     } while (pair != RT_NO_PRIM);
     return best;
 }

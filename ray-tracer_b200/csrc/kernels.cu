@@ -237,11 +237,12 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
     MediumKey key{0u, 0u, 0u, seed_lo, seed_hi};
     uint32_t stack_spill[RT_STACK_DEPTH - RT_SMEM_STACK];
     uint32_t ray_i = RT_NO_PRIM, self_prim = RT_NO_PRIM, pair = RT_NO_PRIM;
+    uint32_t leaf_begin = 0u, leaf_end = 0u;  // pending primitive range of this lane (while-while: tested together with the other lanes')
     int sp = 0;
     const uint32_t root_pair = __float_as_uint(load_node(S, sm, 0).w);
 
     for (;;) {
-        const bool idle = pair == RT_NO_PRIM;
+        const bool idle = pair == RT_NO_PRIM && leaf_end == leaf_begin;
         const uint32_t m_idle = __ballot_sync(0xFFFFFFFFu, idle);
         if (m_idle == 0xFFFFFFFFu || (uint32_t)__popc(m_idle) >= (uint32_t)RT_REFILL_MIN) {
             if (idle && ray_i != RT_NO_PRIM) {
@@ -280,15 +281,26 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
                     if (COUNT) work.prim_tests += S.n_always;
                     sp = 0;
                     pair = root_pair;
+                    leaf_begin = leaf_end = 0u;
                 }
                 const uint32_t got = __ballot_sync(0xFFFFFFFFu, mine);
                 want &= ~got;
                 F.cur_pos += (uint32_t)__popc(got);
                 __syncwarp();  // every lane has read its slot before the buffer can be refilled
             }
-            if (__ballot_sync(0xFFFFFFFFu, pair != RT_NO_PRIM) == 0u) break;  // no lane has work and the queue is exhausted
+            if (__ballot_sync(0xFFFFFFFFu, pair != RT_NO_PRIM || leaf_end != leaf_begin) == 0u) break;  // no lane has work and the queue is exhausted
         }
-        if (pair != RT_NO_PRIM) pair = traverse_step<COUNT>(S, sm, R, self_prim, key, best, pair, sp, stack_spill, &work);
+        // pending leaves: intersected once RT_LEAF_MIN lanes hold one, or when no lane can take a node step
+        const bool pend = leaf_end != leaf_begin;
+        const uint32_t m_pend = __ballot_sync(0xFFFFFFFFu, pend);
+        const uint32_t m_trav = __ballot_sync(0xFFFFFFFFu, pair != RT_NO_PRIM && !pend);
+        if (m_pend != 0u && ((uint32_t)__popc(m_pend) >= (uint32_t)RT_LEAF_MIN || m_trav == 0u)) {
+            if (pend) {
+                leaf_tests<COUNT>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, &work);
+                leaf_begin = leaf_end = 0u;
+            }
+        }
+        if (pair != RT_NO_PRIM && leaf_end == leaf_begin) pair = node_step<COUNT>(S, sm, R, best, pair, sp, stack_spill, leaf_begin, leaf_end, &work);
     }
     if (COUNT) {
         uint32_t bt = work.box_tests, pt = work.prim_tests;

@@ -22,6 +22,9 @@
 #ifndef RT_PERSISTENT_MIN_NODES
 #define RT_PERSISTENT_MIN_NODES 65536u  // BVH size from which extend runs in its persistent, lane-refilling form
 #endif
+#ifndef RT_LEAF_MIN
+#define RT_LEAF_MIN 8        // persistent extend: pending leaf ranges are intersected once this many lanes hold one
+#endif
 #ifndef RT_FEED_RANGE
 #define RT_FEED_RANGE 128    // ray indices a warp claims per global atomic (multiple of 32)
 #endif

@@ -451,3 +451,32 @@ def test_color_rays_matches_oracle_color(rt, orc, device, name):
     assert np.all(zero == 0.0)
     with pytest.raises(rt.BackendError):
         sg.color_rays(np.zeros((0, 6), dtype=np.float32), 1, 5)
+
+
+@pytest.mark.gpu
+def test_parallel_bvh_build_is_thread_count_independent(rt, device):
+    """The host SAH builder hands subtrees to worker threads (csrc/bvh_build.cpp); the emitted tree must not depend on how many."""
+    import time
+    out = {}
+    for threads in ["1", "5", ""]:
+        old = os.environ.get("RT_B200_BVH_THREADS")
+        if threads:
+            os.environ["RT_B200_BVH_THREADS"] = threads
+        else:
+            os.environ.pop("RT_B200_BVH_THREADS", None)
+        try:
+            t0 = time.time()
+            scene = rt.Scene.example(device, "stress:200000", 1)
+            dt = time.time() - t0
+        finally:
+            if old is None:
+                os.environ.pop("RT_B200_BVH_THREADS", None)
+            else:
+                os.environ["RT_B200_BVH_THREADS"] = old
+        s, _, st = scene.render(scene.flat.camera(16 / 9), 96, 54, 2, 16, seed=2)
+        out[threads] = (scene.bvh_info(), int(st.rays), s)
+        print(f"stress:200000 scene build+upload with RT_B200_BVH_THREADS={threads or 'default'}: {dt:.3f} s, bvh {scene.bvh_info()}")
+        scene.close()
+    for threads in ["5", ""]:
+        assert out[threads][0] == out["1"][0] and out[threads][1] == out["1"][1]
+        assert np.allclose(out[threads][2], out["1"][2], rtol=1e-5, atol=1e-5)
