@@ -346,7 +346,12 @@ def main():
         rays_per_s_kernel = tot_rays / world / max(extend_s, 1e-12)  # per GPU, inside k_extend
         fp32_peak = 148 * 128 * sm_mhz * 1e6
         l2_bytes_per_ray = box_per_ray * 32 + prim_per_ray * (rect_frac * 64 + (1 - rect_frac) * 16)
-        if l2_peak:
+        tables_in_smem = info["nodes"] <= 2048  # whole tree + primitive heads (or the frame-rect list) staged in shared memory
+        if l2_peak and tables_in_smem:
+            line["roofline_l2"] = {"kernel": kernel, "bound": "l2", "achieved": None, "peak": l2_peak["l2_read_gbs_32MB"], "unit": "GB/s", "frac": None,
+                                   "peak_source": "measured now by ray-tracer_b200/tools/l2bw (32 MB read stream, ld.global.cg)", "l2bw": l2_peak,
+                                   "note": "not applicable: this scene's node / primitive tables are staged in shared memory, extend reads no table from L2"}
+        elif l2_peak:
             l2_gbs = l2_peak["l2_read_gbs_32MB"]
             line["roofline_l2"] = {"kernel": kernel, "bound": "l2", "achieved": rays_per_s_kernel * l2_bytes_per_ray / 1e9, "peak": l2_gbs, "unit": "GB/s",
                                    "frac": rays_per_s_kernel * l2_bytes_per_ray / 1e9 / l2_gbs, "bytes_per_ray": l2_bytes_per_ray,
