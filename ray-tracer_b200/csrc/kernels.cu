@@ -72,10 +72,17 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
     const uint32_t room = rc.capacity - surv;
     const uint32_t n_new = left < (uint64_t)room ? (uint32_t)left : room;
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    // path = sample * pixels_local + pixel: one 64-bit division per thread, then (sample, pixel) advance by the grid stride
+    // (the division per path was ~a third of this kernel's instructions)
+    uint32_t sample = 0u, qi = 0u;
+    if (tid < n_new) {
+        const uint64_t path0 = issued + tid;
+        sample = (uint32_t)(path0 / rc.pixels_local);
+        qi = (uint32_t)(path0 - (uint64_t)sample * rc.pixels_local);
+    }
+    const uint32_t pixels = (uint32_t)rc.pixels_local;
+    const uint32_t stride_s = stride / pixels, stride_q = stride - stride_s * pixels;
     for (uint32_t i = tid; i < n_new; i += stride) {
-        const uint64_t path = issued + i;
-        const uint32_t sample = (uint32_t)(path / rc.pixels_local);
-        const uint32_t qi = (uint32_t)(path - (uint64_t)sample * rc.pixels_local);
         uint32_t x, yl;
         pixel_from_index(qi, rc.width, rc.rows_local, x, yl);
         const uint32_t y = rc.row_begin + yl * rc.row_stride;
@@ -93,6 +100,9 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
         q.a[slot] = make_float4(o.x, o.y, o.z, __uint_as_float(RT_NO_PRIM));
         q.b[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(gp));
         q.c[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float((sample << 8) | 1u));
+        sample += stride_s;
+        qi += stride_q;
+        if (qi >= pixels) { qi -= pixels; ++sample; }
     }
     if (tid == 0) {
         const uint32_t total = surv + n_new;
