@@ -480,3 +480,24 @@ def test_parallel_bvh_build_is_thread_count_independent(rt, device):
     for threads in ["5", ""]:
         assert out[threads][0] == out["1"][0] and out[threads][1] == out["1"][1]
         assert np.allclose(out[threads][2], out["1"][2], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_full_size_config2_properties(rt, orc, device):
+    """BASELINE configs[1] at full size (cornell-box 600x600, 1024 spp, depth 50 — the bench workload): size-independent
+    properties.  Radiance is bounded by emission x throughput <= 15; the image mean is resolution independent, so it must agree
+    with a coarse FAITHFUL oracle render of the same frame; two interleaved row shards reassemble the full image exactly."""
+    w = h = 600
+    spp = 1024
+    scene = rt.Scene.example(device, "cornell-box", 1)
+    cam = scene.flat.camera(1.0)
+    s, _, st = scene.render(cam, w, h, spp, 50, seed=1, want_sumsq=False)
+    assert st.paths == w * h * spp and np.all(np.isfinite(s)) and np.all(s >= 0)
+    assert 6.2 < st.rays / st.paths < 6.6
+    assert s.max() / spp <= 15.0 + 1e-3
+    assert s.max() / spp > 14.9  # pixels that lie on the light (emission 15, seen from below) return it on every sample
+    coarse, _, _ = orc.Scene("cornell-box", 1).render(40, 40, 256, 50, seed=7, mode=orc.FAITHFUL)
+    assert abs(s.mean() / spp - coarse.mean() / 256) < 0.02 * coarse.mean() / 256
+    parts = [scene.render(cam, w, h, 8, 50, seed=4, row_begin=r, row_stride=2, want_sumsq=False)[0] for r in range(2)]
+    full8, _, _ = scene.render(cam, w, h, 8, 50, seed=4, want_sumsq=False)
+    assert np.allclose(full8[0::2], parts[0], rtol=1e-5, atol=1e-5) and np.allclose(full8[1::2], parts[1], rtol=1e-5, atol=1e-5)
