@@ -44,6 +44,16 @@ typedef enum RthImageFormat { RTH_IMAGE_PPM_P3 = 0, RTH_IMAGE_PNG_RGBA8 = 1 } Rt
 int rth_encode_image(int format, const uint8_t* rgb_top_down, uint32_t width, uint32_t height, uint8_t* out, uint64_t capacity,
                      uint64_t* needed);
 
+
+/* Texture ingestion (examples/main.rs:266 `image::open("./earthmap.jpg")`): decode a PNG (8-bit, colour types
+ * 0/2/3/4/6, non-interlaced) or PPM (P3/P6, maxval <= 255) byte stream to top-down 8-bit RGB — what `as_rgb8()` gives the texture
+ * closure of main.rs:267-280.  Same two-call pattern as rth_encode_image.  RT_ERR_UNSUPPORTED: 16-bit / interlaced / JPEG-free build. */
+int rth_decode_image(const uint8_t* bytes, uint64_t n, uint32_t* width, uint32_t* height, uint8_t* out_rgb_top_down, uint64_t capacity,
+                     uint64_t* needed);
+/* Install (or with NULL remove) the image that the "book-two" example maps onto its earth sphere instead of the synthetic
+ * stand-in; takes effect for scenes built afterwards (rth_example_scene). */
+int rth_set_earth_image(const uint8_t* rgb_top_down, uint32_t width, uint32_t height);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,6 +27,7 @@ struct OracleApi {
     using DiffuseLight = orc::DiffuseLight;
     using Isotropic = orc::Isotropic;
     using ImageTexture = orc::ImageTexture;
+    static void setBakeSize(ImageTexture&, uint32_t, uint32_t) {}  // the oracle evaluates the closure itself
     using CheckerTexture = orc::CheckerTexture;
 };
 
@@ -160,6 +161,14 @@ OrcScene* orc_scene_create(const char* name, uint64_t seed) {
 }
 
 void orc_scene_destroy(OrcScene* s) { delete s; }
+
+// the image book-two maps onto its earth sphere (examples/main.rs:266-281); null restores the synthetic stand-in
+void orc_set_earth_image(const uint8_t* rgb_top_down, uint32_t width, uint32_t height) {
+    rtscenes::EarthImage& e = rtscenes::earthOverride();
+    if (!rgb_top_down || !width || !height) { e = rtscenes::EarthImage(); return; }
+    e.width = width; e.height = height;
+    e.rgb = std::make_shared<std::vector<uint8_t>>(rgb_top_down, rgb_top_down + (size_t)width * height * 3);
+}
 
 void orc_scene_camera(const OrcScene* s, double aspect, OrcCameraArgs* out) {
     const auto& c = s->cam;

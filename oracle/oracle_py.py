@@ -176,6 +176,18 @@ class Scene:
         return out
 
 
+def set_earth_image(rgb_top_down):
+    """orc_set_earth_image: the image book-two maps onto its earth sphere (examples/main.rs:266-281); None = synthetic stand-in."""
+    L = lib()
+    L.orc_set_earth_image.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+    L.orc_set_earth_image.restype = None
+    if rgb_top_down is None:
+        L.orc_set_earth_image(None, 0, 0)
+        return
+    img = np.ascontiguousarray(rgb_top_down, dtype=np.uint8)
+    L.orc_set_earth_image(img.ctypes.data_as(C.c_void_p), img.shape[1], img.shape[0])
+
+
 def camera_args(eye, center, up, fov, aspect, focus, lens):
     cam = OrcCameraArgs()
     cam.eye[:], cam.center[:], cam.up[:] = eye, center, up

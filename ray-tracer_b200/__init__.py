@@ -62,7 +62,7 @@ class RthCameraArgs(C.Structure):
 # every symbol include/rt_b200.h and include/rt_b200_host.h declare
 ABI_SYMBOLS = ["rt_init", "rt_shutdown", "rt_scene_create", "rt_scene_destroy", "rt_render", "rt_render_device", "rt_trace", "rt_color_rays", "rt_resolve_u8",
                "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
-               "rth_flat_desc", "rth_scene_upload", "rth_camera", "rth_encode_image"]
+               "rth_flat_desc", "rth_scene_upload", "rth_camera", "rth_encode_image", "rth_decode_image", "rth_set_earth_image"]
 
 
 class BackendError(RuntimeError):
@@ -102,6 +102,8 @@ def _load():
     L.rth_scene_upload.argtypes = [vp, vp, C.POINTER(vp)]
     L.rth_camera.argtypes = [C.POINTER(RthCameraArgs), C.POINTER(RtCamera)]
     L.rth_encode_image.argtypes = [C.c_int, vp, u32, u32, vp, u64, C.POINTER(u64)]
+    L.rth_decode_image.argtypes = [vp, u64, C.POINTER(u32), C.POINTER(u32), vp, u64, C.POINTER(u64)]
+    L.rth_set_earth_image.argtypes = [vp, u32, u32]
     return L
 
 
@@ -161,6 +163,25 @@ def encode_image(rgb_top_down, fmt):
     out = np.empty(need.value, dtype=np.uint8)
     _check(lib.rth_encode_image(fmt, _ptr(img), w, h, _ptr(out), need.value, C.byref(need)))
     return out.tobytes()
+
+
+def decode_image(data):
+    """rth_decode_image: PNG (8-bit, non-interlaced) or PPM (P3 / P6) bytes -> top-down [H, W, 3] uint8 (examples/main.rs:266-268)."""
+    buf = np.frombuffer(bytes(data), dtype=np.uint8)
+    w, h, need = C.c_uint32(0), C.c_uint32(0), C.c_uint64(0)
+    _check(lib.rth_decode_image(_ptr(buf), len(buf), C.byref(w), C.byref(h), None, 0, C.byref(need)))
+    out = np.empty(need.value, dtype=np.uint8)
+    _check(lib.rth_decode_image(_ptr(buf), len(buf), C.byref(w), C.byref(h), _ptr(out), need.value, C.byref(need)))
+    return out.reshape(h.value, w.value, 3)
+
+
+def set_earth_image(rgb_top_down):
+    """rth_set_earth_image: the image the "book-two" example maps onto its earth sphere (None = the synthetic stand-in)."""
+    if rgb_top_down is None:
+        _check(lib.rth_set_earth_image(None, 0, 0))
+        return
+    img = np.ascontiguousarray(rgb_top_down, dtype=np.uint8)
+    _check(lib.rth_set_earth_image(_ptr(img), img.shape[1], img.shape[0]))
 
 
 def camera_args(eye, center, up, fov, aspect, focus, lens):

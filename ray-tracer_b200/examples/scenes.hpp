@@ -53,6 +53,17 @@ inline std::shared_ptr<std::vector<uint8_t>> syntheticEarth(uint32_t w = 1024, u
     return img;
 }
 
+// main.rs:266 loads ./earthmap.jpg; callers that have a decoded image (rth_set_earth_image / orc_set_earth_image) install it
+// here and book-two maps it exactly as main.rs:267-280 does; otherwise the synthetic texture stands in.
+struct EarthImage {
+    uint32_t width = 0, height = 0;
+    std::shared_ptr<std::vector<uint8_t>> rgb;  // top-down 8-bit RGB
+};
+inline EarthImage& earthOverride() {
+    static EarthImage e;
+    return e;
+}
+
 template <class A>
 struct Scenes {
     using Vec3 = typename A::Vec3;
@@ -171,8 +182,9 @@ struct Scenes {
         BoundPtr fog = sprite(std::make_shared<typename A::ConstantMedium>(sphere(5000.0), 0.0001),
                               std::make_shared<typename A::Isotropic>(Vec3(1.0, 1.0, 1.0)));
         // earth: nearest-texel closure as in main.rs:267-280 (clamped instead of panicking at u == 1)
-        auto image = syntheticEarth();
-        const uint32_t iw = 1024, ih = 512;
+        const EarthImage& override_image = earthOverride();
+        auto image = override_image.rgb ? override_image.rgb : syntheticEarth();
+        const uint32_t iw = override_image.rgb ? override_image.width : 1024u, ih = override_image.rgb ? override_image.height : 512u;
         std::function<Vec3(double, double)> mapping = [image, iw, ih](double u, double v) {
             double fx = u * (double)iw, fy = (1.0 - v) * (double)ih;
             uint32_t px = fx > 0.0 ? (uint32_t)fx : 0u, py = fy > 0.0 ? (uint32_t)fy : 0u;  // `as u32` saturates
@@ -182,6 +194,7 @@ struct Scenes {
             return Vec3((double)p[0] / 255.0, (double)p[1] / 255.0, (double)p[2] / 255.0);
         };
         auto earthTexture = std::make_shared<typename A::ImageTexture>(mapping);
+        A::setBakeSize(*earthTexture, iw, ih);  // the device bakes the closure at the image's own resolution: nearest lookup stays exact
         BoundPtr earth = sprite(sphere(100.0), std::make_shared<typename A::Lambertian>(earthTexture), Mat4::translation(Vec3(400.0, 200.0, 400.0)));
         auto white = std::make_shared<typename A::Lambertian>(Vec3(0.73, 0.73, 0.73));
         List spheres;

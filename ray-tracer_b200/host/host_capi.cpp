@@ -29,6 +29,7 @@ struct HostApi {  // the type bundle scenes.hpp is instantiated with
     using DiffuseLight = rtb::host::DiffuseLight;
     using Isotropic = rtb::host::Isotropic;
     using ImageTexture = rtb::host::ImageTexture;
+    static void setBakeSize(ImageTexture& t, uint32_t w, uint32_t h) { t.bakeWidth = w; t.bakeHeight = h; }
     using CheckerTexture = rtb::host::CheckerTexture;
 };
 
@@ -98,6 +99,28 @@ int rth_camera(const RthCameraArgs* a, RtCamera* out) {
     const rtb::host::PerspectiveCamera cam({a->eye[0], a->eye[1], a->eye[2]}, {a->center[0], a->center[1], a->center[2]}, {a->up[0], a->up[1], a->up[2]},
                                            a->fov, a->aspect, a->focus_distance, a->lens_radius);
     *out = rtb::host::flattenCamera(cam);
+    return RT_OK;
+}
+
+int rth_decode_image(const uint8_t* bytes, uint64_t n, uint32_t* width, uint32_t* height, uint8_t* out_rgb, uint64_t capacity, uint64_t* needed) {
+    if (!bytes || !width || !height || !needed) return RT_ERR_INVALID;
+    std::vector<uint8_t> rgb;
+    const int rc = rth::decode_image(bytes, (size_t)n, *width, *height, rgb);
+    if (rc == -2) return RT_ERR_UNSUPPORTED;
+    if (rc != 0) return RT_ERR_INVALID;
+    *needed = rgb.size();
+    if (!out_rgb) return RT_OK;
+    if (capacity < rgb.size()) return RT_ERR_INVALID;
+    std::memcpy(out_rgb, rgb.data(), rgb.size());
+    return RT_OK;
+}
+
+int rth_set_earth_image(const uint8_t* rgb_top_down, uint32_t width, uint32_t height) {
+    rtscenes::EarthImage& e = rtscenes::earthOverride();
+    if (!rgb_top_down) { e = rtscenes::EarthImage(); return RT_OK; }
+    if (width == 0 || height == 0) return RT_ERR_INVALID;
+    e.width = width; e.height = height;
+    e.rgb = std::make_shared<std::vector<uint8_t>>(rgb_top_down, rgb_top_down + (size_t)width * height * 3);
     return RT_OK;
 }
 

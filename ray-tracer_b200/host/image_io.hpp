@@ -10,8 +10,12 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <string>
 #include <vector>
+
+#include <zlib.h>
 
 namespace rth {
 
@@ -93,6 +97,114 @@ inline std::vector<uint8_t> encode_png_rgba8(const uint8_t* rgb_top_down, uint32
     put_chunk(png, "IDAT", z);
     put_chunk(png, "IEND", {});
     return png;
+}
+
+// ---- decoders (texture ingestion; examples/main.rs:266 opens earthmap.jpg with the `image` crate) ----------
+// PNG (8-bit, colour types 0 / 2 / 3 / 4 / 6, non-interlaced; zlib inflates the IDAT stream) and PPM (P3 / P6, maxval <= 255) to
+// top-down 8-bit RGB — what `image.as_rgb8()` hands the texture closure of main.rs:267-280.  JPEG is not decoded.
+// Returns 0, -1 malformed (bad signature / CRC / truncated), -2 unsupported (16-bit, interlaced, maxval > 255).
+namespace detail {
+inline uint32_t get_be32(const uint8_t* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
+inline int paeth(int a, int b, int c) {
+    const int p = a + b - c, pa = std::abs(p - a), pb = std::abs(p - b), pc = std::abs(p - c);
+    return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+}  // namespace detail
+
+inline int decode_png(const uint8_t* data, size_t n, uint32_t& width, uint32_t& height, std::vector<uint8_t>& rgb) {
+    using namespace detail;
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+    if (n < 8 || std::memcmp(data, sig, 8) != 0) return -1;
+    size_t pos = 8;
+    uint32_t depth = 0, ctype = 0, interlace = 0;
+    bool have_ihdr = false, have_end = false;
+    std::vector<uint8_t> idat, plte;
+    while (pos + 12 <= n && !have_end) {
+        const uint32_t len = get_be32(data + pos);
+        if (pos + 12 + (size_t)len > n) return -1;
+        const uint8_t* type = data + pos + 4;
+        const uint8_t* body = data + pos + 8;
+        if ((crc32_update(0xFFFFFFFFu, type, 4 + (size_t)len) ^ 0xFFFFFFFFu) != get_be32(body + len)) return -1;
+        if (!std::memcmp(type, "IHDR", 4)) {
+            if (len != 13) return -1;
+            width = get_be32(body); height = get_be32(body + 4); depth = body[8]; ctype = body[9]; interlace = body[12];
+            have_ihdr = true;
+        } else if (!std::memcmp(type, "PLTE", 4)) {
+            plte.assign(body, body + len);
+        } else if (!std::memcmp(type, "IDAT", 4)) {
+            idat.insert(idat.end(), body, body + len);
+        } else if (!std::memcmp(type, "IEND", 4)) {
+            have_end = true;
+        }
+        pos += 12 + (size_t)len;
+    }
+    if (!have_ihdr || !have_end || width == 0 || height == 0) return -1;
+    if (depth != 8 || interlace != 0) return -2;
+    const uint32_t channels = ctype == 0 ? 1u : ctype == 2 ? 3u : ctype == 3 ? 1u : ctype == 4 ? 2u : ctype == 6 ? 4u : 0u;
+    if (!channels) return -2;
+    if (ctype == 3 && plte.empty()) return -1;
+    const size_t stride = (size_t)width * channels;
+    std::vector<uint8_t> raw((stride + 1) * height);
+    uLongf out_len = (uLongf)raw.size();
+    if (uncompress(raw.data(), &out_len, idat.data(), (uLong)idat.size()) != Z_OK || out_len != raw.size()) return -1;
+    std::vector<uint8_t> prev(stride, 0), cur(stride);
+    rgb.resize((size_t)width * height * 3);
+    for (uint32_t y = 0; y < height; ++y) {
+        const uint8_t* line = raw.data() + (stride + 1) * y;
+        const uint8_t filter = line[0];
+        if (filter > 4) return -1;
+        for (size_t i = 0; i < stride; ++i) {
+            const int a = i >= channels ? cur[i - channels] : 0, b = prev[i], c = i >= channels ? prev[i - channels] : 0;
+            const int x = line[1 + i];
+            const int v = filter == 0 ? x : filter == 1 ? x + a : filter == 2 ? x + b : filter == 3 ? x + ((a + b) >> 1) : x + paeth(a, b, c);
+            cur[i] = (uint8_t)v;
+        }
+        for (uint32_t xx = 0; xx < width; ++xx) {
+            uint8_t* o = rgb.data() + 3 * ((size_t)y * width + xx);
+            const uint8_t* p = cur.data() + (size_t)xx * channels;
+            if (ctype == 2 || ctype == 6) { o[0] = p[0]; o[1] = p[1]; o[2] = p[2]; }
+            else if (ctype == 3) { if ((size_t)p[0] * 3 + 2 >= plte.size()) return -1; o[0] = plte[p[0] * 3]; o[1] = plte[p[0] * 3 + 1]; o[2] = plte[p[0] * 3 + 2]; }
+            else { o[0] = o[1] = o[2] = p[0]; }
+        }
+        prev.swap(cur);
+    }
+    return 0;
+}
+
+inline int decode_ppm(const uint8_t* data, size_t n, uint32_t& width, uint32_t& height, std::vector<uint8_t>& rgb) {
+    if (n < 2 || data[0] != 'P' || (data[1] != '3' && data[1] != '6')) return -1;
+    const bool text = data[1] == '3';
+    size_t pos = 2;
+    auto token = [&](uint32_t& out) -> bool {  // next unsigned integer, skipping whitespace and # comments
+        for (;;) {
+            while (pos < n && (data[pos] == ' ' || data[pos] == '\t' || data[pos] == '\n' || data[pos] == '\r')) ++pos;
+            if (pos < n && data[pos] == '#') { while (pos < n && data[pos] != '\n') ++pos; continue; }
+            break;
+        }
+        if (pos >= n || data[pos] < '0' || data[pos] > '9') return false;
+        uint64_t v = 0;
+        while (pos < n && data[pos] >= '0' && data[pos] <= '9') { v = v * 10 + (data[pos] - '0'); if (v > 0xFFFFFFFFull) return false; ++pos; }
+        out = (uint32_t)v;
+        return true;
+    };
+    uint32_t maxval = 0;
+    if (!token(width) || !token(height) || !token(maxval) || width == 0 || height == 0 || maxval == 0) return -1;
+    if (maxval > 255) return -2;
+    const size_t count = (size_t)width * height * 3;
+    rgb.resize(count);
+    if (text) {
+        for (size_t i = 0; i < count; ++i) { uint32_t v; if (!token(v) || v > maxval) return -1; rgb[i] = (uint8_t)v; }
+    } else {
+        ++pos;  // the single whitespace byte after maxval
+        if (pos + count > n) return -1;
+        std::memcpy(rgb.data(), data + pos, count);
+    }
+    return 0;
+}
+
+inline int decode_image(const uint8_t* data, size_t n, uint32_t& width, uint32_t& height, std::vector<uint8_t>& rgb) {
+    if (n >= 2 && data[0] == 'P') return decode_ppm(data, n, width, height, rgb);
+    return decode_png(data, n, width, height, rgb);
 }
 
 }  // namespace rth

@@ -501,3 +501,28 @@ def test_full_size_config2_properties(rt, orc, device):
     parts = [scene.render(cam, w, h, 8, 50, seed=4, row_begin=r, row_stride=2, want_sumsq=False)[0] for r in range(2)]
     full8, _, _ = scene.render(cam, w, h, 8, 50, seed=4, want_sumsq=False)
     assert np.allclose(full8[0::2], parts[0], rtol=1e-5, atol=1e-5) and np.allclose(full8[1::2], parts[1], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_ingested_earth_texture_renders_like_the_oracle(rt, orc, device):
+    """a decoded image installed as book-two's earth texture (examples/main.rs:266-281) on both sides — the GPU
+    bakes it 1:1 into its texel table, the oracle evaluates the closure — gives the same paths; and it is not the synthetic one."""
+    rng = np.random.default_rng(21)
+    earth = np.repeat(np.repeat(rng.integers(0, 256, size=(8, 16, 3), dtype=np.uint8), 6, axis=0), 5, axis=1)  # 48 x 80 blocks
+    png = rt.encode_image(earth, rt.IMAGE_PNG_RGBA8)
+    decoded = rt.decode_image(png)
+    w = h = 72
+    base, _, _ = rt.Scene.example(device, "book-two", 1).render(rt.FlatScene("book-two", 1).camera(1.0), w, h, 4, 50, seed=1)
+    rt.set_earth_image(decoded)
+    orc.set_earth_image(decoded)
+    try:
+        scene = rt.Scene.example(device, "book-two", 1)
+        s_g, _, st = scene.render(scene.flat.camera(1.0), w, h, 4, 50, seed=1)
+        s_o, _, sto = orc.Scene("book-two", 1).render(w, h, 4, 50, seed=1, mode=orc.PAIRED)
+    finally:
+        rt.set_earth_image(None)
+        orc.set_earth_image(None)
+    ok = np.abs(s_g - s_o).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(s_o).max(axis=2))
+    assert ok.mean() >= 0.985, ok.mean()
+    assert abs(int(st.rays) - int(sto.segments)) <= 0.01 * sto.segments
+    assert not np.allclose(s_g, base, rtol=1e-3, atol=1e-3)  # the earth sphere is in view: the texture matters

@@ -246,3 +246,54 @@ def test_image_encoders_match_the_example_drivers_formats(rt):
             pass
     with pytest.raises(rt.BackendError):
         rt.encode_image(np.zeros((2, 2, 3), dtype=np.uint8), 9)
+
+
+def test_image_decoders_and_earth_texture_ingestion(rt):
+    """rth_decode_image: PNGs written by an independent encoder (PIL: deflate-compressed, adaptive filters,
+    every 8-bit colour type), our own stored-deflate PNGs and PPM P3 / P6 decode to the exact pixels; malformed and unsupported
+    streams are refused.  rth_set_earth_image: book-two bakes the installed image 1:1 into its texel table (examples/main.rs:266-281)."""
+    import io
+    rng = np.random.default_rng(8)
+    img = rng.integers(0, 256, size=(37, 53, 3), dtype=np.uint8)
+    img[5:20, 5:30] = (10, 200, 30)  # flat area + noise: PIL picks different filters per row
+    assert np.array_equal(rt.decode_image(rt.encode_image(img, rt.IMAGE_PNG_RGBA8)), img)
+    assert np.array_equal(rt.decode_image(rt.encode_image(img, rt.IMAGE_PPM_P3)), img)
+    p6 = b"P6\n# a comment\n53 37\n255\n" + img.tobytes()
+    assert np.array_equal(rt.decode_image(p6), img)
+    try:
+        from PIL import Image
+    except ImportError:
+        Image = None
+    if Image is not None:
+        for mode in ["RGB", "RGBA", "L", "LA", "P"]:
+            pil = Image.fromarray(img).convert(mode)
+            buf = io.BytesIO()
+            pil.save(buf, format="PNG")
+            expect = np.asarray(pil.convert("RGB") if mode != "LA" else pil.convert("L").convert("RGB"))
+            assert np.array_equal(rt.decode_image(buf.getvalue()), expect), mode
+        buf = io.BytesIO()
+        Image.fromarray((img.astype(np.uint32).sum(axis=2) * 80).astype(np.uint16)).save(buf, format="PNG")  # 16-bit greyscale
+        with pytest.raises(rt.BackendError) as e:
+            rt.decode_image(buf.getvalue())
+        assert e.value.code == rt.RT_ERR_UNSUPPORTED
+    good = bytearray(rt.encode_image(img, rt.IMAGE_PNG_RGBA8))
+    good[60] ^= 0xFF  # corrupt IDAT: the chunk CRC no longer matches
+    for bad in [bytes(good), bytes(good[:100]), b"JFIF not a png", b"P6\n2 2\n65535\n" + bytes(24)]:
+        with pytest.raises(rt.BackendError):
+            rt.decode_image(bad)
+
+    earth = rng.integers(0, 256, size=(16, 32, 3), dtype=np.uint8)
+    rt.set_earth_image(earth)
+    try:
+        flat = rt.FlatScene("book-two", 1)
+        tex = flat.textures()
+        images = tex[tex["kind"] == rt.TEX_IMAGE]
+        assert len(images) == 1 and images[0]["width"] == 32 and images[0]["height"] == 16
+        d = flat.desc()
+        texels = np.ctypeslib.as_array(C.cast(d.texels, C.POINTER(C.c_float)), shape=(d.n_texels, 4))
+        off = int(images[0]["texel_offset"])
+        assert np.allclose(texels[off:off + 512, :3].reshape(16, 32, 3), earth / 255.0, atol=1e-7)
+    finally:
+        rt.set_earth_image(None)
+    tex = rt.FlatScene("book-two", 1).textures()
+    assert tex[tex["kind"] == rt.TEX_IMAGE][0]["width"] == 1024
