@@ -62,6 +62,18 @@ __device__ __forceinline__ void pixel_from_index(uint32_t q, uint32_t W, uint32_
     x = q - r * W;
 }
 
+// L2 prefetch of the queue entries a persistent grid-stride loop will read in its NEXT round (the 4 M-ray queues stream from
+// HBM): one lane per 128-byte line issues `prefetch.global.L2`, no registers are held across the round.  k_shade +2 % (r1s);
+// k_extend_rects, whose 48 resident warps already cover the latency, lost 2 % and does not prefetch.
+#ifndef RT_PREFETCH_L2
+#define RT_PREFETCH_L2 1
+#endif
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+#if RT_PREFETCH_L2
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#endif
+}
+
 // ---- generate --------------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue q, WaveCounters* __restrict__ wc, uint32_t k) {
@@ -472,6 +484,14 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
     const uint32_t stride = gridDim.x * blockDim.x * R;
     // whole blocks iterate together: the slot allocation below synchronises the block
     for (uint32_t base = blockIdx.x * blockDim.x * R; base < n; base += stride) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t nx = base + stride + r * blockDim.x + threadIdx.x;
+            if (nx < n) {
+                if ((lane & 7u) == 0u) { prefetch_l2(&qin.a[nx]); prefetch_l2(&qin.b[nx]); prefetch_l2(&qin.c[nx]); }
+                if ((lane & 15u) == 0u) prefetch_l2(&hits[nx]);
+            }
+        }
         float4 a[R], b[R], c[R];
         float2 h[R];
 #pragma unroll
