@@ -145,31 +145,41 @@ void emitNode(BvhNode32& out, const TmpNode& t, uint32_t ref, uint32_t count) {
 
 }  // namespace
 
+std::vector<uint32_t> select_always(const std::vector<Box3>& boxes, const BvhOptions& opt) {
+    // primitives that span most of what is left (sky, ground, fog): always-tested prefix
+    const uint32_t n = (uint32_t)boxes.size();
+    std::vector<uint8_t> pulled(n, 0);
+    std::vector<uint32_t> always;
+    std::vector<uint32_t> byArea(n);
+    std::iota(byArea.begin(), byArea.end(), 0u);
+    const uint32_t keep = std::min<uint32_t>(n, opt.max_always + 1);
+    std::partial_sort(byArea.begin(), byArea.begin() + keep, byArea.end(),
+                      [&](uint32_t a, uint32_t b) { const double aa = boxArea(boxes[a]), ab = boxArea(boxes[b]); return aa > ab || (aa == ab && a < b); });
+    for (uint32_t k = 0; k < keep && always.size() < opt.max_always; ++k) {
+        const uint32_t cand = byArea[k];
+        Grow rest;
+        for (uint32_t i = 0; i < n; ++i)
+            if (!pulled[i]) rest.add(boxes[i]);
+        if (boxArea(boxes[cand]) >= opt.always_area_fraction * rest.area()) {
+            pulled[cand] = 1;
+            always.push_back(cand);
+        } else {
+            break;
+        }
+    }
+    return always;
+}
+
 BvhResult build_bvh(const std::vector<Box3>& boxes, const BvhOptions& opt) {
     BvhResult res;
     const uint32_t n = (uint32_t)boxes.size();
     std::vector<uint8_t> pulled(n, 0);
 
-    // 1. peel primitives that span most of what is left (sky, ground, fog): always-tested prefix
-    {
-        std::vector<uint32_t> byArea(n);
-        std::iota(byArea.begin(), byArea.end(), 0u);
-        const uint32_t keep = std::min<uint32_t>(n, opt.max_always + 1);
-        std::partial_sort(byArea.begin(), byArea.begin() + keep, byArea.end(),
-                          [&](uint32_t a, uint32_t b) { const double aa = boxArea(boxes[a]), ab = boxArea(boxes[b]); return aa > ab || (aa == ab && a < b); });
-        for (uint32_t k = 0; k < keep && res.n_always < opt.max_always; ++k) {
-            const uint32_t cand = byArea[k];
-            Grow rest;
-            for (uint32_t i = 0; i < n; ++i)
-                if (!pulled[i]) rest.add(boxes[i]);
-            if (boxArea(boxes[cand]) >= opt.always_area_fraction * rest.area()) {
-                pulled[cand] = 1;
-                res.order.push_back(cand);
-                res.n_always++;
-            } else {
-                break;
-            }
-        }
+    // 1. peel the always-tested prefix
+    for (uint32_t id : select_always(boxes, opt)) {
+        pulled[id] = 1;
+        res.order.push_back(id);
+        res.n_always++;
     }
 
     // 2. SAH tree over the rest

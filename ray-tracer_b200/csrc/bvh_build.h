@@ -42,5 +42,7 @@ struct BvhOptions {
 };
 
 BvhResult build_bvh(const std::vector<Box3>& boxes, const BvhOptions& opt = BvhOptions());
+// Input ids of the primitives that go to the always-tested list (largest first); shared with the device builder (lbvh.cu).
+std::vector<uint32_t> select_always(const std::vector<Box3>& boxes, const BvhOptions& opt);
 
 }  // namespace rtb

@@ -36,6 +36,7 @@ constexpr uint32_t RT_MAX_STAGED_PRIMS = 1024;  // primitive heads (16 KB) stage
 constexpr uint32_t RT_MAX_STAGED_RECTS = 256;   // compact rectangle records (16 KB) staged together with the heads
 constexpr uint32_t RT_SMALL_SCENE = 32;         // at most this many primitives: linear list instead of a BVH
 constexpr uint32_t RT_MAX_ALWAYS = 8;           // always-tested list (sky / ground / fog)
+constexpr uint32_t RT_DEVICE_BUILD_MIN_PRIMS = 65536;  // from this many primitives the BVH is built on the GPU (lbvh.cu)
 constexpr uint32_t RT_MAX_FRAMES = 8;           // frame-rect list: distinct orthonormal frames the rectangles of a small scene are aligned to
 
 struct DMaterial {       // 32 B, read as two float4

@@ -458,6 +458,7 @@ def test_parallel_bvh_build_is_thread_count_independent(rt, device):
     """The host SAH builder hands subtrees to worker threads (csrc/bvh_build.cpp); the emitted tree must not depend on how many."""
     import time
     out = {}
+    os.environ["RT_B200_BVH_BUILDER"] = "host"  # scenes of this size default to the device builder
     for threads in ["1", "5", ""]:
         old = os.environ.get("RT_B200_BVH_THREADS")
         if threads:
@@ -477,6 +478,7 @@ def test_parallel_bvh_build_is_thread_count_independent(rt, device):
         out[threads] = (scene.bvh_info(), int(st.rays), s)
         print(f"stress:200000 scene build+upload with RT_B200_BVH_THREADS={threads or 'default'}: {dt:.3f} s, bvh {scene.bvh_info()}")
         scene.close()
+    os.environ.pop("RT_B200_BVH_BUILDER", None)
     for threads in ["5", ""]:
         assert out[threads][0] == out["1"][0] and out[threads][1] == out["1"][1]
         assert np.allclose(out[threads][2], out["1"][2], rtol=1e-5, atol=1e-5)
@@ -526,3 +528,44 @@ def test_ingested_earth_texture_renders_like_the_oracle(rt, orc, device):
     assert ok.mean() >= 0.985, ok.mean()
     assert abs(int(st.rays) - int(sto.segments)) <= 0.01 * sto.segments
     assert not np.allclose(s_g, base, rtol=1e-3, atol=1e-3)  # the earth sphere is in view: the texture matters
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["stress:20000", "book-two", "stress:300000"])
+def test_device_lbvh_build_gives_the_same_hits_as_the_host_sah_tree(rt, orc, device, name):
+    """the BVH built on the GPU (csrc/lbvh.cu: Morton sort, Karras radix tree, bottom-up fit) against the host
+    SAH tree.  Closest hits do not depend on topology and both trees run the same primitive arithmetic, so rt_trace must return
+    identical records, and renders with the same seed identical paths."""
+    import time
+    so = orc.Scene(name if name != "stress:300000" else "stress:20000", 1)
+    rng = np.random.default_rng(4)
+    cam_rays = orc.camera_rays(so.camera(16 / 9), 96, 54)
+    d = rng.normal(size=(20000, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = rng.uniform(-40, 40, size=(20000, 3)) if name.startswith("stress") else rng.uniform(0, 555, size=(20000, 3))
+    rays = np.concatenate([cam_rays, np.concatenate([o, d], axis=1)]).astype(np.float32)
+    res = {}
+    for builder in ["host", "device"]:
+        old = os.environ.get("RT_B200_BVH_BUILDER")
+        os.environ["RT_B200_BVH_BUILDER"] = builder
+        try:
+            t0 = time.time()
+            scene = rt.Scene.example(device, name, 1)
+            dt = time.time() - t0
+        finally:
+            if old is None:
+                os.environ.pop("RT_B200_BVH_BUILDER", None)
+            else:
+                os.environ["RT_B200_BVH_BUILDER"] = old
+        hits = scene.trace(rays, seed=1)
+        s, _, st = scene.render(scene.flat.camera(16 / 9), 96, 54, 2, 16, seed=2)
+        res[builder] = (hits, s, int(st.rays), scene.bvh_info())
+        print(f"{name}: {builder} build+upload {dt:.3f} s, bvh {scene.bvh_info()}")
+        scene.close()
+    hh, hd = res["host"][0], res["device"][0]
+    assert res["host"][3] != res["device"][3]  # really two different trees
+    for field in ["hit", "prim", "material"]:
+        assert np.array_equal(hh[field], hd[field]), field
+    assert np.array_equal(hh["t"], hd["t"]) and np.array_equal(hh["p"], hd["p"]) and np.array_equal(hh["n"], hd["n"])
+    assert res["host"][2] == res["device"][2]
+    assert np.allclose(res["host"][1], res["device"][1], rtol=1e-5, atol=1e-5)
