@@ -26,18 +26,6 @@ namespace rtb {
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
-// Warp-aggregated append: one atomic per warp, returns this lane's slot (valid where `pred`).
-__device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
-    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, pred);
-    if (mask == 0u) return 0u;
-    const uint32_t lane = lane_id();
-    const int leader = __ffs(mask) - 1;
-    uint32_t base = 0u;
-    if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
-    base = __shfl_sync(0xFFFFFFFFu, base, leader);
-    return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
-}
-
 // local linear index -> (x, local row): 8x4 pixel tiles per warp where they fit, scanline remainders
 __device__ __forceinline__ void pixel_from_index(uint32_t q, uint32_t W, uint32_t rows, uint32_t& x, uint32_t& yl) {
     const uint32_t W8 = W & ~7u, R4 = rows & ~3u;

@@ -1,5 +1,5 @@
 import importlib, sys
-sys.path.insert(0,'/root/repo')
+import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 rt = importlib.import_module("ray-tracer_b200")
 dev = rt.Device(0)
 for name,w,h,spp,d in [("book-one",960,540,8,50),("cornell-box",600,600,8,50),("book-two",400,400,8,50),("stress:1000000",960,540,4,16)]:
