@@ -527,6 +527,128 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
     }
 }
 
+// ---- shade, warp-specialised form ---------------------------------------------------------------------------------
+//
+// k_shade's slot allocation costs every round two block barriers with a global atomic round trip between them (r1o: 28 % of
+// the kernel's stall samples sit on those barriers).  Here the block is RT_SHADE_WARPS producer warps plus ONE scanner warp,
+// coupled by named barriers (bar.arrive / bar.sync) and double-buffered counters:
+//   producer, round j:   shade -> counts[j & 1] -> bar.arrive(A[j & 1])           (does not wait)
+//                        then COMMIT round j - 1: bar.sync(B[(j - 1) & 1]) -> slots -> stores of the rays kept in registers
+//   scanner,  round j:   bar.sync(A[j & 1]) -> scan the warp counts, the two global atomics -> offsets[j & 1] -> bar.arrive(B[j & 1])
+// so the atomic latency and the wait for the slowest warp overlap the producers' next round of shading.
+#ifndef RT_SHADE_WARPS
+#define RT_SHADE_WARPS 8
+#endif
+constexpr uint32_t RT_SHADEP_THREADS = 32u * (RT_SHADE_WARPS + 1u);
+#ifndef RT_SHADEP_MIN_BLOCKS
+#define RT_SHADEP_MIN_BLOCKS 3
+#endif
+
+// (immediate barrier ids: with a register id ptxas reserves all 16 named barriers of the CTA)
+template <uint32_t ID>
+__device__ __forceinline__ void named_arrive_id() { asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(RT_SHADEP_THREADS) : "memory"); }
+template <uint32_t ID>
+__device__ __forceinline__ void named_sync_id() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(RT_SHADEP_THREADS) : "memory"); }
+__device__ __forceinline__ void named_arrive(uint32_t id, uint32_t) {
+    if (id == 1u) named_arrive_id<1>(); else if (id == 2u) named_arrive_id<2>(); else if (id == 3u) named_arrive_id<3>(); else named_arrive_id<4>();
+}
+__device__ __forceinline__ void named_sync(uint32_t id, uint32_t) {
+    if (id == 1u) named_sync_id<1>(); else if (id == 2u) named_sync_id<2>(); else if (id == 3u) named_sync_id<3>(); else named_sync_id<4>();
+}
+
+__global__ void __launch_bounds__(RT_SHADEP_THREADS, RT_SHADEP_MIN_BLOCKS) k_shade_pipe(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
+                                                                                      const float2* __restrict__ hits, float4* __restrict__ done,
+                                                                                      WaveCounters* __restrict__ wc, uint32_t k) {
+    extern __shared__ float4 shade_smem[];
+    __shared__ uint32_t s_cnt[2][RT_SHADE_WARPS][2];  // [buffer][producer warp][alive, record] counts of a round
+    __shared__ uint32_t s_off[2][RT_SHADE_WARPS][2];  // [buffer][producer warp] first slot of the warp in qout / done
+    const uint32_t n_staged = min(S0.n_mats, RT_MAX_STAGED_MATS);
+    const uint32_t n_sp = S0.n_staged_prims, n_sr = n_sp ? S0.n_rects : 0u;
+    float4* smats = shade_smem;
+    float4* s_head = smats + 2u * n_staged;
+    float4* s_nrm = s_head + n_sp;
+    uint2* s_meta = reinterpret_cast<uint2*>(s_nrm + n_sr);
+    for (uint32_t i = threadIdx.x; i < 2u * n_staged; i += blockDim.x) smats[i] = reinterpret_cast<const float4*>(S0.mats)[i];
+    for (uint32_t i = threadIdx.x; i < n_sp; i += blockDim.x) { s_head[i] = S0.prim_head[i]; s_meta[i] = S0.prim_meta[i]; }
+    for (uint32_t i = threadIdx.x; i < n_sr; i += blockDim.x) s_nrm[i] = S0.rect_nrm[i];
+    DScene S = S0;
+    if (n_sp) { S.prim_head = s_head; S.prim_meta = s_meta; S.rect_nrm = s_nrm; }
+    __syncthreads();
+    const uint32_t s = k % RT_RING;
+    const uint32_t n = wc->total[s];
+    uint32_t* surv_next = &wc->surv[(k + 1) % RT_RING];
+    uint32_t* done_cnt = &wc->done[s];
+    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
+    constexpr uint32_t PT = 32u * RT_SHADE_WARPS;  // producer threads = rays per block round
+    const uint32_t stride = gridDim.x * PT;
+    const uint32_t first = blockIdx.x * PT;
+    const uint32_t rounds = first < n ? (n - first + stride - 1u) / stride : 0u;  // block-uniform
+    constexpr uint32_t BAR_A = 1u, BAR_B = 3u;  // barrier ids A0, A1 = 1, 2; B0, B1 = 3, 4 (0 is __syncthreads)
+
+    if (warp == RT_SHADE_WARPS) {  // ---- scanner warp
+        for (uint32_t j = 0; j < rounds; ++j) {
+            const uint32_t buf = j & 1u;
+            named_sync(BAR_A + buf, RT_SHADEP_THREADS);
+            uint32_t ca = lane < RT_SHADE_WARPS ? s_cnt[buf][lane][0] : 0u, cb = lane < RT_SHADE_WARPS ? s_cnt[buf][lane][1] : 0u;
+            uint32_t pa = ca, pb = cb;  // inclusive warp scan over the producer warps
+#pragma unroll
+            for (int d = 1; d < (int)RT_SHADE_WARPS; d <<= 1) {
+                const uint32_t ua = __shfl_up_sync(0xFFFFFFFFu, pa, d), ub = __shfl_up_sync(0xFFFFFFFFu, pb, d);
+                if ((int)lane >= d) { pa += ua; pb += ub; }
+            }
+            const uint32_t ta = __shfl_sync(0xFFFFFFFFu, pa, RT_SHADE_WARPS - 1), tb = __shfl_sync(0xFFFFFFFFu, pb, RT_SHADE_WARPS - 1);
+            uint32_t base_a = 0u, base_b = 0u;
+            if (lane == 0) {
+                base_a = ta ? atomicAdd(surv_next, ta) : 0u;
+                base_b = tb ? atomicAdd(done_cnt, tb) : 0u;
+            }
+            base_a = __shfl_sync(0xFFFFFFFFu, base_a, 0);
+            base_b = __shfl_sync(0xFFFFFFFFu, base_b, 0);
+            if (lane < RT_SHADE_WARPS) { s_off[buf][lane][0] = base_a + pa - ca; s_off[buf][lane][1] = base_b + pb - cb; }
+            __threadfence_block();
+            named_arrive(BAR_B + buf, RT_SHADEP_THREADS);
+        }
+        return;
+    }
+
+    // ---- producer warps
+    ShadeOne prev;
+    prev.alive = prev.record = false;
+    prev.o0 = prev.o1 = prev.o2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t prev_ma = 0u, prev_mb = 0u;
+    const uint32_t lt = (1u << lane) - 1u;
+    auto commit = [&](uint32_t buf) {
+        named_sync(BAR_B + buf, RT_SHADEP_THREADS);
+        const uint32_t slot = s_off[buf][warp][0] + (uint32_t)__popc(prev_ma & lt), dslot = s_off[buf][warp][1] + (uint32_t)__popc(prev_mb & lt);
+        if (prev.alive) { qout.a[slot] = prev.o0; qout.b[slot] = prev.o1; qout.c[slot] = prev.o2; }
+        if (prev.record) done[dslot] = prev.o0;
+    };
+    const uint32_t t_in = threadIdx.x;  // < PT
+    for (uint32_t j = 0; j < rounds; ++j) {
+        const uint32_t buf = j & 1u;
+        const uint32_t i = first + j * stride + t_in;
+        const uint32_t nx = i + stride;
+        if (nx < n) {
+            if ((lane & 7u) == 0u) { prefetch_l2(&qin.a[nx]); prefetch_l2(&qin.b[nx]); prefetch_l2(&qin.c[nx]); }
+            if ((lane & 15u) == 0u) prefetch_l2(&hits[nx]);
+        }
+        float4 a, b, c;
+        float2 h;
+        if (i < n) { h = hits[i]; a = qin.a[i]; b = qin.b[i]; c = qin.c[i]; }
+        else { h = make_float2(0.f, __uint_as_float(RT_NO_PRIM)); a = b = c = make_float4(0.f, 0.f, 0.f, 0.f); }
+        const ShadeOne cur = shade_one(S, rc, smats, n_staged, a, b, c, h);
+        const uint32_t ma = __ballot_sync(0xFFFFFFFFu, cur.alive), mb = __ballot_sync(0xFFFFFFFFu, cur.record);
+        if (lane == 0) { s_cnt[buf][warp][0] = (uint32_t)__popc(ma); s_cnt[buf][warp][1] = (uint32_t)__popc(mb); }
+        __threadfence_block();
+        named_arrive(BAR_A + buf, RT_SHADEP_THREADS);
+        if (j > 0) commit(buf ^ 1u);
+        prev = cur;
+        prev_ma = ma;
+        prev_mb = mb;
+    }
+    if (rounds > 0) commit((rounds - 1u) & 1u);
+}
+
 // ---- accumulate ------------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const float4* __restrict__ done, const WaveCounters* __restrict__ wc,
@@ -620,6 +742,7 @@ static size_t g_extend_smem = ~(size_t)0, g_shade_smem = ~(size_t)0, g_rects_sme
 static int g_rects_blocks_per_sm = 0, g_bvh_blocks_per_sm = 0;
 static size_t g_bvh_smem = 0, g_scene_smem = 0;
 static int g_persistent = -1;
+static int g_shade_pipe = -1, g_shadep_blocks_per_sm = 0;
 
 cudaError_t kernels_init(int device) {
     if (g_num_sms > 0) return cudaSuccess;
@@ -647,7 +770,16 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shade_blocks_per_sm, k_shade, RT_SHADE_BLOCK, shade_bytes);
         if (e != cudaSuccess) return e;
         if (g_shade_blocks_per_sm < 1) g_shade_blocks_per_sm = 1;
+        e = cudaFuncSetAttribute(k_shade_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shadep_blocks_per_sm, k_shade_pipe, RT_SHADEP_THREADS, shade_bytes);
+        if (e != cudaSuccess) return e;
+        if (g_shadep_blocks_per_sm < 1) g_shadep_blocks_per_sm = 1;
         g_shade_smem = shade_bytes;
+    }
+    {
+        const char* sp = getenv("RT_B200_SHADE_PIPE");
+        g_shade_pipe = sp ? atoi(sp) : RT_SHADE_PIPE_DEFAULT;
     }
     const size_t staged_bytes = scene_bytes + (size_t)RT_SMEM_STACK * RT_EXTEND_BLOCK * sizeof(uint32_t);
     if (staged_bytes != g_extend_smem) {
@@ -706,7 +838,8 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st) {
-    k_shade<<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    if (g_shade_pipe) k_shade_pipe<<<g_num_sms * g_shadep_blocks_per_sm, RT_SHADEP_THREADS, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    else k_shade<<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
 void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
     k_accumulate<<<g_num_sms * 2, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);

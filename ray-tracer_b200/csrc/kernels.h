@@ -22,6 +22,9 @@
 #ifndef RT_PERSISTENT_MIN_NODES
 #define RT_PERSISTENT_MIN_NODES 65536u  // BVH size from which extend runs in its persistent, lane-refilling form
 #endif
+#ifndef RT_SHADE_PIPE_DEFAULT
+#define RT_SHADE_PIPE_DEFAULT 0  // 1: shade runs in its warp-specialised form (k_shade_pipe); RT_B200_SHADE_PIPE=0|1 overrides
+#endif
 #ifndef RT_LEAF_MIN
 #define RT_LEAF_MIN 8        // persistent extend: pending leaf ranges are intersected once this many lanes hold one
 #endif

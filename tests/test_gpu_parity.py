@@ -569,3 +569,17 @@ def test_device_lbvh_build_gives_the_same_hits_as_the_host_sah_tree(rt, orc, dev
     assert np.array_equal(hh["t"], hd["t"]) and np.array_equal(hh["p"], hd["p"]) and np.array_equal(hh["n"], hd["n"])
     assert res["host"][2] == res["device"][2]
     assert np.allclose(res["host"][1], res["device"][1], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["cornell-box", "book-one"])
+def test_warp_specialised_shade_matches_block_scan_shade(rt, device, name):
+    """k_shade_pipe (producer warps + a scanner warp coupled by named barriers, RT_B200_SHADE_PIPE=1) compacts in a different
+    order than k_shade but shades the same rays with the same Philox keys: identical images and ray counts."""
+    a, qa, sa = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "0"}, 96, 54, 8)
+    b, qb, sb = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "1"}, 96, 54, 8)
+    assert sa.rays == sb.rays and sa.paths == sb.paths
+    assert np.allclose(a, b, rtol=1e-5, atol=1e-5) and np.allclose(qa, qb, rtol=1e-5, atol=1e-5)
+    c, _, sc = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "1"}, 96, 54, 2, queue_capacity=1056)
+    d, _, sd = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "0"}, 96, 54, 2, queue_capacity=1056)
+    assert sc.rays == sd.rays and np.allclose(c, d, rtol=1e-5, atol=1e-5)
