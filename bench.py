@@ -247,19 +247,26 @@ def main():
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record(stream)
-    paths = rays = launches = iters = 0
-    ms_stage = np.zeros(4)
+    paths = rays = launches = 0
     for i in range(args.steps):
-        full, st = step(2000 + i, rt.RENDER_STAGE_TIMING)
+        full, st = step(2000 + i)
         paths += st.paths
         rays += st.rays
-        iters += st.iterations
         launches += st.launches + (1 if world > 1 else 0) + 1  # + de-interleave kernel, + the L2-flush memset
-        ms_stage += [st.ms_generate, st.ms_extend, st.ms_shade, st.ms_accumulate]
     ev1.record(stream)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     ms = ev0.elapsed_time(ev1)
+    # ---- per-stage launch durations: the same steps again with CUDA events around the launches of every 8th wavefront iteration.
+    # A stage-timed render runs as ONE wavefront lane, so that a timed launch has the device to itself (the timed region above runs
+    # two interleaved lanes whose kernels share the SMs); these are the durations the rooflines are computed from. ----
+    iters = 0
+    ms_stage = np.zeros(4)
+    for i in range(args.steps):
+        _, st = step(2000 + i, rt.RENDER_STAGE_TIMING)
+        iters += st.iterations
+        ms_stage += [st.ms_generate, st.ms_extend, st.ms_shade, st.ms_accumulate]
+    barrier()
     counts = torch.tensor([ms, float(paths), float(rays), float(launches), float(ms_stage[1]), float(iters)], dtype=torch.float64, device="cuda")
     if world > 1:
         mx = counts.clone()
@@ -327,7 +334,8 @@ def main():
             "config": {"workload": cfg, "scene": scene_name, "width": W, "height": H, "spp": spp, "max_depth": depth, "seed_scene": 1,
                        "sharding": f"rows y % {world} == rank, NCCL all-gather + de-interleave" if world > 1 else "single GPU",
                        "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": info,
-                       "queue_capacity": args.queue_capacity or 1 << 22},
+                       "queue_capacity": args.queue_capacity or 1 << 22,
+                       "wavefront_lanes": int(os.environ.get("RT_B200_LANES", "2"))},
             "grays_per_s": tot_rays / (ms_all * 1e-3) / 1e9, "rays_per_path": tot_rays / tot_paths, "mean_radiance": mean_check,
             "gpu_launches": tot_launches,
             "stage_ms_per_step": {"generate": ms_stage[0] / args.steps, "extend": ms_stage[1] / args.steps, "shade": ms_stage[2] / args.steps,
@@ -338,7 +346,8 @@ def main():
                          "traffic": bytes_per_ray * rays_per_launch if bytes_per_ray else None, "traffic_source": traffic_src,
                          "peak_source": peak_src, "launch_us": dur * 1e6, "rays_per_launch": rays_per_launch,
                          "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY,
-                         "timing": "CUDA events around the kernel's launches of every 8th wavefront iteration inside the timed region",
+                         "timing": "CUDA events around the kernel's launches of every 8th wavefront iteration, in a single-lane repeat of the "
+                                   "timed steps right after the timed region (the timed region itself overlaps two wavefront lanes)",
                          "note": "extend is FP32-issue/latency bound, not HBM bound; see roofline_fp32 and DESIGN.md"},
             "clocks": clocks,
         }

@@ -10,6 +10,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "bvh_build.h"
@@ -73,6 +74,10 @@ struct RtContext {
     DevBuf<uint8_t> scratch;
     WaveCounters* h_status = nullptr;  // pinned
     bool stage_timing = false;
+    std::vector<RtContext*> lanes;  // sub-contexts (own streams, queues, accumulators) of the concurrent wavefronts of one render
+    cudaEvent_t ev_lane_begin = nullptr;
+    DevBuf<float> lane_sum, lane_sumsq;  // the lanes' compact row shards before they are interleaved into the caller's buffer
+    uint32_t n_lanes = 2;
     uint32_t default_capacity = 1u << 22;  // 4 M live rays (570 MB of wavefront state): per-launch fixed costs amortise, +20 % over 1 M (r1c)
 };
 
@@ -294,12 +299,18 @@ int rt_init(int device_id, RtContext** out) {
         const long v = std::atol(cap);
         if (v > 0) ctx->default_capacity = (uint32_t)v;
     }
+    if (const char* ln = std::getenv("RT_B200_LANES")) { const int v = std::atoi(ln); if (v >= 1 && v <= 4) ctx->n_lanes = (uint32_t)v; }
+    RT_CUDA(cudaEventCreateWithFlags(&ctx->ev_lane_begin, cudaEventDisableTiming));
     *out = ctx;
     return RT_OK;
 }
 
 void rt_shutdown(RtContext* ctx) {
     if (!ctx) return;
+    for (RtContext* lane : ctx->lanes) rt_shutdown(lane);
+    ctx->lanes.clear();
+    ctx->lane_sum.release(); ctx->lane_sumsq.release();
+    if (ctx->ev_lane_begin) cudaEventDestroy(ctx->ev_lane_begin);
     cudaSetDevice(ctx->device);
     for (int i = 0; i < 2; ++i) { ctx->qa[i].release(); ctx->qb[i].release(); ctx->qc[i].release(); }
     ctx->done[0].release(); ctx->done[1].release(); ctx->hits.release(); ctx->counters.release(); ctx->fb_sum.release(); ctx->fb_sumsq.release(); ctx->acc.release(); ctx->scratch.release();
@@ -508,12 +519,13 @@ int rt_deinterleave_rows(RtContext* ctx, const float* d_gathered, float* d_full,
     return RT_OK;
 }
 
-static int render_core(RtScene* scene, const RtCamera* cam, const RtRayIn* d_user_rays, const RtRenderParams* prm, float* d_sum, float* d_sumsq,
-                       void* cuda_stream, RtStats* stats);
+static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, const RtRayIn* d_user_rays, const RtRenderParams* prm, float* d_sum,
+                       float* d_sumsq, void* cuda_stream, RtStats* stats);
+static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats);
 
 int rt_render_device(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
     if (!scene || !cam || !prm || !d_sum) return fail(RT_ERR_INVALID, "null argument");
-    return render_core(scene, cam, nullptr, prm, d_sum, d_sumsq, cuda_stream, stats);
+    return render_lanes(scene, cam, prm, d_sum, d_sumsq, cuda_stream, stats);
 }
 
 // Batched `render::color(&ray, world, max_depth)` (src/render.rs:5-29) on caller rays: ray i is "pixel" i of an n x 1 image,
@@ -531,7 +543,7 @@ int rt_color_rays(RtScene* scene, const RtRayIn* rays, uint64_t n, uint32_t spp,
     RtRenderParams prm{};
     prm.width = (uint32_t)n; prm.height = 1; prm.spp = spp; prm.max_depth = max_depth; prm.seed = seed; prm.row_begin = 0; prm.row_stride = 1;
     RtCamera cam{};
-    const int rc = render_core(scene, &cam, reinterpret_cast<const RtRayIn*>(ctx->scratch.p), &prm, ctx->fb_sum.p, out_sumsq ? ctx->fb_sumsq.p : nullptr, nullptr, stats);
+    const int rc = render_core(ctx, scene, &cam, reinterpret_cast<const RtRayIn*>(ctx->scratch.p), &prm, ctx->fb_sum.p, out_sumsq ? ctx->fb_sumsq.p : nullptr, nullptr, stats);
     if (rc != RT_OK) return rc;
     RT_CUDA(cudaMemcpy(out_sum, ctx->fb_sum.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost));
     if (out_sumsq) RT_CUDA(cudaMemcpy(out_sumsq, ctx->fb_sumsq.p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost));
@@ -540,9 +552,87 @@ int rt_color_rays(RtScene* scene, const RtRayIn* rays, uint64_t n, uint32_t spp,
 
 }  // extern "C" (render_core is internal)
 
-static int render_core(RtScene* scene, const RtCamera* cam, const RtRayIn* d_user_rays, const RtRenderParams* prm, float* d_sum, float* d_sumsq,
-                       void* cuda_stream, RtStats* stats) {
+// Several wavefronts per render.  One wavefront leaves the SMs idle at every kernel boundary (the tail of a persistent grid,
+// the launch of the next: ~7-12 % of each launch, ncu cycles_active vs elapsed) and during the drain at the end of the image.
+// rt_render_device therefore splits its rows over `n_lanes` interleaved sub-shards — the same partition as the multi-GPU one — and
+// runs one complete wavefront per lane, each with its own streams, queues and accumulators, driven by its own host thread; the
+// blocks of one lane's kernel start as the other lane's blocks retire.  Measured (scripts/two_lane_experiment.py, r2a):
+// cornell-box 2987 -> 3613 Mpaths/s, book-one 1080p 2930 -> 3423.  Philox keys are functions of the global pixel, so the image
+// does not depend on the number of lanes.  Instrumented renders (stage timing, work counters) run as one lane so that a timed
+// launch has the device to itself.
+static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
     RtContext* ctx = scene->ctx;
+    if (prm->row_stride == 0 || prm->row_begin >= prm->height || prm->width == 0) return render_core(ctx, scene, cam, nullptr, prm, d_sum, d_sumsq, cuda_stream, stats);
+    const uint32_t rows_local = (prm->height - prm->row_begin + prm->row_stride - 1) / prm->row_stride;
+    uint32_t L = ctx->n_lanes;
+    if ((prm->flags & (RT_RENDER_STAGE_TIMING | RT_RENDER_COUNT_WORK)) || ctx->stage_timing) L = 1;
+    if (rows_local < 4u * L || prm->max_depth == 0) L = 1;
+    if ((uint64_t)prm->width * rows_local * prm->spp < (uint64_t)L * (1u << 20)) L = 1;  // too little work to fill two queues
+    if ((uint64_t)prm->row_stride * L > 0xFFFFFFFFull) L = 1;
+    if (L == 1) return render_core(ctx, scene, cam, nullptr, prm, d_sum, d_sumsq, cuda_stream, stats);
+
+    RT_CUDA(cudaSetDevice(ctx->device));
+    while (ctx->lanes.size() < L) {
+        RtContext* lane = nullptr;
+        const int rc = rt_init(ctx->device, &lane);
+        if (rc != RT_OK) return rc;
+        lane->n_lanes = 1;
+        lane->default_capacity = ctx->default_capacity;
+        ctx->lanes.push_back(lane);
+    }
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+    const uint32_t rows_padded = (rows_local + L - 1) / L;
+    const size_t shard = (size_t)rows_padded * prm->width * 3;
+    RT_CUDA(ctx->lane_sum.ensure(shard * L));
+    if (d_sumsq) RT_CUDA(ctx->lane_sumsq.ensure(shard * L));
+    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes, scene->shade_bytes, scene->fr_bytes));  // once, before the lane threads
+    RT_CUDA(cudaEventRecord(ctx->ev0, st));
+    RT_CUDA(cudaEventRecord(ctx->ev_lane_begin, st));
+    std::vector<RtStats> lane_stats(L);
+    std::vector<int> lane_rc(L, RT_OK);
+    std::vector<std::string> lane_err(L);
+    std::vector<std::thread> pool;
+    for (uint32_t l = 0; l < L; ++l) {
+        pool.emplace_back([&, l]() {
+            RtContext* lane = ctx->lanes[l];
+            RtRenderParams lp = *prm;
+            lp.row_begin = prm->row_begin + l * prm->row_stride;
+            lp.row_stride = prm->row_stride * L;
+            if (!lp.queue_capacity) lp.queue_capacity = ctx->default_capacity;
+            cudaSetDevice(ctx->device);
+            cudaError_t e = cudaStreamWaitEvent(lane->stream, ctx->ev_lane_begin, 0);  // after whatever the caller queued before the render
+            if (e != cudaSuccess) { lane_rc[l] = RT_ERR_CUDA; lane_err[l] = cudaGetErrorString(e); return; }
+            lane_rc[l] = render_core(lane, scene, cam, nullptr, &lp, ctx->lane_sum.p + shard * l, d_sumsq ? ctx->lane_sumsq.p + shard * l : nullptr, nullptr,
+                                     &lane_stats[l]);
+            if (lane_rc[l] != RT_OK) lane_err[l] = g_error;
+        });
+    }
+    for (auto& t : pool) t.join();
+    for (uint32_t l = 0; l < L; ++l)
+        if (lane_rc[l] != RT_OK) return fail(lane_rc[l], "%s", lane_err[l].c_str());
+    // render_core returned after its lane's stream drained: the shards are complete; interleave them on the caller's stream
+    launch_deinterleave(ctx->lane_sum.p, d_sum, prm->width, rows_local, L, st);
+    if (d_sumsq) launch_deinterleave(ctx->lane_sumsq.p, d_sumsq, prm->width, rows_local, L, st);
+    RT_CUDA(cudaEventRecord(ctx->ev1, st));
+    RT_CUDA(cudaEventSynchronize(ctx->ev1));
+    RT_CUDA(cudaGetLastError());
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        float ms = 0;
+        RT_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        for (const RtStats& ls : lane_stats) {
+            stats->paths += ls.paths; stats->rays += ls.rays; stats->launches += ls.launches;
+            stats->iterations = std::max(stats->iterations, ls.iterations);
+        }
+        stats->launches += d_sumsq ? 2 : 1;
+        stats->ms_total = ms;
+        stats->bvh_nodes = scene->d.n_nodes; stats->bvh_always = scene->d.n_always;
+    }
+    return RT_OK;
+}
+
+static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, const RtRayIn* d_user_rays, const RtRenderParams* prm, float* d_sum,
+                       float* d_sumsq, void* cuda_stream, RtStats* stats) {
     if (prm->width == 0 || prm->height == 0 || prm->spp == 0) return fail(RT_ERR_INVALID, "width/height/spp must be > 0");
     if (prm->row_stride == 0 || prm->row_begin >= prm->height) return fail(RT_ERR_INVALID, "bad row_begin/row_stride");
     if (prm->max_depth > 255u) return fail(RT_ERR_UNSUPPORTED, "max_depth %u > 255", prm->max_depth);

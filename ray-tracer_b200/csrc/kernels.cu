@@ -16,6 +16,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdlib>
+#include <mutex>
 
 #include "device_scene.h"
 #include "intersect.cuh"
@@ -753,7 +754,10 @@ cudaError_t kernels_init(int device) {
     return cudaSuccess;
 }
 
+static std::mutex g_configure_mutex;  // the wavefront lanes of one render configure from their own host threads
+
 cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes, size_t fr_bytes) {
+    std::lock_guard<std::mutex> lock(g_configure_mutex);
     cudaError_t e = kernels_init(device);
     if (e != cudaSuccess) return e;
     if (fr_bytes && fr_bytes != g_rects_smem) {

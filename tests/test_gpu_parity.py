@@ -583,3 +583,29 @@ def test_warp_specialised_shade_matches_block_scan_shade(rt, device, name):
     c, _, sc = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "1"}, 96, 54, 2, queue_capacity=1056)
     d, _, sd = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "0"}, 96, 54, 2, queue_capacity=1056)
     assert sc.rays == sd.rays and np.allclose(c, d, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_wavefront_lanes_do_not_change_the_image(rt):
+    """rt_render_device runs several interleaved wavefronts (lanes) per render, each on its own streams and host thread
+    (capi.cu render_lanes).  Keys are functions of the global pixel: 1, 2 and 3 lanes give the same image, ray count and sums of
+    squares; ragged row counts and a caller-side row shard on top of the lane split included."""
+    out = {}
+    for lanes in ["1", "2", "3"]:
+        os.environ["RT_B200_LANES"] = lanes
+        try:
+            dev = rt.Device(0)
+        finally:
+            os.environ.pop("RT_B200_LANES", None)
+        scene = rt.Scene.example(dev, "cornell-box", 1)
+        cam = scene.flat.camera(301 / 203)
+        s, q, st = scene.render(cam, 301, 203, 40, 50, seed=3)                                   # 2.4 M paths: enough for 2 lanes
+        t, _, st2 = scene.render(cam, 301, 203, 64, 50, seed=4, row_begin=1, row_stride=2, want_sumsq=False)  # shard of a 2-GPU split
+        out[lanes] = (s, q, int(st.rays), t, int(st2.rays), int(st.launches))
+        scene.close()
+        dev.close()
+    assert out["2"][5] != out["1"][5]  # the lanes were really used
+    for lanes in ["2", "3"]:
+        assert out[lanes][2] == out["1"][2] and out[lanes][4] == out["1"][4]
+        assert np.allclose(out[lanes][0], out["1"][0], rtol=1e-5, atol=1e-5) and np.allclose(out[lanes][1], out["1"][1], rtol=1e-5, atol=1e-5)
+        assert np.allclose(out[lanes][3], out["1"][3], rtol=1e-5, atol=1e-5)
