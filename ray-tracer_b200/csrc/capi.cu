@@ -653,6 +653,7 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
     rc.pixels_local = (uint64_t)rc.width * rc.rows_local;
     rc.paths_total = rc.pixels_local * rc.spp;
     rc.user_rays = d_user_rays;
+    { const char* po = std::getenv("RT_B200_PATH_ORDER"); rc.pixel_major = po ? (po[0] != '0') : 1u; }
 
     for (int i = 0; i < 2; ++i) { RT_CUDA(ctx->qa[i].ensure(cap)); RT_CUDA(ctx->qb[i].ensure(cap)); RT_CUDA(ctx->qc[i].ensure(cap)); }
     RT_CUDA(ctx->hits.ensure(cap));

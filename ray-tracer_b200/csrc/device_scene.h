@@ -107,6 +107,7 @@ struct RenderConst {
     uint32_t seed_lo, seed_hi;
     uint32_t row_begin, row_stride, rows_local;
     uint32_t capacity;
+    uint32_t pixel_major;   // path index = pixel * spp + sample (1) or sample * pixels_local + pixel (0)
     uint64_t paths_total;   // width * rows_local * spp
     uint64_t pixels_local;  // width * rows_local
     const RtRayIn* user_rays;  // rt_color_rays: path `pixel` starts from user_rays[pixel] instead of a camera ray (else null)

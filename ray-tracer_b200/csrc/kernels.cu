@@ -73,17 +73,20 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
     const uint32_t room = rc.capacity - surv;
     const uint32_t n_new = left < (uint64_t)room ? (uint32_t)left : room;
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
-    // path = sample * pixels_local + pixel: one 64-bit division per thread, then (sample, pixel) advance by the grid stride
-    // (the division per path was ~a third of this kernel's instructions)
-    uint32_t sample = 0u, qi = 0u;
+    // Path order.  pixel-major (default): path = pixel * spp + sample, so the 32 lanes of a warp start as 32 samples of ONE pixel —
+    // near-identical camera rays (coherent traversal and material branches) whose finished records stay adjacent in the `done`
+    // queue, where k_accumulate folds them into one atomic per run.  sample-major (RT_B200_PATH_ORDER=0): path = sample * pixels
+    // + pixel.  Either way one 64-bit division per thread, then (major, minor) advance by the grid stride.
+    const uint32_t mod = rc.pixel_major ? rc.spp : (uint32_t)rc.pixels_local;
+    uint32_t major = 0u, minor = 0u;
     if (tid < n_new) {
         const uint64_t path0 = issued + tid;
-        sample = (uint32_t)(path0 / rc.pixels_local);
-        qi = (uint32_t)(path0 - (uint64_t)sample * rc.pixels_local);
+        major = (uint32_t)(path0 / mod);
+        minor = (uint32_t)(path0 - (uint64_t)major * mod);
     }
-    const uint32_t pixels = (uint32_t)rc.pixels_local;
-    const uint32_t stride_s = stride / pixels, stride_q = stride - stride_s * pixels;
+    const uint32_t stride_major = stride / mod, stride_minor = stride - stride_major * mod;
     for (uint32_t i = tid; i < n_new; i += stride) {
+        const uint32_t sample = rc.pixel_major ? minor : major, qi = rc.pixel_major ? major : minor;
         uint32_t x, yl;
         pixel_from_index(qi, rc.width, rc.rows_local, x, yl);
         const uint32_t y = rc.row_begin + yl * rc.row_stride;
@@ -101,9 +104,9 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
         q.a[slot] = make_float4(o.x, o.y, o.z, __uint_as_float(RT_NO_PRIM));
         q.b[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(gp));
         q.c[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float((sample << 8) | 1u));
-        sample += stride_s;
-        qi += stride_q;
-        if (qi >= pixels) { qi -= pixels; ++sample; }
+        major += stride_major;
+        minor += stride_minor;
+        if (minor >= mod) { minor -= mod; ++major; }
     }
     if (tid == 0) {
         const uint32_t total = surv + n_new;
@@ -657,20 +660,42 @@ __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const 
     // f64 accumulators (native 64-bit atomics): an f32 running sum of 1024+ equal sky samples rounds the same way on
     // every add and drifts by 1e-4 relative, which the 3-sigma image test sees on zero-variance pixels.
     const uint32_t n = wc->done[k % RT_RING];
-    const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const float4 r = done[i];
+    const uint32_t stride = gridDim.x * blockDim.x, lane = threadIdx.x & 31u;
+    // Runs of records of one pixel (pixel-major path order keeps the samples of a pixel together) are summed in the warp first — a
+    // segmented shuffle reduction over the run heads — and only the head of a run touches the framebuffer: 6 f64 atomics per run
+    // instead of per path (the L2 atomic units were the limit of this kernel: 164 G atomics/s on book-one 4K).
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {  // warp-uniform trip count
+        const uint32_t i = base + threadIdx.x;
+        const bool valid = i < n;
+        const float4 r = valid ? done[i] : make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0xffffffffu));
         const uint32_t gp = __float_as_uint(r.w);
+        double v[6] = {(double)r.x, (double)r.y, (double)r.z, (double)r.x * (double)r.x, (double)r.y * (double)r.y, (double)r.z * (double)r.z};
+        const uint32_t gp_prev = __shfl_up_sync(0xffffffffu, gp, 1);
+        const bool head = lane == 0u || gp != gp_prev;
+        const uint32_t heads = __ballot_sync(0xffffffffu, head);
+        if (heads != 0xffffffffu) {
+            const uint32_t after = lane == 31u ? 0u : heads >> (lane + 1u);  // bit j: lane + 1 + j starts a new run
+#pragma unroll
+            for (uint32_t delta = 1u; delta < 32u; delta <<= 1) {
+                const bool same_run = lane + delta < 32u && (after & ((1u << delta) - 1u)) == 0u;
+#pragma unroll
+                for (int c = 0; c < 6; ++c) {
+                    const double other = __shfl_down_sync(0xffffffffu, v[c], delta);
+                    if (same_run) v[c] += other;
+                }
+            }
+        }
+        if (!head || !valid) continue;
         const uint32_t y = gp / rc.width, x = gp - y * rc.width;
         const uint32_t yl = (y - rc.row_begin) / rc.row_stride;
         const size_t o = ((size_t)yl * rc.width + x) * 3;
-        atomicAdd(&sum[o + 0], (double)r.x);
-        atomicAdd(&sum[o + 1], (double)r.y);
-        atomicAdd(&sum[o + 2], (double)r.z);
+        atomicAdd(&sum[o + 0], v[0]);
+        atomicAdd(&sum[o + 1], v[1]);
+        atomicAdd(&sum[o + 2], v[2]);
         if (sumsq) {
-            atomicAdd(&sumsq[o + 0], (double)r.x * (double)r.x);
-            atomicAdd(&sumsq[o + 1], (double)r.y * (double)r.y);
-            atomicAdd(&sumsq[o + 2], (double)r.z * (double)r.z);
+            atomicAdd(&sumsq[o + 0], v[3]);
+            atomicAdd(&sumsq[o + 1], v[4]);
+            atomicAdd(&sumsq[o + 2], v[5]);
         }
     }
 }
@@ -743,6 +768,7 @@ static size_t g_extend_smem = ~(size_t)0, g_shade_smem = ~(size_t)0, g_rects_sme
 static int g_rects_blocks_per_sm = 0, g_bvh_blocks_per_sm = 0;
 static size_t g_bvh_smem = 0, g_scene_smem = 0;
 static int g_persistent = -1;
+static int g_gen_blocks = 4, g_acc_blocks = 8;  // blocks per SM of k_generate / k_accumulate (RT_B200_GEN_BLOCKS / RT_B200_ACC_BLOCKS)
 static int g_shade_pipe = -1, g_shadep_blocks_per_sm = 0;
 
 cudaError_t kernels_init(int device) {
@@ -815,6 +841,10 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
        // scene so that tests can compare the two forms in one process
         const char* pe = getenv("RT_B200_PERSISTENT");
         g_persistent = pe ? atoi(pe) : 2;
+        const char* gb = getenv("RT_B200_GEN_BLOCKS");
+        const char* ab = getenv("RT_B200_ACC_BLOCKS");
+        g_gen_blocks = gb && atoi(gb) >= 1 && atoi(gb) <= 16 ? atoi(gb) : 4;
+        g_acc_blocks = ab && atoi(ab) >= 1 && atoi(ab) <= 16 ? atoi(ab) : 8;
     }
     return cudaSuccess;
 }
@@ -822,7 +852,7 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
 int kernels_num_sms() { return g_num_sms; }
 
 void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st) {
-    k_generate<<<g_num_sms * 4, 256, 0, st>>>(rc, q, wc, k);
+    k_generate<<<g_num_sms * g_gen_blocks, 256, 0, st>>>(rc, q, wc, k);
 }
 void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                    bool count_work, cudaStream_t st) {
@@ -846,7 +876,7 @@ void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, c
     else k_shade<<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
 void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
-    k_accumulate<<<g_num_sms * 2, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
+    k_accumulate<<<g_num_sms * g_acc_blocks, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
 }
 void launch_finish(const double* acc, size_t n, float* out, cudaStream_t st) { k_finish<<<g_num_sms * 4, 256, 0, st>>>(acc, n, out); }
 void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st) {

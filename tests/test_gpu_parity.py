@@ -609,3 +609,16 @@ def test_wavefront_lanes_do_not_change_the_image(rt):
         assert out[lanes][2] == out["1"][2] and out[lanes][4] == out["1"][4]
         assert np.allclose(out[lanes][0], out["1"][0], rtol=1e-5, atol=1e-5) and np.allclose(out[lanes][1], out["1"][1], rtol=1e-5, atol=1e-5)
         assert np.allclose(out[lanes][3], out["1"][3], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,w,h,spp,cap", [("cornell-box", 97, 61, 40, 0), ("book-one", 128, 72, 7, 5000), ("book-two", 64, 64, 33, 0)])
+def test_path_order_does_not_change_the_image(rt, device, name, w, h, spp, cap):
+    """k_generate issues paths pixel-major (the samples of a pixel next to each other; k_accumulate then folds runs of one pixel in
+    the warp before touching the framebuffer) or sample-major (RT_B200_PATH_ORDER=0).  Philox keys are (global pixel, sample) either
+    way: same paths, same ray count, same sums and sums of squares — spp not a multiple of 32, and a queue far smaller than a
+    pixel's worth of samples × pixels included."""
+    a, qa, sa = _render_with_env(rt, device, name, {"RT_B200_PATH_ORDER": "0", "RT_B200_LANES": "1"}, w, h, spp, queue_capacity=cap)
+    b, qb, sb = _render_with_env(rt, device, name, {"RT_B200_PATH_ORDER": "1", "RT_B200_LANES": "1"}, w, h, spp, queue_capacity=cap)
+    assert sa.rays == sb.rays and sa.paths == sb.paths == w * h * spp
+    assert np.allclose(a, b, rtol=1e-5, atol=1e-5) and np.allclose(qa, qb, rtol=1e-5, atol=1e-5)
