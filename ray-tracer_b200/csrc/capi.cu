@@ -435,6 +435,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     if (!s) return fail(RT_ERR_OOM, "out of host memory");
     s->ctx = ctx;
     s->bvh_depth = bvh.depth;
+    s->d.bvh_depth = bvh.depth;
     cudaError_t e = cudaSuccess;
     static_assert(sizeof(BvhNode32) == 2 * sizeof(float4), "node layout");
     if (use_lbvh) { s->nodes.p = lbvh.d_nodes; s->nodes.n = (size_t)lbvh.n_nodes * 2; }  // built in place: the scene adopts the device array

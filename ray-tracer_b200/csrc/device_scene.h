@@ -58,6 +58,7 @@ struct DScene {
     const float4* texels;
     uint32_t n_nodes, n_prims, n_always, n_gen, n_mats, n_texs;
     uint32_t root_is_leaf;     // BVH over < 2 primitives: node 0 is a leaf
+    uint32_t bvh_depth;        // depth of the tree (levels below the root)
     uint32_t n_staged_nodes;   // prefix of `nodes` staged in shared memory
     uint32_t has_media;
     uint32_t n_rects;

@@ -257,9 +257,10 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
 __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
 
 // Test device primitive `i`.  Returns t or +inf.  BIG = primitive of the always-tested list.
-template <bool BIG>
+// ALL = every node and primitive head of the scene is staged in shared memory (k_extend<.., true>): no per-access range check.
+template <bool BIG, bool ALL = false>
 __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uint32_t i, const RayCtx& R, uint32_t self_prim, const MediumKey& key) {
-    const bool staged = i < S.n_staged_prims;
+    const bool staged = ALL || i < S.n_staged_prims;
     float4 h;
     if (staged) h = lds128(sm.heads + 16u * i);
     else h = __ldg(&S.prim_head[i]);
@@ -294,13 +295,17 @@ __device__ __forceinline__ void take(const DScene& S, uint32_t i, float t, Close
 // origin lies on a slab of a zero direction component), which errs on the side of "hit" like the
 // reference's `if t0 > tmin` form.  1/d comes from MUFU.RCP, so the far distance is widened by 8 ulp
 // (Ize, robust BVH traversal): the test can only err towards visiting a node.
-__device__ __forceinline__ float slab(const float4 lo, const float4 hi, const RayCtx& R, float tmax) {
+__device__ __forceinline__ bool slab_hit(const float4 lo, const float4 hi, const RayCtx& R, float tmax, float& tn) {
     const float x0 = fmaf(lo.x, R.inv.x, -R.oinv.x), x1 = fmaf(hi.x, R.inv.x, -R.oinv.x);
     const float y0 = fmaf(lo.y, R.inv.y, -R.oinv.y), y1 = fmaf(hi.y, R.inv.y, -R.oinv.y);
     const float z0 = fmaf(lo.z, R.inv.z, -R.oinv.z), z1 = fmaf(hi.z, R.inv.z, -R.oinv.z);
-    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+    tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
     const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax)) * 1.000001f;
-    return tn <= tf ? tn : CUDART_INF_F;
+    return tn <= tf;
+}
+__device__ __forceinline__ float slab(const float4 lo, const float4 hi, const RayCtx& R, float tmax) {
+    float tn;
+    return slab_hit(lo, hi, R, tmax, tn) ? tn : CUDART_INF_F;
 }
 
 __device__ __forceinline__ float4 load_node(const DScene& S, const Staged& sm, uint32_t idx4) {
@@ -308,8 +313,9 @@ __device__ __forceinline__ float4 load_node(const DScene& S, const Staged& sm, u
     return __ldg(&S.nodes[idx4]);
 }
 // The four float4 of a sibling pair (64 contiguous bytes); `pair` is even, so the pair is staged or not as a whole.
+template <bool ALL = false>
 __device__ __forceinline__ void load_pair(const DScene& S, const Staged& sm, uint32_t pair, float4& llo, float4& lhi, float4& rlo, float4& rhi) {
-    if (pair < S.n_staged_nodes) {
+    if (ALL || pair < S.n_staged_nodes) {
         const uint32_t a = sm.nodes + 32u * pair;
         llo = lds128(a); lhi = lds128(a + 16u); rlo = lds128(a + 32u); rhi = lds128(a + 48u);
     } else {
@@ -345,52 +351,82 @@ __device__ __forceinline__ RayCtx make_ray(float3 o, float3 d) {
 // ("while-while" traversal, Aila & Laine): in the if-if form the ~140-instruction leaf loop ran on nearly every warp
 // iteration for ~2 of 32 lanes (r1k profile of the 1 M-sphere scene: 192 warp-instructions per iteration, of which the
 // node step is ~60).
-template <bool COUNT>
-__device__ __forceinline__ uint32_t node_step(const DScene& S, const Staged& sm, const RayCtx& R, const ClosestHit& best, uint32_t pair, int& sp,
-                                              uint32_t* stack_spill, uint32_t& leaf_begin, uint32_t& leaf_end, TraversalWork* work) {
+// What a node step found below `pair`: which children are leaves the ray enters, and their primitive ranges.  The range
+// [begin, end) is only formed when a leaf was found (`leaf_range`), not on every step: the step is ALU-pipe bound and the
+// IADD3 / SEL / ISETP chain of the range was a fifth of its ALU instructions (r2i SASS).
+struct LeafPair {
+    bool left, right;
+    uint32_t lref, lcnt, rref, rcnt;
+    __device__ __forceinline__ bool any() const { return left || right; }
+};
+__device__ __forceinline__ void leaf_range(const LeafPair& lp, uint32_t& begin, uint32_t& end) {
+    begin = 0u;
+    end = 0u;
+    if (lp.left) { begin = lp.lref; end = lp.lref + lp.lcnt; }
+    if (lp.right) { if (end == 0u) begin = lp.rref; end = lp.rref + lp.rcnt; }
+}
+
+// ALL (k_extend<.., true>): tree and primitive heads entirely in shared memory and no deeper than the shared-memory stack —
+// no "staged or global" range checks, no spill path.
+template <bool COUNT, bool ALL = false>
+__device__ __forceinline__ uint32_t node_step_core(const DScene& S, const Staged& sm, const RayCtx& R, const ClosestHit& best, uint32_t pair, int& sp,
+                                                   uint32_t* stack_spill, LeafPair& lp, TraversalWork* work) {
     const uint32_t sstride = 4u * blockDim.x;
     float4 llo, lhi, rlo, rhi;
-    load_pair(S, sm, pair, llo, lhi, rlo, rhi);
-    const float tl = slab(llo, lhi, R, best.t);
-    const float tr = slab(rlo, rhi, R, best.t);
+    load_pair<ALL>(S, sm, pair, llo, lhi, rlo, rhi);
+    // hit flags straight from the slab compare (the entry distances only order the two children): the extend kernels are bound by
+    // the ALU pipe (FMNMX / FSETP / SEL at half the FMA rate, r2i profile: 67 % vs 15 %), a +inf sentinel cost 2 FSEL + 2 FSETP here
+    float tl, tr;
+    const bool lhit = slab_hit(llo, lhi, R, best.t, tl);
+    const bool rhit = slab_hit(rlo, rhi, R, best.t, tr);
     if (COUNT) work->box_tests += 2;
-    const uint32_t lcnt = __float_as_uint(lhi.w), rcnt = __float_as_uint(rhi.w);
-    const uint32_t lref = __float_as_uint(llo.w), rref = __float_as_uint(rlo.w);
-    const bool lhit = tl < CUDART_INF_F, rhit = tr < CUDART_INF_F;
-    uint32_t begin = 0u, end = 0u;
-    if (lhit && lcnt) { begin = lref; end = lref + lcnt; }
-    if (rhit && rcnt) { if (end == 0u) begin = rref; end = rref + rcnt; }
-    leaf_begin = begin;
-    leaf_end = end;
+    lp.lcnt = __float_as_uint(lhi.w); lp.rcnt = __float_as_uint(rhi.w);
+    lp.lref = __float_as_uint(llo.w); lp.rref = __float_as_uint(rlo.w);
+    lp.left = lhit && lp.lcnt;
+    lp.right = rhit && lp.rcnt;
     // interior children: descend into the nearer one, push the farther
-    const bool lin = lhit && !lcnt, rin = rhit && !rcnt;
+    const bool lin = lhit && !lp.lcnt, rin = rhit && !lp.rcnt;
     uint32_t next = RT_NO_PRIM;
     if (lin && rin) {
         const bool swap = tr < tl;
-        const uint32_t pushed = swap ? lref : rref;
-        if (sp < (int)RT_SMEM_STACK) sts32(sm.stack + sp * sstride, pushed);
-        else stack_spill[sp - RT_SMEM_STACK] = pushed;
-        sp += (sp < RT_STACK_DEPTH - 1);
-        next = swap ? rref : lref;
+        const uint32_t pushed = swap ? lp.lref : lp.rref;
+        if (ALL) {
+            sts32(sm.stack + sp * sstride, pushed);
+            ++sp;
+        } else {
+            if (sp < (int)RT_SMEM_STACK) sts32(sm.stack + sp * sstride, pushed);
+            else stack_spill[sp - RT_SMEM_STACK] = pushed;
+            sp += (sp < RT_STACK_DEPTH - 1);
+        }
+        next = swap ? lp.rref : lp.lref;
     } else if (lin) {
-        next = lref;
+        next = lp.lref;
     } else if (rin) {
-        next = rref;
+        next = lp.rref;
     } else if (sp > 0) {
         --sp;
-        next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK];
+        if (ALL) next = lds32(sm.stack + sp * sstride);
+        else next = (sp < (int)RT_SMEM_STACK) ? lds32(sm.stack + sp * sstride) : stack_spill[sp - RT_SMEM_STACK];
     }
     return next;
 }
+template <bool COUNT, bool ALL = false>
+__device__ __forceinline__ uint32_t node_step(const DScene& S, const Staged& sm, const RayCtx& R, const ClosestHit& best, uint32_t pair, int& sp,
+                                              uint32_t* stack_spill, uint32_t& leaf_begin, uint32_t& leaf_end, TraversalWork* work) {
+    LeafPair lp;
+    const uint32_t next = node_step_core<COUNT, ALL>(S, sm, R, best, pair, sp, stack_spill, lp, work);
+    leaf_range(lp, leaf_begin, leaf_end);
+    return next;
+}
 
-template <bool COUNT>
+template <bool COUNT, bool ALL = false>
 __device__ __forceinline__ void leaf_tests(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key, ClosestHit& best,
                                            uint32_t begin, uint32_t end, TraversalWork* work) {
-    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false, ALL>(S, sm, i, R, self_prim, key), best);
     if (COUNT) work->prim_tests += end - begin;
 }
 
-template <bool COUNT = false>
+template <bool COUNT = false, bool ALL = false>
 __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged& sm, float3 o, float3 d, uint32_t self_prim, const MediumKey& key,
                                                   TraversalWork* work = nullptr) {
     ClosestHit best{CUDART_INF_F, RT_NO_PRIM};
@@ -420,7 +456,7 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
         if (COUNT) work->prim_tests += S.n_small;
         return best;
     }
-    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true>(S, sm, i, R, self_prim, key), best);
+    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true, ALL>(S, sm, i, R, self_prim, key), best);
     if (COUNT) work->prim_tests += S.n_always;
     if (S.n_nodes == 0) return best;
 
@@ -440,13 +476,31 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     // than RT_SMEM_STACK, i.e. > 16 M well-balanced primitives) spill to a local array.
     uint32_t stack_spill[RT_STACK_DEPTH - RT_SMEM_STACK];
     int sp = 0;
-    uint32_t pair = __float_as_uint(load_node(S, sm, 0).w);  // left child of the root; right = pair + 1
+    uint32_t pair = __float_as_uint(ALL ? lds128(sm.nodes).w : load_node(S, sm, 0).w);  // left child of the root; right = pair + 1
     // while-while: lanes walk nodes until each has found a leaf range (or finished), then the warp intersects the pending
     // ranges together.  One back-edge per loop, so the warp reconverges at both loop heads.
+    LeafPair lp;
+    if (ALL) {
+        do {
+            bool found = false;
+            while (pair != RT_NO_PRIM) {
+                pair = node_step_core<COUNT, true>(S, sm, R, best, pair, sp, stack_spill, lp, work);
+                if (lp.any()) { found = true; break; }
+            }
+            if (found) {
+                uint32_t leaf_begin, leaf_end;
+                leaf_range(lp, leaf_begin, leaf_end);
+                leaf_tests<COUNT, true>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
+            }
+        } while (pair != RT_NO_PRIM);
+        return best;
+    }
+    // trees that reach into global memory: the range is formed in the step (the loop-carried form of the flags costs this variant
+    // more than the range arithmetic: book-two 542 vs 566 ms of extend per image, r2j)
     uint32_t leaf_begin = 0u, leaf_end = 0u;
     do {
-        while (pair != RT_NO_PRIM && leaf_end == leaf_begin) pair = node_step<COUNT>(S, sm, R, best, pair, sp, stack_spill, leaf_begin, leaf_end, work);
-        leaf_tests<COUNT>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
+        while (pair != RT_NO_PRIM && leaf_end == leaf_begin) pair = node_step<COUNT, false>(S, sm, R, best, pair, sp, stack_spill, leaf_begin, leaf_end, work);
+        leaf_tests<COUNT, false>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
         leaf_begin = leaf_end = 0u;
     } while (pair != RT_NO_PRIM);
     return best;

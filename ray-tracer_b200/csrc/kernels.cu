@@ -138,7 +138,9 @@ __device__ __forceinline__ Staged stage_scene(const DScene& S, float4* smem_base
     return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
 }
 
-template <bool COUNT>
+// ALL: the whole tree and every primitive head are in shared memory (book-one: 836 nodes, 487 heads) — the per-access
+// "staged or global" range checks compile away.
+template <bool COUNT, bool ALL>
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
                                                           uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
     extern __shared__ float4 smem4[];
@@ -155,7 +157,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_EXTEND_MIN_BLOCKS) k_exten
             key.k1 = sb >> 8;
             key.segment = sb & 0xFFu;
         }
-        const ClosestHit h = closest_hit<COUNT>(S, sm, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
+        const ClosestHit h = closest_hit<COUNT, ALL>(S, sm, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
         hits[i] = make_float2(h.t, __uint_as_float(h.prim));
     }
     if (COUNT) {  // instrumented build only (RT_RENDER_COUNT_WORK): one atomic pair per warp
@@ -813,13 +815,15 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
     }
     const size_t staged_bytes = scene_bytes + (size_t)RT_SMEM_STACK * RT_EXTEND_BLOCK * sizeof(uint32_t);
     if (staged_bytes != g_extend_smem) {
-        e = cudaFuncSetAttribute(k_extend<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
+        e = cudaFuncSetAttribute(k_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_extend<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
+        e = cudaFuncSetAttribute(k_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_extend<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_extend_blocks_per_sm, k_extend<false>, RT_EXTEND_BLOCK, staged_bytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_extend_blocks_per_sm, k_extend<false, false>, RT_EXTEND_BLOCK, staged_bytes);
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_trace_blocks_per_sm, k_trace, RT_EXTEND_BLOCK, staged_bytes);
         if (e != cudaSuccess) return e;
@@ -867,8 +871,11 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
         else k_extend_bvh<false><<<grid, RT_EXTEND_BLOCK, g_bvh_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)g_scene_smem);
         return;
     }
-    if (count_work) k_extend<true><<<g_num_sms * g_extend_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else k_extend<false><<<g_num_sms * g_extend_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    const int grid = g_num_sms * g_extend_blocks_per_sm;
+    const bool all_staged = S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && S.bvh_depth + 2u <= RT_SMEM_STACK;
+    if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else if (all_staged) k_extend<false, true><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else k_extend<false, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st) {

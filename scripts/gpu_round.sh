@@ -37,7 +37,7 @@ for s in $STEPS; do
       for sc in "${SCS[@]}"; do
         set -- $sc
         timeout 120 python scripts/profile_target.py $sc > $OUT/plain_$1.log 2>&1 &&
-        timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_extend|k_shade' -s ${NCU_SKIP:-40} -c 4 -o $OUT/full_$1 -f \
+        timeout 900 ncu --set full --clock-control none --import-source on -k regex:"${NCU_REGEX:-k_extend|k_shade}" -s ${NCU_SKIP:-40} -c ${NCU_COUNT:-4} -o $OUT/full_$1 -f \
           python scripts/profile_target.py $sc > $OUT/ncu_full_$1.log 2>&1
         echo "full $1 rc=$?"
       done ;;
