@@ -419,6 +419,62 @@ __device__ __forceinline__ uint32_t node_step(const DScene& S, const Staged& sm,
     return next;
 }
 
+// ---- node step of the all-in-shared-memory variant: "octant-ready" pair records --------------------------------------------------
+// k_extend<.., true> re-lays the tree out while staging it: per sibling pair 7 float4 (112 B)
+//   X+ = (l.lo.x, l.hi.x, r.lo.x, r.hi.x)   X- = (l.hi.x, l.lo.x, r.hi.x, r.lo.x)   Y+ Y- Z+ Z- likewise   M = (lref, lcnt, rref, rcnt)
+// A ray picks X+ or X- once, by the sign of its direction, and then every LDS.128 delivers (near, far) of both children for that
+// axis: the 12 FMNMX per pair that sorted the slab planes are gone.  The step is bound by the ALU pipe (FMNMX / FSETP / ISETP /
+// SEL at half the FMA rate; r2i: alu 67 %, fma 15 %), so this is a third of its ALU work.  Same plane distances, same decisions.
+constexpr uint32_t RT_OCT_PAIR_BYTES = 112u;
+struct OctBase {
+    uint32_t x, y, z, m;  // shared-window byte addresses of the chosen X, Y, Z records and of M, for pair 0
+};
+__device__ __forceinline__ OctBase oct_base(const Staged& sm, const RayCtx& R) {
+    OctBase ob{sm.nodes + (R.inv.x < 0.0f ? 16u : 0u), sm.nodes + 32u + (R.inv.y < 0.0f ? 16u : 0u), sm.nodes + 64u + (R.inv.z < 0.0f ? 16u : 0u),
+               sm.nodes + 96u};
+    // keep the three chosen addresses in registers: ptxas otherwise re-derives them from the signs in every step (3 FSETP + 6 integer
+    // ALU instructions per step, on the pipe the step is bound by)
+    asm volatile("" : "+r"(ob.x), "+r"(ob.y), "+r"(ob.z));
+    return ob;
+}
+template <bool COUNT>
+__device__ __forceinline__ uint32_t node_step_oct(const Staged& sm, const OctBase& ob, const RayCtx& R, const ClosestHit& best, uint32_t pair, int& sp,
+                                                  LeafPair& lp, TraversalWork* work) {
+    const uint32_t sstride = 4u * blockDim.x;
+    const uint32_t a = pair * (RT_OCT_PAIR_BYTES / 2u);  // `pair` is the (even) node index of the left child
+    const float4 X = lds128(a + ob.x), Y = lds128(a + ob.y), Z = lds128(a + ob.z), M = lds128(a + ob.m);
+    const float lnx = fmaf(X.x, R.inv.x, -R.oinv.x), lfx = fmaf(X.y, R.inv.x, -R.oinv.x);
+    const float rnx = fmaf(X.z, R.inv.x, -R.oinv.x), rfx = fmaf(X.w, R.inv.x, -R.oinv.x);
+    const float lny = fmaf(Y.x, R.inv.y, -R.oinv.y), lfy = fmaf(Y.y, R.inv.y, -R.oinv.y);
+    const float rny = fmaf(Y.z, R.inv.y, -R.oinv.y), rfy = fmaf(Y.w, R.inv.y, -R.oinv.y);
+    const float lnz = fmaf(Z.x, R.inv.z, -R.oinv.z), lfz = fmaf(Z.y, R.inv.z, -R.oinv.z);
+    const float rnz = fmaf(Z.z, R.inv.z, -R.oinv.z), rfz = fmaf(Z.w, R.inv.z, -R.oinv.z);
+    const float tl = fmaxf(fmaxf(lnx, lny), fmaxf(lnz, 0.0f)), tr = fmaxf(fmaxf(rnx, rny), fmaxf(rnz, 0.0f));
+    const float fl = fminf(fminf(lfx, lfy), fminf(lfz, best.t)) * 1.000001f, fr = fminf(fminf(rfx, rfy), fminf(rfz, best.t)) * 1.000001f;
+    const bool lhit = tl <= fl, rhit = tr <= fr;
+    if (COUNT) work->box_tests += 2;
+    lp.lref = __float_as_uint(M.x); lp.lcnt = __float_as_uint(M.y);
+    lp.rref = __float_as_uint(M.z); lp.rcnt = __float_as_uint(M.w);
+    lp.left = lhit && lp.lcnt;
+    lp.right = rhit && lp.rcnt;
+    const bool lin = lhit && !lp.lcnt, rin = rhit && !lp.rcnt;
+    uint32_t next = RT_NO_PRIM;
+    if (lin && rin) {
+        const bool swap = tr < tl;
+        sts32(sm.stack + sp * sstride, swap ? lp.lref : lp.rref);
+        ++sp;
+        next = swap ? lp.rref : lp.lref;
+    } else if (lin) {
+        next = lp.lref;
+    } else if (rin) {
+        next = lp.rref;
+    } else if (sp > 0) {
+        --sp;
+        next = lds32(sm.stack + sp * sstride);
+    }
+    return next;
+}
+
 template <bool COUNT, bool ALL = false>
 __device__ __forceinline__ void leaf_tests(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key, ClosestHit& best,
                                            uint32_t begin, uint32_t end, TraversalWork* work) {
@@ -476,15 +532,17 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     // than RT_SMEM_STACK, i.e. > 16 M well-balanced primitives) spill to a local array.
     uint32_t stack_spill[RT_STACK_DEPTH - RT_SMEM_STACK];
     int sp = 0;
-    uint32_t pair = __float_as_uint(ALL ? lds128(sm.nodes).w : load_node(S, sm, 0).w);  // left child of the root; right = pair + 1
+    uint32_t pair = ALL ? 0u : __float_as_uint(load_node(S, sm, 0).w);  // left child of the root; right = pair + 1
     // while-while: lanes walk nodes until each has found a leaf range (or finished), then the warp intersects the pending
     // ranges together.  One back-edge per loop, so the warp reconverges at both loop heads.
     LeafPair lp;
     if (ALL) {
+        const OctBase ob = oct_base(sm, R);
+        pair = lds32(ob.m);  // M.lref of pair 0 = left child of the root
         do {
             bool found = false;
             while (pair != RT_NO_PRIM) {
-                pair = node_step_core<COUNT, true>(S, sm, R, best, pair, sp, stack_spill, lp, work);
+                pair = node_step_oct<COUNT>(sm, ob, R, best, pair, sp, lp, work);
                 if (lp.any()) { found = true; break; }
             }
             if (found) {

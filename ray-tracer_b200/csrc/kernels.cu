@@ -138,13 +138,40 @@ __device__ __forceinline__ Staged stage_scene(const DScene& S, float4* smem_base
     return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
 }
 
+// Staging of the all-in-shared-memory variant: [stack (depth + 2) x blockDim words][pairs, 7 float4 each (intersect.cuh: octant-ready
+// records)][heads n_prims][rects 4*n_rects].
+__device__ __forceinline__ Staged stage_scene_oct(const DScene& S, float4* smem_base) {
+    const uint32_t stack_words = (S.bvh_depth + 2u) * blockDim.x;
+    float4* smem4 = smem_base + stack_words / 4u;
+    const uint32_t n_pairs = (S.n_nodes + 1u) / 2u, n_node4 = 7u * n_pairs, n_head4 = S.n_prims, n_rect4 = 4u * S.n_rects;
+    const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    for (uint32_t j = threadIdx.x; j < n_pairs; j += blockDim.x) {
+        const bool has_right = 2u * j + 1u < S.n_nodes;
+        const float4 ll = S.nodes[4u * j], lh = S.nodes[4u * j + 1u], rl = has_right ? S.nodes[4u * j + 2u] : zero, rh = has_right ? S.nodes[4u * j + 3u] : zero;
+        float4* o = smem4 + 7u * j;
+        o[0] = make_float4(ll.x, lh.x, rl.x, rh.x); o[1] = make_float4(lh.x, ll.x, rh.x, rl.x);
+        o[2] = make_float4(ll.y, lh.y, rl.y, rh.y); o[3] = make_float4(lh.y, ll.y, rh.y, rl.y);
+        o[4] = make_float4(ll.z, lh.z, rl.z, rh.z); o[5] = make_float4(lh.z, ll.z, rh.z, rl.z);
+        o[6] = make_float4(ll.w, lh.w, rl.w, rh.w);
+    }
+    for (uint32_t i = threadIdx.x; i < n_head4; i += blockDim.x) smem4[n_node4 + i] = S.prim_head[i];
+    for (uint32_t i = threadIdx.x; i < n_rect4; i += blockDim.x) smem4[n_node4 + n_head4 + i] = S.rects[i];
+    __syncthreads();
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_base);
+    const uint32_t scene = base + stack_words * 4u;
+    return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
+}
+size_t extend_all_smem_bytes(const DScene& S) {
+    return (size_t)(S.bvh_depth + 2u) * RT_EXTEND_BLOCK * 4u + (size_t)RT_OCT_PAIR_BYTES * ((S.n_nodes + 1u) / 2u) + 16u * (size_t)S.n_prims + 64u * (size_t)S.n_rects;
+}
+
 // ALL: the whole tree and every primitive head are in shared memory (book-one: 836 nodes, 487 heads) — the per-access
 // "staged or global" range checks compile away.
 template <bool COUNT, bool ALL>
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
                                                           uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
     extern __shared__ float4 smem4[];
-    const Staged sm = stage_scene(S, smem4);
+    const Staged sm = ALL ? stage_scene_oct(S, smem4) : stage_scene(S, smem4);
     const uint32_t n = wc->total[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x;
     TraversalWork work{0u, 0u};
@@ -770,6 +797,9 @@ static size_t g_extend_smem = ~(size_t)0, g_shade_smem = ~(size_t)0, g_rects_sme
 static int g_rects_blocks_per_sm = 0, g_bvh_blocks_per_sm = 0;
 static size_t g_bvh_smem = 0, g_scene_smem = 0;
 static int g_persistent = -1;
+static size_t g_all_smem = 0;      // k_extend<false, true>: dynamic shared memory of the scene last launched and its occupancy
+static int g_all_blocks_per_sm = 0;
+constexpr size_t RT_EXTEND_ALL_MAX_SMEM = 100u * 1024u;
 static int g_gen_blocks = 4, g_acc_blocks = 8;  // blocks per SM of k_generate / k_accumulate (RT_B200_GEN_BLOCKS / RT_B200_ACC_BLOCKS)
 static int g_shade_pipe = -1, g_shadep_blocks_per_sm = 0;
 
@@ -817,8 +847,6 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
     if (staged_bytes != g_extend_smem) {
         e = cudaFuncSetAttribute(k_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
-        if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(k_extend<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
@@ -840,6 +868,12 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_bvh_blocks_per_sm, k_extend_bvh<false>, RT_EXTEND_BLOCK, g_bvh_smem);
         if (e != cudaSuccess) return e;
         if (g_bvh_blocks_per_sm < 1) g_bvh_blocks_per_sm = 1;
+    }
+    static bool all_attr_set = false;
+    if (!all_attr_set) {
+        e = cudaFuncSetAttribute(k_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RT_EXTEND_ALL_MAX_SMEM);
+        if (e != cudaSuccess) return e;
+        all_attr_set = true;
     }
     {  // 0: never, 1: always (where a tree exists), 2 (default): trees that do not fit shared memory by far; re-read per
        // scene so that tests can compare the two forms in one process
@@ -872,9 +906,27 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
         return;
     }
     const int grid = g_num_sms * g_extend_blocks_per_sm;
-    const bool all_staged = S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && S.bvh_depth + 2u <= RT_SMEM_STACK;
+    // whole tree + heads in shared memory in the octant-ready layout, as long as that keeps the occupancy of the general kernel
+    bool all_staged = !count_work && S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && !S.root_is_leaf;
+    size_t all_bytes = 0;
+    int all_blocks = 0;
+    if (all_staged) {
+        all_bytes = extend_all_smem_bytes(S);
+        if (all_bytes > RT_EXTEND_ALL_MAX_SMEM) all_staged = false;
+        else {
+            std::lock_guard<std::mutex> lock(g_configure_mutex);
+            if (all_bytes != g_all_smem) {
+                int blocks = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, k_extend<false, true>, RT_EXTEND_BLOCK, all_bytes) != cudaSuccess) blocks = 0;
+                g_all_blocks_per_sm = blocks;
+                g_all_smem = all_bytes;
+            }
+            all_blocks = g_all_blocks_per_sm;
+        }
+        if (all_staged && all_blocks < g_extend_blocks_per_sm) all_staged = false;
+    }
     if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else if (all_staged) k_extend<false, true><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else if (all_staged) k_extend<false, true><<<g_num_sms * all_blocks, RT_EXTEND_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
     else k_extend<false, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
