@@ -162,13 +162,13 @@ __device__ __forceinline__ Staged stage_scene_oct(const DScene& S, float4* smem_
     return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
 }
 size_t extend_all_smem_bytes(const DScene& S) {
-    return (size_t)(S.bvh_depth + 2u) * RT_EXTEND_BLOCK * 4u + (size_t)RT_OCT_PAIR_BYTES * ((S.n_nodes + 1u) / 2u) + 16u * (size_t)S.n_prims + 64u * (size_t)S.n_rects;
+    return (size_t)(S.bvh_depth + 2u) * RT_EXTEND_ALL_BLOCK * 4u + (size_t)RT_OCT_PAIR_BYTES * ((S.n_nodes + 1u) / 2u) + 16u * (size_t)S.n_prims + 64u * (size_t)S.n_rects;
 }
 
 // ALL: the whole tree and every primitive head are in shared memory (book-one: 836 nodes, 487 heads) — the per-access
 // "staged or global" range checks compile away.
 template <bool COUNT, bool ALL>
-__global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
+__global__ void __launch_bounds__(ALL ? RT_EXTEND_ALL_BLOCK : RT_EXTEND_BLOCK, ALL ? RT_EXTEND_ALL_MIN_BLOCKS : RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
                                                           uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
     extern __shared__ float4 smem4[];
     const Staged sm = ALL ? stage_scene_oct(S, smem4) : stage_scene(S, smem4);
@@ -917,16 +917,16 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
             std::lock_guard<std::mutex> lock(g_configure_mutex);
             if (all_bytes != g_all_smem) {
                 int blocks = 0;
-                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, k_extend<false, true>, RT_EXTEND_BLOCK, all_bytes) != cudaSuccess) blocks = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, k_extend<false, true>, RT_EXTEND_ALL_BLOCK, all_bytes) != cudaSuccess) blocks = 0;
                 g_all_blocks_per_sm = blocks;
                 g_all_smem = all_bytes;
             }
             all_blocks = g_all_blocks_per_sm;
         }
-        if (all_staged && all_blocks < g_extend_blocks_per_sm) all_staged = false;
+        if (all_staged && all_blocks * RT_EXTEND_ALL_BLOCK < g_extend_blocks_per_sm * RT_EXTEND_BLOCK) all_staged = false;
     }
     if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else if (all_staged) k_extend<false, true><<<g_num_sms * all_blocks, RT_EXTEND_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else if (all_staged) k_extend<false, true><<<g_num_sms * all_blocks, RT_EXTEND_ALL_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
     else k_extend<false, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,

@@ -6,6 +6,14 @@
 
 #ifndef RT_EXTEND_BLOCK
 #define RT_EXTEND_BLOCK 256
+// k_extend<.., true> (tree in shared memory, octant-ready records): the tree copy dominates a block's shared memory, so larger blocks
+// buy resident warps: 2 x 512 threads at <= 64 registers = 32 warps per SM against 24 for 3 x 256 at 74 registers
+#ifndef RT_EXTEND_ALL_BLOCK
+#define RT_EXTEND_ALL_BLOCK 512
+#endif
+#ifndef RT_EXTEND_ALL_MIN_BLOCKS
+#define RT_EXTEND_ALL_MIN_BLOCKS 2
+#endif
 #endif
 #ifndef RT_SHADE_BLOCK
 #define RT_SHADE_BLOCK 256
