@@ -480,11 +480,11 @@ __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst
 // Each thread shades RT_SHADE_RAYS rays per block round (their queue words are all requested before the first is
 // used: RT_SHADE_RAYS x the memory-level parallelism) and the block allocates output slots for the whole round with
 // ONE barrier pair and ONE pair of global atomics (block_append2 generalised to RT_SHADE_RAYS ballots per warp).
+template <int R>
 __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
                                                const float2* __restrict__ hits, float4* __restrict__ done, WaveCounters* __restrict__ wc, uint32_t k) {
     extern __shared__ float4 shade_smem[];
     __shared__ uint32_t s_cnt[RT_SHADE_BLOCK / 32 + 1][2];
-    constexpr int R = RT_SHADE_RAYS;
     const uint32_t n_staged = min(S0.n_mats, RT_MAX_STAGED_MATS);
     const uint32_t n_sp = S0.n_staged_prims, n_sr = n_sp ? S0.n_rects : 0u;
     float4* smats = shade_smem;
@@ -800,6 +800,7 @@ static int g_persistent = -1;
 static size_t g_all_smem = 0;      // k_extend<false, true>: dynamic shared memory of the scene last launched and its occupancy
 static int g_all_blocks_per_sm = 0;
 constexpr size_t RT_EXTEND_ALL_MAX_SMEM = 100u * 1024u;
+static int g_shade_rays2 = 1;  // RT_B200_SHADE_RAYS2=0: one ray per thread per round everywhere
 static int g_gen_blocks = 4, g_acc_blocks = 8;  // blocks per SM of k_generate / k_accumulate (RT_B200_GEN_BLOCKS / RT_B200_ACC_BLOCKS)
 static int g_shade_pipe = -1, g_shadep_blocks_per_sm = 0;
 
@@ -827,9 +828,11 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
         g_rects_smem = fr_bytes;
     }
     if (shade_bytes != g_shade_smem) {
-        e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
+        e = cudaFuncSetAttribute(k_shade<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shade_blocks_per_sm, k_shade, RT_SHADE_BLOCK, shade_bytes);
+        e = cudaFuncSetAttribute(k_shade<RT_SHADE_RAYS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shade_blocks_per_sm, k_shade<RT_SHADE_RAYS>, RT_SHADE_BLOCK, shade_bytes);
         if (e != cudaSuccess) return e;
         if (g_shade_blocks_per_sm < 1) g_shade_blocks_per_sm = 1;
         e = cudaFuncSetAttribute(k_shade_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
@@ -879,6 +882,8 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
        // scene so that tests can compare the two forms in one process
         const char* pe = getenv("RT_B200_PERSISTENT");
         g_persistent = pe ? atoi(pe) : 2;
+        const char* r2 = getenv("RT_B200_SHADE_RAYS2");
+        g_shade_rays2 = r2 ? atoi(r2) : 1;
         const char* gb = getenv("RT_B200_GEN_BLOCKS");
         const char* ab = getenv("RT_B200_ACC_BLOCKS");
         g_gen_blocks = gb && atoi(gb) >= 1 && atoi(gb) <= 16 ? atoi(gb) : 4;
@@ -932,7 +937,10 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st) {
     if (g_shade_pipe) k_shade_pipe<<<g_num_sms * g_shadep_blocks_per_sm, RT_SHADEP_THREADS, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
-    else k_shade<<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    // two rays per thread per barrier round where shading is light on registers (small all-rectangle scenes: no f64 sphere re-solve);
+    // +5 % there, -7 % on the sphere scenes (r1f), hence per scene
+    else if (S.fr_n && g_shade_rays2) k_shade<2><<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    else k_shade<RT_SHADE_RAYS><<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
 void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
     k_accumulate<<<g_num_sms * g_acc_blocks, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
