@@ -15,11 +15,14 @@
 #define RT_EXTEND_ALL_MIN_BLOCKS 2
 #endif
 #endif
+// k_shade: 8 blocks of 128 threads per SM.  The two barriers per round wait for the slowest of a block's warps (divergent material
+// code) and for the slot-allocation atomics: 4 warps per barrier instead of 8 is +3.5 % (book-one) to +5 % (cornell) on the kernel,
+// 2 warps per barrier (64 x 16) loses to the doubled atomics and staging prologues (profiles/r3c_*, r3d_*).
 #ifndef RT_SHADE_BLOCK
-#define RT_SHADE_BLOCK 256
+#define RT_SHADE_BLOCK 128
 #endif
 #ifndef RT_SHADE_MIN_BLOCKS
-#define RT_SHADE_MIN_BLOCKS 4
+#define RT_SHADE_MIN_BLOCKS 8
 #endif
 #ifndef RT_SHADE_RAYS
 #define RT_SHADE_RAYS 1   // rays shaded per thread per block round (one barrier pair / atomic pair per round)
