@@ -371,6 +371,14 @@ def main():
                                  "achieved": rays_per_s_kernel * instr_per_ray / 1e12, "peak": fp32_peak / 1e12, "unit": "T lane-instr/s",
                                  "frac": rays_per_s_kernel * instr_per_ray / fp32_peak, "sm_mhz": sm_mhz,
                                  "l2_bytes_per_ray": l2_bytes_per_ray}
+        # the whole wavefront against HBM: every stage's algorithmic queue traffic over the timed step (lanes on).  Per ray segment:
+        # extend reads a, b and writes the hit (40 B), shade reads a, b, c and the hit (56 B); a surviving ray is written back (48 B),
+        # a finished path writes and accumulate reads a 16-byte record, generate writes 48 B per path  ->  144 B x rays + 32 B x paths
+        wf_bytes = 144.0 * tot_rays + 32.0 * tot_paths
+        wf_gbs = wf_bytes / (ms_all * 1e-3) / 1e9 / world  # per GPU
+        line["roofline_wavefront_hbm"] = {"bound": "hbm", "achieved": wf_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": wf_gbs / hbm_peak,
+                                          "bytes_per_ray": wf_bytes / max(tot_rays, 1.0), "per": "GPU, all four stage kernels over the timed step",
+                                          "peak_source": peak_src}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
         print(json.dumps(line), flush=True)

@@ -800,6 +800,7 @@ static int g_persistent = -1;
 static size_t g_all_smem = 0;      // k_extend<false, true>: dynamic shared memory of the scene last launched and its occupancy
 static int g_all_blocks_per_sm = 0;
 constexpr size_t RT_EXTEND_ALL_MAX_SMEM = 100u * 1024u;
+static int g_grid_div = 1;     // experiment (RT_B200_GRID_DIV): extend / shade grids of blocks_per_sm / div, so that two lanes' kernels co-reside
 static int g_shade_rays2 = 1;  // RT_B200_SHADE_RAYS2=0: one ray per thread per round everywhere
 static int g_gen_blocks = 4, g_acc_blocks = 8;  // blocks per SM of k_generate / k_accumulate (RT_B200_GEN_BLOCKS / RT_B200_ACC_BLOCKS)
 static int g_shade_pipe = -1, g_shadep_blocks_per_sm = 0;
@@ -882,6 +883,8 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
        // scene so that tests can compare the two forms in one process
         const char* pe = getenv("RT_B200_PERSISTENT");
         g_persistent = pe ? atoi(pe) : 2;
+        const char* gd = getenv("RT_B200_GRID_DIV");
+        g_grid_div = gd && atoi(gd) >= 1 && atoi(gd) <= 4 ? atoi(gd) : 1;
         const char* r2 = getenv("RT_B200_SHADE_RAYS2");
         g_shade_rays2 = r2 ? atoi(r2) : 1;
         const char* gb = getenv("RT_B200_GEN_BLOCKS");
@@ -894,12 +897,14 @@ cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes
 
 int kernels_num_sms() { return g_num_sms; }
 
+static inline int sub_grid(int blocks_per_sm) { return blocks_per_sm / g_grid_div > 0 ? blocks_per_sm / g_grid_div : 1; }
+
 void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st) {
     k_generate<<<g_num_sms * g_gen_blocks, 256, 0, st>>>(rc, q, wc, k);
 }
 void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                    bool count_work, cudaStream_t st) {
-    if (S.fr_n && !count_work) { k_extend_rects<<<g_num_sms * g_rects_blocks_per_sm, RT_EXTEND_BLOCK, g_rects_smem, st>>>(S, q, hits, wc, k); return; }
+    if (S.fr_n && !count_work) { k_extend_rects<<<g_num_sms * sub_grid(g_rects_blocks_per_sm), RT_EXTEND_BLOCK, g_rects_smem, st>>>(S, q, hits, wc, k); return; }
     // The persistent form pays where rays are long and uneven (1 M spheres: 69 box tests per ray, +20 %); on trees that
     // live in shared memory (book-one: 18 box tests) the per-ray set-up at partial warp occupancy costs more than the
     // idle lanes it saves (r1e: 7.1 vs 12.6 Grays/s), so those keep one ray per thread.
@@ -931,7 +936,7 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
         if (all_staged && all_blocks * RT_EXTEND_ALL_BLOCK < g_extend_blocks_per_sm * RT_EXTEND_BLOCK) all_staged = false;
     }
     if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else if (all_staged) k_extend<false, true><<<g_num_sms * all_blocks, RT_EXTEND_ALL_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else if (all_staged) k_extend<false, true><<<g_num_sms * sub_grid(all_blocks), RT_EXTEND_ALL_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
     else k_extend<false, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
@@ -939,8 +944,8 @@ void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, c
     if (g_shade_pipe) k_shade_pipe<<<g_num_sms * g_shadep_blocks_per_sm, RT_SHADEP_THREADS, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
     // two rays per thread per barrier round where shading is light on registers (small all-rectangle scenes: no f64 sphere re-solve);
     // +5 % there, -7 % on the sphere scenes (r1f), hence per scene
-    else if (S.fr_n && g_shade_rays2) k_shade<2><<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
-    else k_shade<RT_SHADE_RAYS><<<g_num_sms * g_shade_blocks_per_sm, RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    else if (S.fr_n && g_shade_rays2) k_shade<2><<<g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    else k_shade<RT_SHADE_RAYS><<<g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
 void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
     k_accumulate<<<g_num_sms * g_acc_blocks, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
