@@ -612,12 +612,13 @@ def test_wavefront_lanes_do_not_change_the_image(rt):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,w,h,spp,cap", [("cornell-box", 97, 61, 40, 0), ("book-one", 128, 72, 7, 5000), ("book-two", 64, 64, 33, 0)])
+@pytest.mark.parametrize("name,w,h,spp,cap", [("cornell-box", 97, 61, 40, 0), ("book-one", 128, 72, 7, 5000), ("book-two", 64, 64, 33, 0),
+                                              ("cornell-box", 3, 2, 70001, 0), ("book-one", 2, 1, 200003, 30000)])
 def test_path_order_does_not_change_the_image(rt, device, name, w, h, spp, cap):
     """k_generate issues paths pixel-major (the samples of a pixel next to each other; k_accumulate then folds runs of one pixel in
     the warp before touching the framebuffer) or sample-major (RT_B200_PATH_ORDER=0).  Philox keys are (global pixel, sample) either
-    way: same paths, same ray count, same sums and sums of squares — spp not a multiple of 32, and a queue far smaller than a
-    pixel's worth of samples × pixels included."""
+    way: same paths, same ray count, same sums and sums of squares — spp not a multiple of 32, a queue far smaller than a
+    pixel's worth of samples × pixels, and more samples per pixel than the generate grid has threads included."""
     a, qa, sa = _render_with_env(rt, device, name, {"RT_B200_PATH_ORDER": "0", "RT_B200_LANES": "1"}, w, h, spp, queue_capacity=cap)
     b, qb, sb = _render_with_env(rt, device, name, {"RT_B200_PATH_ORDER": "1", "RT_B200_LANES": "1"}, w, h, spp, queue_capacity=cap)
     assert sa.rays == sb.rays and sa.paths == sb.paths == w * h * spp
