@@ -10,7 +10,10 @@
  * Conventions: every struct is plain-old-data, little-endian; all entry points return 0 on success
  * and a negative RtStatus on failure (never abort/unwind across the boundary); rt_last_error()
  * returns a thread-local message.  Opaque handles own all device memory.  One RtContext is driven
- * by one host thread at a time.  There is no CPU fallback: without a CUDA device rt_init fails.
+ * by one host thread at a time, and renders of DIFFERENT scenes must not overlap within one process (the
+ * kernels' launch configuration — shared-memory sizes, occupancy — is per process and set by the scene being
+ * rendered); rt_render_device itself runs its wavefront lanes on internal host threads.  There is no CPU
+ * fallback: without a CUDA device rt_init fails.
  */
 #ifndef RT_B200_H
 #define RT_B200_H
