@@ -709,6 +709,7 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
     };
 
     RT_CUDA(cudaEventRecord(ctx->ev0, st));
+    kernels_set_work_hint(0xFFFFFFFFu);
     uint64_t k = 0;
     bool finished = false;
     while (!finished) {
@@ -739,10 +740,12 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
         if (k >= min_iters && ((k - min_iters) % poll == 0)) {
             RT_CUDA(cudaMemcpyAsync(ctx->h_status, wc, sizeof(WaveCounters), cudaMemcpyDeviceToHost, st));
             RT_CUDA(cudaStreamSynchronize(st));
+            if (ctx->h_status->st_issued == rc.paths_total && !count_work) kernels_set_work_hint(ctx->h_status->st_total);  // the queue only shrinks from here
             if (ctx->h_status->st_issued == rc.paths_total && ctx->h_status->st_total == 0) finished = true;
             else if (k > iter_limit) return fail(RT_ERR_CUDA, "wavefront did not terminate after %llu iterations", (unsigned long long)k);
         }
     }
+    kernels_set_work_hint(0xFFFFFFFFu);
     if (overlap) {  // the last two accumulates join the render stream before the accumulators are read
         RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[0], 0));
         if (k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[1], 0));

@@ -899,12 +899,24 @@ int kernels_num_sms() { return g_num_sms; }
 
 static inline int sub_grid(int blocks_per_sm) { return blocks_per_sm / g_grid_div > 0 ? blocks_per_sm / g_grid_div : 1; }
 
+// Tail of a render: once every path has been issued the queue only shrinks, and the host knows an upper bound of what is left from
+// its last status poll.  A full persistent grid (hundreds of blocks, each staging its tables) for a few thousand rays costs ~2 us more
+// per launch than the blocks the rays need; the ~50 iterations of a depth-50 tail are all of that kind.  Per host thread (each
+// wavefront lane launches from its own).
+static thread_local uint32_t t_work_hint = 0xFFFFFFFFu;
+void kernels_set_work_hint(uint32_t rays_upper_bound) { t_work_hint = rays_upper_bound; }
+static inline int fit_grid(int full_grid, int threads) {
+    if (t_work_hint == 0xFFFFFFFFu) return full_grid;
+    const uint64_t need = ((uint64_t)t_work_hint + (uint32_t)threads - 1u) / (uint32_t)threads;
+    return (int)(need < 1u ? 1u : (need < (uint64_t)full_grid ? need : (uint64_t)full_grid));
+}
+
 void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st) {
-    k_generate<<<g_num_sms * g_gen_blocks, 256, 0, st>>>(rc, q, wc, k);
+    k_generate<<<t_work_hint == 0xFFFFFFFFu ? g_num_sms * g_gen_blocks : 1, 256, 0, st>>>(rc, q, wc, k);  // nothing left to issue: thread 0 rolls the counters
 }
 void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                    bool count_work, cudaStream_t st) {
-    if (S.fr_n && !count_work) { k_extend_rects<<<g_num_sms * sub_grid(g_rects_blocks_per_sm), RT_EXTEND_BLOCK, g_rects_smem, st>>>(S, q, hits, wc, k); return; }
+    if (S.fr_n && !count_work) { k_extend_rects<<<fit_grid(g_num_sms * sub_grid(g_rects_blocks_per_sm), RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, g_rects_smem, st>>>(S, q, hits, wc, k); return; }
     // The persistent form pays where rays are long and uneven (1 M spheres: 69 box tests per ray, +20 %); on trees that
     // live in shared memory (book-one: 18 box tests) the per-ray set-up at partial warp occupancy costs more than the
     // idle lanes it saves (r1e: 7.1 vs 12.6 Grays/s), so those keep one ray per thread.
@@ -936,19 +948,19 @@ void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounter
         if (all_staged && all_blocks * RT_EXTEND_ALL_BLOCK < g_extend_blocks_per_sm * RT_EXTEND_BLOCK) all_staged = false;
     }
     if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else if (all_staged) k_extend<false, true><<<g_num_sms * sub_grid(all_blocks), RT_EXTEND_ALL_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else k_extend<false, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else if (all_staged) k_extend<false, true><<<fit_grid(g_num_sms * sub_grid(all_blocks), RT_EXTEND_ALL_BLOCK), RT_EXTEND_ALL_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else k_extend<false, false><<<fit_grid(grid, RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
 void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k, cudaStream_t st) {
     if (g_shade_pipe) k_shade_pipe<<<g_num_sms * g_shadep_blocks_per_sm, RT_SHADEP_THREADS, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
     // two rays per thread per barrier round where shading is light on registers (small all-rectangle scenes: no f64 sphere re-solve);
     // +5 % there, -7 % on the sphere scenes (r1f), hence per scene
-    else if (S.fr_n && g_shade_rays2) k_shade<2><<<g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
-    else k_shade<RT_SHADE_RAYS><<<g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    else if (S.fr_n && g_shade_rays2) k_shade<2><<<fit_grid(g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    else k_shade<RT_SHADE_RAYS><<<fit_grid(g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
 void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
-    k_accumulate<<<g_num_sms * g_acc_blocks, 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
+    k_accumulate<<<fit_grid(g_num_sms * g_acc_blocks, 256), 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
 }
 void launch_finish(const double* acc, size_t n, float* out, cudaStream_t st) { k_finish<<<g_num_sms * 4, 256, 0, st>>>(acc, n, out); }
 void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st) {

@@ -61,6 +61,8 @@ cudaError_t kernels_configure(int device, size_t staged_bytes, size_t shade_byte
 cudaError_t kernels_init(int device);
 int kernels_num_sms();
 
+// upper bound of the rays left in the queue once every path has been issued (0xFFFFFFFF = unknown: full grids); per host thread
+void kernels_set_work_hint(uint32_t rays_upper_bound);
 void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st);
 void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                    bool count_work, cudaStream_t st);
