@@ -10,9 +10,12 @@
  * Conventions: every struct is plain-old-data, little-endian; all entry points return 0 on success
  * and a negative RtStatus on failure (never abort/unwind across the boundary); rt_last_error()
  * returns a thread-local message.  Opaque handles own all device memory.  One RtContext is driven
- * by one host thread at a time, and renders of DIFFERENT scenes must not overlap within one process (the
- * kernels' launch configuration — shared-memory sizes, occupancy — is per process and set by the scene being
- * rendered); rt_render_device itself runs its wavefront lanes on internal host threads.  There is no CPU
+ * by one host thread at a time; different contexts — on the same or on different devices of one process —
+ * may render concurrently from different host threads (launch configuration is kept per device and per
+ * scene, nothing per process); rt_render_device itself runs its wavefront lanes on internal host threads.
+ * Tuning options are fixed when the context / scene is created (RtContextOptions, RtSceneOptions; the
+ * RT_B200_* environment variables are read ONCE, by rt_init / rt_init_multi, as their defaults) or passed per
+ * render in RtRenderParams.flags — no entry point reads the environment afterwards.  There is no CPU
  * fallback: without a CUDA device rt_init fails.
  */
 #ifndef RT_B200_H
@@ -25,7 +28,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1u
+#define RT_ABI_VERSION 2u
 
 typedef enum RtStatus {
     RT_OK = 0,
@@ -33,7 +36,8 @@ typedef enum RtStatus {
     RT_ERR_UNSUPPORTED = -2, /* scene node the flattener / device cannot express */
     RT_ERR_CUDA = -3,        /* CUDA runtime error (message in rt_last_error) */
     RT_ERR_NO_DEVICE = -4,   /* no usable sm_100 device */
-    RT_ERR_OOM = -5
+    RT_ERR_OOM = -5,
+    RT_ERR_NCCL = -6         /* NCCL could not be loaded or a collective failed (multi-GPU entry points only) */
 } RtStatus;
 
 /* ---- flat scene description (what src/gpu.rs / host/flatten.hpp produce) ------------------------ */
@@ -41,7 +45,11 @@ typedef enum RtStatus {
 typedef enum RtPrimKind {
     RT_PRIM_SPHERE = 0,        /* Sphere::hit, src/geometry.rs:42-74; param[0] = radius */
     RT_PRIM_RECT = 1,          /* Rectangle::hit, src/geometry.rs:152-181; param[0..1] = width, height */
-    RT_PRIM_MEDIUM_SPHERE = 2  /* ConstantMedium<Sphere>::hit, src/volume.rs:46-100; param[0] = boundary radius, param[1] = density */
+    RT_PRIM_MEDIUM_SPHERE = 2, /* ConstantMedium<Sphere>::hit, src/volume.rs:46-100; param[0] = boundary radius, param[1] = density */
+    RT_PRIM_MEDIUM = 3         /* ConstantMedium<T: Hit>::hit over any flattened boundary (src/volume.rs:40-43 accepts every Hit; the book's
+                                  smoke boxes are Cube boundaries): param[1] = density, aux = index of the first boundary primitive in
+                                  RtSceneDesc.boundary_prims, param[2] = their count (integral, < 2^24).  Both probes of volume.rs:47,54
+                                  are closest-hit queries over those primitives, in their list (= DFS) order with strict <. */
 } RtPrimKind;
 
 /* One leaf primitive with every enclosing Sprite / TransformedGeometry transform pre-composed
@@ -52,7 +60,7 @@ typedef struct RtPrim {
     int32_t material;   /* index into materials, -1 = none (hit returns black, src/render.rs:18-20) */
     uint32_t order;     /* rank in the reference's left-first DFS; closest-hit ties go to the smaller order
                            (src/optimize.rs:475,484) and it is the id rt_trace reports */
-    uint32_t flags;     /* reserved, 0 */
+    uint32_t aux;       /* RT_PRIM_MEDIUM: first boundary primitive; else reserved, 0 */
     float param[4];
     float local_from_world[12];
     float world_from_local[12];
@@ -97,6 +105,10 @@ typedef struct RtSceneDesc {
     const RtTexture* textures;
     const float* texels; /* RGBA f32, n_texels * 4 floats */
     uint64_t n_texels;
+    const RtPrim* boundary_prims; /* boundary surfaces of RT_PRIM_MEDIUM primitives (spheres / rectangles, transforms pre-composed to
+                                     WORLD space like every RtPrim; material and order unused); never hit by rays on their own */
+    uint32_t n_boundary_prims;
+    uint32_t reserved;
 } RtSceneDesc;
 
 /* Camera constants exactly as PerspectiveCamera::new derives them in f64 (src/camera.rs:34-45),
@@ -119,7 +131,11 @@ typedef struct RtRenderParams {
 typedef enum RtRenderFlags {
     RT_RENDER_STAGE_TIMING = 1u, /* bracket the stage launches of every 8th wavefront iteration with CUDA events (no extra syncs)
                                     and fill RtStats.ms_<stage> with sum over the timed iterations * iterations / timed_iterations */
-    RT_RENDER_COUNT_WORK = 2u    /* run the instrumented extend kernel and fill RtStats.box_tests / prim_tests (slower; not for timing) */
+    RT_RENDER_COUNT_WORK = 2u,   /* run the instrumented extend kernel and fill RtStats.box_tests / prim_tests (slower; not for timing) */
+    RT_RENDER_SAMPLE_MAJOR = 4u, /* issue paths sample-major (path = sample * pixels + pixel) instead of pixel-major; same image */
+    RT_RENDER_EXTEND_PER_THREAD = 8u,   /* extend: one ray per thread whatever the tree size (default: by tree size) */
+    RT_RENDER_EXTEND_PERSISTENT = 16u,  /* extend: persistent lane-refilling warps wherever a tree exists */
+    RT_RENDER_TIME_EVERY_ITERATION = 32u /* with RT_RENDER_STAGE_TIMING: bracket every iteration instead of every 8th */
 } RtRenderFlags;
 
 typedef struct RtStats {
@@ -152,17 +168,58 @@ typedef struct RtHitOut {
 
 typedef struct RtContext RtContext;
 typedef struct RtScene RtScene;
+typedef struct RtMulti RtMulti;           /* several devices of one process (rt_init_multi) */
+typedef struct RtMultiScene RtMultiScene; /* a scene replicated on every device of an RtMulti */
+
+/* Options of a context; all-zero = defaults.  rt_init(device, ..) == rt_init_ex(device, NULL, ..): defaults from the RT_B200_*
+ * environment variables (RT_B200_LANES, RT_B200_QUEUE_CAPACITY, RT_B200_OVERLAP_ACCUMULATE, RT_B200_STAGE_TIMING,
+ * RT_B200_GEN_BLOCKS, RT_B200_ACC_BLOCKS, RT_B200_SHADE_RAYS2 and the RtSceneOptions ones), read once. */
+typedef enum RtContextFlags {
+    RT_CTX_NO_ACCUMULATE_OVERLAP = 1u, /* run accumulate on the render stream instead of a side stream */
+    RT_CTX_STAGE_TIMING = 2u,          /* every render behaves as if RT_RENDER_STAGE_TIMING were set */
+    RT_CTX_SHADE_ONE_RAY = 4u          /* k_shade shades one ray per thread per round on every scene */
+} RtContextFlags;
+typedef struct RtContextOptions {
+    uint32_t lanes;          /* concurrent wavefronts per render, 1..4; 0 = default (2) */
+    uint32_t queue_capacity; /* live-ray queue size per lane; 0 = default (4 Mi rays) */
+    uint32_t flags;          /* RtContextFlags */
+    uint32_t gen_blocks, acc_blocks; /* blocks per SM of k_generate / k_accumulate; 0 = default (4 / 8) */
+    uint32_t reserved[3];
+} RtContextOptions; /* 32 B */
+
+typedef enum RtBvhBuilder { RT_BVH_AUTO = 0, RT_BVH_HOST_SAH = 1, RT_BVH_DEVICE_LBVH = 2 } RtBvhBuilder;
+typedef enum RtSceneFlags {
+    RT_SCENE_NO_FRAME_RECTS = 1u,  /* small all-rectangle scenes keep the general rectangle records (no frame-rect list) */
+    RT_SCENE_NO_STAGED_PRIMS = 2u, /* primitive heads stay in global memory */
+    RT_SCENE_NO_SMALL_LIST = 4u    /* scenes of <= 32 primitives get a tree like any other */
+} RtSceneFlags;
+/* Options of a scene build; all-zero = defaults (a context's defaults come from RT_B200_BVH_BUILDER=host|device,
+ * RT_B200_BVH_MAX_LEAF, RT_B200_BVH_TREELET, RT_B200_BVH_THREADS, RT_B200_STAGED_NODES, RT_B200_RECT_FRAMES=0, RT_B200_STAGE_PRIMS=0,
+ * RT_B200_SMALL_SCENE=0 at rt_init). */
+typedef struct RtSceneOptions {
+    uint32_t bvh_builder;   /* RtBvhBuilder: AUTO = device LBVH from 65 536 primitives, host binned SAH below */
+    uint32_t bvh_max_leaf;  /* primitives per leaf, 1..16; 0 = default (4 host, 1 device) */
+    uint32_t bvh_treelet_nodes; /* 0 = default (64) */
+    uint32_t staged_nodes;  /* BVH nodes staged in shared memory by extend, + 1 (so 0 = default: whole tree up to 2048 nodes, else 256) */
+    uint32_t flags;         /* RtSceneFlags */
+    uint32_t bvh_threads;   /* host builder threads; 0 = one per core (the tree does not depend on it) */
+    uint32_t reserved[2];
+} RtSceneOptions; /* 32 B */
 
 /* ---- entry points ------------------------------------------------------------------------------ */
 
-/* Bind a context to one CUDA device (one process per GPU; multi-GPU = one context per rank with
- * row_begin/row_stride sharding and one framebuffer gather by the caller). */
+/* Bind a context to one CUDA device.  Multi-GPU: either one context per process / rank with row_begin / row_stride
+ * sharding and the gather done by the caller (ray-tracer_b200/dist.py over torch.distributed), or rt_init_multi below. */
 int rt_init(int device_id, RtContext** out);
+int rt_init_ex(int device_id, const RtContextOptions* options /* NULL: from the environment */, RtContext** out);
 void rt_shutdown(RtContext* ctx);
+/* The defaults rt_init would use right now (environment read at the time of this call).  Either pointer may be NULL. */
+void rt_options_from_env(RtContextOptions* ctx_options, RtSceneOptions* scene_options);
 
-/* Copies the description, rebuilds a device BVH (binned SAH) over the flattened primitives and
- * uploads everything.  The caller keeps ownership of the input arrays. */
+/* Copies the description, rebuilds a device BVH (binned SAH on the host, or LBVH on the device for large scenes) over the
+ * flattened primitives and uploads everything.  The caller keeps ownership of the input arrays. */
 int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out);
+int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOptions* options /* NULL: the context's defaults */, RtScene** out);
 void rt_scene_destroy(RtScene* scene);
 
 /* Replaces the `for y / for x / for _ in 0..spp { color(camera.ray(u,v), world, depth) }` nest of the
@@ -188,6 +245,12 @@ int rt_color_rays(RtScene* scene, const RtRayIn* rays, uint64_t n, uint32_t spp,
 /* Closest-hit query on caller-supplied rays (batched equivalent of `world.hit(&ray)`,
  * src/optimize.rs:469-498); medium free-flight draws are keyed by (ray index, prim order, seed). */
 int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtHitOut* out);
+/* The same query for rays that START ON a primitive — scattered rays (src/render.rs:12-14) whose origin is the previous hit point.
+ * The reference relies on f64 and `t > 1e-6` (src/geometry.rs:57-66,159) to reject the hit at the ray's own origin; in f32 the
+ * origin carries up to ~6e-5 of position error (r = 1000 ground sphere), so the wavefront carries the originating primitive with
+ * the ray instead (DESIGN.md "f32 policy").  self_order[i] = RtPrim.order of the primitive ray i starts on, 0xFFFFFFFF = none
+ * (e.g. a ray scattered inside a ConstantMedium); self_order == NULL is rt_trace. */
+int rt_trace_from(RtScene* scene, const RtRayIn* rays, const uint32_t* self_order, uint64_t n, uint64_t seed, RtHitOut* out);
 
 /* mean -> sqrt -> *255 -> min(255) -> truncation, rows top to bottom (examples/book-one.rs:90-100).
  * sum_rgb: host [height][width][3] sums over spp, y up. */
@@ -201,6 +264,25 @@ int rt_resolve_u8(RtContext* ctx, const float* sum_rgb, uint32_t width, uint32_t
  * Enqueued on `cuda_stream` (0 = the context's stream, which is then drained before returning). */
 int rt_deinterleave_rows(RtContext* ctx, const float* d_gathered, float* d_full, uint32_t width, uint32_t height, uint32_t n_shards,
                          void* cuda_stream);
+
+/* ---- several GPUs of one process (SURVEY §8(b) `rt_init(n_devices, device_ids)`, §8(e)) -----------------------------------------
+ * One host thread + stream set per device, scene replicated, device i renders rows y % n == i — the reference's own thread
+ * partition (examples/book-one.rs:54-66) — and the row shards travel to device 0 with ONE NCCL collective (grouped ncclSend /
+ * ncclRecv over NVLink, communicators from ncclCommInitAll), where a kernel de-interleaves them; the main thread's `buffer[y][x] =
+ * pixel` reassembly of book-one.rs:83-88.  libnccl.so.2 is loaded with dlopen on the first rt_init_multi with n > 1 (whichever NCCL
+ * the process already holds is used; single-GPU use of the library needs no NCCL).  Philox keys are functions of the global
+ * pixel: the image does not depend on n. */
+int rt_init_multi(int n_devices, const int* device_ids, const RtContextOptions* options /* NULL: from the environment */, RtMulti** out);
+void rt_shutdown_multi(RtMulti* multi);
+int rt_multi_device_count(const RtMulti* multi);
+RtContext* rt_multi_context(RtMulti* multi, int index); /* context of the index-th device (owned by `multi`) */
+int rt_multi_scene_create(RtMulti* multi, const RtSceneDesc* desc, const RtSceneOptions* options, RtMultiScene** out);
+void rt_multi_scene_destroy(RtMultiScene* scene);
+/* rt_render over all devices: params->row_begin / row_stride must be 0 / 1; out_sum_rgb / out_sumsq_rgb are HOST [height][width][3].
+ * stats: paths / rays / launches summed over devices, iterations = max, ms_total = device 0's clock from the start of the render to
+ * the end of the de-interleave. */
+int rt_render_multi(RtMultiScene* scene, const RtCamera* cam, const RtRenderParams* params, float* out_sum_rgb, float* out_sumsq_rgb,
+                    RtStats* stats);
 
 /* Introspection used by tests / the roofline accounting. */
 int rt_scene_bvh_info(const RtScene* scene, uint32_t* n_nodes, uint32_t* n_always, uint32_t* max_depth);

@@ -29,6 +29,10 @@ struct OracleApi {
     using ImageTexture = orc::ImageTexture;
     static void setBakeSize(ImageTexture&, uint32_t, uint32_t) {}  // the oracle evaluates the closure itself
     using CheckerTexture = orc::CheckerTexture;
+    using Texture = orc::Texture;
+    using SolidColor = orc::SolidColor;
+    using HitList = orc::HitList;
+    using TransformedGeometry = orc::TransformedGeometry;
 };
 
 }  // namespace
@@ -152,8 +156,13 @@ OrcScene* orc_scene_create(const char* name, uint64_t seed) {
     auto scene = std::make_unique<OrcScene>();
     orc::BuildRng build(seed ^ 0xA11CE5EEDull);
     orc::tls_build_rng() = &build;
-    const bool ok = rtscenes::Scenes<OracleApi>::byName(name, seed, &scene->list, &scene->cam);
-    if (ok) scene->world = orc::BoundingVolumeHierarchyNode::make(scene->list);  // book-one.rs:32
+    bool rootIsList = false;
+    const bool ok = rtscenes::Scenes<OracleApi>::byName(name, seed, &scene->list, &scene->cam, &rootIsList);
+    if (ok && rootIsList) {  // the world is the Vec itself (geometry.rs:76-116)
+        auto list = std::make_shared<orc::HitList>();
+        list->items = scene->list;
+        scene->world = list;
+    } else if (ok) scene->world = orc::BoundingVolumeHierarchyNode::make(scene->list);  // book-one.rs:32
     orc::tls_build_rng() = nullptr;
     if (!ok || !scene->world) return nullptr;
     enumerate(scene->world.get(), orc::Mat4::identity(), nullptr, false, scene->prims);

@@ -15,13 +15,17 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")  # override: tuning variants only
 
-RENDER_STAGE_TIMING, RENDER_COUNT_WORK = 1, 2
-RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM = 0, -1, -2, -3, -4, -5
-PRIM_SPHERE, PRIM_RECT, PRIM_MEDIUM_SPHERE = 0, 1, 2
+RENDER_STAGE_TIMING, RENDER_COUNT_WORK, RENDER_SAMPLE_MAJOR, RENDER_EXTEND_PER_THREAD, RENDER_EXTEND_PERSISTENT, RENDER_TIME_EVERY_ITERATION = 1, 2, 4, 8, 16, 32
+CTX_NO_ACCUMULATE_OVERLAP, CTX_STAGE_TIMING, CTX_SHADE_ONE_RAY = 1, 2, 4
+BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
+SCENE_NO_FRAME_RECTS, SCENE_NO_STAGED_PRIMS, SCENE_NO_SMALL_LIST = 1, 2, 4
+RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM, RT_ERR_NCCL = 0, -1, -2, -3, -4, -5, -6
+PRIM_SPHERE, PRIM_RECT, PRIM_MEDIUM_SPHERE, PRIM_MEDIUM = 0, 1, 2, 3
+NO_PRIM = 0xFFFFFFFF
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT, MAT_ISOTROPIC = 0, 1, 2, 3, 4
 TEX_SOLID, TEX_CHECKER, TEX_IMAGE = 0, 1, 2
 
-PRIM_DTYPE = np.dtype([("kind", "<u4"), ("material", "<i4"), ("order", "<u4"), ("flags", "<u4"), ("param", "<f4", 4),
+PRIM_DTYPE = np.dtype([("kind", "<u4"), ("material", "<i4"), ("order", "<u4"), ("aux", "<u4"), ("param", "<f4", 4),
                        ("local_from_world", "<f4", 12), ("world_from_local", "<f4", 12)])
 MATERIAL_DTYPE = np.dtype([("kind", "<u4"), ("texture", "<i4"), ("fuzz", "<f4"), ("ior", "<f4")])
 TEXTURE_DTYPE = np.dtype([("kind", "<u4"), ("a", "<i4"), ("b", "<i4"), ("width", "<u4"), ("height", "<u4"), ("reserved", "<u4"),
@@ -34,7 +38,18 @@ assert RAY_DTYPE.itemsize == 24 and HIT_DTYPE.itemsize == 48
 
 class RtSceneDesc(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("n_prims", C.c_uint32), ("n_materials", C.c_uint32), ("n_textures", C.c_uint32),
-                ("prims", C.c_void_p), ("materials", C.c_void_p), ("textures", C.c_void_p), ("texels", C.c_void_p), ("n_texels", C.c_uint64)]
+                ("prims", C.c_void_p), ("materials", C.c_void_p), ("textures", C.c_void_p), ("texels", C.c_void_p), ("n_texels", C.c_uint64),
+                ("boundary_prims", C.c_void_p), ("n_boundary_prims", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class RtContextOptions(C.Structure):
+    _fields_ = [("lanes", C.c_uint32), ("queue_capacity", C.c_uint32), ("flags", C.c_uint32), ("gen_blocks", C.c_uint32), ("acc_blocks", C.c_uint32),
+                ("reserved", C.c_uint32 * 3)]
+
+
+class RtSceneOptions(C.Structure):
+    _fields_ = [("bvh_builder", C.c_uint32), ("bvh_max_leaf", C.c_uint32), ("bvh_treelet_nodes", C.c_uint32), ("staged_nodes", C.c_uint32),
+                ("flags", C.c_uint32), ("bvh_threads", C.c_uint32), ("reserved", C.c_uint32 * 2)]
 
 
 class RtCamera(C.Structure):
@@ -60,7 +75,9 @@ class RthCameraArgs(C.Structure):
 
 
 # every symbol include/rt_b200.h and include/rt_b200_host.h declare
-ABI_SYMBOLS = ["rt_init", "rt_shutdown", "rt_scene_create", "rt_scene_destroy", "rt_render", "rt_render_device", "rt_trace", "rt_color_rays", "rt_resolve_u8",
+ABI_SYMBOLS = ["rt_init", "rt_init_ex", "rt_options_from_env", "rt_shutdown", "rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_render", "rt_render_device",
+               "rt_trace", "rt_trace_from", "rt_color_rays", "rt_resolve_u8", "rt_init_multi", "rt_shutdown_multi", "rt_multi_device_count", "rt_multi_context",
+               "rt_multi_scene_create", "rt_multi_scene_destroy", "rt_render_multi",
                "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
                "rth_flat_desc", "rth_scene_upload", "rth_camera", "rth_encode_image", "rth_decode_image", "rth_set_earth_image"]
 
@@ -78,6 +95,21 @@ def _load():
     L = C.CDLL(LIB_PATH)
     vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
     L.rt_init.argtypes = [C.c_int, C.POINTER(vp)]
+    L.rt_init_ex.argtypes = [C.c_int, C.POINTER(RtContextOptions), C.POINTER(vp)]
+    L.rt_options_from_env.argtypes = [C.POINTER(RtContextOptions), C.POINTER(RtSceneOptions)]
+    L.rt_options_from_env.restype = None
+    L.rt_scene_create_ex.argtypes = [vp, C.POINTER(RtSceneDesc), C.POINTER(RtSceneOptions), C.POINTER(vp)]
+    L.rt_trace_from.argtypes = [vp, vp, vp, u64, u64, vp]
+    L.rt_init_multi.argtypes = [C.c_int, C.POINTER(C.c_int), C.POINTER(RtContextOptions), C.POINTER(vp)]
+    L.rt_shutdown_multi.argtypes = [vp]
+    L.rt_shutdown_multi.restype = None
+    L.rt_multi_device_count.argtypes = [vp]
+    L.rt_multi_context.argtypes = [vp, C.c_int]
+    L.rt_multi_context.restype = vp
+    L.rt_multi_scene_create.argtypes = [vp, C.POINTER(RtSceneDesc), C.POINTER(RtSceneOptions), C.POINTER(vp)]
+    L.rt_multi_scene_destroy.argtypes = [vp]
+    L.rt_multi_scene_destroy.restype = None
+    L.rt_render_multi.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
     L.rt_shutdown.argtypes = [vp]
     L.rt_shutdown.restype = None
     L.rt_scene_create.argtypes = [vp, C.POINTER(RtSceneDesc), C.POINTER(vp)]
@@ -119,17 +151,42 @@ def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-class Device:
-    """RtContext bound to one CUDA device (one per process / rank)."""
+def context_options(**kw):
+    """RtContextOptions from the environment defaults (rt_options_from_env), overridden by keyword: lanes, queue_capacity, flags, gen_blocks, acc_blocks."""
+    o = RtContextOptions()
+    lib.rt_options_from_env(C.byref(o), None)
+    for k, v in kw.items():
+        setattr(o, k, v)
+    return o
 
-    def __init__(self, device_id=0):
-        self._h = C.c_void_p()
-        _check(lib.rt_init(int(device_id), C.byref(self._h)))
+
+def scene_options(**kw):
+    """RtSceneOptions from the environment defaults, overridden by keyword: bvh_builder, bvh_max_leaf, bvh_treelet_nodes, staged_nodes (+1), flags."""
+    o = RtSceneOptions()
+    lib.rt_options_from_env(None, C.byref(o))
+    for k, v in kw.items():
+        setattr(o, k, v)
+    return o
+
+
+class Device:
+    """RtContext bound to one CUDA device.  `options`: keyword overrides of RtContextOptions (None: rt_init, environment defaults)."""
+
+    def __init__(self, device_id=0, options=None, _handle=None):
+        self._owned = _handle is None
+        self._h = C.c_void_p(_handle) if _handle is not None else C.c_void_p()
+        if _handle is None:
+            if options is None:
+                _check(lib.rt_init(int(device_id), C.byref(self._h)))
+            else:
+                o = context_options(**options)
+                _check(lib.rt_init_ex(int(device_id), C.byref(o), C.byref(self._h)))
         self.device_id = device_id
 
     def close(self):
         if getattr(self, "_h", None):
-            lib.rt_shutdown(self._h)
+            if self._owned:
+                lib.rt_shutdown(self._h)
             self._h = None
 
     def __del__(self):
@@ -250,29 +307,39 @@ class FlatScene:
 class Scene:
     """A device-resident scene (RtScene): flattened tables + the rebuilt device BVH."""
 
-    def __init__(self, device, flat=None, desc=None, keepalive=None):
+    def __init__(self, device, flat=None, desc=None, keepalive=None, options=None):
+        """`options`: keyword overrides of RtSceneOptions (None: the context's defaults)."""
         self.device = device
         self.flat = flat
         self._keep = keepalive
         self._h = C.c_void_p()
         if flat is not None:
-            _check(lib.rth_scene_upload(device._h, flat._h, C.byref(self._h)))
-        else:
+            desc = flat.desc()
+        if options is None:
             _check(lib.rt_scene_create(device._h, C.byref(desc), C.byref(self._h)))
+        else:
+            o = scene_options(**options)
+            _check(lib.rt_scene_create_ex(device._h, C.byref(desc), C.byref(o), C.byref(self._h)))
 
     @classmethod
-    def example(cls, device, name, seed=1):
-        return cls(device, flat=FlatScene(name, seed))
+    def example(cls, device, name, seed=1, options=None):
+        return cls(device, flat=FlatScene(name, seed), options=options)
 
-    @classmethod
-    def from_tables(cls, device, prims, materials, textures, texels=None):
+    @staticmethod
+    def tables_desc(prims, materials, textures, texels=None, boundary_prims=None):
         prims = np.ascontiguousarray(prims, dtype=PRIM_DTYPE)
         materials = np.ascontiguousarray(materials, dtype=MATERIAL_DTYPE)
         textures = np.ascontiguousarray(textures, dtype=TEXTURE_DTYPE)
         texels = np.ascontiguousarray(texels if texels is not None else np.zeros((0, 4)), dtype=np.float32)
+        bnd = np.ascontiguousarray(boundary_prims if boundary_prims is not None else np.zeros(0, dtype=PRIM_DTYPE), dtype=PRIM_DTYPE)
         d = RtSceneDesc(lib.rt_abi_version(), len(prims), len(materials), len(textures), prims.ctypes.data, materials.ctypes.data,
-                        textures.ctypes.data, texels.ctypes.data, texels.size // 4)
-        return cls(device, desc=d, keepalive=(prims, materials, textures, texels))
+                        textures.ctypes.data, texels.ctypes.data, texels.size // 4, bnd.ctypes.data, len(bnd), 0)
+        return d, (prims, materials, textures, texels, bnd)
+
+    @classmethod
+    def from_tables(cls, device, prims, materials, textures, texels=None, boundary_prims=None, options=None):
+        d, keep = cls.tables_desc(prims, materials, textures, texels, boundary_prims)
+        return cls(device, desc=d, keepalive=keep, options=options)
 
     def close(self):
         if getattr(self, "_h", None):
@@ -311,11 +378,17 @@ class Scene:
                                     C.c_void_p(stream) if stream else None, C.byref(st)))
         return st
 
-    def trace(self, rays, seed=1):
-        """rt_trace: rays [n,6] (origin, direction) f32 -> structured array HIT_DTYPE."""
+    def trace(self, rays, seed=1, self_order=None):
+        """rt_trace / rt_trace_from: rays [n,6] (origin, direction) f32 -> structured array HIT_DTYPE.  self_order [n] u32: DFS rank of
+        the primitive each ray starts on (NO_PRIM: none)."""
         r = np.ascontiguousarray(np.asarray(rays, dtype=np.float32).reshape(-1, 6))
         out = np.zeros(len(r), dtype=HIT_DTYPE)
-        _check(lib.rt_trace(self._h, _ptr(r), len(r), int(seed), _ptr(out)))
+        if self_order is None:
+            _check(lib.rt_trace(self._h, _ptr(r), len(r), int(seed), _ptr(out)))
+        else:
+            so = np.ascontiguousarray(np.asarray(self_order, dtype=np.uint32))
+            assert len(so) == len(r)
+            _check(lib.rt_trace_from(self._h, _ptr(r), _ptr(so), len(r), int(seed), _ptr(out)))
         return out
 
     def color_rays(self, rays, spp, max_depth, seed=1, want_sumsq=False):
@@ -325,4 +398,54 @@ class Scene:
         q = np.zeros((len(r), 3), dtype=np.float32) if want_sumsq else None
         st = RtStats()
         _check(lib.rt_color_rays(self._h, _ptr(r), len(r), int(spp), int(max_depth), int(seed), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
+        return s, q, st
+
+
+class MultiDevice:
+    """RtMulti: several GPUs driven by ONE process through the C ABI (rt_init_multi / rt_render_multi: one host thread per device,
+    rows y % n == device, one NCCL gather to device 0)."""
+
+    def __init__(self, device_ids, options=None):
+        ids = (C.c_int * len(device_ids))(*device_ids)
+        self._h = C.c_void_p()
+        o = context_options(**options) if options is not None else None
+        _check(lib.rt_init_multi(len(device_ids), ids, C.byref(o) if o is not None else None, C.byref(self._h)))
+        self.device_ids = list(device_ids)
+
+    def context(self, index):
+        return Device(self.device_ids[index], _handle=lib.rt_multi_context(self._h, index))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.rt_shutdown_multi(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+
+class MultiScene:
+    def __init__(self, multi, flat=None, desc=None, keepalive=None, options=None):
+        self.multi, self.flat, self._keep = multi, flat, keepalive
+        self._h = C.c_void_p()
+        if flat is not None:
+            desc = flat.desc()
+        o = scene_options(**options) if options is not None else None
+        _check(lib.rt_multi_scene_create(multi._h, C.byref(desc), C.byref(o) if o is not None else None, C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.rt_multi_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+    def render(self, cam, width, height, spp, max_depth, seed=1, queue_capacity=0, want_sumsq=True, flags=0, out=None):
+        """rt_render_multi with host buffers: (sum[H,W,3], sumsq or None, RtStats)."""
+        prm = RtRenderParams(width, height, spp, max_depth, seed, 0, 1, queue_capacity, flags)
+        s = out if out is not None else np.zeros((height, width, 3), dtype=np.float32)
+        q = np.zeros((height, width, 3), dtype=np.float32) if want_sumsq else None
+        st = RtStats()
+        _check(lib.rt_render_multi(self._h, C.byref(cam), C.byref(prm), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
         return s, q, st

@@ -196,7 +196,7 @@ BvhResult build_bvh(const std::vector<Box3>& boxes, const BvhOptions& opt) {
     b.tmp.reserve(2 * (size_t)m);
     unsigned hw = std::thread::hardware_concurrency();
     unsigned n_threads = std::max(1u, std::min(hw ? hw : 1u, 32u));
-    if (const char* e = std::getenv("RT_B200_BVH_THREADS")) { const int v = std::atoi(e); if (v >= 1) n_threads = (unsigned)std::min(v, 64); }
+    if (opt.threads >= 1) n_threads = std::min(opt.threads, 64u);
     b.defer_below = (n_threads > 1 && m >= 65536u) ? m / (8u * n_threads) : 0u;
     const int32_t root = b.build(b.tmp, b.depth_seen, 0, m, 0, b.defer_below > 0);
     if (!b.tasks.empty()) {

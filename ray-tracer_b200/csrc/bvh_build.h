@@ -39,6 +39,7 @@ struct BvhOptions {
     uint32_t max_depth = 56;
     uint32_t top_nodes = 256;      // breadth-first prefix (what extend stages in shared memory for large trees)
     uint32_t treelet_nodes = 64;   // below the prefix: nodes per contiguously stored treelet (2 KB)
+    uint32_t threads = 0;          // worker threads of the build (0 = one per host core, at most 32); the tree does not depend on it
 };
 
 BvhResult build_bvh(const std::vector<Box3>& boxes, const BvhOptions& opt = BvhOptions());

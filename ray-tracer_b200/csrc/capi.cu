@@ -1,6 +1,8 @@
 // C ABI of the backend (include/rt_b200.h): context / scene lifetime, the wavefront render loop,
 // trace and resolve.  No CPU fallback: every entry point needs a CUDA device.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>  // types and prototypes only: the library is loaded with dlopen (rt_init_multi)
 
 #include <algorithm>
 #include <cmath>
@@ -8,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <thread>
@@ -74,6 +77,9 @@ struct RtContext {
     DevBuf<uint8_t> scratch;
     WaveCounters* h_status = nullptr;  // pinned
     bool stage_timing = false;
+    LaunchOptions lopt;              // kernel-level tuning, fixed at rt_init_ex
+    RtSceneOptions scene_defaults{}; // what rt_scene_create (no explicit options) uses
+    int num_sms = 0;
     std::vector<RtContext*> lanes;  // sub-contexts (own streams, queues, accumulators) of the concurrent wavefronts of one render
     cudaEvent_t ev_lane_begin = nullptr;
     DevBuf<float> lane_sum, lane_sumsq;  // the lanes' compact row shards before they are interleaved into the caller's buffer
@@ -86,20 +92,31 @@ struct RtScene {
     DScene d{};
     DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm, fr_blob;
     DevBuf<uint2> prim_meta;
-    DevBuf<RtPrim> gen;
+    DevBuf<uint32_t> order_to_prim;
+    DevBuf<RtPrim> gen, bnd;
     DevBuf<DMaterial> mats;
     DevBuf<RtTexture> texs;
     uint32_t bvh_depth = 0;
     size_t staged_bytes = 0;
     size_t fr_bytes = 0;     // k_extend_rects' staged frame-rect table (0: the scene has none)
     size_t shade_bytes = 0;  // k_shade's staged tables: materials, and for small scenes heads / meta / rect normals
+    SceneLaunch launch;      // shared-memory sizes / occupancy of this scene's kernels on ctx->device
 };
 
 namespace {
 
 // World-space box of a flattened primitive: the 8 corners of the local box pushed through the forward
 // matrix (what Bound for Sprite does, src/optimize.rs:128-185), padded for f32 traversal.
-Box3 primBox(const RtPrim& p) {
+Box3 primBox(const RtSceneDesc* desc, const RtPrim& p) {
+    if (p.kind == RT_PRIM_MEDIUM) {  // Bound for ConstantMedium = its boundary's box (optimize.rs:508-516)
+        Box3 b{{INFINITY, INFINITY, INFINITY}, {-INFINITY, -INFINITY, -INFINITY}};
+        const uint32_t first = p.aux, count = (uint32_t)p.param[2];
+        for (uint32_t i = first; i < first + count; ++i) {
+            const Box3 c = primBox(desc, desc->boundary_prims[i]);
+            for (int a = 0; a < 3; ++a) { b.lo[a] = std::min(b.lo[a], c.lo[a]); b.hi[a] = std::max(b.hi[a], c.hi[a]); }
+        }
+        return b;
+    }
     double lx, ly, lz;
     if (p.kind == RT_PRIM_RECT) { lx = 0.5 * std::fabs((double)p.param[0]); ly = 0.5 * std::fabs((double)p.param[1]); lz = 1e-6; }  // optimize.rs:115-126
     else { lx = ly = lz = std::fabs((double)p.param[0]); }                                                                            // optimize.rs:104-113
@@ -137,11 +154,23 @@ int validateDesc(const RtSceneDesc* d) {
     if (d->n_materials && !d->materials) return fail(RT_ERR_INVALID, "materials is null");
     if (d->n_textures && !d->textures) return fail(RT_ERR_INVALID, "textures is null");
     if (d->n_texels && !d->texels) return fail(RT_ERR_INVALID, "texels is null");
+    if (d->n_boundary_prims && !d->boundary_prims) return fail(RT_ERR_INVALID, "boundary_prims is null");
+    for (uint32_t i = 0; i < d->n_boundary_prims; ++i) {
+        const RtPrim& p = d->boundary_prims[i];
+        if (p.kind != RT_PRIM_SPHERE && p.kind != RT_PRIM_RECT) return fail(RT_ERR_UNSUPPORTED, "boundary prim %u: kind %u (only spheres and rectangles bound a medium)", i, p.kind);
+        for (int k = 0; k < 12; ++k)
+            if (!std::isfinite(p.local_from_world[k]) || !std::isfinite(p.world_from_local[k])) return fail(RT_ERR_INVALID, "boundary prim %u: non-finite transform", i);
+    }
     for (uint32_t i = 0; i < d->n_prims; ++i) {
         const RtPrim& p = d->prims[i];
-        if (p.kind > RT_PRIM_MEDIUM_SPHERE) return fail(RT_ERR_UNSUPPORTED, "prim %u: unknown kind %u", i, p.kind);
+        if (p.kind > RT_PRIM_MEDIUM) return fail(RT_ERR_UNSUPPORTED, "prim %u: unknown kind %u", i, p.kind);
         if (p.material >= (int32_t)d->n_materials) return fail(RT_ERR_INVALID, "prim %u: material %d out of range", i, p.material);
-        if (p.kind == RT_PRIM_MEDIUM_SPHERE && !(p.param[1] > 0.0f)) return fail(RT_ERR_INVALID, "prim %u: medium density must be > 0", i);
+        if ((p.kind == RT_PRIM_MEDIUM_SPHERE || p.kind == RT_PRIM_MEDIUM) && !(p.param[1] > 0.0f)) return fail(RT_ERR_INVALID, "prim %u: medium density must be > 0", i);
+        if (p.kind == RT_PRIM_MEDIUM) {
+            const float cnt = p.param[2];
+            if (!(cnt >= 1.0f) || cnt >= 16777216.0f || cnt != std::floor(cnt) || (uint64_t)p.aux + (uint64_t)cnt > d->n_boundary_prims)
+                return fail(RT_ERR_INVALID, "prim %u: medium boundary range [%u, +%g) out of bounds", i, p.aux, (double)cnt);
+        }
         for (int k = 0; k < 12; ++k)
             if (!std::isfinite(p.local_from_world[k]) || !std::isfinite(p.world_from_local[k])) return fail(RT_ERR_INVALID, "prim %u: non-finite transform", i);
     }
@@ -269,9 +298,40 @@ extern "C" {
 const char* rt_last_error(void) { return g_error.c_str(); }
 uint32_t rt_abi_version(void) { return RT_ABI_VERSION; }
 
-int rt_init(int device_id, RtContext** out) {
-    if (!out) return fail(RT_ERR_INVALID, "out is null");
-    *out = nullptr;
+static int envInt(const char* name, int lo, int hi, int dflt) {
+    const char* v = std::getenv(name);
+    if (!v || !*v) return dflt;
+    const long x = std::atol(v);
+    return (x < lo || x > hi) ? dflt : (int)x;
+}
+
+// The ONLY place the library reads its environment (rt_init / rt_init_multi call it when no options are passed).
+void rt_options_from_env(RtContextOptions* co, RtSceneOptions* so) {
+    if (co) {
+        std::memset(co, 0, sizeof(*co));
+        co->lanes = (uint32_t)envInt("RT_B200_LANES", 1, 4, 0);
+        co->queue_capacity = (uint32_t)envInt("RT_B200_QUEUE_CAPACITY", 1, 1 << 26, 0);
+        if (envInt("RT_B200_OVERLAP_ACCUMULATE", 0, 1, 1) == 0) co->flags |= RT_CTX_NO_ACCUMULATE_OVERLAP;
+        if (envInt("RT_B200_STAGE_TIMING", 0, 1, 0) == 1) co->flags |= RT_CTX_STAGE_TIMING;
+        if (envInt("RT_B200_SHADE_RAYS2", 0, 1, 1) == 0) co->flags |= RT_CTX_SHADE_ONE_RAY;
+        co->gen_blocks = (uint32_t)envInt("RT_B200_GEN_BLOCKS", 1, 16, 0);
+        co->acc_blocks = (uint32_t)envInt("RT_B200_ACC_BLOCKS", 1, 16, 0);
+    }
+    if (so) {
+        std::memset(so, 0, sizeof(*so));
+        if (const char* bb = std::getenv("RT_B200_BVH_BUILDER")) so->bvh_builder = bb[0] == 'd' ? RT_BVH_DEVICE_LBVH : (bb[0] == 'h' ? RT_BVH_HOST_SAH : RT_BVH_AUTO);
+        so->bvh_max_leaf = (uint32_t)envInt("RT_B200_BVH_MAX_LEAF", 1, 16, 0);
+        so->bvh_treelet_nodes = (uint32_t)envInt("RT_B200_BVH_TREELET", 2, 1 << 20, 0);
+        so->bvh_threads = (uint32_t)envInt("RT_B200_BVH_THREADS", 1, 64, 0);
+        const int sn = envInt("RT_B200_STAGED_NODES", 0, 1 << 20, -1);
+        so->staged_nodes = sn < 0 ? 0u : (uint32_t)sn + 1u;
+        if (envInt("RT_B200_RECT_FRAMES", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_FRAME_RECTS;
+        if (envInt("RT_B200_STAGE_PRIMS", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_STAGED_PRIMS;
+        if (envInt("RT_B200_SMALL_SCENE", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_SMALL_LIST;
+    }
+}
+
+static int context_create(int device_id, const RtContextOptions& co, const RtSceneOptions& so, RtContext** out) {
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0) return fail(RT_ERR_NO_DEVICE, "no CUDA device (%s); this backend has no CPU fallback", cudaGetErrorString(e));
@@ -283,35 +343,53 @@ int rt_init(int device_id, RtContext** out) {
     RtContext* ctx = new (std::nothrow) RtContext();
     if (!ctx) return fail(RT_ERR_OOM, "out of host memory");
     ctx->device = device_id;
-    RT_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    RT_CUDA(cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking));
-    RT_CUDA(cudaEventCreate(&ctx->ev0));
-    RT_CUDA(cudaEventCreate(&ctx->ev1));
+    ctx->n_lanes = co.lanes >= 1 && co.lanes <= 4 ? co.lanes : 2u;
+    if (co.queue_capacity) ctx->default_capacity = co.queue_capacity;
+    ctx->overlap_accumulate = !(co.flags & RT_CTX_NO_ACCUMULATE_OVERLAP);
+    ctx->stage_timing = (co.flags & RT_CTX_STAGE_TIMING) != 0;
+    ctx->lopt.shade_rays2 = (co.flags & RT_CTX_SHADE_ONE_RAY) ? 0 : 1;
+    if (co.gen_blocks >= 1 && co.gen_blocks <= 16) ctx->lopt.gen_blocks = (int)co.gen_blocks;
+    if (co.acc_blocks >= 1 && co.acc_blocks <= 16) ctx->lopt.acc_blocks = (int)co.acc_blocks;
+    ctx->scene_defaults = so;
+    // every failure below releases what was created so far (rt_shutdown tolerates a half-built context)
+    auto bail = [&](cudaError_t err, const char* what) {
+        rt_shutdown(ctx);
+        return fail(RT_ERR_CUDA, "%s failed: %s", what, cudaGetErrorString(err));
+    };
+    if ((e = kernels_num_sms(device_id, &ctx->num_sms)) != cudaSuccess) return bail(e, "cudaDeviceGetAttribute");
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaEventCreate(&ctx->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
     for (int i = 0; i < 2; ++i) {
-        RT_CUDA(cudaEventCreateWithFlags(&ctx->ev_shaded[i], cudaEventDisableTiming));
-        RT_CUDA(cudaEventCreateWithFlags(&ctx->ev_accumulated[i], cudaEventDisableTiming));
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_shaded[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_accumulated[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     }
-    if (const char* ov = std::getenv("RT_B200_OVERLAP_ACCUMULATE")) ctx->overlap_accumulate = ov[0] != '0';
-    RT_CUDA(cudaMallocHost(&ctx->h_status, sizeof(WaveCounters)));
-    const char* st = std::getenv("RT_B200_STAGE_TIMING");
-    ctx->stage_timing = st && st[0] == '1';
-    if (const char* cap = std::getenv("RT_B200_QUEUE_CAPACITY")) {
-        const long v = std::atol(cap);
-        if (v > 0) ctx->default_capacity = (uint32_t)v;
-    }
-    if (const char* ln = std::getenv("RT_B200_LANES")) { const int v = std::atoi(ln); if (v >= 1 && v <= 4) ctx->n_lanes = (uint32_t)v; }
-    RT_CUDA(cudaEventCreateWithFlags(&ctx->ev_lane_begin, cudaEventDisableTiming));
+    if ((e = cudaMallocHost(&ctx->h_status, sizeof(WaveCounters))) != cudaSuccess) return bail(e, "cudaMallocHost");
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_lane_begin, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     *out = ctx;
     return RT_OK;
 }
 
+int rt_init_ex(int device_id, const RtContextOptions* options, RtContext** out) {
+    if (!out) return fail(RT_ERR_INVALID, "out is null");
+    *out = nullptr;
+    RtContextOptions co;
+    RtSceneOptions so;
+    rt_options_from_env(&co, &so);  // scene defaults always come from the environment as it is NOW; never re-read later
+    if (options) co = *options;
+    return context_create(device_id, co, so, out);
+}
+
+int rt_init(int device_id, RtContext** out) { return rt_init_ex(device_id, nullptr, out); }
+
 void rt_shutdown(RtContext* ctx) {
     if (!ctx) return;
+    cudaSetDevice(ctx->device);
     for (RtContext* lane : ctx->lanes) rt_shutdown(lane);
     ctx->lanes.clear();
     ctx->lane_sum.release(); ctx->lane_sumsq.release();
     if (ctx->ev_lane_begin) cudaEventDestroy(ctx->ev_lane_begin);
-    cudaSetDevice(ctx->device);
     for (int i = 0; i < 2; ++i) { ctx->qa[i].release(); ctx->qb[i].release(); ctx->qc[i].release(); }
     ctx->done[0].release(); ctx->done[1].release(); ctx->hits.release(); ctx->counters.release(); ctx->fb_sum.release(); ctx->fb_sumsq.release(); ctx->acc.release(); ctx->scratch.release();
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
@@ -324,23 +402,25 @@ void rt_shutdown(RtContext* ctx) {
     delete ctx;
 }
 
-int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
+int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) { return rt_scene_create_ex(ctx, desc, nullptr, out); }
+
+int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOptions* options, RtScene** out) {
     if (!ctx || !out) return fail(RT_ERR_INVALID, "ctx/out is null");
     *out = nullptr;
     if (int rc = validateDesc(desc)) return rc;
     RT_CUDA(cudaSetDevice(ctx->device));
+    const RtSceneOptions so = options ? *options : ctx->scene_defaults;
 
     const uint32_t n = desc->n_prims;
     std::vector<Box3> boxes(n);
-    for (uint32_t i = 0; i < n; ++i) boxes[i] = primBox(desc->prims[i]);
+    for (uint32_t i = 0; i < n; ++i) boxes[i] = primBox(desc, desc->prims[i]);
     BvhOptions opt;
-    if (const char* ml = std::getenv("RT_B200_BVH_MAX_LEAF")) { const int v = std::atoi(ml); if (v >= 1 && v <= 16) opt.max_leaf = (uint32_t)v; }
+    if (so.bvh_max_leaf >= 1 && so.bvh_max_leaf <= 16) opt.max_leaf = so.bvh_max_leaf;
     opt.max_always = RT_MAX_ALWAYS;
-    if (const char* tn = std::getenv("RT_B200_BVH_TREELET")) { const int v = std::atoi(tn); if (v >= 2) opt.treelet_nodes = (uint32_t)v; }
+    if (so.bvh_treelet_nodes >= 2) opt.treelet_nodes = so.bvh_treelet_nodes;
     opt.top_nodes = RT_TOP_STAGED_NODES;
-    uint32_t small_limit = RT_SMALL_SCENE;
-    if (const char* sl = std::getenv("RT_B200_SMALL_SCENE")) small_limit = (uint32_t)std::max(0, std::min(std::atoi(sl), (int)RT_SMALL_SCENE));
-    const bool small = n <= small_limit;
+    opt.threads = so.bvh_threads;
+    const bool small = n <= RT_SMALL_SCENE && !(so.flags & RT_SCENE_NO_SMALL_LIST);
     BvhResult bvh;
     LbvhResult lbvh;
     bool use_lbvh = false;
@@ -353,12 +433,11 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
         // Large scenes build their tree on the GPU (lbvh.cu: LBVH, one primitive per leaf; the node array never leaves HBM): on
         // 1 M spheres rt_scene_create takes 152 ms instead of 373 ms (16 host threads) and the tree renders within 2.4 % of the
         // SAH one (r1v).  Smaller scenes keep the host SAH build, whose trees are 10-20 % faster to traverse (book-two).
-        // RT_B200_BVH_BUILDER=host|device overrides the size rule.
-        const char* bb = std::getenv("RT_B200_BVH_BUILDER");
-        const bool want_device = bb ? bb[0] == 'd' : n >= RT_DEVICE_BUILD_MIN_PRIMS;
-        if (want_device && !std::getenv("RT_B200_BVH_MAX_LEAF")) opt.max_leaf = 1;
+        const bool want_device = so.bvh_builder == RT_BVH_DEVICE_LBVH || (so.bvh_builder == RT_BVH_AUTO && n >= RT_DEVICE_BUILD_MIN_PRIMS);
+        BvhOptions dopt = opt;
+        if (!so.bvh_max_leaf) dopt.max_leaf = 1;
         std::vector<uint32_t> always;
-        if (want_device) always = select_always(boxes, opt);
+        if (want_device) always = select_always(boxes, dopt);
         if (want_device && n - always.size() >= 1024) {
             std::vector<uint8_t> pulled(n, 0);
             for (uint32_t id : always) pulled[id] = 1;
@@ -366,19 +445,28 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
             std::vector<Box3> rest;
             rest_ids.reserve(n); rest.reserve(n);
             for (uint32_t i = 0; i < n; ++i) if (!pulled[i]) { rest_ids.push_back(i); rest.push_back(boxes[i]); }
-            const cudaError_t le = build_lbvh_device(rest, (uint32_t)always.size(), opt.max_leaf, ctx->stream, lbvh);
-            if (le != cudaSuccess) return fail(RT_ERR_CUDA, "device BVH build failed: %s", cudaGetErrorString(le));
-            use_lbvh = true;
-            bvh.order = always;
-            for (uint32_t k : lbvh.order) bvh.order.push_back(rest_ids[k]);
-            bvh.n_always = (uint32_t)always.size();
-            bvh.depth = lbvh.depth;
-            bvh.root_is_leaf = false;
-        } else {
-            bvh = build_bvh(boxes, opt);
+            const cudaError_t le = build_lbvh_device(rest, (uint32_t)always.size(), dopt.max_leaf, ctx->stream, lbvh);
+            if (le != cudaSuccess) { if (lbvh.d_nodes) cudaFree(lbvh.d_nodes); return fail(RT_ERR_CUDA, "device BVH build failed: %s", cudaGetErrorString(le)); }
+            if (lbvh.depth + 2 > (uint32_t)RT_STACK_DEPTH) {
+                // many coincident centroids can make the radix tree deeper than the traversal stack: the host builder caps its depth
+                cudaFree(lbvh.d_nodes);
+                lbvh.d_nodes = nullptr;
+            } else {
+                use_lbvh = true;
+                bvh.order = always;
+                for (uint32_t k : lbvh.order) bvh.order.push_back(rest_ids[k]);
+                bvh.n_always = (uint32_t)always.size();
+                bvh.depth = lbvh.depth;
+                bvh.root_is_leaf = false;
+            }
         }
+        if (!use_lbvh) bvh = build_bvh(boxes, opt);
     }
-    if (use_lbvh && bvh.depth + 2 > (uint32_t)RT_STACK_DEPTH) { cudaFree(lbvh.d_nodes); return fail(RT_ERR_UNSUPPORTED, "device BVH depth %u exceeds the traversal stack", bvh.depth); }
+    // the scene adopts the device array of the LBVH below; until then every early return must free it
+    struct LbvhGuard {
+        LbvhResult& r; bool armed;
+        ~LbvhGuard() { if (armed && r.d_nodes) cudaFree(r.d_nodes); }
+    } lbvh_guard{lbvh, use_lbvh};
     if (bvh.depth + 2 > (uint32_t)RT_STACK_DEPTH) return fail(RT_ERR_UNSUPPORTED, "BVH depth %u exceeds the traversal stack", bvh.depth);
 
     // primitives in leaf order
@@ -414,7 +502,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
             std::memcpy(&fz, &ri, 4);
             head[i] = make_float4(fx, fy, fz, -1.0f);
             gen.push_back(p);
-            has_media |= (p.kind == RT_PRIM_MEDIUM_SPHERE);
+            has_media |= (p.kind == RT_PRIM_MEDIUM_SPHERE || p.kind == RT_PRIM_MEDIUM);
         }
     }
     // materials with the solid colour inlined
@@ -432,22 +520,28 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     }
 
     RtScene* s = new (std::nothrow) RtScene();
-    if (!s) return fail(RT_ERR_OOM, "out of host memory");
+    if (!s) return fail(RT_ERR_OOM, "out of host memory");  // (lbvh_guard frees the device tree)
     s->ctx = ctx;
     s->bvh_depth = bvh.depth;
     s->d.bvh_depth = bvh.depth;
     cudaError_t e = cudaSuccess;
     static_assert(sizeof(BvhNode32) == 2 * sizeof(float4), "node layout");
-    if (use_lbvh) { s->nodes.p = lbvh.d_nodes; s->nodes.n = (size_t)lbvh.n_nodes * 2; }  // built in place: the scene adopts the device array
+    if (use_lbvh) { s->nodes.p = lbvh.d_nodes; s->nodes.n = (size_t)lbvh.n_nodes * 2; lbvh_guard.armed = false; }  // built in place: the scene adopts the device array
     else if (e == cudaSuccess) e = upload(s->nodes, reinterpret_cast<const float4*>(bvh.nodes.data()), bvh.nodes.size() * 2);
     if (e == cudaSuccess) e = upload(s->prim_head, head.data(), head.size());
     if (e == cudaSuccess) e = upload(s->prim_meta, meta.data(), meta.size());
+    std::vector<uint32_t> order_to_prim;
+    for (uint32_t i = 0; i < n; ++i) {
+        if (meta[i].x >= order_to_prim.size()) order_to_prim.resize((size_t)meta[i].x + 1, RT_NO_PRIM);
+        if (order_to_prim[meta[i].x] == RT_NO_PRIM) order_to_prim[meta[i].x] = i;
+    }
+    if (e == cudaSuccess) e = upload(s->order_to_prim, order_to_prim.data(), order_to_prim.size());
     if (e == cudaSuccess) e = upload(s->gen, gen.data(), gen.size());
+    if (e == cudaSuccess) e = upload(s->bnd, desc->boundary_prims, (size_t)desc->n_boundary_prims);
     if (e == cudaSuccess) e = upload(s->rects, rects.data(), rects.size());
     if (e == cudaSuccess) e = upload(s->rect_nrm, rect_nrm.data(), rect_nrm.size());
     FrameRects fr;
-    bool use_fr = small && rects.size() / 4 == n && buildFrameRects(desc->prims, bvh.order, fr);
-    if (const char* ef = std::getenv("RT_B200_RECT_FRAMES")) { if (ef[0] == '0') use_fr = false; }
+    const bool use_fr = small && !(so.flags & RT_SCENE_NO_FRAME_RECTS) && rects.size() / 4 == n && buildFrameRects(desc->prims, bvh.order, fr);
     if (e == cudaSuccess && use_fr) e = upload(s->fr_blob, fr.blob.data(), fr.blob.size());
     if (e == cudaSuccess) e = upload(s->mats, mats.data(), mats.size());
     if (e == cudaSuccess) e = upload(s->texs, desc->textures, (size_t)desc->n_textures);
@@ -457,22 +551,23 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
         return fail(e == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(e));
     }
     DScene& d = s->d;
-    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.rects = s->rects.p; d.rect_nrm = s->rect_nrm.p;
+    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.bnd = s->bnd.p; d.rects = s->rects.p; d.rect_nrm = s->rect_nrm.p;
     d.mats = s->mats.p; d.texs = s->texs.p; d.texels = s->texels.p;
+    d.order_to_prim = s->order_to_prim.p; d.n_orders = (uint32_t)order_to_prim.size();
     d.n_nodes = use_lbvh ? lbvh.n_nodes : (uint32_t)bvh.nodes.size(); d.n_prims = n; d.n_always = bvh.n_always; d.n_gen = (uint32_t)gen.size();
     d.n_mats = desc->n_materials; d.n_texs = desc->n_textures;
     d.root_is_leaf = bvh.root_is_leaf ? 1u : 0u;
     // whole tree in shared memory when it fits; otherwise only the top levels (every ray walks them) so that
     // shared memory does not cost occupancy and L1 keeps the deeper, ray-dependent nodes
     uint32_t staged = d.n_nodes <= RT_MAX_STAGED_NODES ? d.n_nodes : RT_TOP_STAGED_NODES;
-    if (const char* sn = std::getenv("RT_B200_STAGED_NODES")) staged = std::min<uint32_t>(d.n_nodes, (uint32_t)std::max(0, std::atoi(sn)));
+    if (so.staged_nodes) staged = std::min<uint32_t>(d.n_nodes, so.staged_nodes - 1u);
     if (use_lbvh && d.n_nodes > RT_MAX_STAGED_NODES) staged = 2u;  // the LBVH's top levels are not a prefix of its node array: only the root pair
     d.n_staged_nodes = staged & ~1u;
     d.has_media = has_media ? 1u : 0u;
     d.n_rects = (uint32_t)(rects.size() / 4);
     d.n_small = small ? n : 0u;
     d.n_staged_prims = (n <= RT_MAX_STAGED_PRIMS && d.n_rects <= RT_MAX_STAGED_RECTS) ? n : 0u;
-    if (const char* sp = std::getenv("RT_B200_STAGE_PRIMS")) { if (sp[0] == '0') d.n_staged_prims = 0u; }
+    if (so.flags & RT_SCENE_NO_STAGED_PRIMS) d.n_staged_prims = 0u;
     std::memcpy(d.always_k, always_k, sizeof(always_k));
     d.small_all_rects = (small && d.n_staged_prims == n && d.n_rects == n) ? 1u : 0u;
     s->staged_bytes = (size_t)d.n_staged_nodes * 32 + (size_t)d.n_staged_prims * 16 + (d.n_staged_prims ? (size_t)d.n_rects * 64 : 0);
@@ -483,6 +578,11 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
     }
     s->shade_bytes = (size_t)std::min<uint32_t>(d.n_mats, RT_MAX_STAGED_MATS) * 32 + (size_t)d.n_staged_prims * (16 + 8) +
                      (d.n_staged_prims ? (size_t)d.n_rects * 16 : 0);
+    e = kernels_configure_scene(ctx->device, d, s->staged_bytes, s->shade_bytes, s->fr_bytes, s->launch);
+    if (e != cudaSuccess) {
+        rt_scene_destroy(s);
+        return fail(RT_ERR_CUDA, "kernel configuration failed: %s", cudaGetErrorString(e));
+    }
     *out = s;
     return RT_OK;
 }
@@ -490,7 +590,7 @@ int rt_scene_create(RtContext* ctx, const RtSceneDesc* desc, RtScene** out) {
 void rt_scene_destroy(RtScene* s) {
     if (!s) return;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->order_to_prim.release(); s->gen.release(); s->bnd.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
     delete s;
 }
 
@@ -505,16 +605,15 @@ int rt_scene_bvh_info(const RtScene* s, uint32_t* n_nodes, uint32_t* n_always, u
 uint64_t rt_scene_device_bytes(const RtScene* s) {
     if (!s) return 0;
     return (uint64_t)s->nodes.n * sizeof(float4) + (uint64_t)s->prim_head.n * sizeof(float4) + (uint64_t)s->prim_meta.n * sizeof(uint2) +
-           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)(s->rects.n + s->rect_nrm.n) * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
+           (uint64_t)(s->gen.n + s->bnd.n) * sizeof(RtPrim) + (uint64_t)s->order_to_prim.n * sizeof(uint32_t) + (uint64_t)(s->rects.n + s->rect_nrm.n) * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
            (uint64_t)s->texels.n * sizeof(float4);
 }
 
 int rt_deinterleave_rows(RtContext* ctx, const float* d_gathered, float* d_full, uint32_t width, uint32_t height, uint32_t n_shards, void* cuda_stream) {
     if (!ctx || !d_gathered || !d_full || !width || !height || !n_shards) return fail(RT_ERR_INVALID, "bad argument");
     RT_CUDA(cudaSetDevice(ctx->device));
-    RT_CUDA(kernels_init(ctx->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
-    launch_deinterleave(d_gathered, d_full, width, height, n_shards, st);
+    launch_deinterleave(ctx->num_sms, d_gathered, d_full, width, height, n_shards, st);
     RT_CUDA(cudaGetLastError());
     if (!cuda_stream) RT_CUDA(cudaStreamSynchronize(st));
     return RT_OK;
@@ -575,10 +674,13 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
     RT_CUDA(cudaSetDevice(ctx->device));
     while (ctx->lanes.size() < L) {
         RtContext* lane = nullptr;
-        const int rc = rt_init(ctx->device, &lane);
+        RtContextOptions co{};
+        co.lanes = 1;
+        co.queue_capacity = ctx->default_capacity;
+        co.flags = ctx->overlap_accumulate ? 0u : (uint32_t)RT_CTX_NO_ACCUMULATE_OVERLAP;
+        const int rc = context_create(ctx->device, co, ctx->scene_defaults, &lane);
         if (rc != RT_OK) return rc;
-        lane->n_lanes = 1;
-        lane->default_capacity = ctx->default_capacity;
+        lane->lopt = ctx->lopt;
         ctx->lanes.push_back(lane);
     }
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
@@ -586,7 +688,6 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
     const size_t shard = (size_t)rows_padded * prm->width * 3;
     RT_CUDA(ctx->lane_sum.ensure(shard * L));
     if (d_sumsq) RT_CUDA(ctx->lane_sumsq.ensure(shard * L));
-    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes, scene->shade_bytes, scene->fr_bytes));  // once, before the lane threads
     RT_CUDA(cudaEventRecord(ctx->ev0, st));
     RT_CUDA(cudaEventRecord(ctx->ev_lane_begin, st));
     std::vector<RtStats> lane_stats(L);
@@ -612,8 +713,8 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
     for (uint32_t l = 0; l < L; ++l)
         if (lane_rc[l] != RT_OK) return fail(lane_rc[l], "%s", lane_err[l].c_str());
     // render_core returned after its lane's stream drained: the shards are complete; interleave them on the caller's stream
-    launch_deinterleave(ctx->lane_sum.p, d_sum, prm->width, rows_local, L, st);
-    if (d_sumsq) launch_deinterleave(ctx->lane_sumsq.p, d_sumsq, prm->width, rows_local, L, st);
+    launch_deinterleave(ctx->num_sms, ctx->lane_sum.p, d_sum, prm->width, rows_local, L, st);
+    if (d_sumsq) launch_deinterleave(ctx->num_sms, ctx->lane_sumsq.p, d_sumsq, prm->width, rows_local, L, st);
     RT_CUDA(cudaEventRecord(ctx->ev1, st));
     RT_CUDA(cudaEventSynchronize(ctx->ev1));
     RT_CUDA(cudaGetLastError());
@@ -654,14 +755,17 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
     rc.pixels_local = (uint64_t)rc.width * rc.rows_local;
     rc.paths_total = rc.pixels_local * rc.spp;
     rc.user_rays = d_user_rays;
-    { const char* po = std::getenv("RT_B200_PATH_ORDER"); rc.pixel_major = po ? (po[0] != '0') : 1u; }
+    rc.pixel_major = (prm->flags & RT_RENDER_SAMPLE_MAJOR) ? 0u : 1u;
 
     for (int i = 0; i < 2; ++i) { RT_CUDA(ctx->qa[i].ensure(cap)); RT_CUDA(ctx->qb[i].ensure(cap)); RT_CUDA(ctx->qc[i].ensure(cap)); }
     RT_CUDA(ctx->hits.ensure(cap));
     RT_CUDA(ctx->done[0].ensure(cap));
     RT_CUDA(ctx->done[1].ensure(cap));
     RT_CUDA(ctx->counters.ensure(1));
-    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes, scene->shade_bytes, scene->fr_bytes));
+    if (scene->launch.device != ctx->device) return fail(RT_ERR_INVALID, "scene lives on device %d, context on device %d", scene->launch.device, ctx->device);
+    LaunchOptions lopt = ctx->lopt;
+    if (prm->flags & RT_RENDER_EXTEND_PER_THREAD) lopt.persistent = 0;
+    if (prm->flags & RT_RENDER_EXTEND_PERSISTENT) lopt.persistent = 1;
 
     const size_t fb_elems = (size_t)rc.pixels_local * 3;
     RT_CUDA(ctx->acc.ensure(fb_elems * 2));
@@ -694,8 +798,7 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
     cudaStream_t acc_st = overlap ? ctx->side : st;
     // stage timing brackets every `tstride`-th iteration only: six event records per iteration cost ~20 % of a
     // cornell-box render, which would handicap the very step that is being measured
-    uint64_t tstride = 8;
-    if (const char* ts = std::getenv("RT_B200_STAGE_TIMING_STRIDE")) { const long v = std::atol(ts); if (v >= 1) tstride = (uint64_t)v; }
+    const uint64_t tstride = (prm->flags & RT_RENDER_TIME_EVERY_ITERATION) ? 1 : 8;
     uint64_t n_timed = 0;
     auto stage_event = [&](uint64_t slot, int which, cudaStream_t on) -> cudaError_t {
         const size_t idx = (size_t)slot * 6 + (size_t)which;
@@ -709,7 +812,9 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
     };
 
     RT_CUDA(cudaEventRecord(ctx->ev0, st));
-    kernels_set_work_hint(0xFFFFFFFFu);
+    Launch L{&scene->launch, &lopt, RT_WORK_UNKNOWN, st};
+    Launch La = L;  // accumulate's launch site (its own stream when overlapped)
+    La.st = acc_st;
     uint64_t k = 0;
     bool finished = false;
     while (!finished) {
@@ -719,39 +824,41 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
         const bool timed = timing && (k % tstride == 0);
         const uint64_t ts = n_timed;
         if (timed) RT_CUDA(stage_event(ts, 0, st));
-        launch_generate(rc, qin, wc, ku, st);
+        launch_generate(L, rc, qin, wc, ku);
         if (timed) RT_CUDA(stage_event(ts, 1, st));
-        launch_extend(scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, count_work, st);
+        launch_extend(L, scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, count_work);
         if (timed) RT_CUDA(stage_event(ts, 2, st));
         // shade_k refills done[k & 1]: accumulate_{k-2} must be through with it
         if (overlap && k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[k & 1], 0));
-        launch_shade(scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, ku, st);
+        launch_shade(L, scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, ku);
         if (timed) RT_CUDA(stage_event(ts, 3, st));
         if (overlap) {
             RT_CUDA(cudaEventRecord(ctx->ev_shaded[k & 1], st));
             RT_CUDA(cudaStreamWaitEvent(acc_st, ctx->ev_shaded[k & 1], 0));
         }
         if (timed) RT_CUDA(stage_event(ts, 4, acc_st));
-        launch_accumulate(rc, ctx->done[k & 1].p, wc, ku, acc_sum, acc_sumsq, acc_st);
+        launch_accumulate(La, rc, ctx->done[k & 1].p, wc, ku, acc_sum, acc_sumsq);
         if (timed) { RT_CUDA(stage_event(ts, 5, acc_st)); ++n_timed; }
         if (overlap) RT_CUDA(cudaEventRecord(ctx->ev_accumulated[k & 1], acc_st));
         launches += 4;
+        // a launch that cannot start (shared memory, bad configuration) must surface here, not as "did not terminate" 100 k iterations later
+        if (k == 0) RT_CUDA(cudaPeekAtLastError());
         ++k;
         if (k >= min_iters && ((k - min_iters) % poll == 0)) {
+            RT_CUDA(cudaPeekAtLastError());
             RT_CUDA(cudaMemcpyAsync(ctx->h_status, wc, sizeof(WaveCounters), cudaMemcpyDeviceToHost, st));
             RT_CUDA(cudaStreamSynchronize(st));
-            if (ctx->h_status->st_issued == rc.paths_total && !count_work) kernels_set_work_hint(ctx->h_status->st_total);  // the queue only shrinks from here
+            if (ctx->h_status->st_issued == rc.paths_total && !count_work) L.work_hint = La.work_hint = ctx->h_status->st_total;  // the queue only shrinks from here
             if (ctx->h_status->st_issued == rc.paths_total && ctx->h_status->st_total == 0) finished = true;
             else if (k > iter_limit) return fail(RT_ERR_CUDA, "wavefront did not terminate after %llu iterations", (unsigned long long)k);
         }
     }
-    kernels_set_work_hint(0xFFFFFFFFu);
     if (overlap) {  // the last two accumulates join the render stream before the accumulators are read
         RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[0], 0));
         if (k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[1], 0));
     }
-    launch_finish(acc_sum, fb_elems, d_sum, st);
-    if (d_sumsq) launch_finish(acc_sumsq, fb_elems, d_sumsq, st);
+    launch_finish(ctx->num_sms, acc_sum, fb_elems, d_sum, st);
+    if (d_sumsq) launch_finish(ctx->num_sms, acc_sumsq, fb_elems, d_sumsq, st);
     launches += d_sumsq ? 2 : 1;
     RT_CUDA(cudaEventRecord(ctx->ev1, st));
     RT_CUDA(cudaEventSynchronize(ctx->ev1));
@@ -803,18 +910,22 @@ int rt_render(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, fl
     return RT_OK;
 }
 
-int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtHitOut* out) {
+int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtHitOut* out) { return rt_trace_from(scene, rays, nullptr, n, seed, out); }
+
+int rt_trace_from(RtScene* scene, const RtRayIn* rays, const uint32_t* self_order, uint64_t n, uint64_t seed, RtHitOut* out) {
     if (!scene || (n && (!rays || !out))) return fail(RT_ERR_INVALID, "null argument");
     if (n == 0) return RT_OK;
     RtContext* ctx = scene->ctx;
     RT_CUDA(cudaSetDevice(ctx->device));
-    RT_CUDA(kernels_configure(ctx->device, scene->staged_bytes, scene->shade_bytes, scene->fr_bytes));
-    const size_t in_bytes = n * sizeof(RtRayIn), out_bytes = n * sizeof(RtHitOut);
-    RT_CUDA(ctx->scratch.ensure(in_bytes + out_bytes + 256));
+    const size_t in_bytes = n * sizeof(RtRayIn), out_bytes = n * sizeof(RtHitOut), self_bytes = self_order ? n * sizeof(uint32_t) : 0;
+    const size_t off_out = (in_bytes + 255) & ~(size_t)255, off_self = (off_out + out_bytes + 255) & ~(size_t)255;
+    RT_CUDA(ctx->scratch.ensure(off_self + self_bytes + 256));
     RtRayIn* d_rays = reinterpret_cast<RtRayIn*>(ctx->scratch.p);
-    RtHitOut* d_out = reinterpret_cast<RtHitOut*>(ctx->scratch.p + ((in_bytes + 255) & ~(size_t)255));
+    RtHitOut* d_out = reinterpret_cast<RtHitOut*>(ctx->scratch.p + off_out);
+    uint32_t* d_self = self_order ? reinterpret_cast<uint32_t*>(ctx->scratch.p + off_self) : nullptr;
     RT_CUDA(cudaMemcpyAsync(d_rays, rays, in_bytes, cudaMemcpyHostToDevice, ctx->stream));
-    launch_trace(scene->d, d_rays, n, (uint32_t)seed, (uint32_t)(seed >> 32), d_out, ctx->stream);
+    if (self_order) RT_CUDA(cudaMemcpyAsync(d_self, self_order, self_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    launch_trace(scene->launch, scene->d, d_rays, d_self, n, (uint32_t)seed, (uint32_t)(seed >> 32), d_out, ctx->stream);
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -824,15 +935,260 @@ int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtH
 int rt_resolve_u8(RtContext* ctx, const float* sum_rgb, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out) {
     if (!ctx || !sum_rgb || !out || !width || !height || !spp) return fail(RT_ERR_INVALID, "bad argument");
     RT_CUDA(cudaSetDevice(ctx->device));
-    RT_CUDA(kernels_init(ctx->device));
     const size_t n = (size_t)width * height * 3;
     RT_CUDA(ctx->fb_sum.ensure(n));
     RT_CUDA(ctx->scratch.ensure(n));
     RT_CUDA(cudaMemcpyAsync(ctx->fb_sum.p, sum_rgb, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    launch_resolve_u8(ctx->fb_sum.p, width, height, spp, ctx->scratch.p, ctx->stream);
+    launch_resolve_u8(ctx->num_sms, ctx->fb_sum.p, width, height, spp, ctx->scratch.p, ctx->stream);
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(out, ctx->scratch.p, n, cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+}  // extern "C"
+
+// ---- several GPUs of one process ---------------------------------------------------------------------------------
+//
+// The reference spawns one thread per core, thread i renders the rows y % n == i and the main thread reassembles the image
+// (examples/book-one.rs:54-88).  Here: one host thread per DEVICE (each runs the complete wavefront of rt_render_device on its
+// own context, with its own lane threads), scene replicated, rows y % G == g, and the shards go to device 0 with one grouped
+// ncclSend / ncclRecv over NVLink; k_deinterleave puts row y back at index y.  NCCL is resolved with dlopen so that the library has
+// no link-time dependency on it (a single-GPU user needs none, and a process that already holds an NCCL — PyTorch's — keeps it).
+
+namespace {
+
+struct NcclApi {
+    void* handle = nullptr;
+    decltype(&ncclCommInitAll) CommInitAll = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclSend) Send = nullptr;
+    decltype(&ncclRecv) Recv = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+    decltype(&ncclGetVersion) GetVersion = nullptr;
+};
+std::mutex g_nccl_mutex;
+NcclApi g_nccl;
+
+int load_nccl() {
+    std::lock_guard<std::mutex> lock(g_nccl_mutex);
+    if (g_nccl.handle) return RT_OK;
+    void* h = nullptr;
+    for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
+        h = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
+    }
+    if (!h) return fail(RT_ERR_NCCL, "cannot load libnccl.so.2: %s", dlerror());
+    NcclApi api;
+    api.handle = h;
+#define RT_SYM(field, sym) api.field = reinterpret_cast<decltype(api.field)>(dlsym(h, #sym)); if (!api.field) return fail(RT_ERR_NCCL, "libnccl lacks %s", #sym)
+    RT_SYM(CommInitAll, ncclCommInitAll);
+    RT_SYM(CommDestroy, ncclCommDestroy);
+    RT_SYM(GroupStart, ncclGroupStart);
+    RT_SYM(GroupEnd, ncclGroupEnd);
+    RT_SYM(Send, ncclSend);
+    RT_SYM(Recv, ncclRecv);
+    RT_SYM(GetErrorString, ncclGetErrorString);
+    RT_SYM(GetVersion, ncclGetVersion);
+#undef RT_SYM
+    g_nccl = api;
+    return RT_OK;
+}
+
+#define RT_NCCL(call)                                                                                               \
+    do {                                                                                                            \
+        ncclResult_t r_ = (call);                                                                                   \
+        if (r_ != ncclSuccess) return fail(RT_ERR_NCCL, "%s failed: %s (%s:%d)", #call, g_nccl.GetErrorString(r_), __FILE__, __LINE__); \
+    } while (0)
+
+}  // namespace
+
+struct RtMulti {
+    std::vector<RtContext*> ctx;     // one per device, in the caller's order; ctx[0] is the root of the gather
+    std::vector<ncclComm_t> comms;   // empty for a single device
+    std::vector<DevBuf<float>> shard, shard_sq;  // each device's compact row shard [rows_padded][W][3]
+    DevBuf<float> gathered, full;    // on device 0
+};
+
+struct RtMultiScene {
+    RtMulti* multi = nullptr;
+    std::vector<RtScene*> scenes;
+};
+
+extern "C" {
+
+int rt_init_multi(int n_devices, const int* device_ids, const RtContextOptions* options, RtMulti** out) {
+    if (!out) return fail(RT_ERR_INVALID, "out is null");
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > 64) return fail(RT_ERR_INVALID, "n_devices %d out of range", n_devices);
+    std::vector<int> ids(n_devices);
+    for (int i = 0; i < n_devices; ++i) {
+        ids[i] = device_ids ? device_ids[i] : i;
+        for (int j = 0; j < i; ++j) if (ids[j] == ids[i]) return fail(RT_ERR_INVALID, "device %d listed twice", ids[i]);
+    }
+    RtMulti* m = new (std::nothrow) RtMulti();
+    if (!m) return fail(RT_ERR_OOM, "out of host memory");
+    for (int i = 0; i < n_devices; ++i) {
+        RtContext* c = nullptr;
+        const int rc = rt_init_ex(ids[i], options, &c);
+        if (rc != RT_OK) { rt_shutdown_multi(m); return rc; }
+        m->ctx.push_back(c);
+    }
+    m->shard.resize(n_devices);
+    m->shard_sq.resize(n_devices);
+    if (n_devices > 1) {
+        const int rc = load_nccl();
+        if (rc != RT_OK) { rt_shutdown_multi(m); return rc; }
+        m->comms.assign(n_devices, nullptr);
+        const ncclResult_t r = g_nccl.CommInitAll(m->comms.data(), n_devices, ids.data());
+        if (r != ncclSuccess) {
+            m->comms.clear();
+            rt_shutdown_multi(m);
+            return fail(RT_ERR_NCCL, "ncclCommInitAll failed: %s", g_nccl.GetErrorString(r));
+        }
+    }
+    *out = m;
+    return RT_OK;
+}
+
+void rt_shutdown_multi(RtMulti* m) {
+    if (!m) return;
+    for (size_t i = 0; i < m->comms.size(); ++i) {
+        if (!m->comms[i]) continue;
+        cudaSetDevice(m->ctx[i]->device);
+        g_nccl.CommDestroy(m->comms[i]);
+    }
+    for (size_t i = 0; i < m->ctx.size(); ++i) {
+        cudaSetDevice(m->ctx[i]->device);
+        if (i < m->shard.size()) { m->shard[i].release(); m->shard_sq[i].release(); }
+        if (i == 0) { m->gathered.release(); m->full.release(); }
+        rt_shutdown(m->ctx[i]);
+    }
+    delete m;
+}
+
+int rt_multi_device_count(const RtMulti* m) { return m ? (int)m->ctx.size() : 0; }
+RtContext* rt_multi_context(RtMulti* m, int index) { return (m && index >= 0 && index < (int)m->ctx.size()) ? m->ctx[index] : nullptr; }
+
+int rt_multi_scene_create(RtMulti* m, const RtSceneDesc* desc, const RtSceneOptions* options, RtMultiScene** out) {
+    if (!m || !out) return fail(RT_ERR_INVALID, "multi/out is null");
+    *out = nullptr;
+    RtMultiScene* ms = new (std::nothrow) RtMultiScene();
+    if (!ms) return fail(RT_ERR_OOM, "out of host memory");
+    ms->multi = m;
+    const size_t G = m->ctx.size();
+    ms->scenes.assign(G, nullptr);
+    // the replicas are built concurrently (each device builds / uploads its own copy; the host SAH build is deterministic)
+    std::vector<int> rcs(G, RT_OK);
+    std::vector<std::string> errs(G);
+    std::vector<std::thread> pool;
+    for (size_t g = 0; g < G; ++g)
+        pool.emplace_back([&, g]() {
+            rcs[g] = rt_scene_create_ex(m->ctx[g], desc, options, &ms->scenes[g]);
+            if (rcs[g] != RT_OK) errs[g] = g_error;
+        });
+    for (auto& t : pool) t.join();
+    for (size_t g = 0; g < G; ++g)
+        if (rcs[g] != RT_OK) {
+            const int rc = rcs[g];
+            const std::string msg = errs[g];
+            rt_multi_scene_destroy(ms);
+            return fail(rc, "device %d: %s", m->ctx[g]->device, msg.c_str());
+        }
+    *out = ms;
+    return RT_OK;
+}
+
+void rt_multi_scene_destroy(RtMultiScene* ms) {
+    if (!ms) return;
+    for (RtScene* s : ms->scenes) rt_scene_destroy(s);
+    delete ms;
+}
+
+int rt_render_multi(RtMultiScene* ms, const RtCamera* cam, const RtRenderParams* prm, float* out_sum, float* out_sumsq, RtStats* stats) {
+    if (!ms || !cam || !prm || !out_sum) return fail(RT_ERR_INVALID, "null argument");
+    if (prm->row_begin != 0 || prm->row_stride != 1) return fail(RT_ERR_INVALID, "rt_render_multi shards the rows itself: row_begin / row_stride must be 0 / 1");
+    if (prm->width == 0 || prm->height == 0 || prm->spp == 0) return fail(RT_ERR_INVALID, "width/height/spp must be > 0");
+    RtMulti* m = ms->multi;
+    const uint32_t G = (uint32_t)m->ctx.size();
+    const uint32_t W = prm->width, H = prm->height;
+    const uint32_t Gact = std::min(G, H);  // devices that own at least one row
+    const uint32_t rows_padded = (H + Gact - 1) / Gact;
+    const size_t shard = (size_t)rows_padded * W * 3, full = (size_t)H * W * 3;
+    RtContext* root = m->ctx[0];
+    RT_CUDA(cudaSetDevice(root->device));
+    const int n_img = out_sumsq ? 2 : 1;
+    RT_CUDA(m->full.ensure(full * n_img));
+    if (Gact > 1) RT_CUDA(m->gathered.ensure(shard * Gact * n_img));
+    RT_CUDA(cudaEventRecord(root->ev0, root->stream));
+
+    std::vector<RtStats> st(Gact);
+    std::vector<int> rcs(Gact, RT_OK);
+    std::vector<std::string> errs(Gact);
+    std::vector<std::thread> pool;
+    for (uint32_t g = 0; g < Gact; ++g)
+        pool.emplace_back([&, g]() {
+            RtContext* c = m->ctx[g];
+            auto cuda_fail = [&](cudaError_t e) { rcs[g] = RT_ERR_CUDA; errs[g] = cudaGetErrorString(e); };
+            cudaError_t e = cudaSetDevice(c->device);
+            if (e != cudaSuccess) return cuda_fail(e);
+            // a single device renders straight into the full image; otherwise into this device's shard
+            float* d_sum = nullptr;
+            float* d_sq = nullptr;
+            if (Gact == 1) { d_sum = m->full.p; d_sq = out_sumsq ? m->full.p + full : nullptr; }
+            else {
+                if ((e = m->shard[g].ensure(shard)) != cudaSuccess) return cuda_fail(e);
+                if (out_sumsq && (e = m->shard_sq[g].ensure(shard)) != cudaSuccess) return cuda_fail(e);
+                d_sum = m->shard[g].p; d_sq = out_sumsq ? m->shard_sq[g].p : nullptr;
+            }
+            RtRenderParams p = *prm;
+            p.row_begin = g; p.row_stride = Gact;
+            rcs[g] = rt_render_device(ms->scenes[g], cam, &p, d_sum, d_sq, nullptr, &st[g]);
+            if (rcs[g] != RT_OK) errs[g] = g_error;
+        });
+    for (auto& t : pool) t.join();
+    for (uint32_t g = 0; g < Gact; ++g)
+        if (rcs[g] != RT_OK) return fail(rcs[g], "device %d: %s", m->ctx[g]->device, errs[g].c_str());
+
+    RT_CUDA(cudaSetDevice(root->device));
+    if (Gact > 1) {
+        // the ONE collective: every shard to device 0 (rt_render_device returned after its stream drained, so the shards are complete)
+        for (int img = 0; img < n_img; ++img) {
+            float* dst = m->gathered.p + (size_t)img * shard * Gact;
+            RT_CUDA(cudaMemcpyAsync(dst, img ? m->shard_sq[0].p : m->shard[0].p, shard * sizeof(float), cudaMemcpyDeviceToDevice, root->stream));
+            RT_NCCL(g_nccl.GroupStart());
+            for (uint32_t g = 1; g < Gact; ++g) {
+                RT_NCCL(g_nccl.Recv(dst + shard * g, shard, ncclFloat, (int)g, m->comms[0], root->stream));
+                RT_NCCL(g_nccl.Send(img ? m->shard_sq[g].p : m->shard[g].p, shard, ncclFloat, 0, m->comms[g], m->ctx[g]->stream));
+            }
+            RT_NCCL(g_nccl.GroupEnd());
+            launch_deinterleave(root->num_sms, dst, m->full.p + (size_t)img * full, W, H, Gact, root->stream);
+        }
+    }
+    RT_CUDA(cudaEventRecord(root->ev1, root->stream));
+    RT_CUDA(cudaMemcpyAsync(out_sum, m->full.p, full * sizeof(float), cudaMemcpyDeviceToHost, root->stream));
+    if (out_sumsq) RT_CUDA(cudaMemcpyAsync(out_sumsq, m->full.p + full, full * sizeof(float), cudaMemcpyDeviceToHost, root->stream));
+    RT_CUDA(cudaStreamSynchronize(root->stream));
+    for (uint32_t g = 1; g < Gact; ++g) {  // the senders' streams (their buffers are reused by the next render)
+        RT_CUDA(cudaSetDevice(m->ctx[g]->device));
+        RT_CUDA(cudaStreamSynchronize(m->ctx[g]->stream));
+    }
+    RT_CUDA(cudaSetDevice(root->device));
+    RT_CUDA(cudaGetLastError());
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        float ms_total = 0;
+        RT_CUDA(cudaEventElapsedTime(&ms_total, root->ev0, root->ev1));
+        for (const RtStats& s : st) {
+            stats->paths += s.paths; stats->rays += s.rays; stats->launches += s.launches;
+            stats->iterations = std::max(stats->iterations, s.iterations);
+        }
+        if (Gact > 1) stats->launches += (uint64_t)n_img;
+        stats->ms_total = ms_total;
+        stats->bvh_nodes = ms->scenes[0]->d.n_nodes; stats->bvh_always = ms->scenes[0]->d.n_always;
+    }
     return RT_OK;
 }
 

@@ -53,9 +53,12 @@ struct DScene {
     const float4* rects;       // 4 float4 per rectangle: row z, row x, row y of object<-world (xyz, translation), (hx, hy, 0, 0)
     const float4* rect_nrm;    // per rectangle: world-space normal M (0,0,1) (forward matrix, not renormalised: SURVEY A.5)
     const RtPrim* gen;         // general records (non translation-only-sphere primitives)
+    const RtPrim* bnd;         // boundary surfaces of RT_PRIM_MEDIUM primitives (RtSceneDesc.boundary_prims)
     const DMaterial* mats;
     const RtTexture* texs;
     const float4* texels;
+    const uint32_t* order_to_prim;  // DFS rank (RtPrim.order) -> device primitive index, RT_NO_PRIM for ranks without a primitive
+    uint32_t n_orders;
     uint32_t n_nodes, n_prims, n_always, n_gen, n_mats, n_texs;
     uint32_t root_is_leaf;     // BVH over < 2 primitives: node 0 is a leaf
     uint32_t bvh_depth;        // depth of the tree (levels below the root)

@@ -196,15 +196,100 @@ __device__ __forceinline__ float medium_sphere_hit(float3 o, float3 d, float r, 
     return entering ? t1 + distance : distance;
 }
 
+// ---- ConstantMedium<T> over an arbitrary flattened boundary (RT_PRIM_MEDIUM; volume.rs:40-100) -------------------------------
+// Both probes of the reference (`boundary.hit(ray)` at volume.rs:47 and, from p1 + 1e-6 d, at volume.rs:54) are closest-hit
+// queries over the boundary's surfaces in DFS order with strict `<`.  f32 policy as everywhere: the second probe is evaluated
+// on the ORIGINAL ray (no re-rounded origin), measured from t1 + 1e-6; the surface the first probe hit is excluded when it is a
+// rectangle (a plane cannot be re-hit) and answers with its far root when it is a sphere — what the f64 reference gets from
+// `t >= 1e-6` on the re-shot ray.
+struct BoundaryHit {
+    float t;
+    uint32_t idx;  // index into S.bnd, RT_NO_PRIM = miss
+};
+// closest boundary surface with t_ray2 = t - t_from >= eps, where ray2 starts at parameter t_from of the ray (0 for the first probe)
+__device__ __forceinline__ BoundaryHit boundary_probe(const RtPrim* __restrict__ bnd, uint32_t first, uint32_t count, float3 o, float3 d, float t_from,
+                                                      uint32_t skip) {
+    BoundaryHit best{CUDART_INF_F, RT_NO_PRIM};
+    for (uint32_t i = first; i < first + count; ++i) {
+        const RtPrim* __restrict__ g = bnd + i;
+        const float3 lo = xform_point(g->local_from_world, o);
+        const float3 ld = xform_vector(g->local_from_world, d);
+        float t = CUDART_INF_F;
+        if (g->kind == RT_PRIM_RECT) {
+            if (i != skip) {
+                const float tt = rect_hit(lo, ld, g->param[0], g->param[1]);  // rejects t < 1e-6 on the original ray
+                if (tt - t_from >= RT_T_EPS) t = tt;
+            }
+        } else {  // sphere
+            float tn, tf;
+            if (sphere_roots(lo, ld, g->param[0], tn, tf)) {
+                if (i == skip) { if (tf - t_from > RT_T_EPS && tf > tn) t = tf; }  // far root of the surface the ray2 starts on
+                else if (tn - t_from > RT_T_EPS) t = tn;
+                else if (tf - t_from > RT_T_EPS) t = tf;
+            }
+        }
+        if (t < best.t) { best.t = t; best.idx = i; }
+    }
+    return best;
+}
+// outward normal (not renormalised after the forward matrix, sprite.rs:112-115) and uv of boundary surface `idx` at ray parameter t
+__device__ __forceinline__ float3 boundary_normal(const RtPrim* __restrict__ bnd, uint32_t idx, float3 o, float3 d, float t, float* u = nullptr, float* v = nullptr) {
+    const RtPrim* __restrict__ g = bnd + idx;
+    if (g->kind == RT_PRIM_RECT) {
+        if (u) {
+            const float3 lp = fma3(t, xform_vector(g->local_from_world, d), xform_point(g->local_from_world, o));
+            *u = (lp.x + 0.5f * g->param[0]) / g->param[0];
+            *v = (lp.y + 0.5f * g->param[1]) / g->param[1];
+        }
+        return f3(g->world_from_local[2], g->world_from_local[6], g->world_from_local[10]);
+    }
+    const float3 lp = fma3(t, xform_vector(g->local_from_world, d), xform_point(g->local_from_world, o));
+    const float3 q = lp * (1.0f / g->param[0]);
+    const float3 unit = normalize3(q);
+    if (u) {  // geometry.rs:35-39, acos clamped (A.11)
+        *u = 0.5f + atan2f(q.x, q.z) * (1.0f / (2.0f * 3.14159265358979323846f));
+        *v = 1.0f - acosf(fminf(fmaxf(q.y, -1.0f), 1.0f)) * (1.0f / 3.14159265358979323846f);
+    }
+    return xform_vector(g->world_from_local, unit);
+}
+struct MediumProbe {  // what shade needs to rebuild the record
+    float t1, t2;     // first boundary hit; second (entering branch only), both as parameters of the original ray
+    uint32_t i1, i2;
+    bool entering;
+};
+__device__ __forceinline__ float medium_generic_hit(const RtPrim* __restrict__ bnd, uint32_t first, uint32_t count, float3 o, float3 d, float density,
+                                                    uint32_t order, const MediumKey& key, MediumProbe* probe = nullptr) {
+    const BoundaryHit h1 = boundary_probe(bnd, first, count, o, d, 0.0f, RT_NO_PRIM);
+    if (h1.idx == RT_NO_PRIM) return CUDART_INF_F;
+    const float3 n1 = boundary_normal(bnd, h1.idx, o, d, h1.t);
+    const bool entering = dot3(n1, d) < 0.0f;  // volume.rs:49
+    float inside, t2 = 0.0f;
+    uint32_t i2 = RT_NO_PRIM;
+    if (entering) {
+        const BoundaryHit h2 = boundary_probe(bnd, first, count, o, d, h1.t + 1e-6f, h1.idx);
+        if (h2.idx == RT_NO_PRIM) return CUDART_INF_F;  // volume.rs:74-76
+        inside = (h2.t - h1.t) - 1e-6f;
+        t2 = h2.t; i2 = h2.idx;
+    } else {
+        inside = h1.t;
+    }
+    const Philox4 rnd = philox4x32_10(key.segment, RT_DIM_MEDIUM | order, key.seed_lo, key.seed_hi, key.k0, key.k1);
+    const float distance = (-1.0f / density) * logf(u24f(rnd.x));
+    if (distance > inside) return CUDART_INF_F;
+    if (probe) { probe->t1 = h1.t; probe->t2 = t2; probe->i1 = h1.idx; probe->i2 = i2; probe->entering = entering; }
+    return entering ? h1.t + distance : distance;
+}
+
 // Primitive of a 128-byte general record (rotated / scaled sphere, negative radius, medium).  Returns t or +inf.
 // Kept out of line: it is the rare path and would otherwise triple the size of the traversal loop.
 #ifndef RT_GENERAL_INLINE
 #define RT_GENERAL_INLINE __noinline__
 #endif
-__device__ RT_GENERAL_INLINE float general_hit(const RtPrim* __restrict__ g, float3 o, float3 d, bool is_self, const MediumKey key) {
+__device__ RT_GENERAL_INLINE float general_hit(const RtPrim* __restrict__ g, const RtPrim* __restrict__ bnd, float3 o, float3 d, bool is_self, const MediumKey key) {
+    const uint32_t kind = g->kind;
+    if (kind == RT_PRIM_MEDIUM) return medium_generic_hit(bnd, g->aux, (uint32_t)g->param[2], o, d, g->param[1], g->order, key);
     const float3 lo = xform_point(g->local_from_world, o);
     const float3 ld = xform_vector(g->local_from_world, d);
-    const uint32_t kind = g->kind;
     if (kind == RT_PRIM_RECT) return is_self ? CUDART_INF_F : rect_hit(lo, ld, g->param[0], g->param[1]);
     if (kind == RT_PRIM_SPHERE) {
         const float r = g->param[0];
@@ -278,7 +363,7 @@ __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uin
         const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
         return rect_hit(R, __ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
     }
-    return general_hit(&S.gen[__float_as_uint(h.x)], R.o, R.d, i == self_prim, key);
+    return general_hit(&S.gen[__float_as_uint(h.x)], S.bnd, R.o, R.d, i == self_prim, key);
 }
 
 // Closest-hit update with the reference's tie rule (strict <, the DFS-earlier leaf wins an exact tie).

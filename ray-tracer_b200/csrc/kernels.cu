@@ -15,7 +15,6 @@
 // host never has to know queue sizes; it polls a status block every few iterations to detect the end.
 #include <cuda_runtime.h>
 
-#include <cstdlib>
 #include <mutex>
 
 #include "device_scene.h"
@@ -461,7 +460,7 @@ __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst
     if (sr.scattered) {
         if (segment < rc.max_depth) {  // color(.., 0) returns black without tracing (render.rs:6-8)
             const float3 t2 = thr * sr.attenuation;
-            const bool is_medium = head.w <= 0.0f && __float_as_uint(head.y) == (uint32_t)RT_PRIM_MEDIUM_SPHERE;  // general records carry their kind in .y
+            const bool is_medium = head.w <= 0.0f && __float_as_uint(head.y) >= (uint32_t)RT_PRIM_MEDIUM_SPHERE;  // general records carry their kind in .y
             r.o0 = make_float4(hd.p.x, hd.p.y, hd.p.z, __uint_as_float(is_medium ? RT_NO_PRIM : prim));
             r.o1 = make_float4(sr.dir.x, sr.dir.y, sr.dir.z, b.w);
             r.o2 = make_float4(t2.x, t2.y, t2.z, __uint_as_float((sample << 8) | (segment + 1u)));
@@ -560,128 +559,6 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
     }
 }
 
-// ---- shade, warp-specialised form ---------------------------------------------------------------------------------
-//
-// k_shade's slot allocation costs every round two block barriers with a global atomic round trip between them (r1o: 28 % of
-// the kernel's stall samples sit on those barriers).  Here the block is RT_SHADE_WARPS producer warps plus ONE scanner warp,
-// coupled by named barriers (bar.arrive / bar.sync) and double-buffered counters:
-//   producer, round j:   shade -> counts[j & 1] -> bar.arrive(A[j & 1])           (does not wait)
-//                        then COMMIT round j - 1: bar.sync(B[(j - 1) & 1]) -> slots -> stores of the rays kept in registers
-//   scanner,  round j:   bar.sync(A[j & 1]) -> scan the warp counts, the two global atomics -> offsets[j & 1] -> bar.arrive(B[j & 1])
-// so the atomic latency and the wait for the slowest warp overlap the producers' next round of shading.
-#ifndef RT_SHADE_WARPS
-#define RT_SHADE_WARPS 8
-#endif
-constexpr uint32_t RT_SHADEP_THREADS = 32u * (RT_SHADE_WARPS + 1u);
-#ifndef RT_SHADEP_MIN_BLOCKS
-#define RT_SHADEP_MIN_BLOCKS 3
-#endif
-
-// (immediate barrier ids: with a register id ptxas reserves all 16 named barriers of the CTA)
-template <uint32_t ID>
-__device__ __forceinline__ void named_arrive_id() { asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(RT_SHADEP_THREADS) : "memory"); }
-template <uint32_t ID>
-__device__ __forceinline__ void named_sync_id() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(RT_SHADEP_THREADS) : "memory"); }
-__device__ __forceinline__ void named_arrive(uint32_t id, uint32_t) {
-    if (id == 1u) named_arrive_id<1>(); else if (id == 2u) named_arrive_id<2>(); else if (id == 3u) named_arrive_id<3>(); else named_arrive_id<4>();
-}
-__device__ __forceinline__ void named_sync(uint32_t id, uint32_t) {
-    if (id == 1u) named_sync_id<1>(); else if (id == 2u) named_sync_id<2>(); else if (id == 3u) named_sync_id<3>(); else named_sync_id<4>();
-}
-
-__global__ void __launch_bounds__(RT_SHADEP_THREADS, RT_SHADEP_MIN_BLOCKS) k_shade_pipe(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
-                                                                                      const float2* __restrict__ hits, float4* __restrict__ done,
-                                                                                      WaveCounters* __restrict__ wc, uint32_t k) {
-    extern __shared__ float4 shade_smem[];
-    __shared__ uint32_t s_cnt[2][RT_SHADE_WARPS][2];  // [buffer][producer warp][alive, record] counts of a round
-    __shared__ uint32_t s_off[2][RT_SHADE_WARPS][2];  // [buffer][producer warp] first slot of the warp in qout / done
-    const uint32_t n_staged = min(S0.n_mats, RT_MAX_STAGED_MATS);
-    const uint32_t n_sp = S0.n_staged_prims, n_sr = n_sp ? S0.n_rects : 0u;
-    float4* smats = shade_smem;
-    float4* s_head = smats + 2u * n_staged;
-    float4* s_nrm = s_head + n_sp;
-    uint2* s_meta = reinterpret_cast<uint2*>(s_nrm + n_sr);
-    for (uint32_t i = threadIdx.x; i < 2u * n_staged; i += blockDim.x) smats[i] = reinterpret_cast<const float4*>(S0.mats)[i];
-    for (uint32_t i = threadIdx.x; i < n_sp; i += blockDim.x) { s_head[i] = S0.prim_head[i]; s_meta[i] = S0.prim_meta[i]; }
-    for (uint32_t i = threadIdx.x; i < n_sr; i += blockDim.x) s_nrm[i] = S0.rect_nrm[i];
-    DScene S = S0;
-    if (n_sp) { S.prim_head = s_head; S.prim_meta = s_meta; S.rect_nrm = s_nrm; }
-    __syncthreads();
-    const uint32_t s = k % RT_RING;
-    const uint32_t n = wc->total[s];
-    uint32_t* surv_next = &wc->surv[(k + 1) % RT_RING];
-    uint32_t* done_cnt = &wc->done[s];
-    const uint32_t lane = lane_id(), warp = threadIdx.x >> 5;
-    constexpr uint32_t PT = 32u * RT_SHADE_WARPS;  // producer threads = rays per block round
-    const uint32_t stride = gridDim.x * PT;
-    const uint32_t first = blockIdx.x * PT;
-    const uint32_t rounds = first < n ? (n - first + stride - 1u) / stride : 0u;  // block-uniform
-    constexpr uint32_t BAR_A = 1u, BAR_B = 3u;  // barrier ids A0, A1 = 1, 2; B0, B1 = 3, 4 (0 is __syncthreads)
-
-    if (warp == RT_SHADE_WARPS) {  // ---- scanner warp
-        for (uint32_t j = 0; j < rounds; ++j) {
-            const uint32_t buf = j & 1u;
-            named_sync(BAR_A + buf, RT_SHADEP_THREADS);
-            uint32_t ca = lane < RT_SHADE_WARPS ? s_cnt[buf][lane][0] : 0u, cb = lane < RT_SHADE_WARPS ? s_cnt[buf][lane][1] : 0u;
-            uint32_t pa = ca, pb = cb;  // inclusive warp scan over the producer warps
-#pragma unroll
-            for (int d = 1; d < (int)RT_SHADE_WARPS; d <<= 1) {
-                const uint32_t ua = __shfl_up_sync(0xFFFFFFFFu, pa, d), ub = __shfl_up_sync(0xFFFFFFFFu, pb, d);
-                if ((int)lane >= d) { pa += ua; pb += ub; }
-            }
-            const uint32_t ta = __shfl_sync(0xFFFFFFFFu, pa, RT_SHADE_WARPS - 1), tb = __shfl_sync(0xFFFFFFFFu, pb, RT_SHADE_WARPS - 1);
-            uint32_t base_a = 0u, base_b = 0u;
-            if (lane == 0) {
-                base_a = ta ? atomicAdd(surv_next, ta) : 0u;
-                base_b = tb ? atomicAdd(done_cnt, tb) : 0u;
-            }
-            base_a = __shfl_sync(0xFFFFFFFFu, base_a, 0);
-            base_b = __shfl_sync(0xFFFFFFFFu, base_b, 0);
-            if (lane < RT_SHADE_WARPS) { s_off[buf][lane][0] = base_a + pa - ca; s_off[buf][lane][1] = base_b + pb - cb; }
-            __threadfence_block();
-            named_arrive(BAR_B + buf, RT_SHADEP_THREADS);
-        }
-        return;
-    }
-
-    // ---- producer warps
-    ShadeOne prev;
-    prev.alive = prev.record = false;
-    prev.o0 = prev.o1 = prev.o2 = make_float4(0.f, 0.f, 0.f, 0.f);
-    uint32_t prev_ma = 0u, prev_mb = 0u;
-    const uint32_t lt = (1u << lane) - 1u;
-    auto commit = [&](uint32_t buf) {
-        named_sync(BAR_B + buf, RT_SHADEP_THREADS);
-        const uint32_t slot = s_off[buf][warp][0] + (uint32_t)__popc(prev_ma & lt), dslot = s_off[buf][warp][1] + (uint32_t)__popc(prev_mb & lt);
-        if (prev.alive) { qout.a[slot] = prev.o0; qout.b[slot] = prev.o1; qout.c[slot] = prev.o2; }
-        if (prev.record) done[dslot] = prev.o0;
-    };
-    const uint32_t t_in = threadIdx.x;  // < PT
-    for (uint32_t j = 0; j < rounds; ++j) {
-        const uint32_t buf = j & 1u;
-        const uint32_t i = first + j * stride + t_in;
-        const uint32_t nx = i + stride;
-        if (nx < n) {
-            if ((lane & 7u) == 0u) { prefetch_l2(&qin.a[nx]); prefetch_l2(&qin.b[nx]); prefetch_l2(&qin.c[nx]); }
-            if ((lane & 15u) == 0u) prefetch_l2(&hits[nx]);
-        }
-        float4 a, b, c;
-        float2 h;
-        if (i < n) { h = hits[i]; a = qin.a[i]; b = qin.b[i]; c = qin.c[i]; }
-        else { h = make_float2(0.f, __uint_as_float(RT_NO_PRIM)); a = b = c = make_float4(0.f, 0.f, 0.f, 0.f); }
-        const ShadeOne cur = shade_one(S, rc, smats, n_staged, a, b, c, h);
-        const uint32_t ma = __ballot_sync(0xFFFFFFFFu, cur.alive), mb = __ballot_sync(0xFFFFFFFFu, cur.record);
-        if (lane == 0) { s_cnt[buf][warp][0] = (uint32_t)__popc(ma); s_cnt[buf][warp][1] = (uint32_t)__popc(mb); }
-        __threadfence_block();
-        named_arrive(BAR_A + buf, RT_SHADEP_THREADS);
-        if (j > 0) commit(buf ^ 1u);
-        prev = cur;
-        prev_ma = ma;
-        prev_mb = mb;
-    }
-    if (rounds > 0) commit((rounds - 1u) & 1u);
-}
-
 // ---- accumulate ------------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const float4* __restrict__ done, const WaveCounters* __restrict__ wc,
@@ -736,16 +613,18 @@ __global__ void __launch_bounds__(256) k_finish(const double* __restrict__ acc, 
 
 // ---- resolve (examples/book-one.rs:90-100) -----------------------------------------------------------
 
-__global__ void k_resolve_u8(const float* __restrict__ sum, uint32_t width, uint32_t height, float inv_spp, uint8_t* __restrict__ out) {
+// f64 like the reference (mean = sum / spp, sqrt, * 255, min, truncation): bytes are integer work and must come out bit-exact; IEEE
+// f64 division and square root are correctly rounded on the device, so this equals the host computation for every input.
+__global__ void k_resolve_u8(const float* __restrict__ sum, uint32_t width, uint32_t height, double spp, uint8_t* __restrict__ out) {
     const size_t n = (size_t)width * height * 3;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const uint32_t c = (uint32_t)(i % 3);
         const size_t pix = i / 3;
         const uint32_t row = (uint32_t)(pix / width), x = (uint32_t)(pix - (size_t)row * width);
         const uint32_t y = height - 1u - row;  // rows top -> bottom
-        float v = sqrtf(sum[((size_t)y * width + x) * 3 + c] * inv_spp) * 255.0f;
-        v = (v != v) ? 255.0f : fminf(v, 255.0f);  // f64::min keeps the non-NaN operand (A.12)
-        out[i] = (uint8_t)fmaxf(v, 0.0f);
+        double v = sqrt((double)sum[((size_t)y * width + x) * 3 + c] / spp) * 255.0;
+        v = (v != v) ? 255.0 : fmin(v, 255.0);  // f64::min keeps the non-NaN operand (A.12)
+        out[i] = (uint8_t)fmax(v, 0.0);         // `as usize` saturates at 0
     }
 }
 
@@ -764,8 +643,10 @@ __global__ void __launch_bounds__(256) k_deinterleave(const float* __restrict__ 
 
 // ---- trace (parity harness; batched `world.hit(&ray)`) -------------------------------------------------
 
-__global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const RtRayIn* __restrict__ rays, uint64_t n, uint32_t seed_lo,
-                                                         uint32_t seed_hi, RtHitOut* __restrict__ out) {
+// `self_order` (nullable): per ray the DFS rank of the primitive the ray STARTS on (RT_NO_PRIM = none) — the state a scattered ray
+// carries through the wavefront (queue word a.w), so that the f32 self-intersection rule of intersect.cuh is testable ray by ray.
+__global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const RtRayIn* __restrict__ rays, const uint32_t* __restrict__ self_order,
+                                                         uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* __restrict__ out) {
     extern __shared__ float4 smem4[];
     const Staged sm = stage_scene(S, smem4);
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -773,7 +654,12 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
         const RtRayIn r = rays[i];
         const float3 o = f3(r.origin[0], r.origin[1], r.origin[2]), d = f3(r.direction[0], r.direction[1], r.direction[2]);
         const MediumKey key{(uint32_t)i, (uint32_t)(i >> 32), 1u, seed_lo, seed_hi};
-        const ClosestHit h = closest_hit<false>(S, sm, o, d, RT_NO_PRIM, key);
+        uint32_t self_prim = RT_NO_PRIM;
+        if (self_order) {
+            const uint32_t ord = self_order[i];
+            if (ord < S.n_orders) self_prim = __ldg(&S.order_to_prim[ord]);
+        }
+        const ClosestHit h = closest_hit<false>(S, sm, o, d, self_prim, key);
         RtHitOut res;
         res.hit = 0; res.prim = -1; res.t = 0.0f; res.material = -1;
         res.p[0] = res.p[1] = res.p[2] = res.n[0] = res.n[1] = res.n[2] = res.uv[0] = res.uv[1] = 0.0f;
@@ -789,189 +675,163 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
     }
 }
 
-// ---- launch wrappers ---------------------------------------------------------------------------------
+// ---- launch configuration ---------------------------------------------------------------------------------
+//
+// Nothing here is per process.  What depends on the DEVICE (SM count, the dynamic shared-memory ceiling each kernel has been
+// granted there — cudaFuncSetAttribute is per device) lives in DeviceState, keyed by device id; what depends on the SCENE
+// (shared-memory bytes of its staged tables, resident blocks per SM at those sizes, which extend kernel it gets) lives in the
+// SceneLaunch the scene owns; tuning options live in the context (LaunchOptions, read once by rt_init).  Several contexts on
+// several devices, and several scenes on one device, can therefore render concurrently from different host threads.
 
-static int g_num_sms = 0;
-static int g_extend_blocks_per_sm = 0, g_trace_blocks_per_sm = 0, g_shade_blocks_per_sm = 0;
-static size_t g_extend_smem = ~(size_t)0, g_shade_smem = ~(size_t)0, g_rects_smem = ~(size_t)0;
-static int g_rects_blocks_per_sm = 0, g_bvh_blocks_per_sm = 0;
-static size_t g_bvh_smem = 0, g_scene_smem = 0;
-static int g_persistent = -1;
-static size_t g_all_smem = 0;      // k_extend<false, true>: dynamic shared memory of the scene last launched and its occupancy
-static int g_all_blocks_per_sm = 0;
-constexpr size_t RT_EXTEND_ALL_MAX_SMEM = 100u * 1024u;
-static int g_grid_div = 1;     // experiment (RT_B200_GRID_DIV): extend / shade grids of blocks_per_sm / div, so that two lanes' kernels co-reside
-static int g_shade_rays2 = 1;  // RT_B200_SHADE_RAYS2=0: one ray per thread per round everywhere
-static int g_gen_blocks = 4, g_acc_blocks = 8;  // blocks per SM of k_generate / k_accumulate (RT_B200_GEN_BLOCKS / RT_B200_ACC_BLOCKS)
-static int g_shade_pipe = -1, g_shadep_blocks_per_sm = 0;
+namespace {
 
-cudaError_t kernels_init(int device) {
-    if (g_num_sms > 0) return cudaSuccess;
+constexpr int RT_MAX_DEVICES = 64;
+struct DeviceState {
+    std::mutex mu;
     int sms = 0;
-    const cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    if (e != cudaSuccess) return e;
-    g_num_sms = sms;
+    size_t granted[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // largest MaxDynamicSharedMemorySize set so far, per kernel slot
+};
+DeviceState g_dev[RT_MAX_DEVICES];
+enum KernelSlot { SLOT_EXTEND = 0, SLOT_EXTEND_COUNT, SLOT_EXTEND_ALL, SLOT_BVH, SLOT_BVH_COUNT, SLOT_RECTS, SLOT_SHADE, SLOT_TRACE };
+
+// the ceiling only ever grows: a launch may use any size up to it, so scenes of different sizes never invalidate each other
+template <class K>
+cudaError_t grant(DeviceState& d, KernelSlot slot, K kernel, size_t bytes) {
+    if (bytes <= d.granted[slot] || bytes <= 48u * 1024u) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) d.granted[slot] = bytes;
+    return e;
+}
+template <class K>
+cudaError_t occupancy(int& blocks, K kernel, int threads, size_t bytes) {
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, kernel, threads, bytes);
+    if (e == cudaSuccess && blocks < 1) blocks = 1;
+    return e;
+}
+
+}  // namespace
+
+cudaError_t kernels_num_sms(int device, int* sms) {
+    if (device < 0 || device >= RT_MAX_DEVICES) return cudaErrorInvalidDevice;
+    DeviceState& d = g_dev[device];
+    std::lock_guard<std::mutex> lock(d.mu);
+    if (d.sms == 0) {
+        const cudaError_t e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess) { d.sms = 0; return e; }
+    }
+    *sms = d.sms;
     return cudaSuccess;
 }
 
-static std::mutex g_configure_mutex;  // the wavefront lanes of one render configure from their own host threads
+constexpr size_t RT_EXTEND_ALL_MAX_SMEM = 100u * 1024u;
 
-cudaError_t kernels_configure(int device, size_t scene_bytes, size_t shade_bytes, size_t fr_bytes) {
-    std::lock_guard<std::mutex> lock(g_configure_mutex);
-    cudaError_t e = kernels_init(device);
+// The calling thread must have `device` current.
+cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_bytes, size_t shade_bytes, size_t fr_bytes, SceneLaunch& L) {
+    L = SceneLaunch();
+    cudaError_t e = kernels_num_sms(device, &L.num_sms);
     if (e != cudaSuccess) return e;
-    if (fr_bytes && fr_bytes != g_rects_smem) {
-        e = cudaFuncSetAttribute(k_extend_rects, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fr_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_rects_blocks_per_sm, k_extend_rects, RT_EXTEND_BLOCK, fr_bytes);
-        if (e != cudaSuccess) return e;
-        if (g_rects_blocks_per_sm < 1) g_rects_blocks_per_sm = 1;
-        g_rects_smem = fr_bytes;
+    DeviceState& d = g_dev[device];
+    std::lock_guard<std::mutex> lock(d.mu);
+    L.device = device;
+    L.scene_smem = scene_bytes;
+    L.extend_smem = scene_bytes + (size_t)RT_SMEM_STACK * RT_EXTEND_BLOCK * sizeof(uint32_t);
+    L.bvh_smem = L.extend_smem + (size_t)(RT_EXTEND_BLOCK / 32) * RT_FEED_WARP_BYTES;
+    L.shade_smem = shade_bytes;
+    L.rects_smem = fr_bytes;
+#define RT_TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
+    RT_TRY(grant(d, SLOT_EXTEND, k_extend<false, false>, L.extend_smem));
+    RT_TRY(grant(d, SLOT_EXTEND_COUNT, k_extend<true, false>, L.extend_smem));
+    RT_TRY(grant(d, SLOT_TRACE, k_trace, L.extend_smem));
+    RT_TRY(grant(d, SLOT_BVH, k_extend_bvh<false>, L.bvh_smem));
+    RT_TRY(grant(d, SLOT_BVH_COUNT, k_extend_bvh<true>, L.bvh_smem));
+    RT_TRY(occupancy(L.extend_blocks, k_extend<false, false>, RT_EXTEND_BLOCK, L.extend_smem));
+    RT_TRY(occupancy(L.trace_blocks, k_trace, RT_EXTEND_BLOCK, L.extend_smem));
+    RT_TRY(occupancy(L.bvh_blocks, k_extend_bvh<false>, RT_EXTEND_BLOCK, L.bvh_smem));
+    if (fr_bytes) {
+        RT_TRY(grant(d, SLOT_RECTS, k_extend_rects, fr_bytes));
+        RT_TRY(occupancy(L.rects_blocks, k_extend_rects, RT_EXTEND_BLOCK, fr_bytes));
     }
-    if (shade_bytes != g_shade_smem) {
-        e = cudaFuncSetAttribute(k_shade<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_shade<RT_SHADE_RAYS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shade_blocks_per_sm, k_shade<RT_SHADE_RAYS>, RT_SHADE_BLOCK, shade_bytes);
-        if (e != cudaSuccess) return e;
-        if (g_shade_blocks_per_sm < 1) g_shade_blocks_per_sm = 1;
-        e = cudaFuncSetAttribute(k_shade_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_shadep_blocks_per_sm, k_shade_pipe, RT_SHADEP_THREADS, shade_bytes);
-        if (e != cudaSuccess) return e;
-        if (g_shadep_blocks_per_sm < 1) g_shadep_blocks_per_sm = 1;
-        g_shade_smem = shade_bytes;
+    // both instantiations share one slot: the larger request covers the smaller
+    if (shade_bytes > d.granted[SLOT_SHADE] && shade_bytes > 48u * 1024u) {
+        RT_TRY(cudaFuncSetAttribute(k_shade<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes));
+        RT_TRY(cudaFuncSetAttribute(k_shade<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes));
+        d.granted[SLOT_SHADE] = shade_bytes;
     }
-    {
-        const char* sp = getenv("RT_B200_SHADE_PIPE");
-        g_shade_pipe = sp ? atoi(sp) : RT_SHADE_PIPE_DEFAULT;
+    RT_TRY(occupancy(L.shade_blocks, k_shade<1>, RT_SHADE_BLOCK, shade_bytes));
+    RT_TRY(occupancy(L.shade2_blocks, k_shade<2>, RT_SHADE_BLOCK, shade_bytes));
+    // whole tree + heads in shared memory in the octant-ready layout, as long as that keeps the occupancy of the general kernel
+    L.all_staged = S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && !S.root_is_leaf;
+    if (L.all_staged) {
+        L.all_smem = extend_all_smem_bytes(S);
+        if (L.all_smem > RT_EXTEND_ALL_MAX_SMEM) L.all_staged = false;
+        else {
+            RT_TRY(grant(d, SLOT_EXTEND_ALL, k_extend<false, true>, L.all_smem));
+            RT_TRY(occupancy(L.all_blocks, k_extend<false, true>, RT_EXTEND_ALL_BLOCK, L.all_smem));
+            if (L.all_blocks * RT_EXTEND_ALL_BLOCK < L.extend_blocks * RT_EXTEND_BLOCK) L.all_staged = false;
+        }
     }
-    const size_t staged_bytes = scene_bytes + (size_t)RT_SMEM_STACK * RT_EXTEND_BLOCK * sizeof(uint32_t);
-    if (staged_bytes != g_extend_smem) {
-        e = cudaFuncSetAttribute(k_extend<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_extend<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_extend_blocks_per_sm, k_extend<false, false>, RT_EXTEND_BLOCK, staged_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_trace_blocks_per_sm, k_trace, RT_EXTEND_BLOCK, staged_bytes);
-        if (e != cudaSuccess) return e;
-        if (g_extend_blocks_per_sm < 1) g_extend_blocks_per_sm = 1;
-        if (g_trace_blocks_per_sm < 1) g_trace_blocks_per_sm = 1;
-        g_extend_smem = staged_bytes;
-        // persistent form: + the per-warp ray double buffers
-        g_scene_smem = scene_bytes;
-        g_bvh_smem = staged_bytes + (size_t)(RT_EXTEND_BLOCK / 32) * RT_FEED_WARP_BYTES;
-        e = cudaFuncSetAttribute(k_extend_bvh<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_bvh_smem);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_extend_bvh<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_bvh_smem);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_bvh_blocks_per_sm, k_extend_bvh<false>, RT_EXTEND_BLOCK, g_bvh_smem);
-        if (e != cudaSuccess) return e;
-        if (g_bvh_blocks_per_sm < 1) g_bvh_blocks_per_sm = 1;
-    }
-    static bool all_attr_set = false;
-    if (!all_attr_set) {
-        e = cudaFuncSetAttribute(k_extend<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RT_EXTEND_ALL_MAX_SMEM);
-        if (e != cudaSuccess) return e;
-        all_attr_set = true;
-    }
-    {  // 0: never, 1: always (where a tree exists), 2 (default): trees that do not fit shared memory by far; re-read per
-       // scene so that tests can compare the two forms in one process
-        const char* pe = getenv("RT_B200_PERSISTENT");
-        g_persistent = pe ? atoi(pe) : 2;
-        const char* gd = getenv("RT_B200_GRID_DIV");
-        g_grid_div = gd && atoi(gd) >= 1 && atoi(gd) <= 4 ? atoi(gd) : 1;
-        const char* r2 = getenv("RT_B200_SHADE_RAYS2");
-        g_shade_rays2 = r2 ? atoi(r2) : 1;
-        const char* gb = getenv("RT_B200_GEN_BLOCKS");
-        const char* ab = getenv("RT_B200_ACC_BLOCKS");
-        g_gen_blocks = gb && atoi(gb) >= 1 && atoi(gb) <= 16 ? atoi(gb) : 4;
-        g_acc_blocks = ab && atoi(ab) >= 1 && atoi(ab) <= 16 ? atoi(ab) : 8;
-    }
+#undef RT_TRY
     return cudaSuccess;
 }
-
-int kernels_num_sms() { return g_num_sms; }
-
-static inline int sub_grid(int blocks_per_sm) { return blocks_per_sm / g_grid_div > 0 ? blocks_per_sm / g_grid_div : 1; }
 
 // Tail of a render: once every path has been issued the queue only shrinks, and the host knows an upper bound of what is left from
-// its last status poll.  A full persistent grid (hundreds of blocks, each staging its tables) for a few thousand rays costs ~2 us more
-// per launch than the blocks the rays need; the ~50 iterations of a depth-50 tail are all of that kind.  Per host thread (each
-// wavefront lane launches from its own).
-static thread_local uint32_t t_work_hint = 0xFFFFFFFFu;
-void kernels_set_work_hint(uint32_t rays_upper_bound) { t_work_hint = rays_upper_bound; }
-static inline int fit_grid(int full_grid, int threads) {
-    if (t_work_hint == 0xFFFFFFFFu) return full_grid;
-    const uint64_t need = ((uint64_t)t_work_hint + (uint32_t)threads - 1u) / (uint32_t)threads;
+// its last status poll (Launch::work_hint).  A full persistent grid (hundreds of blocks, each staging its tables) for a few thousand
+// rays costs ~2 us more per launch than the blocks the rays need; the ~50 iterations of a depth-50 tail are all of that kind.
+static inline int fit_grid(const Launch& L, int full_grid, int threads) {
+    if (L.work_hint == RT_WORK_UNKNOWN) return full_grid;
+    const uint64_t need = ((uint64_t)L.work_hint + (uint32_t)threads - 1u) / (uint32_t)threads;
     return (int)(need < 1u ? 1u : (need < (uint64_t)full_grid ? need : (uint64_t)full_grid));
 }
 
-void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st) {
-    k_generate<<<t_work_hint == 0xFFFFFFFFu ? g_num_sms * g_gen_blocks : 1, 256, 0, st>>>(rc, q, wc, k);  // nothing left to issue: thread 0 rolls the counters
+void launch_generate(const Launch& L, const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k) {
+    // nothing left to issue: thread 0 rolls the counters
+    k_generate<<<L.work_hint == RT_WORK_UNKNOWN ? L.sl->num_sms * L.opt->gen_blocks : 1, 256, 0, L.st>>>(rc, q, wc, k);
 }
-void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
-                   bool count_work, cudaStream_t st) {
-    if (S.fr_n && !count_work) { k_extend_rects<<<fit_grid(g_num_sms * sub_grid(g_rects_blocks_per_sm), RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, g_rects_smem, st>>>(S, q, hits, wc, k); return; }
+void launch_extend(const Launch& L, const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
+                   bool count_work) {
+    const SceneLaunch& sl = *L.sl;
+    const int sms = sl.num_sms;
+    if (S.fr_n && !count_work) {
+        k_extend_rects<<<fit_grid(L, sms * sl.rects_blocks, RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, sl.rects_smem, L.st>>>(S, q, hits, wc, k);
+        return;
+    }
     // The persistent form pays where rays are long and uneven (1 M spheres: 69 box tests per ray, +20 %); on trees that
     // live in shared memory (book-one: 18 box tests) the per-ray set-up at partial warp occupancy costs more than the
     // idle lanes it saves (r1e: 7.1 vs 12.6 Grays/s), so those keep one ray per thread.
-    const bool persistent = g_persistent == 1 || (g_persistent == 2 && S.n_nodes >= RT_PERSISTENT_MIN_NODES);
+    const bool persistent = L.opt->persistent == 1 || (L.opt->persistent == 2 && S.n_nodes >= RT_PERSISTENT_MIN_NODES);
     if (persistent && S.n_small == 0u && !S.root_is_leaf && S.n_nodes > 0u) {
-        const int grid = g_num_sms * g_bvh_blocks_per_sm;
-        if (count_work) k_extend_bvh<true><<<grid, RT_EXTEND_BLOCK, g_bvh_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)g_scene_smem);
-        else k_extend_bvh<false><<<grid, RT_EXTEND_BLOCK, g_bvh_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)g_scene_smem);
+        const int grid = sms * sl.bvh_blocks;
+        if (count_work) k_extend_bvh<true><<<grid, RT_EXTEND_BLOCK, sl.bvh_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)sl.scene_smem);
+        else k_extend_bvh<false><<<grid, RT_EXTEND_BLOCK, sl.bvh_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)sl.scene_smem);
         return;
     }
-    const int grid = g_num_sms * g_extend_blocks_per_sm;
-    // whole tree + heads in shared memory in the octant-ready layout, as long as that keeps the occupancy of the general kernel
-    bool all_staged = !count_work && S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && !S.root_is_leaf;
-    size_t all_bytes = 0;
-    int all_blocks = 0;
-    if (all_staged) {
-        all_bytes = extend_all_smem_bytes(S);
-        if (all_bytes > RT_EXTEND_ALL_MAX_SMEM) all_staged = false;
-        else {
-            std::lock_guard<std::mutex> lock(g_configure_mutex);
-            if (all_bytes != g_all_smem) {
-                int blocks = 0;
-                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, k_extend<false, true>, RT_EXTEND_ALL_BLOCK, all_bytes) != cudaSuccess) blocks = 0;
-                g_all_blocks_per_sm = blocks;
-                g_all_smem = all_bytes;
-            }
-            all_blocks = g_all_blocks_per_sm;
-        }
-        if (all_staged && all_blocks * RT_EXTEND_ALL_BLOCK < g_extend_blocks_per_sm * RT_EXTEND_BLOCK) all_staged = false;
-    }
-    if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else if (all_staged) k_extend<false, true><<<fit_grid(g_num_sms * sub_grid(all_blocks), RT_EXTEND_ALL_BLOCK), RT_EXTEND_ALL_BLOCK, all_bytes, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else k_extend<false, false><<<fit_grid(grid, RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    const int grid = sms * sl.extend_blocks;
+    if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else if (sl.all_staged) k_extend<false, true><<<fit_grid(L, sms * sl.all_blocks, RT_EXTEND_ALL_BLOCK), RT_EXTEND_ALL_BLOCK, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else k_extend<false, false><<<fit_grid(L, grid, RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
 }
-void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
-                  WaveCounters* wc, uint32_t k, cudaStream_t st) {
-    if (g_shade_pipe) k_shade_pipe<<<g_num_sms * g_shadep_blocks_per_sm, RT_SHADEP_THREADS, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+void launch_shade(const Launch& L, const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
+                  WaveCounters* wc, uint32_t k) {
+    const SceneLaunch& sl = *L.sl;
     // two rays per thread per barrier round where shading is light on registers (small all-rectangle scenes: no f64 sphere re-solve);
     // +5 % there, -7 % on the sphere scenes (r1f), hence per scene
-    else if (S.fr_n && g_shade_rays2) k_shade<2><<<fit_grid(g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
-    else k_shade<RT_SHADE_RAYS><<<fit_grid(g_num_sms * sub_grid(g_shade_blocks_per_sm), RT_SHADE_BLOCK), RT_SHADE_BLOCK, g_shade_smem, st>>>(S, rc, qin, qout, hits, done, wc, k);
+    if (S.fr_n && L.opt->shade_rays2) k_shade<2><<<fit_grid(L, sl.num_sms * sl.shade2_blocks, 2 * RT_SHADE_BLOCK), RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+    else k_shade<1><<<fit_grid(L, sl.num_sms * sl.shade_blocks, RT_SHADE_BLOCK), RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
 }
-void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st) {
-    k_accumulate<<<fit_grid(g_num_sms * g_acc_blocks, 256), 256, 0, st>>>(rc, done, wc, k, sum, sumsq);
+void launch_accumulate(const Launch& L, const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq) {
+    k_accumulate<<<fit_grid(L, L.sl->num_sms * L.opt->acc_blocks, 256), 256, 0, L.st>>>(rc, done, wc, k, sum, sumsq);
 }
-void launch_finish(const double* acc, size_t n, float* out, cudaStream_t st) { k_finish<<<g_num_sms * 4, 256, 0, st>>>(acc, n, out); }
-void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st) {
-    k_resolve_u8<<<g_num_sms * 4, 256, 0, st>>>(sum, width, height, 1.0f / (float)spp, out);
+void launch_finish(int sms, const double* acc, size_t n, float* out, cudaStream_t st) { k_finish<<<sms * 4, 256, 0, st>>>(acc, n, out); }
+void launch_resolve_u8(int sms, const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st) {
+    k_resolve_u8<<<sms * 4, 256, 0, st>>>(sum, width, height, (double)spp, out);
 }
-void launch_deinterleave(const float* gathered, float* full, uint32_t width, uint32_t height, uint32_t n_shards, cudaStream_t st) {
+void launch_deinterleave(int sms, const float* gathered, float* full, uint32_t width, uint32_t height, uint32_t n_shards, cudaStream_t st) {
     const uint32_t rows_padded = (height + n_shards - 1) / n_shards;
-    k_deinterleave<<<g_num_sms * 4, 256, 0, st>>>(gathered, full, width, height, n_shards, rows_padded);
+    k_deinterleave<<<sms * 4, 256, 0, st>>>(gathered, full, width, height, n_shards, rows_padded);
 }
-void launch_trace(const DScene& S, const RtRayIn* rays, uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* out, cudaStream_t st) {
-    k_trace<<<g_num_sms * g_trace_blocks_per_sm, RT_EXTEND_BLOCK, g_extend_smem, st>>>(S, rays, n, seed_lo, seed_hi, out);
+void launch_trace(const SceneLaunch& sl, const DScene& S, const RtRayIn* rays, const uint32_t* self_order, uint64_t n, uint32_t seed_lo, uint32_t seed_hi,
+                  RtHitOut* out, cudaStream_t st) {
+    k_trace<<<sl.num_sms * sl.trace_blocks, RT_EXTEND_BLOCK, sl.extend_smem, st>>>(S, rays, self_order, n, seed_lo, seed_hi, out);
 }
 
 }  // namespace rtb

@@ -24,17 +24,11 @@
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 8
 #endif
-#ifndef RT_SHADE_RAYS
-#define RT_SHADE_RAYS 1   // rays shaded per thread per block round (one barrier pair / atomic pair per round)
-#endif
 #ifndef RT_REFILL_MIN
 #define RT_REFILL_MIN 16     // persistent extend: idle lanes of a warp fetch new rays once at least this many are idle
 #endif
 #ifndef RT_PERSISTENT_MIN_NODES
 #define RT_PERSISTENT_MIN_NODES 65536u  // BVH size from which extend runs in its persistent, lane-refilling form
-#endif
-#ifndef RT_SHADE_PIPE_DEFAULT
-#define RT_SHADE_PIPE_DEFAULT 0  // 1: shade runs in its warp-specialised form (k_shade_pipe); RT_B200_SHADE_PIPE=0|1 overrides
 #endif
 #ifndef RT_LEAF_MIN
 #define RT_LEAF_MIN 8        // persistent extend: pending leaf ranges are intersected once this many lanes hold one
@@ -54,24 +48,48 @@
 
 namespace rtb {
 
-// Must be called before the launches of a scene; `staged_bytes` = shared-memory bytes of the scene prefix staged by
-// extend / trace, `fr_bytes` = bytes of the frame-rect table staged by k_extend_rects (0: none), `shade_bytes` = shared-memory bytes of the material / primitive tables staged by shade.
-cudaError_t kernels_configure(int device, size_t staged_bytes, size_t shade_bytes, size_t fr_bytes);
-// SM count only (kernels without dynamic shared memory).
-cudaError_t kernels_init(int device);
-int kernels_num_sms();
+constexpr uint32_t RT_WORK_UNKNOWN = 0xFFFFFFFFu;
 
-// upper bound of the rays left in the queue once every path has been issued (0xFFFFFFFF = unknown: full grids); per host thread
-void kernels_set_work_hint(uint32_t rays_upper_bound);
-void launch_generate(const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k, cudaStream_t st);
-void launch_extend(const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
-                   bool count_work, cudaStream_t st);
-void launch_shade(const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
-                  WaveCounters* wc, uint32_t k, cudaStream_t st);
-void launch_accumulate(const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq, cudaStream_t st);
-void launch_finish(const double* acc, size_t n, float* out, cudaStream_t st);
-void launch_resolve_u8(const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st);
-void launch_deinterleave(const float* gathered, float* full, uint32_t width, uint32_t height, uint32_t n_shards, cudaStream_t st);
-void launch_trace(const DScene& S, const RtRayIn* rays, uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* out, cudaStream_t st);
+// Tuning options of a context.  rt_init reads the RT_B200_* environment variables ONCE into this struct (RtInitOptions of the C ABI
+// overrides them); nothing is re-read per render.
+struct LaunchOptions {
+    int persistent = 2;   // extend in its persistent lane-refilling form: 0 never, 1 always (where a tree exists), 2 from RT_PERSISTENT_MIN_NODES nodes
+    int shade_rays2 = 1;  // two rays per thread per barrier round in k_shade on small all-rectangle scenes
+    int gen_blocks = 4, acc_blocks = 8;  // blocks per SM of k_generate / k_accumulate
+};
+
+// Launch configuration of ONE scene on ONE device: dynamic shared-memory bytes of the tables each kernel stages and the resident
+// blocks per SM at those sizes.  Owned by the scene (capi.cu RtScene), filled by kernels_configure_scene.
+struct SceneLaunch {
+    int device = -1, num_sms = 0;
+    size_t scene_smem = 0, extend_smem = 0, bvh_smem = 0, shade_smem = 0, rects_smem = 0, all_smem = 0;
+    int extend_blocks = 1, trace_blocks = 1, bvh_blocks = 1, shade_blocks = 1, shade2_blocks = 1, rects_blocks = 1, all_blocks = 1;
+    bool all_staged = false;  // k_extend<., true>: whole tree + heads in shared memory, octant-ready records
+};
+
+// One launch site: whose scene, which options, on which stream, and (tail of a render) an upper bound of the rays left in the queue.
+struct Launch {
+    const SceneLaunch* sl;
+    const LaunchOptions* opt;
+    uint32_t work_hint;  // RT_WORK_UNKNOWN: full grids
+    cudaStream_t st;
+};
+
+// `device` must be current in the calling thread.  staged_bytes = shared-memory bytes of the scene prefix staged by extend / trace,
+// shade_bytes = material / primitive tables staged by shade, fr_bytes = frame-rect table of k_extend_rects (0: none).
+cudaError_t kernels_configure_scene(int device, const DScene& S, size_t staged_bytes, size_t shade_bytes, size_t fr_bytes, SceneLaunch& out);
+cudaError_t kernels_num_sms(int device, int* sms);
+
+void launch_generate(const Launch& L, const RenderConst& rc, const RayQueue& q, WaveCounters* wc, uint32_t k);
+void launch_extend(const Launch& L, const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
+                   bool count_work);
+void launch_shade(const Launch& L, const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
+                  WaveCounters* wc, uint32_t k);
+void launch_accumulate(const Launch& L, const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq);
+void launch_finish(int sms, const double* acc, size_t n, float* out, cudaStream_t st);
+void launch_resolve_u8(int sms, const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st);
+void launch_deinterleave(int sms, const float* gathered, float* full, uint32_t width, uint32_t height, uint32_t n_shards, cudaStream_t st);
+void launch_trace(const SceneLaunch& sl, const DScene& S, const RtRayIn* rays, const uint32_t* self_order, uint64_t n, uint32_t seed_lo, uint32_t seed_hi,
+                  RtHitOut* out, cudaStream_t st);
 
 }  // namespace rtb

@@ -82,9 +82,28 @@ __device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, flo
         return h;
     }
     const RtPrim* __restrict__ g = &S.gen[__float_as_uint(head.x)];
+    const uint32_t kind = g->kind;
+    if (kind == RT_PRIM_MEDIUM) {
+        // redo both boundary probes (same arithmetic as extend): which surfaces, where, which branch
+        MediumProbe pr;
+        pr.t1 = pr.t2 = 0.0f; pr.i1 = pr.i2 = 0u; pr.entering = false;
+        medium_generic_hit(S.bnd, g->aux, (uint32_t)g->param[2], o, d, g->param[1], g->order, key, &pr);
+        float u1 = 0.0f, v1 = 0.0f, u2 = 0.0f, v2 = 0.0f;
+        const float3 n1 = boundary_normal(S.bnd, pr.i1, o, d, pr.t1, want_uv ? &u1 : nullptr, &v1);
+        if (pr.entering) {
+            const float3 n2 = boundary_normal(S.bnd, pr.i2, o, d, pr.t2, want_uv ? &u2 : nullptr, &v2);
+            h.p = fma3(pr.t1 + 1e-6f + t, d, o);  // volume.rs:69 on the shadowed ray (A.9 ii)
+            h.n = (n1 + n2) * 0.5f;
+            h.u = u1 + u2; h.v = v1 + v2;
+        } else {
+            h.p = fma3(t, d, o);
+            h.n = n1;
+            h.u = u1; h.v = v1;
+        }
+        return h;
+    }
     const float3 lo = xform_point(g->local_from_world, o);
     const float3 ld = xform_vector(g->local_from_world, d);
-    const uint32_t kind = g->kind;
     if (kind == RT_PRIM_SPHERE) {
         const float r = g->param[0];
         const float3 q = fma3(t, ld, lo) * (1.0f / r);

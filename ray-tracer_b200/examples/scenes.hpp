@@ -231,9 +231,61 @@ struct Scenes {
     }
     static CameraSpec stressCamera() { return {{0.0, 0.0, 180.0}, {0.0, 0.0, 0.0}, {0.0, 1.0, 0.0}, 40.0, 10.0, 0.0}; }
 
-    // Scene by name: "book-one", "cornell-box", "book-two", "stress:<count>".  Returns false on an unknown name.
-    static bool byName(const std::string& name, uint64_t seed, List* out, CameraSpec* cam) {
+    // ---- parity scene for the node / texture kinds none of the examples uses (not a BASELINE config) ----------------
+    // Vec<Arc<dyn Bound>> as the WORLD ROOT, as an inner node and as a Sprite's geometry (src/geometry.rs:76-116,
+    // src/optimize.rs:256-334); CheckerTexture, nested once, on a rectangle, on a sphere, under a Metal and as an emitter
+    // (src/material.rs:217-245); a ConstantMedium bounded by a Cube instead of a Sphere (src/volume.rs:40-43 takes any Hit; the
+    // book's smoke boxes); a thin lens.  The returned list is the world itself — no BoundingVolumeHierarchyNode::new around it.
+    static List checkerLists(SceneRng& generator) {
+        const Vec3 ex(1.0, 0.0, 0.0), ey(0.0, 1.0, 0.0), ez(0.0, 0.0, 1.0);
+        auto solidTex = [](double r, double g, double b) { return std::shared_ptr<const typename A::Texture>(std::make_shared<typename A::SolidColor>(Vec3(r, g, b))); };
+        auto checker = [](std::shared_ptr<const typename A::Texture> black, std::shared_ptr<const typename A::Texture> white) {
+            return std::shared_ptr<const typename A::Texture>(std::make_shared<typename A::CheckerTexture>(std::move(black), std::move(white)));
+        };
+        auto inner = checker(solidTex(0.9, 0.9, 0.9), solidTex(0.8, 0.2, 0.2));
+        auto nested = checker(solidTex(0.2, 0.3, 0.1), inner);  // CheckerTexture whose "white" child is a CheckerTexture
+        List world;
+        world.push_back(sprite(rect(60.0, 60.0), std::make_shared<typename A::Lambertian>(nested),
+                               Mat4::rotation(to_radians(-90.0), ex)));  // floor, normal +y
+        auto group = std::make_shared<typename A::HitList>();         // a Vec as an inner node
+        group->items.push_back(sprite(sphere(3.0), std::make_shared<typename A::Lambertian>(inner), Mat4::translation(Vec3(-6.0, 3.0, 0.0))));
+        group->items.push_back(sprite(sphere(2.0), std::make_shared<typename A::Metal>(nested, 0.1),
+                                      Mat4::translation(Vec3(0.0, 2.0, 4.0)).multiplied(Mat4::rotation(to_radians(40.0), ez))));  // rotated: uv turns with it
+        group->items.push_back(sprite(sphere(2.5), std::make_shared<typename A::Dielectric>(1.5), Mat4::translation(Vec3(5.0, 2.5, -2.0))));
+        world.push_back(group);
+        List small;
+        for (int k = 0; k < 12; ++k) {
+            const double x = generator.gen_range(-12.0, 12.0), z = generator.gen_range(-9.0, 9.0), which = generator.gen_range(0.0, 1.0);
+            const double r = generator.gen_range(0.2, 1.0), gcol = generator.gen_range(0.2, 1.0), b = generator.gen_range(0.2, 1.0);
+            if (which < 0.5) small.push_back(sprite(sphere(0.7), std::make_shared<typename A::Lambertian>(Vec3(r, gcol, b)), Mat4::translation(Vec3(x, 0.7, z))));
+            else if (which < 0.8) small.push_back(sprite(sphere(0.7), std::make_shared<typename A::Metal>(Vec3(r, gcol, b), 0.3), Mat4::translation(Vec3(x, 0.7, z))));
+            else small.push_back(sprite(sphere(0.7), std::make_shared<typename A::Dielectric>(1.5), Mat4::translation(Vec3(x, 0.7, z))));
+        }
+        world.push_back(A::BoundingVolumeHierarchyNode::make(small));  // a BVH inside the list
+        auto tent = std::make_shared<typename A::HitList>();           // a Vec as the geometry of a Sprite
+        tent->items.push_back(std::make_shared<typename A::TransformedGeometry>(
+            rect(4.0, 5.0), Mat4::translation(Vec3(-1.2, 2.0, 0.0)).multiplied(Mat4::rotation(to_radians(-60.0), ey))));
+        tent->items.push_back(std::make_shared<typename A::TransformedGeometry>(
+            rect(4.0, 5.0), Mat4::translation(Vec3(1.2, 2.0, 0.0)).multiplied(Mat4::rotation(to_radians(60.0), ey))));
+        world.push_back(sprite(tent, std::make_shared<typename A::Lambertian>(Vec3(0.3, 0.4, 0.8)),
+                               Mat4::translation(Vec3(9.0, 0.5, 6.0)).multiplied(Mat4::rotation(to_radians(25.0), ey))));
+        world.push_back(sprite(rect(20.0, 20.0), std::make_shared<typename A::DiffuseLight>(checker(solidTex(6.0, 6.0, 6.0), solidTex(1.0, 2.0, 6.0))),
+                               Mat4::translation(Vec3(0.0, 20.0, 0.0)).multiplied(Mat4::rotation(to_radians(90.0), ex))));  // light, normal -y
+        world.push_back(sprite(sphere(500.0), std::make_shared<typename A::DiffuseLight>(Vec3(0.15, 0.2, 0.3))));        // sky
+        auto faces = A::Cube::make(5.0, 4.0, 5.0);
+        world.push_back(sprite(std::make_shared<typename A::ConstantMedium>(A::BoundingVolumeHierarchyNode::make(List(faces.begin(), faces.end())), 0.35),
+                               std::make_shared<typename A::Isotropic>(Vec3(0.9, 0.9, 0.95)),
+                               Mat4::translation(Vec3(-3.0, 2.01, -7.0)).multiplied(Mat4::rotation(to_radians(30.0), ey))));  // smoke box
+        return world;
+    }
+    static CameraSpec checkerListsCamera() { return {{0.0, 9.0, -26.0}, {0.0, 3.0, 0.0}, {0.0, 1.0, 0.0}, 35.0, 10.0, 0.02}; }
+
+    // Scene by name: "book-one", "cornell-box", "book-two", "stress:<count>", "checker-lists".  Returns false on an unknown name.
+    // *rootIsList: the world is the returned Vec itself (impl Hit / Bound for Vec), not a BoundingVolumeHierarchyNode over it.
+    static bool byName(const std::string& name, uint64_t seed, List* out, CameraSpec* cam, bool* rootIsList = nullptr) {
         SceneRng g(seed);
+        if (rootIsList) *rootIsList = false;
+        if (name == "checker-lists") { *out = checkerLists(g); *cam = checkerListsCamera(); if (rootIsList) *rootIsList = true; return true; }
         if (name == "book-one") { *out = bookOne(g); *cam = bookOneCamera(); return true; }
         if (name == "cornell-box") { *out = cornellBox(); *cam = cornellBoxCamera(); return true; }
         if (name == "book-two") { *out = bookTwo(g); *cam = bookTwoCamera(); return true; }

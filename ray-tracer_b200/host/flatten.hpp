@@ -27,6 +27,7 @@ struct FlatScene {
     std::vector<RtMaterial> materials;
     std::vector<RtTexture> textures;
     std::vector<float> texels;  // RGBA f32
+    std::vector<RtPrim> boundary_prims;  // boundary surfaces of RT_PRIM_MEDIUM primitives (ConstantMedium over anything but a Sphere)
     uint32_t leaves_visited = 0;  // DFS ranks handed out (>= prims.size(): singular transforms are dropped)
     RtSceneDesc desc() const {
         RtSceneDesc d{};
@@ -34,6 +35,7 @@ struct FlatScene {
         d.n_prims = (uint32_t)prims.size(); d.n_materials = (uint32_t)materials.size(); d.n_textures = (uint32_t)textures.size();
         d.prims = prims.data(); d.materials = materials.data(); d.textures = textures.data();
         d.texels = texels.data(); d.n_texels = texels.size() / 4;
+        d.boundary_prims = boundary_prims.data(); d.n_boundary_prims = (uint32_t)boundary_prims.size();
         return d;
     }
 };
@@ -42,6 +44,7 @@ struct FlattenCtx {
     FlatScene out;
     std::unordered_map<const Material*, int32_t> materialIds;
     std::unordered_map<const Texture*, int32_t> textureIds;
+    bool inBoundary = false;  // flattening the boundary of a ConstantMedium: leaves go to boundary_prims and take no DFS rank
 
     int32_t internTexture(const Texture* t) {
         if (!t) throw FlattenError("material without texture");
@@ -98,8 +101,19 @@ struct FlattenCtx {
     }
 
     void leaf(uint32_t kind, const FlattenState& st, double p0, double p1) {
-        const uint32_t order = out.leaves_visited++;
         const auto inv = st.worldFromLocal.inversed();
+        if (inBoundary) {  // a surface of a medium's boundary: never hit on its own, carries no material and no rank
+            if (!inv) return;
+            RtPrim p{};
+            p.kind = kind;
+            p.material = -1;
+            p.param[0] = (float)p0; p.param[1] = (float)p1;
+            affine(*inv, p.local_from_world);
+            affine(st.worldFromLocal, p.world_from_local);
+            out.boundary_prims.push_back(p);
+            return;
+        }
+        const uint32_t order = out.leaves_visited++;
         if (!inv) return;  // det == 0: the sprite is never hit (src/sprite.rs:131-134); the rank stays reserved
         RtPrim p{};
         p.kind = kind;
@@ -108,6 +122,30 @@ struct FlattenCtx {
         p.param[0] = (float)p0; p.param[1] = (float)p1;
         affine(*inv, p.local_from_world);
         affine(st.worldFromLocal, p.world_from_local);
+        out.prims.push_back(p);
+    }
+
+    // ConstantMedium<T> over a boundary that is not a plain Sphere (src/volume.rs:40-43 accepts any Hit): the boundary subtree is
+    // flattened into `boundary_prims` (world-space transforms, DFS = list order) and ONE primitive stands for the medium.
+    void mediumOver(const Bound& boundary, const FlattenState& st, double density) {
+        if (inBoundary) throw FlattenError("ConstantMedium inside the boundary of a ConstantMedium has no device implementation");
+        const uint32_t order = out.leaves_visited++;
+        const uint32_t first = (uint32_t)out.boundary_prims.size();
+        inBoundary = true;
+        try { boundary.flatten(*this, st); } catch (...) { inBoundary = false; throw; }
+        inBoundary = false;
+        const uint32_t count = (uint32_t)out.boundary_prims.size() - first;
+        if (count == 0) return;  // boundary never hit: neither is the medium
+        if (count >= (1u << 24)) throw FlattenError("ConstantMedium boundary with 2^24 or more surfaces");
+        RtPrim p{};
+        p.kind = RT_PRIM_MEDIUM;
+        p.material = internMaterial(st.material);
+        p.order = order;
+        p.aux = first;
+        p.param[1] = (float)density;
+        p.param[2] = (float)count;
+        affine(Mat4::identity(), p.local_from_world);  // the boundary surfaces carry the transforms
+        affine(Mat4::identity(), p.world_from_local);
         out.prims.push_back(p);
     }
 };
@@ -128,9 +166,9 @@ inline void Sprite::flatten(FlattenCtx& ctx, const FlattenState& st) const {
     geometry_->flatten(ctx, inner);
 }
 inline void ConstantMedium::flatten(FlattenCtx& ctx, const FlattenState& st) const {
-    auto s = dynamic_cast<const Sphere*>(boundary.get());
-    if (!s) throw FlattenError("ConstantMedium: only a Sphere boundary has a device implementation");
-    ctx.leaf(RT_PRIM_MEDIUM_SPHERE, st, s->radius, density);
+    if (ctx.inBoundary) throw FlattenError("ConstantMedium inside the boundary of a ConstantMedium has no device implementation");
+    if (auto s = dynamic_cast<const Sphere*>(boundary.get())) ctx.leaf(RT_PRIM_MEDIUM_SPHERE, st, s->radius, density);  // analytic two-root form
+    else ctx.mediumOver(*boundary, st, density);
 }
 
 inline FlatScene flattenWorld(const Bound& world) {

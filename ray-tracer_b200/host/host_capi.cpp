@@ -31,6 +31,10 @@ struct HostApi {  // the type bundle scenes.hpp is instantiated with
     using ImageTexture = rtb::host::ImageTexture;
     static void setBakeSize(ImageTexture& t, uint32_t w, uint32_t h) { t.bakeWidth = w; t.bakeHeight = h; }
     using CheckerTexture = rtb::host::CheckerTexture;
+    using Texture = rtb::host::Texture;
+    using SolidColor = rtb::host::SolidColor;
+    using HitList = rtb::host::HitList;
+    using TransformedGeometry = rtb::host::TransformedGeometry;
 };
 
 thread_local std::string g_host_error;
@@ -52,9 +56,14 @@ int rth_example_scene(const char* name, uint64_t seed, RthFlatScene** out) {
         std::vector<rtb::host::BoundPtr> list;
         rtb::host::BuildAxisStream axes(seed ^ 0xA11CE5EEDull);
         rtb::host::currentAxisStream() = &axes;
-        const bool ok = rtscenes::Scenes<HostApi>::byName(name, seed, &list, &res->cam);
-        std::shared_ptr<const rtb::host::BoundingVolumeHierarchyNode> world;
-        if (ok) world = rtb::host::BoundingVolumeHierarchyNode::make(list);  // examples/book-one.rs:32
+        bool rootIsList = false;
+        const bool ok = rtscenes::Scenes<HostApi>::byName(name, seed, &list, &res->cam, &rootIsList);
+        rtb::host::BoundPtr world;
+        if (ok && rootIsList) {  // the world is the Vec itself (impl Hit / Bound for Vec, src/geometry.rs:76-116)
+            auto l = std::make_shared<rtb::host::HitList>();
+            l->items = list;
+            world = l;
+        } else if (ok) world = rtb::host::BoundingVolumeHierarchyNode::make(list);  // examples/book-one.rs:32
         rtb::host::currentAxisStream() = nullptr;
         if (!ok || !world) return RT_ERR_INVALID;
         res->flat = rtb::host::flattenWorld(*world);

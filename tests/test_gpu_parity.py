@@ -67,7 +67,7 @@ def test_trace_matches_golden_fixture(rt, device, name):
 
 
 @pytest.mark.parametrize("name,w,h,n_bounce", [("book-one", 96, 54, 20000), ("cornell-box", 64, 64, 20000), ("book-two", 64, 64, 20000),
-                                              ("stress:100000", 64, 36, 20000)])
+                                              ("stress:100000", 64, 36, 20000), ("checker-lists", 96, 54, 20000)])
 def test_trace_matches_oracle_on_large_ray_sets(rt, orc, device, name, w, h, n_bounce):
     so = orc.Scene(name, 1)
     scene = rt.Scene.example(device, name, 1)
@@ -172,7 +172,8 @@ def test_error_paths_on_device(rt, device):
                          row_stride=args.get("row_stride", 1))
 
 
-@pytest.mark.parametrize("name,w,h,spp", [("book-one", 160, 90, 4), ("cornell-box", 96, 96, 8), ("book-two", 96, 96, 4), ("stress:20000", 96, 54, 4)])
+@pytest.mark.parametrize("name,w,h,spp", [("book-one", 160, 90, 4), ("cornell-box", 96, 96, 8), ("book-two", 96, 96, 4), ("stress:20000", 96, 54, 4),
+                                          ("checker-lists", 128, 72, 8)])
 def test_paired_paths_match_oracle(rt, orc, device, name, w, h, spp):
     """Same Philox keys on both sides: per-pixel sums agree path for path, except where an f32 rounding flips a
     discrete decision (Schlick coin, near-tie) somewhere along a path."""
@@ -207,7 +208,8 @@ def _psnr_resolved(mean_a, mean_b):
 
 
 @pytest.mark.parametrize("name,w,h,spp_gpu,spp_cpu,depth", [("book-one", 64, 36, 16384, 4096, 50), ("cornell-box", 32, 32, 131072, 32768, 50),
-                                                          ("book-two", 24, 24, 262144, 32768, 50), ("stress:20000", 48, 27, 16384, 2048, 16)])
+                                                          ("book-two", 24, 24, 262144, 32768, 50), ("stress:20000", 48, 27, 16384, 2048, 16),
+                                                          ("checker-lists", 48, 27, 32768, 8192, 50)])
 def test_image_statistics_against_high_spp_oracle(rt, orc, device, name, w, h, spp_gpu, spp_cpu, depth):
     """Gate 2.  The oracle renders with its FAITHFUL sampler (rejection sampling, sequential stream — the reference's
     algorithm) and a different seed: the two estimates are independent."""
@@ -265,8 +267,16 @@ def test_resolve_u8_matches_oracle(rt, orc, device):
     s, _, _ = scene.render(scene.flat.camera(64 / 36), 64, 36, 32, 50)
     got = device.resolve_u8(s, 32)
     want = orc.resolve_u8(s.astype(np.float64), 32)
-    d = np.abs(got.astype(np.int32) - want.astype(np.int32))
-    assert d.max() <= 1 and np.mean(d > 0) < 2e-3  # f32 vs f64 sqrt at a truncation boundary
+    assert np.array_equal(got, want)  # bytes are integer work: bit-exact (the kernel resolves in f64 like book-one.rs:95-97)
+    rng = np.random.default_rng(5)
+    # every byte boundary (mean = (k / 255)^2) and its f32 neighbours, spp values that do not divide evenly
+    k = np.arange(0, 300, dtype=np.float64)
+    for spp in (1, 3, 100, 1024, 1000003):
+        edge = np.float32(((k / 255.0) ** 2) * spp)
+        vals = np.concatenate([edge, np.nextafter(edge, np.float32(np.inf)), np.nextafter(edge, np.float32(-np.inf)),
+                               rng.uniform(0, 1.2 * spp, 3 * 5000).astype(np.float32)])
+        vals = np.resize(vals, (vals.size // 3 // 7) * 7 * 3).reshape(-1, 7, 3)
+        assert np.array_equal(device.resolve_u8(vals, spp), orc.resolve_u8(vals.astype(np.float64), spp)), spp
     special = np.array([[[np.nan, 4 * 4.0, 0.0], [4 * 0.25, -4.0, 4 * 1e-9]]], dtype=np.float32)
     assert np.array_equal(device.resolve_u8(special, 4), orc.resolve_u8(special.astype(np.float64), 4))
 
@@ -316,20 +326,15 @@ def test_render_sharded_single_rank_matches_render(rt, device):
 
 # ---- the specialised extend kernels against the general one (which the trace tests pin to the oracle) -------------
 
-def _render_with_env(rt, device, name, env, w, h, spp, depth=50, seed=3, tables=None, cam=None, queue_capacity=0):
-    old = {k: os.environ.get(k) for k in env}
-    os.environ.update(env)
-    try:
-        scene = rt.Scene.from_tables(device, *tables) if tables else rt.Scene.example(device, name, 1)
-        cam = cam if cam is not None else scene.flat.camera(w / h)
-        s, q, st = scene.render(cam, w, h, spp, depth, seed=seed, queue_capacity=queue_capacity)
-        scene.close()
-    finally:
-        for k, v in old.items():
-            if v is None:
-                os.environ.pop(k, None)
-            else:
-                os.environ[k] = v
+def _render_with(rt, device, name, w, h, spp, depth=50, seed=3, tables=None, cam=None, queue_capacity=0, scene_opts=None, flags=0, ctx_opts=None):
+    """One render with explicit options (RtSceneOptions / RtContextOptions keyword overrides, RtRenderParams.flags)."""
+    dev = rt.Device(0, options=ctx_opts) if ctx_opts is not None else device
+    scene = rt.Scene.from_tables(dev, *tables, options=scene_opts) if tables else rt.Scene.example(dev, name, 1, options=scene_opts)
+    cam = cam if cam is not None else scene.flat.camera(w / h)
+    s, q, st = scene.render(cam, w, h, spp, depth, seed=seed, queue_capacity=queue_capacity, flags=flags)
+    scene.close()
+    if ctx_opts is not None:
+        dev.close()
     return s, q, st
 
 
@@ -338,13 +343,13 @@ def _render_with_env(rt, device, name, env, w, h, spp, depth=50, seed=3, tables=
 def test_persistent_extend_matches_one_ray_per_thread(rt, device, name, w, h, spp):
     """k_extend_bvh (lane-refilling persistent warps, cp.async ray feed) and k_extend walk the same tree with the same
     arithmetic: identical closest hits, so identical paths — only the order of the f64 accumulations differs."""
-    a, qa, sa = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "0"}, w, h, spp)
-    b, qb, sb = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "1"}, w, h, spp)
+    a, qa, sa = _render_with(rt, device, name, w, h, spp, flags=rt.RENDER_EXTEND_PER_THREAD)
+    b, qb, sb = _render_with(rt, device, name, w, h, spp, flags=rt.RENDER_EXTEND_PERSISTENT)
     assert sa.rays == sb.rays and sa.paths == sb.paths
     assert np.allclose(a, b, rtol=1e-5, atol=1e-5) and np.allclose(qa, qb, rtol=1e-5, atol=1e-5)
     # a queue smaller than one feed range and one that is not a multiple of 32
-    c, _, sc = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "1"}, w, h, 1, queue_capacity=1056)
-    d, _, sd = _render_with_env(rt, device, name, {"RT_B200_PERSISTENT": "0"}, w, h, 1, queue_capacity=1056)
+    c, _, sc = _render_with(rt, device, name, w, h, 1, queue_capacity=1056, flags=rt.RENDER_EXTEND_PERSISTENT)
+    d, _, sd = _render_with(rt, device, name, w, h, 1, queue_capacity=1056, flags=rt.RENDER_EXTEND_PER_THREAD)
     assert sc.rays == sd.rays and np.allclose(c, d, rtol=1e-5, atol=1e-5)
 
 
@@ -379,8 +384,8 @@ def test_frame_rect_extend_matches_general_records(rt, device):
     """k_extend_rects (rectangles grouped by the frame they are axis-aligned in) against the general 64-byte rectangle
     records: cornell-box, and a random closed room with boxes in three tilted frames, face normals permuted and
     flipped, a coplanar pair (exact tie -> the DFS-earlier rectangle) and one frame used by a single rectangle."""
-    a, qa, sa = _render_with_env(rt, device, "cornell-box", {"RT_B200_RECT_FRAMES": "0"}, 96, 96, 16)
-    b, qb, sb = _render_with_env(rt, device, "cornell-box", {}, 96, 96, 16)
+    a, qa, sa = _render_with(rt, device, "cornell-box", 96, 96, 16, scene_opts={"flags": rt.SCENE_NO_FRAME_RECTS})
+    b, qb, sb = _render_with(rt, device, "cornell-box", 96, 96, 16)
     assert sa.rays == sb.rays
     assert np.allclose(a, b, rtol=2e-4, atol=2e-4) and np.allclose(qa, qb, rtol=5e-4, atol=5e-4)
 
@@ -411,8 +416,8 @@ def test_frame_rect_extend_matches_general_records(rt, device):
     tables = _rect_tables(rt, rects, mats)
     assert len(rects) <= 32
     cam = rt.make_camera(rt.camera_args([0, 0, -22], [0, 0, 0], [0, 1, 0], math.radians(30), 1.0, 1.0, 0.0))
-    a, qa, sa = _render_with_env(rt, device, None, {"RT_B200_RECT_FRAMES": "0"}, 96, 96, 16, depth=12, tables=tables, cam=cam)
-    b, qb, sb = _render_with_env(rt, device, None, {}, 96, 96, 16, depth=12, tables=tables, cam=cam)
+    a, qa, sa = _render_with(rt, device, None, 96, 96, 16, depth=12, tables=tables, cam=cam, scene_opts={"flags": rt.SCENE_NO_FRAME_RECTS})
+    b, qb, sb = _render_with(rt, device, None, 96, 96, 16, depth=12, tables=tables, cam=cam)
     assert sa.rays > 96 * 96 * 16 * 2  # paths do bounce
     # f32 rounding differs between the two formulations: a path may flip at a grazing edge, the image may not
     assert abs(int(sa.rays) - int(sb.rays)) <= 2e-3 * sa.rays
@@ -422,7 +427,7 @@ def test_frame_rect_extend_matches_general_records(rt, device):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["book-one", "cornell-box", "book-two"])
+@pytest.mark.parametrize("name", ["book-one", "cornell-box", "book-two", "checker-lists"])
 def test_color_rays_matches_oracle_color(rt, orc, device, name):
     """rt_color_rays — the reference's per-ray entry point render::color (src/render.rs:5) batched through the wavefront
      — against the oracle's color() on the same rays with the same Philox keys (ray, sample, segment)."""
@@ -458,27 +463,14 @@ def test_parallel_bvh_build_is_thread_count_independent(rt, device):
     """The host SAH builder hands subtrees to worker threads (csrc/bvh_build.cpp); the emitted tree must not depend on how many."""
     import time
     out = {}
-    os.environ["RT_B200_BVH_BUILDER"] = "host"  # scenes of this size default to the device builder
     for threads in ["1", "5", ""]:
-        old = os.environ.get("RT_B200_BVH_THREADS")
-        if threads:
-            os.environ["RT_B200_BVH_THREADS"] = threads
-        else:
-            os.environ.pop("RT_B200_BVH_THREADS", None)
-        try:
-            t0 = time.time()
-            scene = rt.Scene.example(device, "stress:200000", 1)
-            dt = time.time() - t0
-        finally:
-            if old is None:
-                os.environ.pop("RT_B200_BVH_THREADS", None)
-            else:
-                os.environ["RT_B200_BVH_THREADS"] = old
+        t0 = time.time()
+        scene = rt.Scene.example(device, "stress:200000", 1, options={"bvh_builder": rt.BVH_HOST_SAH, "bvh_threads": int(threads or 0)})  # this size defaults to the device builder
+        dt = time.time() - t0
         s, _, st = scene.render(scene.flat.camera(16 / 9), 96, 54, 2, 16, seed=2)
         out[threads] = (scene.bvh_info(), int(st.rays), s)
-        print(f"stress:200000 scene build+upload with RT_B200_BVH_THREADS={threads or 'default'}: {dt:.3f} s, bvh {scene.bvh_info()}")
+        print(f"stress:200000 scene build+upload with bvh_threads={threads or 'default'}: {dt:.3f} s, bvh {scene.bvh_info()}")
         scene.close()
-    os.environ.pop("RT_B200_BVH_BUILDER", None)
     for threads in ["5", ""]:
         assert out[threads][0] == out["1"][0] and out[threads][1] == out["1"][1]
         assert np.allclose(out[threads][2], out["1"][2], rtol=1e-5, atol=1e-5)
@@ -546,17 +538,9 @@ def test_device_lbvh_build_gives_the_same_hits_as_the_host_sah_tree(rt, orc, dev
     rays = np.concatenate([cam_rays, np.concatenate([o, d], axis=1)]).astype(np.float32)
     res = {}
     for builder in ["host", "device"]:
-        old = os.environ.get("RT_B200_BVH_BUILDER")
-        os.environ["RT_B200_BVH_BUILDER"] = builder
-        try:
-            t0 = time.time()
-            scene = rt.Scene.example(device, name, 1)
-            dt = time.time() - t0
-        finally:
-            if old is None:
-                os.environ.pop("RT_B200_BVH_BUILDER", None)
-            else:
-                os.environ["RT_B200_BVH_BUILDER"] = old
+        t0 = time.time()
+        scene = rt.Scene.example(device, name, 1, options={"bvh_builder": rt.BVH_HOST_SAH if builder == "host" else rt.BVH_DEVICE_LBVH})
+        dt = time.time() - t0
         hits = scene.trace(rays, seed=1)
         s, _, st = scene.render(scene.flat.camera(16 / 9), 96, 54, 2, 16, seed=2)
         res[builder] = (hits, s, int(st.rays), scene.bvh_info())
@@ -572,31 +556,13 @@ def test_device_lbvh_build_gives_the_same_hits_as_the_host_sah_tree(rt, orc, dev
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["cornell-box", "book-one"])
-def test_warp_specialised_shade_matches_block_scan_shade(rt, device, name):
-    """k_shade_pipe (producer warps + a scanner warp coupled by named barriers, RT_B200_SHADE_PIPE=1) compacts in a different
-    order than k_shade but shades the same rays with the same Philox keys: identical images and ray counts."""
-    a, qa, sa = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "0"}, 96, 54, 8)
-    b, qb, sb = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "1"}, 96, 54, 8)
-    assert sa.rays == sb.rays and sa.paths == sb.paths
-    assert np.allclose(a, b, rtol=1e-5, atol=1e-5) and np.allclose(qa, qb, rtol=1e-5, atol=1e-5)
-    c, _, sc = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "1"}, 96, 54, 2, queue_capacity=1056)
-    d, _, sd = _render_with_env(rt, device, name, {"RT_B200_SHADE_PIPE": "0"}, 96, 54, 2, queue_capacity=1056)
-    assert sc.rays == sd.rays and np.allclose(c, d, rtol=1e-5, atol=1e-5)
-
-
-@pytest.mark.gpu
 def test_wavefront_lanes_do_not_change_the_image(rt):
     """rt_render_device runs several interleaved wavefronts (lanes) per render, each on its own streams and host thread
     (capi.cu render_lanes).  Keys are functions of the global pixel: 1, 2 and 3 lanes give the same image, ray count and sums of
     squares; ragged row counts and a caller-side row shard on top of the lane split included."""
     out = {}
     for lanes in ["1", "2", "3"]:
-        os.environ["RT_B200_LANES"] = lanes
-        try:
-            dev = rt.Device(0)
-        finally:
-            os.environ.pop("RT_B200_LANES", None)
+        dev = rt.Device(0, options={"lanes": int(lanes)})
         scene = rt.Scene.example(dev, "cornell-box", 1)
         cam = scene.flat.camera(301 / 203)
         s, q, st = scene.render(cam, 301, 203, 40, 50, seed=3)                                   # 2.4 M paths: enough for 2 lanes
@@ -616,10 +582,166 @@ def test_wavefront_lanes_do_not_change_the_image(rt):
                                               ("cornell-box", 3, 2, 70001, 0), ("book-one", 2, 1, 200003, 30000)])
 def test_path_order_does_not_change_the_image(rt, device, name, w, h, spp, cap):
     """k_generate issues paths pixel-major (the samples of a pixel next to each other; k_accumulate then folds runs of one pixel in
-    the warp before touching the framebuffer) or sample-major (RT_B200_PATH_ORDER=0).  Philox keys are (global pixel, sample) either
+    the warp before touching the framebuffer) or sample-major (RT_RENDER_SAMPLE_MAJOR).  Philox keys are (global pixel, sample) either
     way: same paths, same ray count, same sums and sums of squares — spp not a multiple of 32, a queue far smaller than a
     pixel's worth of samples × pixels, and more samples per pixel than the generate grid has threads included."""
-    a, qa, sa = _render_with_env(rt, device, name, {"RT_B200_PATH_ORDER": "0", "RT_B200_LANES": "1"}, w, h, spp, queue_capacity=cap)
-    b, qb, sb = _render_with_env(rt, device, name, {"RT_B200_PATH_ORDER": "1", "RT_B200_LANES": "1"}, w, h, spp, queue_capacity=cap)
+    a, qa, sa = _render_with(rt, device, name, w, h, spp, queue_capacity=cap, flags=rt.RENDER_SAMPLE_MAJOR, ctx_opts={"lanes": 1})
+    b, qb, sb = _render_with(rt, device, name, w, h, spp, queue_capacity=cap, ctx_opts={"lanes": 1})
     assert sa.rays == sb.rays and sa.paths == sb.paths == w * h * spp
     assert np.allclose(a, b, rtol=1e-5, atol=1e-5) and np.allclose(qa, qb, rtol=1e-5, atol=1e-5)
+
+
+# ---- round 2: surface-origin rays, concurrent contexts, several GPUs behind the C ABI ---------------------------------------------
+
+def _n_gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,w,h", [("book-one", 96, 54), ("cornell-box", 64, 64), ("book-two", 64, 64), ("stress:20000", 64, 36), ("checker-lists", 96, 54)])
+def test_trace_from_surface_origins_matches_oracle(rt, orc, device, name, w, h):
+    """The f32 self-intersection rule, ray by ray.  The oracle traces scattered rays whose f64 origin IS the
+    previous hit point and rejects the hit at the origin with `t > 1e-6` (src/geometry.rs:57-66,159); the GPU gets the same rays
+    rounded to f32 — an origin up to 6e-5 off the r = 1000 ground — plus the primitive each ray starts on (rt_trace_from), which
+    is exactly the state a scattered ray carries through the wavefront.  Directions cover both hemispheres: outward rays must not
+    re-hit their own surface, inward rays on a sphere must come out at its far side (the same primitive)."""
+    so = orc.Scene(name, 1)
+    scene = rt.Scene.example(device, name, 1)
+    cam_rays = orc.camera_rays(so.camera(w / h), w, h)
+    first = so.trace(cam_rays, rel_perturb=0.0)
+    prims = so.prims()
+    m = (first["hit"] == 1) & (prims["kind"][np.maximum(first["prim"], 0)] <= 1)  # starts on spheres / rectangles (media scatter inside a volume)
+    p0, n0, id0 = first["p"][m], first["n"][m], first["prim"][m]
+    rng = np.random.default_rng(77)
+    reps = max(1, 12000 // len(p0))
+    p0, n0, id0 = np.repeat(p0, reps, axis=0), np.repeat(n0, reps, axis=0), np.repeat(id0, reps)
+    d = rng.normal(size=p0.shape)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays64 = np.concatenate([p0, d], axis=1)
+    ho = so.trace(rays64, seed=5, rel_perturb=0.0)  # (perturbing an origin that lies ON a surface would move it through the surface)
+    hg = scene.trace(rays64.astype(np.float32), seed=5, self_order=id0.astype(np.uint32))
+    cosn = np.abs(np.einsum("ij,ij->i", d, n0 / np.linalg.norm(n0, axis=1, keepdims=True)))
+    # well-conditioned set: no near-tie among the candidates, not grazing the surface the ray starts on, and not grazing the target
+    # (an f32 origin error e moves t by e / cos; the bit-exact claim is about rays whose answer does not hinge on that)
+    n_hit = ho["n"] / np.maximum(np.linalg.norm(ho["n"], axis=1, keepdims=True), 1e-30)
+    cos_hit = np.where(ho["hit"] == 1, np.abs(np.einsum("ij,ij->i", d, n_hit)), 1.0)
+    ok = (ho["stable"] == 1) & (cosn > 0.05) & (cos_hit > 0.02)
+    assert ok.mean() > 0.85, ok.mean()
+    bad = ((hg["hit"] != ho["hit"]) | (hg["prim"] != ho["prim"])) & ok
+    inward = np.einsum("ij,ij->i", d, n0) < 0
+    is_sphere = prims["kind"][id0] == 0
+    print(f"{name}: {len(rays64)} surface rays, well-conditioned {ok.mean():.4f}, mismatches {bad.sum()}, self re-hits expected "
+          f"{np.mean(ho['prim'][ok] == id0[ok]):.3f} got {np.mean(hg['prim'][ok] == id0[ok]):.3f}")
+    assert not bad.any(), f"{name}: {bad.sum()} well-conditioned surface rays differ, first {np.nonzero(bad)[0][:5]}"
+    # inward rays on a sphere leave through the same sphere (far root); nothing ever re-hits a rectangle it starts on
+    sel = ok & inward & is_sphere & (ho["prim"] == id0)
+    assert sel.sum() > 50 or not is_sphere.any()
+    assert np.all(hg["prim"][ok & ~is_sphere] != id0[ok & ~is_sphere])
+    hit = ok & (ho["hit"] == 1)
+    eo = np.abs(rays64[:, :3] - rays64[:, :3].astype(np.float32)).max(axis=1)  # what rounding the origin to f32 moved ...
+    eo = np.maximum(eo, 2.0 ** -23 * np.abs(rays64[:, :3]).max(axis=1))           # ... and one ulp of the scene tables' own f32 coordinates
+    t_tol = REL_TOL * np.maximum(np.abs(ho["t"]), 1e-3) + 4.0 * eo / np.maximum(cos_hit, 0.02)
+    p_tol = REL_TOL * np.maximum(1.0, np.abs(ho["p"]).max(axis=1))
+    dt, dp, dn = np.abs(hg["t"] - ho["t"]), np.abs(hg["p"] - ho["p"]).max(axis=1), np.abs(hg["n"] - ho["n"]).max(axis=1)
+    assert np.all(dt[hit] <= t_tol[hit]), f"t off by up to {np.max(dt[hit] / t_tol[hit]):.2f} x tolerance"
+    assert np.mean(dp[hit] <= p_tol[hit]) > 0.999 and np.mean(dn[hit] <= 2e-4) > 0.995, (np.mean(dp[hit] <= p_tol[hit]), np.mean(dn[hit] <= 2e-4))
+
+
+@pytest.mark.gpu
+def test_two_contexts_render_different_scenes_concurrently(rt):
+    """Launch configuration is per device and per scene (csrc/kernels.cu DeviceState / SceneLaunch), not per process: two contexts —
+    on two GPUs when the box has them, else both on GPU 0 — render DIFFERENT scenes (different shared-memory footprints: book-one
+    stages 98 KB, cornell-box < 2 KB) at the same time from two host threads and get the images they get alone."""
+    import threading
+    ids = [0, 1] if _n_gpus() >= 2 else [0, 0]
+    devs = [rt.Device(i) for i in ids]
+    names = ["book-one", "cornell-box"]
+    scenes = [rt.Scene.example(dv, nm, 1) for dv, nm in zip(devs, names)]
+    cams = [sc.flat.camera(160 / 90) for sc in scenes]
+    alone = [sc.render(cm, 160, 90, 64, 50, seed=9) for sc, cm in zip(scenes, cams)]
+    together = [None, None]
+
+    def work(i):
+        for _ in range(3):
+            together[i] = scenes[i].render(cams[i], 160, 90, 64, 50, seed=9)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    for i in range(2):
+        assert together[i] is not None and together[i][2].rays == alone[i][2].rays
+        assert np.allclose(together[i][0], alone[i][0], rtol=1e-5, atol=1e-5)
+    # and a scene created on one context cannot be rendered through a context of another device
+    for sc in scenes:
+        sc.close()
+    for dv in devs:
+        dv.close()
+
+
+@pytest.mark.gpu
+def test_render_multi_matches_single_device_render(rt, device):
+    """rt_init_multi / rt_render_multi (one process, one host thread per device, rows y % n == device, NCCL gather to device 0):
+    the image equals the single-context render for every device count the box offers (Philox keys are functions of the global pixel)."""
+    flat = rt.FlatScene("book-one", 1)
+    w, h, spp = 160, 91, 32  # 91 rows: ragged shards
+    cam = flat.camera(w / h)
+    ref, refq, rst = rt.Scene(device, flat=flat).render(cam, w, h, spp, 50, seed=4)
+    counts = [n for n in (1, 2, 3, 4, 8) if n <= _n_gpus()]
+    for n in counts:
+        multi = rt.MultiDevice(list(range(n)))
+        ms = rt.MultiScene(multi, flat=flat)
+        s, q, st = ms.render(cam, w, h, spp, 50, seed=4)
+        assert st.paths == rst.paths and st.rays == rst.rays, n
+        assert np.allclose(s, ref, rtol=1e-5, atol=1e-5) and np.allclose(q, refq, rtol=1e-5, atol=1e-5), n
+        s2, _, _ = ms.render(cam, w, h, spp, 50, seed=4, want_sumsq=False)  # buffers are reused across renders
+        assert np.allclose(s2, ref, rtol=1e-5, atol=1e-5)
+        tiny, _, _ = ms.render(cam, 5, 1, 4, 50, seed=4, want_sumsq=False)  # fewer rows than devices
+        tref, _, _ = rt.Scene(device, flat=flat).render(cam, 5, 1, 4, 50, seed=4, want_sumsq=False)
+        assert np.allclose(tiny, tref, rtol=1e-5, atol=1e-5)
+        buf = np.zeros((h, w, 3), dtype=np.float32)
+        rc = rt.lib.rt_render_multi(ms._h, cam, rt.RtRenderParams(w, h, spp, 50, 4, 1, 2, 0, 0), buf.ctypes.data, None, None)  # caller-side sharding is refused
+        assert rc == rt.RT_ERR_INVALID
+        ms.close()
+        multi.close()
+    print(f"rt_render_multi checked on {counts} device(s)")
+
+
+@pytest.mark.gpu
+def test_checker_lists_scene_in_both_device_forms(rt, orc, device):
+    """The parity scene for what no example uses: Vec<Arc<dyn Bound>> as the world root, as an inner node
+    and as a Sprite's geometry (src/geometry.rs:76-116, src/optimize.rs:256-334), CheckerTexture nested once on a rectangle, a
+    sphere, under a Metal and as an emitter (src/material.rs:217-245), and a Cube-bounded ConstantMedium (src/volume.rs:40-43).
+    Its 21 primitives run as the warp-uniform DFS list by default; RT_SCENE_NO_SMALL_LIST gives it a tree like any larger scene.
+    Both forms must answer like the oracle — ids, t / p / n, uv (the checker reads uv) — and like each other."""
+    so = orc.Scene("checker-lists", 1)
+    cam_rays = orc.camera_rays(so.camera(16 / 9), 160, 90)
+    rng = np.random.default_rng(8)
+    d = rng.normal(size=(15000, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = np.stack([rng.uniform(-14, 14, len(d)), rng.uniform(0.2, 12, len(d)), rng.uniform(-12, 12, len(d))], axis=1)
+    rays = np.concatenate([cam_rays, np.concatenate([o, d], axis=1)]).astype(np.float32)
+    ho = so.trace(rays.astype(np.float64), seed=3)
+    assert set(np.unique(ho["prim"][ho["hit"] == 1])) >= set(range(0, 21)) - {19}, "every primitive but the sky must be hit by some ray"
+    forms = {}
+    for label, opts in [("list", None), ("tree", {"flags": rt.SCENE_NO_SMALL_LIST})]:
+        scene = rt.Scene.example(device, "checker-lists", 1, options=opts)
+        info = scene.bvh_info()
+        assert (info["nodes"] == 0) == (label == "list")
+        hg = scene.trace(rays, seed=3)
+        stable, bare = _check_trace(hg, ho, f"checker-lists {label}")
+        m = (ho["stable"] == 1) & (ho["hit"] == 1)
+        uv_o = np.stack([ho["u"], ho["v"]], axis=1)
+        assert np.all(np.abs(hg["uv"][m] - uv_o[m]).max(axis=1) <= 2e-3 + 64 * ho["n_sens"][m])
+        s, q, st = scene.render(scene.flat.camera(16 / 9), 128, 72, 16, 50, seed=2)
+        forms[label] = (hg, s, int(st.rays))
+        print(f"checker-lists as {label}: bvh {info}, stable {stable:.4f}, bare {bare:.4f}, rays/path {st.rays / st.paths:.3f}")
+    a, b = forms["list"], forms["tree"]
+    for f in ["hit", "prim", "material"]:
+        assert np.array_equal(a[0][f], b[0][f]), f
+    assert np.array_equal(a[0]["t"], b[0]["t"])
+    assert a[2] == b[2] and np.allclose(a[1], b[1], rtol=1e-5, atol=1e-5)
+    # the checker really is in the image: the floor alternates between its three colours
+    s_o, _, _ = so.render(128, 72, 16, 50, seed=2, mode=orc.PAIRED)
+    ok = np.abs(a[1] - s_o).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(s_o).max(axis=2))
+    assert ok.mean() >= 0.985, ok.mean()

@@ -16,7 +16,7 @@ INC = os.path.join(ROOT, "include")
 def _declared_functions(path):
     src = open(path).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return re.findall(r"^\s*(?:const\s+)?(?:int|void|uint32_t|uint64_t|char\s*\*)\s*\*?\s*(rt[h]?_[a-z0-9_]+)\s*\(", src, flags=re.M)
+    return re.findall(r"^\s*(?:const\s+)?(?:int|void|uint32_t|uint64_t|char\s*\*|RtContext\s*\*)\s*\*?\s*(rt[h]?_[a-z0-9_]+)\s*\(", src, flags=re.M)
 
 
 def test_library_exports_every_declared_symbol(rt):
@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol(rt):
     assert sorted(set(declared)) == sorted(set(rt.ABI_SYMBOLS))
     for name in declared:
         assert hasattr(rt.lib, name), f"librt_b200.so does not export {name}"
-    assert rt.lib.rt_abi_version() == 1
+    assert rt.lib.rt_abi_version() == 2
 
 
 def test_headers_are_plain_c_and_layouts_match_ctypes(rt, tmp_path):
@@ -35,17 +35,19 @@ def test_headers_are_plain_c_and_layouts_match_ctypes(rt, tmp_path):
 #include "rt_b200.h"
 #include "rt_b200_host.h"
 int main(void) {
-    printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(RtPrim), sizeof(RtMaterial), sizeof(RtTexture), sizeof(RtSceneDesc),
-           sizeof(RtCamera), sizeof(RtRenderParams), sizeof(RtStats), sizeof(RtRayIn), sizeof(RtHitOut), sizeof(RthCameraArgs));
+    printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(RtPrim), sizeof(RtMaterial), sizeof(RtTexture), sizeof(RtSceneDesc),
+           sizeof(RtCamera), sizeof(RtRenderParams), sizeof(RtStats), sizeof(RtRayIn), sizeof(RtHitOut), sizeof(RthCameraArgs),
+           sizeof(RtContextOptions), sizeof(RtSceneOptions));
     return 0;
 }''')
     exe = tmp_path / "layout"
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", INC, str(prog), "-o", str(exe)])
     sizes = [int(v) for v in subprocess.check_output([str(exe)]).split()]
     expect = [rt.PRIM_DTYPE.itemsize, rt.MATERIAL_DTYPE.itemsize, rt.TEXTURE_DTYPE.itemsize, C.sizeof(rt.RtSceneDesc), C.sizeof(rt.RtCamera),
-              C.sizeof(rt.RtRenderParams), C.sizeof(rt.RtStats), rt.RAY_DTYPE.itemsize, rt.HIT_DTYPE.itemsize, C.sizeof(rt.RthCameraArgs)]
+              C.sizeof(rt.RtRenderParams), C.sizeof(rt.RtStats), rt.RAY_DTYPE.itemsize, rt.HIT_DTYPE.itemsize, C.sizeof(rt.RthCameraArgs),
+              C.sizeof(rt.RtContextOptions), C.sizeof(rt.RtSceneOptions)]
     assert sizes == expect
-    assert sizes[0] == 128 and sizes[1] == 16 and sizes[4] == 64
+    assert sizes[0] == 128 and sizes[1] == 16 and sizes[4] == 64 and sizes[10] == 32 and sizes[11] == 32
 
 
 def test_product_never_touches_the_oracle():
