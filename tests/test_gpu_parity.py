@@ -25,10 +25,25 @@ def _golden(name):
     return np.load(os.path.join(GOLDEN, name.replace(":", "_") + ".npz"))
 
 
+# Floors of (stable fraction, fraction of stable hits inside the BARE 1e-4 bound) per scene, set 0.004 below what the B200 measures
+# (r2: book-one 0.9994 / 0.9960, cornell-box 0.9844 / 1.0000, book-two 0.9646 / 0.9979, stress:100000 0.9992 / 0.9853,
+# checker-lists 0.9994 / 0.9998): the conditioning slack in the tolerances below must stay the exception, at its measured size.
+TRACE_FLOORS = {"book-one": (0.995, 0.992), "cornell-box": (0.980, 0.996), "book-two": (0.960, 0.993), "stress": (0.995, 0.981),
+                "checker-lists": (0.995, 0.995)}
+
+
+def _floors(label):
+    for key, v in TRACE_FLOORS.items():
+        if key in label:
+            return v
+    return (0.95, 0.98)
+
+
 def _check_trace(hg, ho, label):
     """hg: GPU RtHitOut records, ho: oracle records (dict-like with hit/prim/stable/t/p/n/*_sens)."""
     stable = np.asarray(ho["stable"]) == 1
-    assert stable.mean() > 0.95, f"{label}: only {stable.mean():.3f} of the rays are well-conditioned"
+    floor_stable, floor_bare = _floors(label)
+    assert stable.mean() >= floor_stable, f"{label}: only {stable.mean():.4f} of the rays are well-conditioned (floor {floor_stable})"
     hit_o, prim_o = np.asarray(ho["hit"]).astype(np.int32), np.asarray(ho["prim"]).astype(np.int32)
     bad = ((hg["hit"] != hit_o) | (hg["prim"] != prim_o)) & stable
     assert not bad.any(), f"{label}: {bad.sum()} stable rays differ in hit/primitive id, first {np.nonzero(bad)[0][:5]}"
@@ -48,11 +63,11 @@ def _check_trace(hg, ho, label):
     # 2e-6 — moves t by more than 1e-4 relative; point and normal stay within the bare bound)
     bt, bp, bn = dt <= REL_TOL * np.maximum(np.abs(t_o), 1e-3), dp <= REL_TOL * np.maximum(1.0, np.abs(p_o).max(axis=1)), dn <= REL_TOL * 1.0
     bare = bt & bp & bn
-    if bare.mean() <= 0.98:
+    if bare.mean() < floor_bare:
         worst = np.argsort(-(dt / np.maximum(np.abs(t_o), 1e-3)))[:5]
         print(f"{label}: bare pass t {bt.mean():.4f} p {bp.mean():.4f} n {bn.mean():.4f}; worst t: gpu {hg['t'][m][worst]} oracle {t_o[worst]} "
               f"prim {np.asarray(ho['prim'])[m][worst]} rays {np.nonzero(m)[0][worst]}")
-    assert bare.mean() > 0.98 and bp.mean() > 0.999 and bn.mean() > 0.999, f"{label}: only {bare.mean():.4f} of stable hits are within the bare 1e-4 bound"
+    assert bare.mean() >= floor_bare and bp.mean() > 0.999 and bn.mean() > 0.999, f"{label}: only {bare.mean():.4f} of stable hits are within the bare 1e-4 bound (floor {floor_bare})"
     return stable.mean(), bare.mean()
 
 
@@ -627,7 +642,7 @@ def test_trace_from_surface_origins_matches_oracle(rt, orc, device, name, w, h):
     n_hit = ho["n"] / np.maximum(np.linalg.norm(ho["n"], axis=1, keepdims=True), 1e-30)
     cos_hit = np.where(ho["hit"] == 1, np.abs(np.einsum("ij,ij->i", d, n_hit)), 1.0)
     ok = (ho["stable"] == 1) & (cosn > 0.05) & (cos_hit > 0.02)
-    assert ok.mean() > 0.85, ok.mean()
+    assert ok.mean() > 0.8, ok.mean()
     bad = ((hg["hit"] != ho["hit"]) | (hg["prim"] != ho["prim"])) & ok
     inward = np.einsum("ij,ij->i", d, n0) < 0
     is_sphere = prims["kind"][id0] == 0
@@ -745,3 +760,80 @@ def test_checker_lists_scene_in_both_device_forms(rt, orc, device):
     s_o, _, _ = so.render(128, 72, 16, 50, seed=2, mode=orc.PAIRED)
     ok = np.abs(a[1] - s_o).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(s_o).max(axis=2))
     assert ok.mean() >= 0.985, ok.mean()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("builder", ["host", "device"])
+def test_trace_config4_one_million_spheres_matches_oracle(rt, orc, device, builder):
+    """BASELINE configs[3] at its real size — 1 000 000 spheres under one BVH — against the oracle (the reference's random-axis
+    median-split tree, unpruned recursion), ray by ray, for BOTH device trees: the host binned-SAH build and the LBVH built on the GPU."""
+    so = orc.Scene("stress:1000000", 1)
+    scene = rt.Scene.example(device, "stress:1000000", 1, options={"bvh_builder": rt.BVH_HOST_SAH if builder == "host" else rt.BVH_DEVICE_LBVH})
+    info = scene.bvh_info()
+    assert info["nodes"] > 1_000_000
+    cam_rays = orc.camera_rays(so.camera(16 / 9), 64, 36).astype(np.float32)
+    first = so.trace(cam_rays.astype(np.float64), rel_perturb=0.0)
+    pts = first["p"][first["hit"] == 1]
+    rng = np.random.default_rng(31)
+    n_b = 6000
+    d = rng.normal(size=(n_b, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = pts[rng.integers(0, len(pts), n_b)] + 1e-3 * d * 50.0
+    inside = np.concatenate([rng.uniform(-50, 50, size=(3000, 3)), rng.normal(size=(3000, 3))], axis=1)  # rays from anywhere in the cloud
+    inside[:, 3:] /= np.linalg.norm(inside[:, 3:], axis=1, keepdims=True)
+    rays = np.concatenate([cam_rays, np.concatenate([o, d], axis=1).astype(np.float32), inside.astype(np.float32)])
+    ho = so.trace(rays.astype(np.float64), seed=9)
+    hg = scene.trace(rays, seed=9)
+    stable, bare = _check_trace(hg, ho, f"stress:1000000 ({builder} tree)")
+    print(f"stress:1000000 {builder}: bvh {info}, {len(rays)} rays, stable {stable:.4f}, within bare 1e-4 {bare:.4f}, hit fraction {hg['hit'].mean():.3f}")
+
+
+def _gate2(rt, orc, device, name, w, h, spp_gpu, spp_cpu, depth, block):
+    scene = rt.Scene.example(device, name, 1)
+    s_g, q_g, st = scene.render(scene.flat.camera(w / h), w, h, spp_gpu, depth, seed=11)
+    s_o, q_o, sto = orc.Scene(name, 1).render(w, h, spp_cpu, depth, seed=22, mode=orc.FAITHFUL)
+    assert np.all(np.isfinite(s_g)) and np.all(s_g >= 0)
+    m_g, m_o = s_g.astype(np.float64) / spp_gpu, s_o / spp_cpu
+    var_g = np.maximum(q_g.astype(np.float64) / spp_gpu - m_g ** 2, 0) / spp_gpu
+    var_o = np.maximum(q_o / spp_cpu - m_o ** 2, 0) / spp_cpu
+    floor = 2e-5 * np.maximum(np.maximum(m_g, m_o), 1e-3)
+    z = (m_g - m_o) / np.sqrt(var_g + var_o + floor ** 2)
+    exceed = float(np.mean(np.abs(z) > 3.0))
+    # block means: the same statistics on (block x block)-pixel averages — 1/block of the per-pixel standard error, so a bias of a
+    # fraction of a sigma per pixel, invisible above, shows here
+    hb, wb = (h // block) * block, (w // block) * block
+    def blk(a):
+        return a[:hb, :wb].reshape(hb // block, block, wb // block, block, 3).mean(axis=(1, 3))
+    bm_g, bm_o = blk(m_g), blk(m_o)
+    bvar = (blk(var_g) + blk(var_o)) / (block * block)
+    zb = (bm_g - bm_o) / np.sqrt(bvar + blk(floor) ** 2)
+    exceed_b = float(np.mean(np.abs(zb) > 3.0))
+    psnr_px = _psnr_resolved(m_g, m_o)
+    psnr_blk = _psnr_resolved(bm_g, bm_o)
+    # what Monte-Carlo noise alone does to the per-pixel PSNR of two independent renders (delta method on the sqrt display transform)
+    mid = np.clip(0.5 * (m_g + m_o), 1e-6, 1.0)
+    noise_mse = np.mean(np.where((m_g < 1.0) | (m_o < 1.0), (var_g + var_o) / (4.0 * mid), 0.0))
+    psnr_noise = 10 * math.log10(1.0 / max(noise_mse, 1e-30))
+    print(f"{name} {w}x{h}: gpu {spp_gpu} spp vs FAITHFUL oracle {spp_cpu} spp ({sto.seconds:.1f} s on {sto.threads} threads): |z|>3 {exceed:.4f} per pixel, "
+          f"{exceed_b:.4f} per {block}x{block} block (chance 0.0027), max |z| {np.abs(z).max():.2f}, mean z {z.mean():+.3f}; PSNR {psnr_px:.1f} dB per pixel "
+          f"(noise alone: {psnr_noise:.1f}), {psnr_blk:.1f} dB on block means; rays/path gpu {st.rays / st.paths:.4f} oracle {sto.segments / sto.paths:.4f}")
+    assert exceed <= 0.005 and np.abs(z).max() < 6.0
+    assert exceed_b <= 0.01 and abs(z.mean()) < 0.05
+    assert psnr_px >= psnr_noise - 1.0   # the per-pixel difference is what the two renders' own standard errors predict
+    assert psnr_blk >= 40.0
+    assert abs(st.rays / st.paths - sto.segments / sto.paths) < 0.005 * sto.segments / sto.paths
+
+
+@pytest.mark.gpu
+def test_gate2_config1_full_size(rt, orc, device):
+    """Gate 2 at BASELINE configs[0]'s own size: book-one 400x225, depth 50, the GPU at 1024 spp (>= 1024 as the north star asks)
+    against an independent FAITHFUL oracle render (rejection sampling, sequential stream: the reference's algorithm) at 1024 spp."""
+    _gate2(rt, orc, device, "book-one", 400, 225, 1024, 1024, 50, 5)
+
+
+@pytest.mark.gpu
+def test_gate2_config2_full_size(rt, orc, device):
+    """Gate 2 at BASELINE configs[1]'s own size: cornell-box 600x600, 1024 spp, depth 50 on the GPU against the FAITHFUL oracle at
+    256 spp (92 M CPU paths).  Two 1024-spp cornell renders differ by ~27 dB of Monte-Carlo noise per pixel (a 130x105 light seen
+    through 6.4 bounces), so PSNR >= 40 dB is asserted on 10x10 block means and the per-pixel PSNR against its noise prediction."""
+    _gate2(rt, orc, device, "cornell-box", 600, 600, 1024, 256, 50, 10)
