@@ -109,6 +109,17 @@ inline std::vector<std::optional<TraceHit>> trace_rays(World& world, const std::
     return res;
 }
 
+// mean -> sqrt -> * 255 -> min(255) -> truncation, rows top to bottom (examples/book-one.rs:90-100), on the pixels render_image
+// returned (means, y up).  The device resolves in f64 like the reference, so the bytes equal the reference's arithmetic on the
+// same f32-rounded means.
+inline std::vector<uint8_t> resolve_u8(Device& dev, const std::vector<Vec3>& pixels, uint32_t width, uint32_t height) {
+    std::vector<float> sums(pixels.size() * 3);
+    for (size_t i = 0; i < pixels.size(); ++i) { sums[3 * i] = (float)pixels[i].x; sums[3 * i + 1] = (float)pixels[i].y; sums[3 * i + 2] = (float)pixels[i].z; }
+    std::vector<uint8_t> out(sums.size());
+    check(rt_resolve_u8(dev.handle(), sums.data(), width, height, 1, out.data()));
+    return out;
+}
+
 // render::color(&ray, world, maxDepth) (src/render.rs:5) for a batch of rays: the mean of `spp` evaluations per ray.
 inline std::vector<Vec3> color(World& world, const std::vector<Ray>& rays, uint32_t maxDepth, uint32_t spp = 1, uint64_t seed = 1) {
     std::vector<RtRayIn> in(rays.size());

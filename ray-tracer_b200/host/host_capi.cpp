@@ -7,35 +7,12 @@
 
 #include "../../include/rt_b200_host.h"
 #include "../examples/scenes.hpp"
+#include "api_bundle.hpp"
 #include "flatten.hpp"
 #include "gpu.hpp"
 #include "image_io.hpp"
 
 namespace {
-
-struct HostApi {  // the type bundle scenes.hpp is instantiated with
-    using Vec3 = rtb::host::Vec3;
-    using Mat4 = rtb::host::Mat4;
-    using BoundPtr = rtb::host::BoundPtr;
-    using Sphere = rtb::host::Sphere;
-    using Rectangle = rtb::host::Rectangle;
-    using Cube = rtb::host::Cube;
-    using Sprite = rtb::host::Sprite;
-    using ConstantMedium = rtb::host::ConstantMedium;
-    using BoundingVolumeHierarchyNode = rtb::host::BoundingVolumeHierarchyNode;
-    using Lambertian = rtb::host::Lambertian;
-    using Metal = rtb::host::Metal;
-    using Dielectric = rtb::host::Dielectric;
-    using DiffuseLight = rtb::host::DiffuseLight;
-    using Isotropic = rtb::host::Isotropic;
-    using ImageTexture = rtb::host::ImageTexture;
-    static void setBakeSize(ImageTexture& t, uint32_t w, uint32_t h) { t.bakeWidth = w; t.bakeHeight = h; }
-    using CheckerTexture = rtb::host::CheckerTexture;
-    using Texture = rtb::host::Texture;
-    using SolidColor = rtb::host::SolidColor;
-    using HitList = rtb::host::HitList;
-    using TransformedGeometry = rtb::host::TransformedGeometry;
-};
 
 thread_local std::string g_host_error;
 
@@ -57,7 +34,7 @@ int rth_example_scene(const char* name, uint64_t seed, RthFlatScene** out) {
         rtb::host::BuildAxisStream axes(seed ^ 0xA11CE5EEDull);
         rtb::host::currentAxisStream() = &axes;
         bool rootIsList = false;
-        const bool ok = rtscenes::Scenes<HostApi>::byName(name, seed, &list, &res->cam, &rootIsList);
+        const bool ok = rtscenes::Scenes<rtb::host::HostApi>::byName(name, seed, &list, &res->cam, &rootIsList);
         rtb::host::BoundPtr world;
         if (ok && rootIsList) {  // the world is the Vec itself (impl Hit / Bound for Vec, src/geometry.rs:76-116)
             auto l = std::make_shared<rtb::host::HitList>();

@@ -17,6 +17,8 @@
 
 #include <zlib.h>
 
+#include "jpeg_decode.hpp"
+
 namespace rth {
 
 inline std::string encode_ppm_p3(const uint8_t* rgb_top_down, uint32_t width, uint32_t height) {
@@ -204,6 +206,7 @@ inline int decode_ppm(const uint8_t* data, size_t n, uint32_t& width, uint32_t& 
 
 inline int decode_image(const uint8_t* data, size_t n, uint32_t& width, uint32_t& height, std::vector<uint8_t>& rgb) {
     if (n >= 2 && data[0] == 'P') return decode_ppm(data, n, width, height, rgb);
+    if (n >= 2 && data[0] == 0xFF && data[1] == 0xD8) return jpeg::decode(data, n, width, height, rgb);  // earthmap.jpg (examples/main.rs:266)
     return decode_png(data, n, width, height, rgb);
 }
 

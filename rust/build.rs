@@ -44,6 +44,8 @@ const HEADERS: &[&str] = &[
     "host/flatten.hpp",
     "host/gpu.hpp",
     "host/image_io.hpp",
+    "host/jpeg_decode.hpp",
+    "host/api_bundle.hpp",
     "examples/scenes.hpp",
     "../include/rt_b200.h",
     "../include/rt_b200_host.h",

@@ -520,6 +520,15 @@ def test_ingested_earth_texture_renders_like_the_oracle(rt, orc, device):
     earth = np.repeat(np.repeat(rng.integers(0, 256, size=(8, 16, 3), dtype=np.uint8), 6, axis=0), 5, axis=1)  # 48 x 80 blocks
     png = rt.encode_image(earth, rt.IMAGE_PNG_RGBA8)
     decoded = rt.decode_image(png)
+    try:  # the format the reference actually opens (examples/main.rs:266 earthmap.jpg): the same picture through the JPEG decoder
+        import io
+        from PIL import Image
+        buf = io.BytesIO()
+        Image.fromarray(decoded).save(buf, format="JPEG", quality=90, subsampling=2)
+        decoded = rt.decode_image(buf.getvalue())
+        assert np.array_equal(decoded, np.asarray(Image.open(io.BytesIO(buf.getvalue())).convert("RGB")))
+    except ImportError:
+        pass
     w = h = 72
     base, _, _ = rt.Scene.example(device, "book-two", 1).render(rt.FlatScene("book-two", 1).camera(1.0), w, h, 4, 50, seed=1)
     rt.set_earth_image(decoded)
@@ -837,3 +846,27 @@ def test_gate2_config2_full_size(rt, orc, device):
     256 spp (92 M CPU paths).  Two 1024-spp cornell renders differ by ~27 dB of Monte-Carlo noise per pixel (a 130x105 light seen
     through 6.4 bounces), so PSNR >= 40 dB is asserted on 10x10 block means and the per-pixel PSNR against its noise prediction."""
     _gate2(rt, orc, device, "cornell-box", 600, 600, 1024, 256, 50, 10)
+
+
+@pytest.mark.gpu
+def test_cpp_example_driver_writes_the_reference_ppm(rt, device, tmp_path):
+    """ray-tracer_b200/examples/book_one.cpp — examples/book-one.rs through the C++ host mirror: scene built with the mirrored
+    API, ONE gpu::render_image call (host/gpu.hpp), gpu::resolve_u8, PPM P3 as book-one.rs:28-30,90-100 prints it.  The file must
+    equal, byte for byte, what the ctypes path produces for the same scene seed and render seed."""
+    import subprocess
+    pkg = os.path.join(os.path.dirname(GOLDEN), "..", "ray-tracer_b200")
+    exe = os.path.join(pkg, "examples", "book_one")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-s", "-C", pkg, "examples/book_one"])
+    w, h, spp, depth, seed = 160, 90, 8, 50, 3
+    out = tmp_path / "book_one.ppm"
+    res = subprocess.run([exe, str(w), str(h), str(spp), str(depth), str(seed), str(out)], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    assert "paths" in res.stderr
+    scene = rt.Scene.example(device, "book-one", seed)
+    s, _, st = scene.render(scene.flat.camera(w / h), w, h, spp, depth, seed=seed, want_sumsq=False)
+    means = (s.astype(np.float64) / spp).astype(np.float32)  # render_image divides in f64 (pixel /= spp, book-one.rs:76); resolve_u8 takes f32
+    want = rt.encode_image(device.resolve_u8(means, 1), rt.IMAGE_PPM_P3)
+    got = out.read_bytes()
+    assert got.startswith(b"P3\n160 90\n255\n")
+    assert got == want

@@ -299,3 +299,65 @@ def test_image_decoders_and_earth_texture_ingestion(rt):
         rt.set_earth_image(None)
     tex = rt.FlatScene("book-two", 1).textures()
     assert tex[tex["kind"] == rt.TEX_IMAGE][0]["width"] == 1024
+
+
+def test_cpp_example_driver_builds_and_has_no_cpu_fallback():
+    """examples/book_one.cpp (the C++ twin of rust/examples/book-one-gpu.rs) compiles against host/gpu.hpp and the C ABI; on a box
+    without a CUDA device it must fail loudly (exit 1, the library's message), never render on the CPU."""
+    pkg = os.path.join(ROOT, "ray-tracer_b200")
+    subprocess.check_call(["make", "-s", "-C", pkg, "examples/book_one"])
+    exe = os.path.join(pkg, "examples", "book_one")
+    assert os.path.exists(exe)
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:  # noqa: BLE001
+        has_gpu = False
+    if not has_gpu:
+        res = subprocess.run([exe, "8", "8", "1", "5", "1"], capture_output=True, text=True)
+        assert res.returncode == 1 and "no CPU fallback" in res.stderr and not res.stdout
+    res = subprocess.run([exe, "0", "8", "1", "5", "1"], capture_output=True, text=True)
+    assert res.returncode == 2
+
+
+def test_jpeg_decoder_matches_libjpeg_bit_for_bit(rt):
+    """SURVEY §8(f) rank 3: the ONE image format the reference opens is JPEG (examples/main.rs:266 `image::open("./earthmap.jpg")`).
+    host/jpeg_decode.hpp (baseline + extended sequential Huffman; islow IDCT, fancy upsampling, fixed-point YCbCr) against PIL's
+    libjpeg on 4:4:4 / 4:2:2 / 4:2:0 / grey streams, optimised Huffman tables, restart intervals, sizes that are not MCU multiples
+    and a 1024x512 equirectangular-sized image: every byte equal.  Progressive streams are refused as unsupported, not mis-decoded."""
+    import io
+    PIL = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(1)
+
+    def picture(h, w):
+        yy, xx = np.mgrid[0:h, 0:w]
+        img = np.stack([127 + 100 * np.sin(xx / 9.0) * np.cos(yy / 7.0), 40 + xx * (200.0 / w), 200 - yy * (150.0 / h)], axis=2) + rng.normal(0, 12, (h, w, 3))
+        return np.clip(img, 0, 255).astype(np.uint8)
+
+    cases = [((93, 141), dict(subsampling=0, quality=90)), ((93, 141), dict(subsampling=1, quality=85)), ((93, 141), dict(subsampling=2, quality=75)),
+             ((64, 64), dict(subsampling=2, quality=30, optimize=True)), ((7, 5), dict(subsampling=2, quality=95)), ((1, 1), dict(quality=50)),
+             ((512, 1024), dict(subsampling=2, quality=80)), ((50, 70), "grey"), ((37, 129), dict(subsampling=2, quality=60, restart_marker_blocks=3)),
+             ((40, 40), dict(subsampling=0, quality=100))]
+    for (h, w), kw in cases:
+        img = picture(h, w)
+        buf = io.BytesIO()
+        if kw == "grey":
+            PIL.fromarray(img[:, :, 0]).save(buf, format="JPEG", quality=80)
+        else:
+            try:
+                PIL.fromarray(img).save(buf, format="JPEG", **kw)
+            except TypeError:
+                continue  # an older Pillow without restart_marker_blocks
+        data = buf.getvalue()
+        want = np.asarray(PIL.open(io.BytesIO(data)).convert("RGB"))
+        got = rt.decode_image(data)
+        assert got.shape == want.shape == (h, w, 3)
+        assert np.array_equal(got, want), f"{h}x{w} {kw}: {np.abs(got.astype(int) - want.astype(int)).max()} off"
+    buf = io.BytesIO()
+    PIL.fromarray(picture(32, 32)).save(buf, format="JPEG", progressive=True)
+    with pytest.raises(rt.BackendError) as e:
+        rt.decode_image(buf.getvalue())
+    assert e.value.code == rt.RT_ERR_UNSUPPORTED
+    data = bytearray(data)
+    with pytest.raises(rt.BackendError):
+        rt.decode_image(bytes(data[:len(data) // 3]))  # truncated stream
