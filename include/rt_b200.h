@@ -191,10 +191,11 @@ typedef enum RtBvhBuilder { RT_BVH_AUTO = 0, RT_BVH_HOST_SAH = 1, RT_BVH_DEVICE_
 typedef enum RtSceneFlags {
     RT_SCENE_NO_FRAME_RECTS = 1u,  /* small all-rectangle scenes keep the general rectangle records (no frame-rect list) */
     RT_SCENE_NO_STAGED_PRIMS = 2u, /* primitive heads stay in global memory */
-    RT_SCENE_NO_SMALL_LIST = 4u    /* scenes of <= 32 primitives get a tree like any other */
+    RT_SCENE_NO_SMALL_LIST = 4u,   /* scenes of <= 32 primitives get a tree like any other */
+    RT_SCENE_NO_FRAME_BOXES = 8u   /* frame-rect list without grouping the faces of a box into one slab test */
 } RtSceneFlags;
 /* Options of a scene build; all-zero = defaults (a context's defaults come from RT_B200_BVH_BUILDER=host|device,
- * RT_B200_BVH_MAX_LEAF, RT_B200_BVH_TREELET, RT_B200_BVH_THREADS, RT_B200_STAGED_NODES, RT_B200_RECT_FRAMES=0, RT_B200_STAGE_PRIMS=0,
+ * RT_B200_BVH_MAX_LEAF, RT_B200_BVH_TREELET, RT_B200_BVH_THREADS, RT_B200_STAGED_NODES, RT_B200_RECT_FRAMES=0, RT_B200_RECT_BOXES=0, RT_B200_STAGE_PRIMS=0,
  * RT_B200_SMALL_SCENE=0 at rt_init). */
 typedef struct RtSceneOptions {
     uint32_t bvh_builder;   /* RtBvhBuilder: AUTO = device LBVH from 65 536 primitives, host binned SAH below */
@@ -286,6 +287,9 @@ int rt_render_multi(RtMultiScene* scene, const RtCamera* cam, const RtRenderPara
 
 /* Introspection used by tests / the roofline accounting. */
 int rt_scene_bvh_info(const RtScene* scene, uint32_t* n_nodes, uint32_t* n_always, uint32_t* max_depth);
+/* Frame-rect list of a small all-rectangle scene (k_extend_rects): frames, frame boxes (faces of one box tested with one slab test)
+ * and loose rectangles; all 0 when the scene does not use it. */
+int rt_scene_frame_rect_info(const RtScene* scene, uint32_t* n_frames, uint32_t* n_boxes, uint32_t* n_loose);
 /* Bytes of device memory the scene occupies (= host->device bytes rt_scene_create copied). */
 uint64_t rt_scene_device_bytes(const RtScene* scene);
 const char* rt_last_error(void);

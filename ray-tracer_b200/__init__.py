@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 RENDER_STAGE_TIMING, RENDER_COUNT_WORK, RENDER_SAMPLE_MAJOR, RENDER_EXTEND_PER_THREAD, RENDER_EXTEND_PERSISTENT, RENDER_TIME_EVERY_ITERATION = 1, 2, 4, 8, 16, 32
 CTX_NO_ACCUMULATE_OVERLAP, CTX_STAGE_TIMING, CTX_SHADE_ONE_RAY = 1, 2, 4
 BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
-SCENE_NO_FRAME_RECTS, SCENE_NO_STAGED_PRIMS, SCENE_NO_SMALL_LIST = 1, 2, 4
+SCENE_NO_FRAME_RECTS, SCENE_NO_STAGED_PRIMS, SCENE_NO_SMALL_LIST, SCENE_NO_FRAME_BOXES = 1, 2, 4, 8
 RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM, RT_ERR_NCCL = 0, -1, -2, -3, -4, -5, -6
 PRIM_SPHERE, PRIM_RECT, PRIM_MEDIUM_SPHERE, PRIM_MEDIUM = 0, 1, 2, 3
 NO_PRIM = 0xFFFFFFFF
@@ -78,7 +78,7 @@ class RthCameraArgs(C.Structure):
 ABI_SYMBOLS = ["rt_init", "rt_init_ex", "rt_options_from_env", "rt_shutdown", "rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_render", "rt_render_device",
                "rt_trace", "rt_trace_from", "rt_color_rays", "rt_resolve_u8", "rt_init_multi", "rt_shutdown_multi", "rt_multi_device_count", "rt_multi_context",
                "rt_multi_scene_create", "rt_multi_scene_destroy", "rt_render_multi",
-               "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
+               "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_frame_rect_info", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
                "rth_flat_desc", "rth_scene_upload", "rth_camera", "rth_encode_image", "rth_decode_image", "rth_set_earth_image"]
 
 
@@ -124,6 +124,7 @@ def _load():
     L.rt_scene_device_bytes.argtypes = [vp]
     L.rt_scene_device_bytes.restype = u64
     L.rt_scene_bvh_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
+    L.rt_scene_frame_rect_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
     L.rt_last_error.restype = C.c_char_p
     L.rt_abi_version.restype = u32
     L.rth_example_scene.argtypes = [C.c_char_p, u64, C.POINTER(vp)]
@@ -353,6 +354,11 @@ class Scene:
         n, a, d = C.c_uint32(), C.c_uint32(), C.c_uint32()
         _check(lib.rt_scene_bvh_info(self._h, C.byref(n), C.byref(a), C.byref(d)))
         return {"nodes": n.value, "always": a.value, "depth": d.value}
+
+    def frame_rect_info(self):
+        f, b, l = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _check(lib.rt_scene_frame_rect_info(self._h, C.byref(f), C.byref(b), C.byref(l)))
+        return {"frames": f.value, "boxes": b.value, "loose": l.value}
 
     def device_bytes(self):
         return int(lib.rt_scene_device_bytes(self._h))

@@ -197,10 +197,11 @@ int validateDesc(const RtSceneDesc* d) {
 // |local x| <= hx  <=>  |U_ka . p - (-s_x t_x)| <= hx.
 struct FrameRects {
     std::vector<float4> blob;
-    uint32_t n = 0, frames = 0, identity = 0;
+    uint32_t n = 0, frames = 0, identity = 0, boxes = 0, loose = 0;
+    uint32_t box_range[RT_MAX_FRAMES + 1] = {0};
     uint32_t range[RT_MAX_FRAMES * 3 + 1] = {0};
 };
-bool buildFrameRects(const RtPrim* prims, const std::vector<uint32_t>& order, FrameRects& out) {
+bool buildFrameRects(const RtPrim* prims, const std::vector<uint32_t>& order, bool find_boxes, FrameRects& out) {
     struct Rec { uint32_t frame, axis, prim; float w, ca, cb, ha, hb; };
     struct Frame { double u[3][3]; bool identity; };
     std::vector<Frame> frames;
@@ -266,21 +267,95 @@ bool buildFrameRects(const RtPrim* prims, const std::vector<uint32_t>& order, Fr
     for (uint32_t j = 0; j < frames.size(); ++j) slot[j] = ((int)j == world) ? 0u : next++;
     for (auto& r : recs) r.frame = slot[r.frame];
     std::stable_sort(recs.begin(), recs.end(), [](const Rec& a, const Rec& b) { return a.frame != b.frame ? a.frame < b.frame : a.axis < b.axis; });
-    out.n = n; out.frames = (uint32_t)frames.size(); out.identity = world >= 0 ? 1u : 0u;
-    out.blob.assign(3 * frames.size() + n + (n + 1) / 2, make_float4(0, 0, 0, 0));
-    for (uint32_t j = 0; j < frames.size(); ++j)
+    // ---- frame boxes: rectangles of one frame that lie on the faces of a common box, each inside its face -------------------
+    // In-plane axes of a rectangle with normal axis k: a = (k == 0 ? 1 : 0), b = (k == 2 ? 1 : 2) (the kernel's convention).
+    struct Box { uint32_t frame; double lo[3], hi[3]; int face[6]; };
+    std::vector<Box> boxes;
+    std::vector<int> owner(recs.size(), -1);
+    auto axA = [](uint32_t k) { return k == 0 ? 1 : 0; };
+    auto axB = [](uint32_t k) { return k == 2 ? 1 : 2; };
+    auto near = [](double x, double y) { return std::fabs(x - y) <= 4e-7 * std::max(1.0, std::max(std::fabs(x), std::fabs(y))); };  // the records are f32: a few ulps
+    auto within = [](double lo, double hi, double blo, double bhi) {
+        const double tol = 4e-7 * std::max(1.0, std::max(std::fabs(blo), std::fabs(bhi)));
+        return lo >= blo - tol && hi <= bhi + tol;
+    };
+    if (find_boxes) {
+        for (size_t i = 0; i < recs.size(); ++i) {
+            if (owner[i] >= 0) continue;
+            for (size_t j = i + 1; j < recs.size() && owner[i] < 0; ++j) {
+                if (owner[j] >= 0 || recs[j].frame != recs[i].frame || recs[j].axis != recs[i].axis || near(recs[i].w, recs[j].w)) continue;
+                const uint32_t k = recs[i].axis, a = axA(k), b = axB(k);
+                Box B{};
+                B.frame = recs[i].frame;
+                for (int s = 0; s < 6; ++s) B.face[s] = -1;
+                const size_t lo_i = recs[i].w < recs[j].w ? i : j, hi_i = lo_i == i ? j : i;
+                B.lo[k] = recs[lo_i].w; B.hi[k] = recs[hi_i].w;
+                B.lo[a] = std::min((double)recs[i].ca - recs[i].ha, (double)recs[j].ca - recs[j].ha);
+                B.hi[a] = std::max((double)recs[i].ca + recs[i].ha, (double)recs[j].ca + recs[j].ha);
+                B.lo[b] = std::min((double)recs[i].cb - recs[i].hb, (double)recs[j].cb - recs[j].hb);
+                B.hi[b] = std::max((double)recs[i].cb + recs[i].hb, (double)recs[j].cb + recs[j].hb);
+                B.face[2 * k] = (int)lo_i; B.face[2 * k + 1] = (int)hi_i;
+                uint32_t count = 2;
+                for (size_t r = 0; r < recs.size(); ++r) {
+                    if (owner[r] >= 0 || r == i || r == j || recs[r].frame != B.frame || recs[r].axis == k) continue;
+                    const uint32_t k2 = recs[r].axis, a2 = axA(k2), b2 = axB(k2);
+                    int slot = -1;
+                    if (near(recs[r].w, B.lo[k2])) slot = 2 * (int)k2;
+                    else if (near(recs[r].w, B.hi[k2])) slot = 2 * (int)k2 + 1;
+                    if (slot < 0 || B.face[slot] >= 0) continue;
+                    if (!within((double)recs[r].ca - recs[r].ha, (double)recs[r].ca + recs[r].ha, B.lo[a2], B.hi[a2])) continue;
+                    if (!within((double)recs[r].cb - recs[r].hb, (double)recs[r].cb + recs[r].hb, B.lo[b2], B.hi[b2])) continue;
+                    B.face[slot] = (int)r;
+                    ++count;
+                }
+                if (count < 3) continue;  // a slab test costs about two rectangle tests
+                for (int s = 0; s < 6; ++s)
+                    if (B.face[s] >= 0) {
+                        owner[(size_t)B.face[s]] = (int)boxes.size();
+                        (s & 1 ? B.hi : B.lo)[s >> 1] = recs[(size_t)B.face[s]].w;  // every face keeps its OWN plane: t is the rectangle's t
+                    }
+                boxes.push_back(B);
+            }
+        }
+    }
+    std::vector<Rec> loose;
+    for (size_t i = 0; i < recs.size(); ++i) if (owner[i] < 0) loose.push_back(recs[i]);
+    const uint32_t nb = (uint32_t)boxes.size(), nl = (uint32_t)loose.size(), nf = (uint32_t)frames.size();
+    out.n = n; out.frames = nf; out.identity = world >= 0 ? 1u : 0u; out.boxes = nb; out.loose = nl;
+    out.blob.assign(3 * (size_t)nf + 10 * (size_t)nb + nl + (nl + 1) / 2, make_float4(0, 0, 0, 0));
+    for (uint32_t j = 0; j < nf; ++j)
         for (int k = 0; k < 3; ++k) out.blob[3 * slot[j] + k] = make_float4((float)frames[j].u[k][0], (float)frames[j].u[k][1], (float)frames[j].u[k][2], 0.0f);
-    float2* ext = reinterpret_cast<float2*>(out.blob.data() + 3 * frames.size() + n);
+    std::stable_sort(boxes.begin(), boxes.end(), [](const Box& a, const Box& b) { return a.frame < b.frame; });
+    {
+        uint32_t g = 0;
+        for (uint32_t i = 0; i < nb; ++i) {
+            while (g <= boxes[i].frame) out.box_range[g++] = i;
+            float4* rec = out.blob.data() + 3 * (size_t)nf + 10 * (size_t)i;
+            rec[0] = make_float4((float)boxes[i].lo[0], (float)boxes[i].lo[1], (float)boxes[i].lo[2], 0.0f);
+            rec[1] = make_float4((float)boxes[i].hi[0], (float)boxes[i].hi[1], (float)boxes[i].hi[2], 0.0f);
+            uint32_t* ids = reinterpret_cast<uint32_t*>(rec + 8);
+            for (int s = 0; s < 8; ++s) ids[s] = RT_NO_PRIM;
+            for (int s = 0; s < 6; ++s) {
+                if (boxes[i].face[s] < 0) continue;
+                const Rec& r = recs[(size_t)boxes[i].face[s]];
+                rec[2 + s] = make_float4(r.ca, r.cb, r.ha, r.hb);
+                ids[s] = r.prim;
+            }
+        }
+        while (g <= RT_MAX_FRAMES) out.box_range[g++] = nb;
+    }
+    float4* lrec = out.blob.data() + 3 * (size_t)nf + 10 * (size_t)nb;
+    float2* ext = reinterpret_cast<float2*>(lrec + nl);
     uint32_t g = 0;
-    for (uint32_t i = 0; i < n; ++i) {
-        const Rec& r = recs[i];
+    for (uint32_t i = 0; i < nl; ++i) {
+        const Rec& r = loose[i];
         while (g <= r.frame * 3 + r.axis) out.range[g++] = i;
         float fi;
         std::memcpy(&fi, &r.prim, 4);
-        out.blob[3 * frames.size() + i] = make_float4(r.w, r.ca, r.cb, fi);
+        lrec[i] = make_float4(r.w, r.ca, r.cb, fi);
         ext[i] = make_float2(r.ha, r.hb);
     }
-    while (g <= RT_MAX_FRAMES * 3) out.range[g++] = n;
+    while (g <= RT_MAX_FRAMES * 3) out.range[g++] = nl;
     return true;
 }
 
@@ -326,6 +401,7 @@ void rt_options_from_env(RtContextOptions* co, RtSceneOptions* so) {
         const int sn = envInt("RT_B200_STAGED_NODES", 0, 1 << 20, -1);
         so->staged_nodes = sn < 0 ? 0u : (uint32_t)sn + 1u;
         if (envInt("RT_B200_RECT_FRAMES", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_FRAME_RECTS;
+        if (envInt("RT_B200_RECT_BOXES", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_FRAME_BOXES;
         if (envInt("RT_B200_STAGE_PRIMS", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_STAGED_PRIMS;
         if (envInt("RT_B200_SMALL_SCENE", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_SMALL_LIST;
     }
@@ -541,7 +617,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     if (e == cudaSuccess) e = upload(s->rects, rects.data(), rects.size());
     if (e == cudaSuccess) e = upload(s->rect_nrm, rect_nrm.data(), rect_nrm.size());
     FrameRects fr;
-    const bool use_fr = small && !(so.flags & RT_SCENE_NO_FRAME_RECTS) && rects.size() / 4 == n && buildFrameRects(desc->prims, bvh.order, fr);
+    const bool use_fr = small && !(so.flags & RT_SCENE_NO_FRAME_RECTS) && rects.size() / 4 == n && buildFrameRects(desc->prims, bvh.order, !(so.flags & RT_SCENE_NO_FRAME_BOXES), fr);
     if (e == cudaSuccess && use_fr) e = upload(s->fr_blob, fr.blob.data(), fr.blob.size());
     if (e == cudaSuccess) e = upload(s->mats, mats.data(), mats.size());
     if (e == cudaSuccess) e = upload(s->texs, desc->textures, (size_t)desc->n_textures);
@@ -573,7 +649,9 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     s->staged_bytes = (size_t)d.n_staged_nodes * 32 + (size_t)d.n_staged_prims * 16 + (d.n_staged_prims ? (size_t)d.n_rects * 64 : 0);
     if (use_fr) {
         d.fr_blob = s->fr_blob.p; d.fr_n = fr.n; d.fr_frames = fr.frames; d.fr_identity = fr.identity;
+        d.fr_boxes = fr.boxes; d.fr_loose = fr.loose; d.fr_blob4 = (uint32_t)fr.blob.size();
         std::memcpy(d.fr_range, fr.range, sizeof(fr.range));
+        std::memcpy(d.fr_box_range, fr.box_range, sizeof(fr.box_range));
         s->fr_bytes = fr.blob.size() * sizeof(float4);
     }
     s->shade_bytes = (size_t)std::min<uint32_t>(d.n_mats, RT_MAX_STAGED_MATS) * 32 + (size_t)d.n_staged_prims * (16 + 8) +
@@ -599,6 +677,15 @@ int rt_scene_bvh_info(const RtScene* s, uint32_t* n_nodes, uint32_t* n_always, u
     if (n_nodes) *n_nodes = s->d.n_nodes;
     if (n_always) *n_always = s->d.n_always;
     if (max_depth) *max_depth = s->bvh_depth;
+    return RT_OK;
+}
+
+int rt_scene_frame_rect_info(const RtScene* s, uint32_t* n_frames, uint32_t* n_boxes, uint32_t* n_loose) {
+    if (!s) return fail(RT_ERR_INVALID, "scene is null");
+    const bool on = s->d.fr_n > 0;
+    if (n_frames) *n_frames = on ? s->d.fr_frames : 0u;
+    if (n_boxes) *n_boxes = on ? s->d.fr_boxes : 0u;
+    if (n_loose) *n_loose = on ? s->d.fr_loose : 0u;
     return RT_OK;
 }
 

@@ -70,13 +70,24 @@ struct DScene {
     uint32_t small_all_rects;  // n_small > 0, every primitive is a rectangle and the records are staged: specialised loop
     float always_k[RT_MAX_ALWAYS];  // |centre|^2 - r^2 of the always-list spheres, rounded from f64 (big_sphere_hit)
     // Frame-rect list (k_extend_rects; small all-rectangle scenes whose transforms are rigid): the rectangles are grouped
-    // by the orthonormal frame they are axis-aligned in (cornell-box: world + one frame per rotated cube) and, inside a
-    // frame, by normal axis.  fr_blob = [3 float4 rows per frame][fr_n x float4 (plane w, centre a, centre b, primitive)]
-    // [fr_n x float2 (half extent a, half extent b)]; group (f, k) = records fr_range[3f+k] .. fr_range[3f+k+1].
+    // by the orthonormal frame they are axis-aligned in (cornell-box: world + one frame per rotated cube).  Inside a frame,
+    // rectangles that lie on the faces of one common box (each within its face) form a FRAME BOX: a Cube::new (geometry.rs:250-287)
+    // in its own frame, or the four walls of a room.  A line crosses the surface of a convex box at most twice, so the closest hit
+    // among the faces is the entry crossing if that face exists and the point is inside ITS rectangle, else the exit crossing —
+    // one slab test instead of up to six rectangle tests, with every rectangle keeping its own plane, extents and `t >= 1e-6`.
+    // The rest stay LOOSE rectangles, grouped by normal axis.
+    // fr_blob = [3 float4 rows per frame]
+    //           [fr_boxes x 10 float4: lo.xyz, hi.xyz, 6 x (centre a, centre b, half a, half b) for the faces x-, x+, y-, y+, z-, z+,
+    //                                   6 primitive ids (RT_NO_PRIM: no rectangle on that face) + 2 pad]
+    //           [fr_loose x float4 (plane w, centre a, centre b, primitive)] [fr_loose x float2 (half extent a, half extent b)]
+    // boxes of frame f = fr_box_range[f] .. fr_box_range[f+1]; loose group (f, k) = records fr_range[3f+k] .. fr_range[3f+k+1].
     const float4* fr_blob;
-    uint32_t fr_n;         // > 0: extend uses the frame-rect list
+    uint32_t fr_n;         // rectangles in the list (boxed + loose); > 0: extend uses k_extend_rects
     uint32_t fr_frames;
     uint32_t fr_identity;  // frame 0 is the world frame: no rotation of the ray
+    uint32_t fr_boxes, fr_loose;
+    uint32_t fr_blob4;     // float4 count of the blob
+    uint32_t fr_box_range[RT_MAX_FRAMES + 1];
     uint32_t fr_range[RT_MAX_FRAMES * 3 + 1];
 };
 

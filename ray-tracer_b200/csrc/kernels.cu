@@ -389,36 +389,81 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
+// One frame box (device_scene.h): slab test against [lo, hi] in the frame's coordinates, then the entry crossing — or, when the
+// entry face carries no rectangle, the point lies outside its rectangle, the ray starts on it or inside the box — the exit
+// crossing.  t is (plane - o_k) * (1 / d_k) exactly as for a loose rectangle, the plane being the face rectangle's own.
+__device__ __forceinline__ void frame_box(uint32_t box, const float3 o, const float3 d, const float3 inv, uint32_t self_prim, float& best_t, uint32_t& best_i) {
+    const float4 L = lds128(box), H = lds128(box + 16u);
+    const float x0 = (L.x - o.x) * inv.x, x1 = (H.x - o.x) * inv.x;
+    const float y0 = (L.y - o.y) * inv.y, y1 = (H.y - o.y) * inv.y;
+    const float z0 = (L.z - o.z) * inv.z, z1 = (H.z - o.z) * inv.z;
+    // fminf / fmaxf drop a NaN operand (0 * inf: origin on a slab plane of a zero direction component): that axis then does not constrain
+    const float nx = fminf(x0, x1), ny = fminf(y0, y1), nz = fminf(z0, z1);
+    const float fx = fmaxf(x0, x1), fy = fmaxf(y0, y1), fz = fmaxf(z0, z1);
+    const float t_en = fmaxf(fmaxf(nx, ny), nz), t_ex = fminf(fminf(fx, fy), fz);
+    const bool crosses = t_en <= t_ex;  // false (also for NaN): the line misses the box, it crosses none of its faces inside their bounds
+    if (__ballot_sync(__activemask(), crosses) == 0u) return;  // warp-uniform skip; everything below is branch-free (32 of 32 lanes per instruction)
+    // face slot = 2 * axis + (hi plane ? 1 : 0); the entry plane of axis k is lo when d_k > 0
+    const uint32_t ke = (nx == t_en) ? 0u : ((ny == t_en) ? 1u : 2u), kx = (fx == t_ex) ? 0u : ((fy == t_ex) ? 1u : 2u);
+    const float de = ke == 0u ? d.x : (ke == 1u ? d.y : d.z), dx = kx == 0u ? d.x : (kx == 1u ? d.y : d.z);
+    const uint32_t slot_en = 2u * ke + (de > 0.0f ? 0u : 1u), slot_ex = 2u * kx + (dx > 0.0f ? 1u : 0u);
+    // both crossings are evaluated; the entry crossing wins when it is a hit (it is the nearer one)
+    const uint32_t id_en = lds32(box + 128u + 4u * slot_en), id_ex = lds32(box + 128u + 4u * slot_ex);
+    const float4 Fe = lds128(box + 32u + 16u * slot_en), Fx = lds128(box + 32u + 16u * slot_ex);  // centre a, centre b, half a, half b of the face's rectangle
+    const float ex = fmaf(t_en, d.x, o.x), ey = fmaf(t_en, d.y, o.y), ez = fmaf(t_en, d.z, o.z);
+    const float xx = fmaf(t_ex, d.x, o.x), xy = fmaf(t_ex, d.y, o.y), xz = fmaf(t_ex, d.z, o.z);
+    const float ea = (ke == 0u ? ey : ex) - Fe.x, eb = (ke == 2u ? ey : ez) - Fe.y;
+    const float xa = (kx == 0u ? xy : xx) - Fx.x, xb = (kx == 2u ? xy : xz) - Fx.y;
+    const bool hit_en = crosses & (t_en >= RT_T_EPS) & (id_en != RT_NO_PRIM) & (id_en != self_prim) & (fabsf(ea) <= Fe.z) & (fabsf(eb) <= Fe.w);
+    const bool hit_ex = crosses & (t_ex >= RT_T_EPS) & (id_ex != RT_NO_PRIM) & (id_ex != self_prim) & (fabsf(xa) <= Fx.z) & (fabsf(xb) <= Fx.w);
+    const float t = hit_en ? t_en : t_ex;
+    const uint32_t idx = hit_en ? id_en : id_ex;
+    const bool closer = (t < best_t) | ((t == best_t) & (idx < best_i));
+    const bool hit = (hit_en | hit_ex) & closer;
+    best_t = hit ? t : best_t;
+    best_i = hit ? idx : best_i;
+}
+
+// Closest hit of one ray against the frame-rect list staged at shared-window address `base` (k_extend_rects and, for scenes that use
+// the list, k_trace — so that the fixed-ray parity tests exercise exactly what renders run).
+__device__ __forceinline__ ClosestHit frame_rects_closest(const DScene& S, uint32_t base, const float3 o, const float3 d, uint32_t self_prim) {
+    const uint32_t boxes = base + 48u * S.fr_frames, recs = boxes + 160u * S.fr_boxes, exts = recs + 16u * S.fr_loose;
+    float best_t = 3.402823466e38f;  // a miss is prim == RT_NO_PRIM; its t is never read
+    uint32_t best_i = RT_NO_PRIM;
+#pragma unroll 1
+    for (uint32_t f = 0; f < S.fr_frames; ++f) {
+        float3 of = o, df = d;
+        if (f > 0u || !S.fr_identity) {
+            const float4 u0 = lds128(base + 48u * f), u1 = lds128(base + 48u * f + 16u), u2 = lds128(base + 48u * f + 32u);
+            of = f3(dot3(u0, o), dot3(u1, o), dot3(u2, o));
+            df = f3(dot3(u0, d), dot3(u1, d), dot3(u2, d));
+        }
+        const float3 inv = f3(rcp_approx(df.x), rcp_approx(df.y), rcp_approx(df.z));
+#pragma unroll 1
+        for (uint32_t bx = S.fr_box_range[f]; bx < S.fr_box_range[f + 1]; ++bx) frame_box(boxes + 160u * bx, of, df, inv, self_prim, best_t, best_i);
+        if (S.fr_range[3u * f] != S.fr_range[3u * f + 3u]) {  // frames made of boxes only (a rotated cube) have no loose rectangles
+            frame_axis_rects<0>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
+            frame_axis_rects<1>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
+            frame_axis_rects<2>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
+        }
+    }
+    return ClosestHit{best_i == RT_NO_PRIM ? CUDART_INF_F : best_t, best_i};
+}
+
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_RECTS_MIN_BLOCKS) k_extend_rects(const DScene S, const RayQueue q, float2* __restrict__ hits,
                                                                                       WaveCounters* __restrict__ wc, uint32_t k) {
     extern __shared__ float4 smem4[];
-    const uint32_t n_blob = 3u * S.fr_frames + S.fr_n + (S.fr_n + 1u) / 2u;
-    for (uint32_t i = threadIdx.x; i < n_blob; i += blockDim.x) smem4[i] = S.fr_blob[i];
+    for (uint32_t i = threadIdx.x; i < S.fr_blob4; i += blockDim.x) smem4[i] = S.fr_blob[i];
     __syncthreads();
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem4);
-    const uint32_t recs = base + 48u * S.fr_frames, exts = recs + 16u * S.fr_n;
     const uint32_t n = wc->total[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const float4 a = q.a[i], b = q.b[i];
         const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z);
         const uint32_t self_prim = __float_as_uint(a.w);
-        float best_t = 3.402823466e38f;  // a miss is prim == RT_NO_PRIM; its t is never read
-        uint32_t best_i = RT_NO_PRIM;
-#pragma unroll 1
-        for (uint32_t f = 0; f < S.fr_frames; ++f) {
-            float3 of = o, df = d;
-            if (f > 0u || !S.fr_identity) {
-                const float4 u0 = lds128(base + 48u * f), u1 = lds128(base + 48u * f + 16u), u2 = lds128(base + 48u * f + 32u);
-                of = f3(dot3(u0, o), dot3(u1, o), dot3(u2, o));
-                df = f3(dot3(u0, d), dot3(u1, d), dot3(u2, d));
-            }
-            const float3 inv = f3(rcp_approx(df.x), rcp_approx(df.y), rcp_approx(df.z));
-            frame_axis_rects<0>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
-            frame_axis_rects<1>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
-            frame_axis_rects<2>(S, recs, exts, f, of, df, inv, self_prim, best_t, best_i);
-        }
-        hits[i] = make_float2(best_i == RT_NO_PRIM ? CUDART_INF_F : best_t, __uint_as_float(best_i));
+        const ClosestHit h = frame_rects_closest(S, base, o, d, self_prim);
+        hits[i] = make_float2(h.t, __uint_as_float(h.prim));
     }
 }
 
@@ -649,6 +694,13 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
                                                          uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* __restrict__ out) {
     extern __shared__ float4 smem4[];
     const Staged sm = stage_scene(S, smem4);
+    // scenes that render through the frame-rect list are traced through it too; its blob sits behind the staged scene prefix
+    float4* fr_smem = smem4 + (RT_SMEM_STACK * blockDim.x) / 4u + 2u * S.n_staged_nodes + S.n_staged_prims + (S.n_staged_prims ? 4u * S.n_rects : 0u);
+    if (S.fr_n) {
+        for (uint32_t i = threadIdx.x; i < S.fr_blob4; i += blockDim.x) fr_smem[i] = S.fr_blob[i];
+        __syncthreads();
+    }
+    const uint32_t fr_base = (uint32_t)__cvta_generic_to_shared(fr_smem);
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const RtRayIn r = rays[i];
@@ -659,7 +711,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const
             const uint32_t ord = self_order[i];
             if (ord < S.n_orders) self_prim = __ldg(&S.order_to_prim[ord]);
         }
-        const ClosestHit h = closest_hit<false>(S, sm, o, d, self_prim, key);
+        const ClosestHit h = S.fr_n ? frame_rects_closest(S, fr_base, o, d, self_prim) : closest_hit<false>(S, sm, o, d, self_prim, key);
         RtHitOut res;
         res.hit = 0; res.prim = -1; res.t = 0.0f; res.material = -1;
         res.p[0] = res.p[1] = res.p[2] = res.n[0] = res.n[1] = res.n[2] = res.uv[0] = res.uv[1] = 0.0f;
@@ -741,11 +793,12 @@ cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_by
 #define RT_TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
     RT_TRY(grant(d, SLOT_EXTEND, k_extend<false, false>, L.extend_smem));
     RT_TRY(grant(d, SLOT_EXTEND_COUNT, k_extend<true, false>, L.extend_smem));
-    RT_TRY(grant(d, SLOT_TRACE, k_trace, L.extend_smem));
+    L.trace_smem = L.extend_smem + fr_bytes;
+    RT_TRY(grant(d, SLOT_TRACE, k_trace, L.trace_smem));
     RT_TRY(grant(d, SLOT_BVH, k_extend_bvh<false>, L.bvh_smem));
     RT_TRY(grant(d, SLOT_BVH_COUNT, k_extend_bvh<true>, L.bvh_smem));
     RT_TRY(occupancy(L.extend_blocks, k_extend<false, false>, RT_EXTEND_BLOCK, L.extend_smem));
-    RT_TRY(occupancy(L.trace_blocks, k_trace, RT_EXTEND_BLOCK, L.extend_smem));
+    RT_TRY(occupancy(L.trace_blocks, k_trace, RT_EXTEND_BLOCK, L.trace_smem));
     RT_TRY(occupancy(L.bvh_blocks, k_extend_bvh<false>, RT_EXTEND_BLOCK, L.bvh_smem));
     if (fr_bytes) {
         RT_TRY(grant(d, SLOT_RECTS, k_extend_rects, fr_bytes));
@@ -831,7 +884,7 @@ void launch_deinterleave(int sms, const float* gathered, float* full, uint32_t w
 }
 void launch_trace(const SceneLaunch& sl, const DScene& S, const RtRayIn* rays, const uint32_t* self_order, uint64_t n, uint32_t seed_lo, uint32_t seed_hi,
                   RtHitOut* out, cudaStream_t st) {
-    k_trace<<<sl.num_sms * sl.trace_blocks, RT_EXTEND_BLOCK, sl.extend_smem, st>>>(S, rays, self_order, n, seed_lo, seed_hi, out);
+    k_trace<<<sl.num_sms * sl.trace_blocks, RT_EXTEND_BLOCK, sl.trace_smem, st>>>(S, rays, self_order, n, seed_lo, seed_hi, out);
 }
 
 }  // namespace rtb

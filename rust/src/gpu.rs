@@ -254,6 +254,7 @@ pub mod ffi {
         pub fn rt_render_multi(scene: *mut RtMultiScene, cam: *const RtCamera, params: *const RtRenderParams, out_sum_rgb: *mut f32,
                                out_sumsq_rgb: *mut f32, stats: *mut RtStats) -> c_int;
         pub fn rt_scene_bvh_info(scene: *const RtScene, n_nodes: *mut u32, n_always: *mut u32, max_depth: *mut u32) -> c_int;
+        pub fn rt_scene_frame_rect_info(scene: *const RtScene, n_frames: *mut u32, n_boxes: *mut u32, n_loose: *mut u32) -> c_int;
         pub fn rt_scene_device_bytes(scene: *const RtScene) -> u64;
         pub fn rt_last_error() -> *const c_char;
         pub fn rt_abi_version() -> u32;
