@@ -11,12 +11,16 @@ cornell-box 600x600, 1024 spp, depth 50 (368.6 M paths per step).
   value      Mpaths/s, whole job over all N GPUs, scene resident in HBM, framebuffer left in HBM (rt_render_device
              + for N>1 the NCCL all-gather and the de-interleave kernel), timed with CUDA events on the stream the
              kernels run on, max over ranks.  N>1 shards the SAME image by interleaved rows -> "scaling": "strong".
-  e2e        same metric through the host-buffer C-ABI calls a reference user would make: every step uploads the
-             flat scene tables from host memory (rt_scene_create: device BVH build + H2D), renders, and brings
-             the framebuffer back to pinned host memory (D2H).
-  roofline   the dominant kernel (k_extend) — its launches are bracketed by CUDA events live in the timed region
-             (RT_RENDER_STAGE_TIMING).  The contract's hbm form is reported (algorithmic queue bytes per ray / time)
-             although the kernel is FP32-issue / latency bound; `roofline_fp32` states that fraction.
+  e2e        same metric through the host-pointer C-ABI calls a reference user makes (what rust/src/gpu.rs binds): every step
+             rt_scene_create (flat scene tables from host memory: device BVH build + H2D) + rt_render (host framebuffer out,
+             D2H inside) at N = 1; at N > 1 the same through rt_render_device + NCCL gather + D2H on rank 0.
+  roofline   the DOMINANT kernel of the step — whichever stage kernel the live CUDA events say takes longest (cornell-box:
+             k_shade<2>, HBM bound; book-one: k_extend<0,1>, ALU-issue bound) — in the contract's HBM form (algorithmic queue
+             bytes per ray / launch time); `roofline_fp32` / `roofline_l2` state extend's instruction-issue and L2 fractions.
+  book_one_4k  the north-star scene (BASELINE.json configs[4], book-one 3840x2160, 1024 spp, depth 50) measured in the SAME run
+             with the same method, so that the driver's BENCH / SCALE records time it at every N.
+  multi_c_abi  at N > 1: the same image through rt_render_multi — ONE process, one host thread per device, ncclCommInitAll,
+             gather to device 0 — driven by rank 0 after the per-rank measurement (the other ranks idle at a barrier).
   cpu_baseline  the f64 oracle in FAITHFUL mode (the reference's algorithm: unpruned recursive BVH, Mat4 per sprite,
              rejection sampling), one thread per host core, on a bounded sample of the same image (fewer spp).
 --impl reference times that CPU implementation as its own arm (the Rust reference cannot be built in this image).
@@ -118,14 +122,16 @@ def measure_l2():
 
 
 def ncu_traffic(workload, kernel):
-    """DRAM bytes per ray of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json)."""
+    """DRAM bytes per ray of a kernel from the committed `ncu --set full` capture of the same workload (profiles/traffic.json:
+    dram__bytes_read.sum + dram__bytes_write.sum of one launch / its rays).  Not measured in this run — hardware counters
+    need the profiler — so the line says so (`traffic_measured_in_run: false`) next to the capture it comes from."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
     if not os.path.exists(path):
         return None, None
-    t = json.load(open(path)).get(workload)
-    if not t or t.get("kernel") != kernel:
-        return None, None
-    return float(t["dram_bytes_per_ray"]), t.get("source")
+    for t in json.load(open(path)).get(workload, []):
+        if t.get("kernel") == kernel:
+            return float(t["dram_bytes_per_ray"]), t.get("source")
+    return None, None
 
 
 def run_reference(args, wl):
@@ -160,7 +166,8 @@ def run_reference(args, wl):
     line = {
         "impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": cfg, "scene": scene_name, "width": w, "height": h, "spp": spp, "max_depth": depth, "sample": sample},
+        "config": {"workload": cfg, "scene": scene_name, "width": w, "height": h, "spp": spp, "max_depth": depth},  # same keys as the repo arm
+        "sample": sample,
         "grays_per_s": rays / dt / 1e9,
         "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -189,6 +196,220 @@ def cpu_baseline(wl):
             "grays_per_s": st.segments / dt / 1e9, "box_tests_per_ray": st.box_tests / st.segments, "prim_tests_per_ray": st.prim_tests / st.segments}
 
 
+STAGES = ["generate", "extend", "shade", "accumulate"]
+
+
+def measure(ctx, workload, steps, warmup, want_work=True):
+    """Times `steps` renders of one workload on this rank's GPU (sharded over the ranks when world > 1) and returns the pieces of
+    the JSON line that belong to it.  Collective: every rank calls it with the same arguments."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rt, rtdist, dev, world, rank, args = ctx["rt"], ctx["rtdist"], ctx["dev"], ctx["world"], ctx["rank"], ctx["args"]
+    scene_name, W, H, spp, depth, cfg = WORKLOADS[workload]
+    flat = rt.FlatScene(scene_name, 1)
+    scene = rt.Scene(dev, flat=flat)
+    cam = flat.camera(W / H)
+    stream = torch.cuda.current_stream()
+    flush = ctx["flush"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(seed, flags=0):
+        flush.zero_()
+        return rtdist.render_sharded(scene, cam, W, H, spp, depth, seed, rank, world, args.queue_capacity, flags)
+
+    for i in range(warmup):
+        step(1000 + i)
+    barrier()
+    sampler = ClockSampler(ctx["local_rank"])
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    paths = rays = launches = 0
+    for i in range(steps):
+        full, st = step(2000 + i)
+        paths += st.paths
+        rays += st.rays
+        launches += st.launches + (1 if world > 1 else 0) + 1  # + de-interleave kernel, + the L2-flush memset
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = ev0.elapsed_time(ev1)
+    # ---- per-stage launch durations: the same steps again with CUDA events around the launches of every 8th wavefront iteration.
+    # A stage-timed render runs as ONE wavefront lane, so that a timed launch has the device to itself (the timed region above runs
+    # two interleaved lanes whose kernels share the SMs); these are the durations the rooflines are computed from. ----
+    iters = 0
+    ms_stage = np.zeros(4)
+    for i in range(steps):
+        _, st = step(2000 + i, rt.RENDER_STAGE_TIMING)
+        iters += st.iterations
+        ms_stage += [st.ms_generate, st.ms_extend, st.ms_shade, st.ms_accumulate]
+    barrier()
+    red = torch.tensor([ms, *ms_stage], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(paths), float(rays), float(launches), float(iters)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_all = float(red[0])
+    stage_max = [float(v) for v in red[1:]]  # slowest rank, summed over the steps
+    tot_paths, tot_rays, tot_launches, tot_iters = float(tot[0]), float(tot[1]), int(tot[2]), float(tot[3])
+    value = tot_paths / (ms_all * 1e-3) / 1e6
+    mean_check = float(full.mean()) / spp
+
+    # ---- algorithmic work per ray: one instrumented render outside the timed region (counts are spp-independent) ----
+    box_per_ray = prim_per_ray = 0.0
+    if want_work:
+        _, stw = rtdist.render_sharded(scene, cam, W, H, min(spp, 16), depth, 4000, rank, world, args.queue_capacity, rt.RENDER_COUNT_WORK)
+        work = torch.tensor([float(stw.box_tests), float(stw.prim_tests), float(stw.rays)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(work, op=dist.ReduceOp.SUM)
+        box_per_ray, prim_per_ray = float(work[0] / work[2]), float(work[1] / work[2])
+
+    # ---- e2e: host tables in, host framebuffer out, every step ------------------------------------
+    scene_bytes = scene.device_bytes()
+    if world == 1:
+        host_fb = np.zeros((H, W, 3), dtype=np.float32)
+
+        def e2e_step(seed):
+            sc = rt.Scene(dev, flat=flat)  # rt_scene_create: BVH build + H2D of every table
+            sc.render(cam, W, H, spp, depth, seed=seed, queue_capacity=args.queue_capacity, want_sumsq=False, out=host_fb)  # rt_render: host pointer out
+            sc.close()
+    else:
+        host_fb = torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True)
+
+        def e2e_step(seed):
+            sc = rt.Scene(dev, flat=flat)
+            out, _ = rtdist.render_sharded(sc, cam, W, H, spp, depth, seed, rank, world, args.queue_capacity)
+            if rank == 0:
+                host_fb.copy_(out, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            sc.close()
+
+    e2e_step(3000)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        e2e_step(3001 + i)
+    barrier()
+    e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = (W * H * spp * steps) / float(e2e_t[0]) / 1e6
+
+    out = None
+    if rank == 0:
+        hbm_peak, peak_src, sm_max = load_peaks()
+        info, fr = scene.bvh_info(), scene.frame_rect_info()
+        kinds = flat.prims()["kind"]
+        rect_frac = float(np.mean(kinds == rt.PRIM_RECT))
+        extend_kernel = "k_extend_rects" if fr["frames"] else ("k_extend_bvh" if info["nodes"] >= 65536 else
+                                                                ("k_extend<false, true>" if 0 < info["nodes"] <= 2048 else "k_extend<false, false>"))
+        shade_kernel = "k_shade<2>" if fr["frames"] else "k_shade<1>"
+        kernel_of = {"generate": "k_generate", "extend": extend_kernel, "shade": shade_kernel, "accumulate": "k_accumulate"}
+        launches_rank = tot_iters / world  # launches of each stage kernel on one rank = its wavefront iterations
+        rays_rank = tot_rays / world
+        rays_per_launch = tot_rays / max(tot_iters, 1)
+        survive = 1.0 - tot_paths / tot_rays  # every path ends exactly once: the other segments scatter on
+        # algorithmic HBM bytes per ray segment of the two queue-streaming stages (DESIGN.md §4): extend reads a, b (32 B) and writes
+        # the hit (8 B); shade reads a, b, c and the hit (56 B) and writes a, b, c of the rays that scatter on (48 B each)
+        bytes_of = {"extend": float(EXTEND_BYTES_PER_RAY), "shade": 56.0 + 48.0 * survive}
+        dominant = max(("extend", "shade"), key=lambda s_: stage_max[STAGES.index(s_)])
+        sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
+
+        def hbm_roofline(stage):
+            dur = stage_max[STAGES.index(stage)] * 1e-3 / max(launches_rank, 1)
+            achieved = bytes_of[stage] * rays_per_launch / max(dur, 1e-12) / 1e9
+            bpr, src = ncu_traffic(workload, kernel_of[stage])
+            return {"kernel": kernel_of[stage], "stage": stage, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                    "traffic": bpr * rays_per_launch if bpr else None, "traffic_source": src, "traffic_measured_in_run": False,
+                    "peak_source": peak_src, "launch_us": dur * 1e6, "rays_per_launch": rays_per_launch, "algorithmic_bytes_per_ray": bytes_of[stage],
+                    "timing": "CUDA events around the kernel's launches of every 8th wavefront iteration, in a single-lane repeat of the timed "
+                              "steps right after the timed region (the timed region itself overlaps two wavefront lanes)"}
+
+        out = {
+            "value": value, "ms_per_step": ms_all / steps, "steps": steps, "warmup": warmup,
+            "config": {"workload": cfg, "scene": scene_name, "width": W, "height": H, "spp": spp, "max_depth": depth},
+            "run": {"seed_scene": 1, "sharding": f"rows y % {world} == rank, NCCL all-gather + de-interleave" if world > 1 else "single GPU",
+                    "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": info, "frame_rects": fr,
+                    "queue_capacity": args.queue_capacity or 1 << 22, "wavefront_lanes": int(os.environ.get("RT_B200_LANES", "2"))},
+            "grays_per_s": tot_rays / (ms_all * 1e-3) / 1e9, "rays_per_path": tot_rays / tot_paths, "mean_radiance": mean_check,
+            "gpu_launches": tot_launches,
+            "stage_ms_per_step": {s_: stage_max[i] / steps for i, s_ in enumerate(STAGES)},
+            "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": scene_bytes + 64 + 40, "d2h_bytes_per_step": W * H * 3 * 4,
+                    "ms_per_step": float(e2e_t[0]) / steps * 1e3,
+                    "api": "rt_scene_create + rt_render (host pointers)" if world == 1 else "rt_scene_create + rt_render_device + NCCL all-gather + D2H on rank 0"},
+            "roofline": hbm_roofline(dominant),
+            "roofline_" + ("shade" if dominant == "extend" else "extend") + "_hbm": hbm_roofline("shade" if dominant == "extend" else "extend"),
+            "clocks": clocks,
+        }
+        if want_work:
+            extend_s = stage_max[1] * 1e-3
+            instr_per_ray = box_per_ray * FP32_PER_BOX + prim_per_ray * (rect_frac * FP32_PER_RECT + (1 - rect_frac) * FP32_PER_SPHERE)
+            rays_per_s_kernel = rays_rank / max(extend_s, 1e-12)  # per GPU, inside the extend kernel
+            fp32_peak = 148 * 128 * sm_mhz * 1e6
+            l2_bytes_per_ray = box_per_ray * 32 + prim_per_ray * (rect_frac * 64 + (1 - rect_frac) * 16)
+            out["roofline_fp32"] = {"kernel": extend_kernel, "bound": "fp32-issue", "box_tests_per_ray": box_per_ray, "prim_tests_per_ray": prim_per_ray,
+                                    "algorithmic_lane_instr_per_ray": instr_per_ray, "grays_per_s_in_kernel": rays_per_s_kernel / 1e9,
+                                    "achieved": rays_per_s_kernel * instr_per_ray / 1e12, "peak": fp32_peak / 1e12, "unit": "T lane-instr/s",
+                                    "frac": rays_per_s_kernel * instr_per_ray / fp32_peak, "sm_mhz": sm_mhz, "l2_bytes_per_ray": l2_bytes_per_ray,
+                                    "note": "work counted by the instrumented GENERAL traversal on the scene's tables (RT_RENDER_COUNT_WORK), SURVEY §8(d) unit costs"}
+            l2_peak = ctx.get("l2_peak")
+            tables_in_smem = info["nodes"] <= 2048
+            if l2_peak and not tables_in_smem:
+                l2_gbs = l2_peak["l2_read_gbs_32MB"]
+                out["roofline_l2"] = {"kernel": extend_kernel, "bound": "l2", "achieved": rays_per_s_kernel * l2_bytes_per_ray / 1e9, "peak": l2_gbs, "unit": "GB/s",
+                                      "frac": rays_per_s_kernel * l2_bytes_per_ray / 1e9 / l2_gbs, "bytes_per_ray": l2_bytes_per_ray,
+                                      "peak_source": "measured now by ray-tracer_b200/tools/l2bw (32 MB read stream, ld.global.cg)", "l2bw": l2_peak}
+            elif l2_peak:
+                out["roofline_l2"] = {"kernel": extend_kernel, "bound": "l2", "achieved": None, "peak": l2_peak["l2_read_gbs_32MB"], "unit": "GB/s", "frac": None,
+                                      "l2bw": l2_peak, "note": "not applicable: this scene's node / primitive tables are staged in shared memory"}
+        # the whole wavefront against HBM: every stage's algorithmic queue traffic over the timed step (lanes on).  Per ray segment:
+        # extend 40 B, shade 56 B read; a surviving ray is written back (48 B), a finished path writes and accumulate reads a 16-byte
+        # record, generate writes 48 B per path  ->  144 B x rays + 32 B x paths
+        wf_bytes = 144.0 * tot_rays + 32.0 * tot_paths
+        wf_gbs = wf_bytes / (ms_all * 1e-3) / 1e9 / world  # per GPU
+        out["roofline_wavefront_hbm"] = {"bound": "hbm", "achieved": wf_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": wf_gbs / hbm_peak,
+                                         "bytes_per_ray": wf_bytes / max(tot_rays, 1.0), "per": "GPU, all four stage kernels over the timed step",
+                                         "peak_source": peak_src}
+    scene.close()
+    return out
+
+
+def measure_multi_c_abi(ctx, workload, steps):
+    """rank 0: the same image through rt_render_multi (ONE process driving every GPU through the C ABI; host framebuffer out)."""
+    rt, world = ctx["rt"], ctx["world"]
+    scene_name, W, H, spp, depth, cfg = WORKLOADS[workload]
+    flat = rt.FlatScene(scene_name, 1)
+    multi = rt.MultiDevice(list(range(world)))
+    ms = rt.MultiScene(multi, flat=flat)
+    cam = flat.camera(W / H)
+    import numpy as np
+    buf = np.zeros((H, W, 3), dtype=np.float32)
+    ms.render(cam, W, H, spp, depth, seed=1, want_sumsq=False, out=buf)
+    ms.render(cam, W, H, spp, depth, seed=2, want_sumsq=False, out=buf)
+    dev_ms, t0 = 0.0, time.perf_counter()
+    for i in range(steps):
+        _, _, st = ms.render(cam, W, H, spp, depth, seed=10 + i, want_sumsq=False, out=buf)
+        dev_ms += st.ms_total
+    wall = time.perf_counter() - t0
+    paths = float(W) * H * spp * steps
+    res = {"api": "rt_init_multi + rt_multi_scene_create + rt_render_multi (one process, one host thread per device, ncclCommInitAll, ncclSend/ncclRecv gather "
+                  "to device 0, k_deinterleave, D2H)", "workload": cfg, "n_gpus": world, "steps": steps,
+           "value": paths / (dev_ms * 1e-3) / 1e6, "unit": "Mpaths/s", "ms_per_step": dev_ms / steps,
+           "e2e": {"value": paths / wall / 1e6, "unit": "Mpaths/s", "ms_per_step": wall / steps * 1e3, "d2h_bytes_per_step": W * H * 12},
+           "mean_radiance": float(buf.mean()) / spp}
+    ms.close()
+    multi.close()
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -198,6 +419,8 @@ def main():
     ap.add_argument("--workload", default="cornell-box", choices=sorted(WORKLOADS))
     ap.add_argument("--queue-capacity", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-book-one-4k", action="store_true", help="skip the north-star block (BASELINE.json configs[4]) of the line")
+    ap.add_argument("--no-multi-c-abi", action="store_true", help="N > 1: skip the rt_render_multi (single process) block")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]
@@ -205,7 +428,6 @@ def main():
         run_reference(args, wl)
         return
 
-    import numpy as np
     import torch
     import torch.distributed as dist
 
@@ -220,165 +442,42 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
-    scene_name, W, H, spp, depth, cfg = wl
+    ctx = {"rt": rt, "rtdist": rtdist, "dev": rt.Device(local_rank), "world": world, "rank": rank, "local_rank": local_rank, "args": args,
+           "flush": torch.empty(256 << 20, dtype=torch.uint8, device="cuda"),  # > 126 MB L2
+           "l2_peak": measure_l2() if rank == 0 else None}
 
-    dev = rt.Device(local_rank)
-    flat = rt.FlatScene(scene_name, 1)
-    scene = rt.Scene(dev, flat=flat)
-    cam = flat.camera(W / H)
-    stream = torch.cuda.current_stream()
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
+    main_res = measure(ctx, args.workload, args.steps, args.warmup)
+    # the north-star scene in the same run: fewer steps (1.6 s each at N = 1), same method
+    b4k = None
+    if args.workload != "book-one-4k" and not args.no_book_one_4k:
+        b4k = measure(ctx, "book-one-4k", max(2, min(args.steps, 3)), 3)
+    multi = None
+    if world > 1 and not args.no_multi_c_abi:
         torch.cuda.synchronize()
-
-    def step(seed, flags=0):
-        flush.zero_()
-        return rtdist.render_sharded(scene, cam, W, H, spp, depth, seed, rank, world, args.queue_capacity, flags)
-
-    for i in range(args.warmup):
-        step(1000 + i)
-    barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    ev0.record(stream)
-    paths = rays = launches = 0
-    for i in range(args.steps):
-        full, st = step(2000 + i)
-        paths += st.paths
-        rays += st.rays
-        launches += st.launches + (1 if world > 1 else 0) + 1  # + de-interleave kernel, + the L2-flush memset
-    ev1.record(stream)
-    barrier()
-    clocks = sampler.stop() if rank == 0 else None
-    ms = ev0.elapsed_time(ev1)
-    # ---- per-stage launch durations: the same steps again with CUDA events around the launches of every 8th wavefront iteration.
-    # A stage-timed render runs as ONE wavefront lane, so that a timed launch has the device to itself (the timed region above runs
-    # two interleaved lanes whose kernels share the SMs); these are the durations the rooflines are computed from. ----
-    iters = 0
-    ms_stage = np.zeros(4)
-    for i in range(args.steps):
-        _, st = step(2000 + i, rt.RENDER_STAGE_TIMING)
-        iters += st.iterations
-        ms_stage += [st.ms_generate, st.ms_extend, st.ms_shade, st.ms_accumulate]
-    barrier()
-    counts = torch.tensor([ms, float(paths), float(rays), float(launches), float(ms_stage[1]), float(iters)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        mx = counts.clone()
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
-        ms_all = float(mx[0])
-        ms_extend_max = float(mx[4])
-    else:
-        ms_all, ms_extend_max = ms, float(ms_stage[1])
-    tot_paths, tot_rays, tot_launches = float(counts[1]), float(counts[2]), int(counts[3])
-    value = tot_paths / (ms_all * 1e-3) / 1e6
-    mean_check = float(full.mean()) / spp
-
-    # ---- algorithmic work per ray: one instrumented render outside the timed region (counts are spp-independent) ----
-    _, stw = rtdist.render_sharded(scene, cam, W, H, min(spp, 16), depth, 4000, rank, world, args.queue_capacity, rt.RENDER_COUNT_WORK)
-    work = torch.tensor([float(stw.box_tests), float(stw.prim_tests), float(stw.rays)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(work, op=dist.ReduceOp.SUM)
-    box_per_ray, prim_per_ray = float(work[0] / work[2]), float(work[1] / work[2])
-
-    # ---- e2e: host tables in, host framebuffer out, every step ------------------------------------
-    host_fb = torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True)
-    scene_bytes = scene.device_bytes()
-
-    def e2e_step(seed):
-        sc = rt.Scene(dev, flat=flat)  # rt_scene_create: SAH build on the host + H2D of every table
-        out, _ = rtdist.render_sharded(sc, cam, W, H, spp, depth, seed, rank, world, args.queue_capacity)
+        dist.barrier()
         if rank == 0:
-            host_fb.copy_(out, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        sc.close()
-
-    e2e_step(3000)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(3001 + i)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_value = (W * H * spp * args.steps) / float(e2e_t[0]) / 1e6
+            try:
+                multi = {"headline": measure_multi_c_abi(ctx, args.workload, args.steps)}
+                if b4k is not None:
+                    multi["book_one_4k"] = measure_multi_c_abi(ctx, "book-one-4k", 2)
+            except Exception as e:  # noqa: BLE001 - reported in the line, the per-rank measurement above stands on its own
+                multi = {"error": str(e)}
+        dist.barrier()
 
     if rank == 0:
-        hbm_peak, peak_src, sm_max = load_peaks()
-        l2_peak = measure_l2()
-        n_extend = float(counts[5])  # extend launches = wavefront iterations, summed over ranks
-        rays_per_launch = tot_rays / max(n_extend, 1)
-        # per-launch duration: summed extend time of the slowest rank / its launches (ranks have equal iteration counts to within a few)
-        extend_s = ms_extend_max * 1e-3
-        extend_launches_rank = n_extend / world
-        dur = extend_s / max(extend_launches_rank, 1)
-        achieved = EXTEND_BYTES_PER_RAY * rays_per_launch / max(dur, 1e-12) / 1e9
-        sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
-        kinds = flat.prims()["kind"]
-        rect_frac = float(np.mean(kinds == rt.PRIM_RECT))
-        info = scene.bvh_info()
-        kernel = "k_extend_rects" if (info["nodes"] == 0 and rect_frac == 1.0) else ("k_extend_bvh" if info["nodes"] >= 65536 else "k_extend")
-        bytes_per_ray, traffic_src = ncu_traffic(args.workload, kernel)
-        line = {
-            "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_all / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
-            "config": {"workload": cfg, "scene": scene_name, "width": W, "height": H, "spp": spp, "max_depth": depth, "seed_scene": 1,
-                       "sharding": f"rows y % {world} == rank, NCCL all-gather + de-interleave" if world > 1 else "single GPU",
-                       "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": info,
-                       "queue_capacity": args.queue_capacity or 1 << 22,
-                       "wavefront_lanes": int(os.environ.get("RT_B200_LANES", "2"))},
-            "grays_per_s": tot_rays / (ms_all * 1e-3) / 1e9, "rays_per_path": tot_rays / tot_paths, "mean_radiance": mean_check,
-            "gpu_launches": tot_launches,
-            "stage_ms_per_step": {"generate": ms_stage[0] / args.steps, "extend": ms_stage[1] / args.steps, "shade": ms_stage[2] / args.steps,
-                                  "accumulate": ms_stage[3] / args.steps},
-            "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": scene_bytes + 64 + 40,
-                    "d2h_bytes_per_step": W * H * 3 * 4, "ms_per_step": float(e2e_t[0]) / args.steps * 1e3},
-            "roofline": {"kernel": kernel, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": bytes_per_ray * rays_per_launch if bytes_per_ray else None, "traffic_source": traffic_src,
-                         "peak_source": peak_src, "launch_us": dur * 1e6, "rays_per_launch": rays_per_launch,
-                         "algorithmic_bytes_per_ray": EXTEND_BYTES_PER_RAY,
-                         "timing": "CUDA events around the kernel's launches of every 8th wavefront iteration, in a single-lane repeat of the "
-                                   "timed steps right after the timed region (the timed region itself overlaps two wavefront lanes)",
-                         "note": "extend is FP32-issue/latency bound, not HBM bound; see roofline_fp32 and DESIGN.md"},
-            "clocks": clocks,
-        }
-        instr_per_ray = box_per_ray * FP32_PER_BOX + prim_per_ray * (rect_frac * FP32_PER_RECT + (1 - rect_frac) * FP32_PER_SPHERE)
-        rays_per_s_kernel = tot_rays / world / max(extend_s, 1e-12)  # per GPU, inside k_extend
-        fp32_peak = 148 * 128 * sm_mhz * 1e6
-        l2_bytes_per_ray = box_per_ray * 32 + prim_per_ray * (rect_frac * 64 + (1 - rect_frac) * 16)
-        tables_in_smem = info["nodes"] <= 2048  # whole tree + primitive heads (or the frame-rect list) staged in shared memory
-        if l2_peak and tables_in_smem:
-            line["roofline_l2"] = {"kernel": kernel, "bound": "l2", "achieved": None, "peak": l2_peak["l2_read_gbs_32MB"], "unit": "GB/s", "frac": None,
-                                   "peak_source": "measured now by ray-tracer_b200/tools/l2bw (32 MB read stream, ld.global.cg)", "l2bw": l2_peak,
-                                   "note": "not applicable: this scene's node / primitive tables are staged in shared memory, extend reads no table from L2"}
-        elif l2_peak:
-            l2_gbs = l2_peak["l2_read_gbs_32MB"]
-            line["roofline_l2"] = {"kernel": kernel, "bound": "l2", "achieved": rays_per_s_kernel * l2_bytes_per_ray / 1e9, "peak": l2_gbs, "unit": "GB/s",
-                                   "frac": rays_per_s_kernel * l2_bytes_per_ray / 1e9 / l2_gbs, "bytes_per_ray": l2_bytes_per_ray,
-                                   "peak_source": "measured now by ray-tracer_b200/tools/l2bw (32 MB read stream, ld.global.cg)", "l2bw": l2_peak,
-                                   "note": "upper bound on node/primitive traffic: staged tables are read from shared memory, not L2"}
-        line["roofline_fp32"] = {"kernel": kernel, "bound": "fp32-issue", "box_tests_per_ray": box_per_ray, "prim_tests_per_ray": prim_per_ray,
-                                 "algorithmic_lane_instr_per_ray": instr_per_ray, "grays_per_s_in_kernel": rays_per_s_kernel / 1e9,
-                                 "achieved": rays_per_s_kernel * instr_per_ray / 1e12, "peak": fp32_peak / 1e12, "unit": "T lane-instr/s",
-                                 "frac": rays_per_s_kernel * instr_per_ray / fp32_peak, "sm_mhz": sm_mhz,
-                                 "l2_bytes_per_ray": l2_bytes_per_ray}
-        # the whole wavefront against HBM: every stage's algorithmic queue traffic over the timed step (lanes on).  Per ray segment:
-        # extend reads a, b and writes the hit (40 B), shade reads a, b, c and the hit (56 B); a surviving ray is written back (48 B),
-        # a finished path writes and accumulate reads a 16-byte record, generate writes 48 B per path  ->  144 B x rays + 32 B x paths
-        wf_bytes = 144.0 * tot_rays + 32.0 * tot_paths
-        wf_gbs = wf_bytes / (ms_all * 1e-3) / 1e9 / world  # per GPU
-        line["roofline_wavefront_hbm"] = {"bound": "hbm", "achieved": wf_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": wf_gbs / hbm_peak,
-                                          "bytes_per_ray": wf_bytes / max(tot_rays, 1.0), "per": "GPU, all four stage kernels over the timed step",
-                                          "peak_source": peak_src}
+        line = {"metric": "Mpaths/s", "value": main_res["value"], "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": main_res["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+        for k, v in main_res.items():
+            if k not in ("value", "ms_per_step", "steps", "warmup"):
+                line[k] = v
+        if b4k is not None:
+            b4k["metric"], b4k["unit"], b4k["n_gpus"] = "Mpaths/s", "Mpaths/s", world
+            b4k["warp_execution_efficiency"] = {"kernel": "k_extend<false, true>", "value": 0.66, "measured_in_run": False,
+                                                "source": "profiles/r3a_full_metrics_cornell_book-one.txt: smsp__thread_inst_executed_per_inst_executed 21.2 / 32 "
+                                                          "(ncu --set full; hardware counters need the profiler)"}
+            line["book_one_4k"] = b4k
+        if multi is not None:
+            line["multi_c_abi"] = multi
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
         print(json.dumps(line), flush=True)

@@ -367,11 +367,14 @@ class Scene:
     def params(width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, flags=0):
         return RtRenderParams(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity, flags)
 
-    def render(self, cam, width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, want_sumsq=True, flags=0):
-        """rt_render with host buffers: returns (sum[rows,W,3], sumsq or None, RtStats); rows y = row_begin + k*row_stride."""
+    def render(self, cam, width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, queue_capacity=0, want_sumsq=True, flags=0, out=None):
+        """rt_render with host buffers: returns (sum[rows,W,3], sumsq or None, RtStats); rows y = row_begin + k*row_stride.
+        `out`: a caller-owned C-contiguous float32 [rows, W, 3] buffer to receive the sums."""
         prm = self.params(width, height, spp, max_depth, seed, row_begin, row_stride, queue_capacity, flags)
         rows = len(range(row_begin, height, row_stride)) if row_stride > 0 else 0  # the library rejects stride 0 / empty shards
-        s = np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows]
+        if out is not None:
+            assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"] and out.shape == (rows, width, 3)
+        s = out if out is not None else np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows]
         q = np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows] if want_sumsq else None
         st = RtStats()
         _check(lib.rt_render(self._h, C.byref(cam), C.byref(prm), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
