@@ -93,7 +93,7 @@ struct RtScene {
     DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm, fr_blob;
     DevBuf<uint2> prim_meta;
     DevBuf<uint32_t> order_to_prim;
-    DevBuf<RtPrim> gen, bnd;
+    DevBuf<RtPrim> gen;
     DevBuf<DMaterial> mats;
     DevBuf<RtTexture> texs;
     uint32_t bvh_depth = 0;
@@ -612,8 +612,13 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
         if (order_to_prim[meta[i].x] == RT_NO_PRIM) order_to_prim[meta[i].x] = i;
     }
     if (e == cudaSuccess) e = upload(s->order_to_prim, order_to_prim.data(), order_to_prim.size());
+    {   // boundary surfaces go behind the general records; each medium points at its own run relative to itself
+        const uint32_t first_boundary = (uint32_t)gen.size();
+        for (uint32_t gi = 0; gi < first_boundary; ++gi)
+            if (gen[gi].kind == RT_PRIM_MEDIUM) gen[gi].aux = first_boundary + gen[gi].aux - gi;
+        gen.insert(gen.end(), desc->boundary_prims, desc->boundary_prims + desc->n_boundary_prims);
+    }
     if (e == cudaSuccess) e = upload(s->gen, gen.data(), gen.size());
-    if (e == cudaSuccess) e = upload(s->bnd, desc->boundary_prims, (size_t)desc->n_boundary_prims);
     if (e == cudaSuccess) e = upload(s->rects, rects.data(), rects.size());
     if (e == cudaSuccess) e = upload(s->rect_nrm, rect_nrm.data(), rect_nrm.size());
     FrameRects fr;
@@ -627,7 +632,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
         return fail(e == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(e));
     }
     DScene& d = s->d;
-    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.bnd = s->bnd.p; d.rects = s->rects.p; d.rect_nrm = s->rect_nrm.p;
+    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.rects = s->rects.p; d.rect_nrm = s->rect_nrm.p;
     d.mats = s->mats.p; d.texs = s->texs.p; d.texels = s->texels.p;
     d.order_to_prim = s->order_to_prim.p; d.n_orders = (uint32_t)order_to_prim.size();
     d.n_nodes = use_lbvh ? lbvh.n_nodes : (uint32_t)bvh.nodes.size(); d.n_prims = n; d.n_always = bvh.n_always; d.n_gen = (uint32_t)gen.size();
@@ -668,7 +673,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
 void rt_scene_destroy(RtScene* s) {
     if (!s) return;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->order_to_prim.release(); s->gen.release(); s->bnd.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->order_to_prim.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
     delete s;
 }
 
@@ -692,7 +697,7 @@ int rt_scene_frame_rect_info(const RtScene* s, uint32_t* n_frames, uint32_t* n_b
 uint64_t rt_scene_device_bytes(const RtScene* s) {
     if (!s) return 0;
     return (uint64_t)s->nodes.n * sizeof(float4) + (uint64_t)s->prim_head.n * sizeof(float4) + (uint64_t)s->prim_meta.n * sizeof(uint2) +
-           (uint64_t)(s->gen.n + s->bnd.n) * sizeof(RtPrim) + (uint64_t)s->order_to_prim.n * sizeof(uint32_t) + (uint64_t)(s->rects.n + s->rect_nrm.n) * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
+           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)s->order_to_prim.n * sizeof(uint32_t) + (uint64_t)(s->rects.n + s->rect_nrm.n) * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
            (uint64_t)s->texels.n * sizeof(float4);
 }
 

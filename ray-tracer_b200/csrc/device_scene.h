@@ -52,8 +52,8 @@ struct DScene {
     const uint2* prim_meta;    // {order, material (int32 bits)}
     const float4* rects;       // 4 float4 per rectangle: row z, row x, row y of object<-world (xyz, translation), (hx, hy, 0, 0)
     const float4* rect_nrm;    // per rectangle: world-space normal M (0,0,1) (forward matrix, not renormalised: SURVEY A.5)
-    const RtPrim* gen;         // general records (non translation-only-sphere primitives)
-    const RtPrim* bnd;         // boundary surfaces of RT_PRIM_MEDIUM primitives (RtSceneDesc.boundary_prims)
+    const RtPrim* gen;         // general records (non translation-only-sphere primitives), then the boundary surfaces of the RT_PRIM_MEDIUM
+                               // records (RtSceneDesc.boundary_prims); a medium record's `aux` is the distance IN RECORDS to its first surface
     const DMaterial* mats;
     const RtTexture* texs;
     const float4* texels;

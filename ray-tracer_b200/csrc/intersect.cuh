@@ -285,9 +285,11 @@ __device__ __forceinline__ float medium_generic_hit(const RtPrim* __restrict__ b
 #ifndef RT_GENERAL_INLINE
 #define RT_GENERAL_INLINE __noinline__
 #endif
-__device__ RT_GENERAL_INLINE float general_hit(const RtPrim* __restrict__ g, const RtPrim* __restrict__ bnd, float3 o, float3 d, bool is_self, const MediumKey key) {
+// (The boundary surfaces of an RT_PRIM_MEDIUM record live in the same table, `aux` records AFTER the record itself — see rt_scene_create —
+// so that this out-of-line function needs no second table pointer: an extra argument here cost k_extend<., true> 24 bytes of spills.)
+__device__ RT_GENERAL_INLINE float general_hit(const RtPrim* __restrict__ g, float3 o, float3 d, bool is_self, const MediumKey key) {
     const uint32_t kind = g->kind;
-    if (kind == RT_PRIM_MEDIUM) return medium_generic_hit(bnd, g->aux, (uint32_t)g->param[2], o, d, g->param[1], g->order, key);
+    if (kind == RT_PRIM_MEDIUM) return medium_generic_hit(g + g->aux, 0u, (uint32_t)g->param[2], o, d, g->param[1], g->order, key);
     const float3 lo = xform_point(g->local_from_world, o);
     const float3 ld = xform_vector(g->local_from_world, d);
     if (kind == RT_PRIM_RECT) return is_self ? CUDART_INF_F : rect_hit(lo, ld, g->param[0], g->param[1]);
@@ -343,7 +345,10 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile(
 
 // Test device primitive `i`.  Returns t or +inf.  BIG = primitive of the always-tested list.
 // ALL = every node and primitive head of the scene is staged in shared memory (k_extend<.., true>): no per-access range check.
-template <bool BIG, bool ALL = false>
+// GEN = the scene has general 128-byte records at all (S.n_gen > 0: rotated / scaled spheres, media).  Scenes without any — book-one,
+// cornell-box, the sphere cloud — run kernels from which the out-of-line general path is compiled away: its mere presence (call ABI,
+// argument marshalling) costs registers in the traversal loop (k_extend<., true>: 24 bytes of spills, -3 %; k_shade: -7 to -11 %).
+template <bool BIG, bool ALL = false, bool GEN = true>
 __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uint32_t i, const RayCtx& R, uint32_t self_prim, const MediumKey& key) {
     const bool staged = ALL || i < S.n_staged_prims;
     float4 h;
@@ -363,7 +368,8 @@ __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uin
         const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
         return rect_hit(R, __ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
     }
-    return general_hit(&S.gen[__float_as_uint(h.x)], S.bnd, R.o, R.d, i == self_prim, key);
+    if (!GEN) return CUDART_INF_F;  // unreachable: a scene rendered by a GEN = false kernel has no such record
+    return general_hit(&S.gen[__float_as_uint(h.x)], R.o, R.d, i == self_prim, key);
 }
 
 // Closest-hit update with the reference's tie rule (strict <, the DFS-earlier leaf wins an exact tie).
@@ -560,14 +566,14 @@ __device__ __forceinline__ uint32_t node_step_oct(const Staged& sm, const OctBas
     return next;
 }
 
-template <bool COUNT, bool ALL = false>
+template <bool COUNT, bool ALL = false, bool GEN = true>
 __device__ __forceinline__ void leaf_tests(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key, ClosestHit& best,
                                            uint32_t begin, uint32_t end, TraversalWork* work) {
-    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false, ALL>(S, sm, i, R, self_prim, key), best);
+    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false, ALL, GEN>(S, sm, i, R, self_prim, key), best);
     if (COUNT) work->prim_tests += end - begin;
 }
 
-template <bool COUNT = false, bool ALL = false>
+template <bool COUNT = false, bool ALL = false, bool GEN = true>
 __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged& sm, float3 o, float3 d, uint32_t self_prim, const MediumKey& key,
                                                   TraversalWork* work = nullptr) {
     ClosestHit best{CUDART_INF_F, RT_NO_PRIM};
@@ -593,11 +599,11 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     }
     if (S.n_small) {
         // small scene: the whole primitive list in DFS order, warp-uniform (geometry.rs:76-116)
-        for (uint32_t i = 0; i < S.n_small; ++i) take<true>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+        for (uint32_t i = 0; i < S.n_small; ++i) take<true>(S, i, prim_hit<false, false, GEN>(S, sm, i, R, self_prim, key), best);
         if (COUNT) work->prim_tests += S.n_small;
         return best;
     }
-    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true, ALL>(S, sm, i, R, self_prim, key), best);
+    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true, ALL, GEN>(S, sm, i, R, self_prim, key), best);
     if (COUNT) work->prim_tests += S.n_always;
     if (S.n_nodes == 0) return best;
 
@@ -606,7 +612,7 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
         if (COUNT) work->box_tests += 1;
         if (slab(lo, hi, R, best.t) < CUDART_INF_F) {
             const uint32_t first = __float_as_uint(lo.w), cnt = __float_as_uint(hi.w);
-            for (uint32_t i = first; i < first + cnt; ++i) take<false>(S, i, prim_hit<false>(S, sm, i, R, self_prim, key), best);
+            for (uint32_t i = first; i < first + cnt; ++i) take<false>(S, i, prim_hit<false, false, GEN>(S, sm, i, R, self_prim, key), best);
             if (COUNT) work->prim_tests += cnt;
         }
         return best;
@@ -633,7 +639,7 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
             if (found) {
                 uint32_t leaf_begin, leaf_end;
                 leaf_range(lp, leaf_begin, leaf_end);
-                leaf_tests<COUNT, true>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
+                leaf_tests<COUNT, true, GEN>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
             }
         } while (pair != RT_NO_PRIM);
         return best;
@@ -643,7 +649,7 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     uint32_t leaf_begin = 0u, leaf_end = 0u;
     do {
         while (pair != RT_NO_PRIM && leaf_end == leaf_begin) pair = node_step<COUNT, false>(S, sm, R, best, pair, sp, stack_spill, leaf_begin, leaf_end, work);
-        leaf_tests<COUNT, false>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
+        leaf_tests<COUNT, false, GEN>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, work);
         leaf_begin = leaf_end = 0u;
     } while (pair != RT_NO_PRIM);
     return best;

@@ -166,7 +166,7 @@ size_t extend_all_smem_bytes(const DScene& S) {
 
 // ALL: the whole tree and every primitive head are in shared memory (book-one: 836 nodes, 487 heads) — the per-access
 // "staged or global" range checks compile away.
-template <bool COUNT, bool ALL>
+template <bool COUNT, bool ALL, bool GEN>
 __global__ void __launch_bounds__(ALL ? RT_EXTEND_ALL_BLOCK : RT_EXTEND_BLOCK, ALL ? RT_EXTEND_ALL_MIN_BLOCKS : RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
                                                           uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
     extern __shared__ float4 smem4[];
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(ALL ? RT_EXTEND_ALL_BLOCK : RT_EXTEND_BLOCK, A
             key.k1 = sb >> 8;
             key.segment = sb & 0xFFu;
         }
-        const ClosestHit h = closest_hit<COUNT, ALL>(S, sm, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
+        const ClosestHit h = closest_hit<COUNT, ALL, GEN>(S, sm, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
         hits[i] = make_float2(h.t, __uint_as_float(h.prim));
     }
     if (COUNT) {  // instrumented build only (RT_RENDER_COUNT_WORK): one atomic pair per warp
@@ -251,7 +251,7 @@ __device__ __forceinline__ void feed_prefetch(const WarpFeed& F, uint32_t which,
     cp_async_commit();
 }
 
-template <bool COUNT>
+template <bool COUNT, bool GEN>
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_bvh(const DScene S, const RayQueue q, float2* __restrict__ hits,
                                                                                   WaveCounters* __restrict__ wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                                                                                   uint32_t staged_bytes) {
@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
                     R = make_ray(f3(ra.x, ra.y, ra.z), f3(rb.x, rb.y, rb.z));
                     best.t = CUDART_INF_F;
                     best.prim = RT_NO_PRIM;
-                    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true>(S, sm, i, R, self_prim, key), best);
+                    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true, false, GEN>(S, sm, i, R, self_prim, key), best);
                     if (COUNT) work.prim_tests += S.n_always;
                     sp = 0;
                     pair = root_pair;
@@ -338,7 +338,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
         const uint32_t m_trav = __ballot_sync(0xFFFFFFFFu, pair != RT_NO_PRIM && !pend);
         if (m_pend != 0u && ((uint32_t)__popc(m_pend) >= (uint32_t)RT_LEAF_MIN || m_trav == 0u)) {
             if (pend) {
-                leaf_tests<COUNT>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, &work);
+                leaf_tests<COUNT, false, GEN>(S, sm, R, self_prim, key, best, leaf_begin, leaf_end, &work);
                 leaf_begin = leaf_end = 0u;
             }
         }
@@ -477,6 +477,7 @@ struct ShadeOne {
     float4 o0, o1, o2;  // alive: the three queue words of the scattered ray; record: o0 = (radiance, pixel)
 };
 
+template <bool GEN>
 __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst& rc, const float4* smats, uint32_t n_staged_mats,
                                               const float4 a, const float4 b, const float4 c, const float2 h) {
     ShadeOne r;
@@ -499,7 +500,7 @@ __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst
     const uint32_t sample = sb >> 8, segment = sb & 0xFFu;
     const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z), thr = f3(c.x, c.y, c.z);
     const MediumKey key{gp, sample, segment, rc.seed_lo, rc.seed_hi};
-    const HitDetail hd = hit_detail(S, prim, o, d, h.x, m.texture >= 0, key, head);
+    const HitDetail hd = hit_detail<GEN>(S, prim, o, d, h.x, m.texture >= 0, key, head);
     const Philox4 rnd = philox4x32_10(segment, RT_DIM_SHADE, rc.seed_lo, rc.seed_hi, gp, sample);
     const ScatterResult sr = shade_material(S, m, d, hd, rnd);
     if (sr.scattered) {
@@ -524,7 +525,7 @@ __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst
 // Each thread shades RT_SHADE_RAYS rays per block round (their queue words are all requested before the first is
 // used: RT_SHADE_RAYS x the memory-level parallelism) and the block allocates output slots for the whole round with
 // ONE barrier pair and ONE pair of global atomics (block_append2 generalised to RT_SHADE_RAYS ballots per warp).
-template <int R>
+template <int R, bool GEN>
 __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
                                                const float2* __restrict__ hits, float4* __restrict__ done, WaveCounters* __restrict__ wc, uint32_t k) {
     extern __shared__ float4 shade_smem[];
@@ -569,7 +570,7 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
         uint32_t ma[R], mb[R], ca = 0u, cb = 0u;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            res[r] = shade_one(S, rc, smats, n_staged, a[r], b[r], c[r], h[r]);
+            res[r] = shade_one<GEN>(S, rc, smats, n_staged, a[r], b[r], c[r], h[r]);
             ma[r] = __ballot_sync(0xFFFFFFFFu, res[r].alive);
             mb[r] = __ballot_sync(0xFFFFFFFFu, res[r].record);
             ca += (uint32_t)__popc(ma[r]);
@@ -741,14 +742,15 @@ constexpr int RT_MAX_DEVICES = 64;
 struct DeviceState {
     std::mutex mu;
     int sms = 0;
-    size_t granted[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // largest MaxDynamicSharedMemorySize set so far, per kernel slot
+    size_t granted[16] = {0};  // largest MaxDynamicSharedMemorySize set so far, per kernel slot
 };
 DeviceState g_dev[RT_MAX_DEVICES];
-enum KernelSlot { SLOT_EXTEND = 0, SLOT_EXTEND_COUNT, SLOT_EXTEND_ALL, SLOT_BVH, SLOT_BVH_COUNT, SLOT_RECTS, SLOT_SHADE, SLOT_TRACE };
+// (kernels that exist in a GEN = false and a GEN = true instantiation take two consecutive slots: slot + gen)
+enum KernelSlot { SLOT_EXTEND = 0, SLOT_EXTEND_ALL = 2, SLOT_BVH = 4, SLOT_SHADE1 = 6, SLOT_SHADE2 = 8, SLOT_EXTEND_COUNT = 10, SLOT_BVH_COUNT, SLOT_RECTS, SLOT_TRACE };
 
 // the ceiling only ever grows: a launch may use any size up to it, so scenes of different sizes never invalidate each other
 template <class K>
-cudaError_t grant(DeviceState& d, KernelSlot slot, K kernel, size_t bytes) {
+cudaError_t grant(DeviceState& d, int slot, K kernel, size_t bytes) {
     if (bytes <= d.granted[slot] || bytes <= 48u * 1024u) return cudaSuccess;
     const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess) d.granted[slot] = bytes;
@@ -791,35 +793,38 @@ cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_by
     L.shade_smem = shade_bytes;
     L.rects_smem = fr_bytes;
 #define RT_TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
-    RT_TRY(grant(d, SLOT_EXTEND, k_extend<false, false>, L.extend_smem));
-    RT_TRY(grant(d, SLOT_EXTEND_COUNT, k_extend<true, false>, L.extend_smem));
+    const bool gen = S.n_gen > 0u;  // general 128-byte records present: the kernels that carry the out-of-line general path
+    L.gen = gen;
+    auto* const extend_k = gen ? k_extend<false, false, true> : k_extend<false, false, false>;
+    auto* const all_k = gen ? k_extend<false, true, true> : k_extend<false, true, false>;
+    auto* const bvh_k = gen ? k_extend_bvh<false, true> : k_extend_bvh<false, false>;
+    auto* const shade1_k = gen ? k_shade<1, true> : k_shade<1, false>;
+    auto* const shade2_k = gen ? k_shade<2, true> : k_shade<2, false>;
+    RT_TRY(grant(d, SLOT_EXTEND + gen, extend_k, L.extend_smem));
+    RT_TRY(grant(d, SLOT_EXTEND_COUNT, k_extend<true, false, true>, L.extend_smem));
     L.trace_smem = L.extend_smem + fr_bytes;
     RT_TRY(grant(d, SLOT_TRACE, k_trace, L.trace_smem));
-    RT_TRY(grant(d, SLOT_BVH, k_extend_bvh<false>, L.bvh_smem));
-    RT_TRY(grant(d, SLOT_BVH_COUNT, k_extend_bvh<true>, L.bvh_smem));
-    RT_TRY(occupancy(L.extend_blocks, k_extend<false, false>, RT_EXTEND_BLOCK, L.extend_smem));
+    RT_TRY(grant(d, SLOT_BVH + gen, bvh_k, L.bvh_smem));
+    RT_TRY(grant(d, SLOT_BVH_COUNT, k_extend_bvh<true, true>, L.bvh_smem));
+    RT_TRY(occupancy(L.extend_blocks, extend_k, RT_EXTEND_BLOCK, L.extend_smem));
     RT_TRY(occupancy(L.trace_blocks, k_trace, RT_EXTEND_BLOCK, L.trace_smem));
-    RT_TRY(occupancy(L.bvh_blocks, k_extend_bvh<false>, RT_EXTEND_BLOCK, L.bvh_smem));
+    RT_TRY(occupancy(L.bvh_blocks, bvh_k, RT_EXTEND_BLOCK, L.bvh_smem));
     if (fr_bytes) {
         RT_TRY(grant(d, SLOT_RECTS, k_extend_rects, fr_bytes));
         RT_TRY(occupancy(L.rects_blocks, k_extend_rects, RT_EXTEND_BLOCK, fr_bytes));
     }
-    // both instantiations share one slot: the larger request covers the smaller
-    if (shade_bytes > d.granted[SLOT_SHADE] && shade_bytes > 48u * 1024u) {
-        RT_TRY(cudaFuncSetAttribute(k_shade<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes));
-        RT_TRY(cudaFuncSetAttribute(k_shade<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shade_bytes));
-        d.granted[SLOT_SHADE] = shade_bytes;
-    }
-    RT_TRY(occupancy(L.shade_blocks, k_shade<1>, RT_SHADE_BLOCK, shade_bytes));
-    RT_TRY(occupancy(L.shade2_blocks, k_shade<2>, RT_SHADE_BLOCK, shade_bytes));
+    RT_TRY(grant(d, SLOT_SHADE1 + gen, shade1_k, shade_bytes));
+    RT_TRY(grant(d, SLOT_SHADE2 + gen, shade2_k, shade_bytes));
+    RT_TRY(occupancy(L.shade_blocks, shade1_k, RT_SHADE_BLOCK, shade_bytes));
+    RT_TRY(occupancy(L.shade2_blocks, shade2_k, RT_SHADE_BLOCK, shade_bytes));
     // whole tree + heads in shared memory in the octant-ready layout, as long as that keeps the occupancy of the general kernel
     L.all_staged = S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && !S.root_is_leaf;
     if (L.all_staged) {
         L.all_smem = extend_all_smem_bytes(S);
         if (L.all_smem > RT_EXTEND_ALL_MAX_SMEM) L.all_staged = false;
         else {
-            RT_TRY(grant(d, SLOT_EXTEND_ALL, k_extend<false, true>, L.all_smem));
-            RT_TRY(occupancy(L.all_blocks, k_extend<false, true>, RT_EXTEND_ALL_BLOCK, L.all_smem));
+            RT_TRY(grant(d, SLOT_EXTEND_ALL + gen, all_k, L.all_smem));
+            RT_TRY(occupancy(L.all_blocks, all_k, RT_EXTEND_ALL_BLOCK, L.all_smem));
             if (L.all_blocks * RT_EXTEND_ALL_BLOCK < L.extend_blocks * RT_EXTEND_BLOCK) L.all_staged = false;
         }
     }
@@ -854,22 +859,37 @@ void launch_extend(const Launch& L, const DScene& S, const RayQueue& q, float2* 
     const bool persistent = L.opt->persistent == 1 || (L.opt->persistent == 2 && S.n_nodes >= RT_PERSISTENT_MIN_NODES);
     if (persistent && S.n_small == 0u && !S.root_is_leaf && S.n_nodes > 0u) {
         const int grid = sms * sl.bvh_blocks;
-        if (count_work) k_extend_bvh<true><<<grid, RT_EXTEND_BLOCK, sl.bvh_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)sl.scene_smem);
-        else k_extend_bvh<false><<<grid, RT_EXTEND_BLOCK, sl.bvh_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)sl.scene_smem);
+        if (count_work) k_extend_bvh<true, true><<<grid, RT_EXTEND_BLOCK, sl.bvh_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)sl.scene_smem);
+        else if (sl.gen) k_extend_bvh<false, true><<<grid, RT_EXTEND_BLOCK, sl.bvh_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)sl.scene_smem);
+        else k_extend_bvh<false, false><<<grid, RT_EXTEND_BLOCK, sl.bvh_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi, (uint32_t)sl.scene_smem);
         return;
     }
     const int grid = sms * sl.extend_blocks;
-    if (count_work) k_extend<true, false><<<grid, RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else if (sl.all_staged) k_extend<false, true><<<fit_grid(L, sms * sl.all_blocks, RT_EXTEND_ALL_BLOCK), RT_EXTEND_ALL_BLOCK, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-    else k_extend<false, false><<<fit_grid(L, grid, RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    if (count_work) k_extend<true, false, true><<<grid, RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    else if (sl.all_staged) {
+        const int g = fit_grid(L, sms * sl.all_blocks, RT_EXTEND_ALL_BLOCK);
+        if (sl.gen) k_extend<false, true, true><<<g, RT_EXTEND_ALL_BLOCK, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+        else k_extend<false, true, false><<<g, RT_EXTEND_ALL_BLOCK, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    } else {
+        const int g = fit_grid(L, grid, RT_EXTEND_BLOCK);
+        if (sl.gen) k_extend<false, false, true><<<g, RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+        else k_extend<false, false, false><<<g, RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+    }
 }
 void launch_shade(const Launch& L, const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
                   WaveCounters* wc, uint32_t k) {
     const SceneLaunch& sl = *L.sl;
     // two rays per thread per barrier round where shading is light on registers (small all-rectangle scenes: no f64 sphere re-solve);
     // +5 % there, -7 % on the sphere scenes (r1f), hence per scene
-    if (S.fr_n && L.opt->shade_rays2) k_shade<2><<<fit_grid(L, sl.num_sms * sl.shade2_blocks, 2 * RT_SHADE_BLOCK), RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
-    else k_shade<1><<<fit_grid(L, sl.num_sms * sl.shade_blocks, RT_SHADE_BLOCK), RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+    if (S.fr_n && L.opt->shade_rays2) {
+        const int g = fit_grid(L, sl.num_sms * sl.shade2_blocks, 2 * RT_SHADE_BLOCK);
+        if (sl.gen) k_shade<2, true><<<g, RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+        else k_shade<2, false><<<g, RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+    } else {
+        const int g = fit_grid(L, sl.num_sms * sl.shade_blocks, RT_SHADE_BLOCK);
+        if (sl.gen) k_shade<1, true><<<g, RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+        else k_shade<1, false><<<g, RT_SHADE_BLOCK, sl.shade_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+    }
 }
 void launch_accumulate(const Launch& L, const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq) {
     k_accumulate<<<fit_grid(L, L.sl->num_sms * L.opt->acc_blocks, 256), 256, 0, L.st>>>(rc, done, wc, k, sum, sumsq);

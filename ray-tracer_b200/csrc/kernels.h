@@ -64,6 +64,7 @@ struct SceneLaunch {
     int device = -1, num_sms = 0;
     size_t scene_smem = 0, extend_smem = 0, trace_smem = 0, bvh_smem = 0, shade_smem = 0, rects_smem = 0, all_smem = 0;
     int extend_blocks = 1, trace_blocks = 1, bvh_blocks = 1, shade_blocks = 1, shade2_blocks = 1, rects_blocks = 1, all_blocks = 1;
+    bool gen = true;          // the scene has general 128-byte records: GEN = true instantiations of extend / shade
     bool all_staged = false;  // k_extend<., true>: whole tree + heads in shared memory, octant-ready records
 };
 

@@ -51,47 +51,24 @@ __device__ __forceinline__ void sphere_uv(float3 unit, float& u, float& v) {  //
     v = 1.0f - acosf(fminf(fmaxf(unit.y, -1.0f), 1.0f)) * (1.0f / RT_PI);
 }
 
-// Rebuild the reference's HitRecord for (ray, t, prim).  `want_uv` skips the atan2/acos when the
-// material's texture does not read uv.
-// S.prim_head / S.rect_nrm are read with plain (generic) loads: k_shade points them at its shared-memory copies when
-// the tables are small enough to be staged (ld.global.nc on a shared address would be illegal).
-__device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, float3 o, float3 d, float t, bool want_uv, const MediumKey& key,
-                                                const float4 head) {
+// General 128-byte records (rotated / scaled spheres, media): the rare path, kept out of line so that the common one — translation-only
+// spheres and rectangles — keeps k_shade's registers (inlined, the generic-medium code cost every scene 7-11 % of k_shade).
+__device__ __noinline__ HitDetail general_detail(const RtPrim* __restrict__ g, float3 o, float3 d, float t, bool want_uv, const MediumKey key) {
     HitDetail h;
     h.u = h.v = 0.0f;
     h.t = t;
     h.uv_valid = want_uv;
-    if (head.w > 0.0f) {  // translation-only sphere
-        sphere_record_f64(o, d, f3(head.x, head.y, head.z), head.w, t, h.p, h.n, h.t);
-        if (want_uv) sphere_uv(h.n, h.u, h.v);
-        return h;
-    }
-    if (__float_as_uint(head.y) == (uint32_t)RT_PRIM_RECT) {
-        // Sprite::hit returns M (o' + t d') = o + t d and M (0,0,1) (sprite.rs:108-115): the world-space point needs no
-        // matrix at all and the normal is one precomputed column — 16 B instead of the 128-byte record
-        const uint32_t ri = __float_as_uint(head.z);
-        const float4 nrm = S.rect_nrm[ri];
-        h.p = fma3(t, d, o);
-        h.n = f3(nrm.x, nrm.y, nrm.z);
-        if (want_uv) {  // geometry.rs:170-171
-            const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
-            const float4 rx = __ldg(q + 1), ry = __ldg(q + 2), ext = __ldg(q + 3);
-            h.u = (dot3(rx, h.p) + rx.w + ext.x) / (2.0f * ext.x);
-            h.v = (dot3(ry, h.p) + ry.w + ext.y) / (2.0f * ext.y);
-        }
-        return h;
-    }
-    const RtPrim* __restrict__ g = &S.gen[__float_as_uint(head.x)];
     const uint32_t kind = g->kind;
     if (kind == RT_PRIM_MEDIUM) {
         // redo both boundary probes (same arithmetic as extend): which surfaces, where, which branch
         MediumProbe pr;
         pr.t1 = pr.t2 = 0.0f; pr.i1 = pr.i2 = 0u; pr.entering = false;
-        medium_generic_hit(S.bnd, g->aux, (uint32_t)g->param[2], o, d, g->param[1], g->order, key, &pr);
+        const RtPrim* __restrict__ bnd = g + g->aux;  // this medium's boundary surfaces (intersect.cuh general_hit)
+        medium_generic_hit(bnd, 0u, (uint32_t)g->param[2], o, d, g->param[1], g->order, key, &pr);
         float u1 = 0.0f, v1 = 0.0f, u2 = 0.0f, v2 = 0.0f;
-        const float3 n1 = boundary_normal(S.bnd, pr.i1, o, d, pr.t1, want_uv ? &u1 : nullptr, &v1);
+        const float3 n1 = boundary_normal(bnd, pr.i1, o, d, pr.t1, want_uv ? &u1 : nullptr, &v1);
         if (pr.entering) {
-            const float3 n2 = boundary_normal(S.bnd, pr.i2, o, d, pr.t2, want_uv ? &u2 : nullptr, &v2);
+            const float3 n2 = boundary_normal(bnd, pr.i2, o, d, pr.t2, want_uv ? &u2 : nullptr, &v2);
             h.p = fma3(pr.t1 + 1e-6f + t, d, o);  // volume.rs:69 on the shadowed ray (A.9 ii)
             h.n = (n1 + n2) * 0.5f;
             h.u = u1 + u2; h.v = v1 + v2;
@@ -136,6 +113,41 @@ __device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, flo
         if (want_uv) sphere_uv(n1, h.u, h.v);
     }
     return h;
+}
+
+// Rebuild the reference's HitRecord for (ray, t, prim).  `want_uv` skips the atan2/acos when the
+// material's texture does not read uv.
+// S.prim_head / S.rect_nrm are read with plain (generic) loads: k_shade points them at its shared-memory copies when
+// the tables are small enough to be staged (ld.global.nc on a shared address would be illegal).
+template <bool GEN = true>
+__device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, float3 o, float3 d, float t, bool want_uv, const MediumKey& key,
+                                                const float4 head) {
+    HitDetail h;
+    h.u = h.v = 0.0f;
+    h.t = t;
+    h.uv_valid = want_uv;
+    if (head.w > 0.0f) {  // translation-only sphere
+        sphere_record_f64(o, d, f3(head.x, head.y, head.z), head.w, t, h.p, h.n, h.t);
+        if (want_uv) sphere_uv(h.n, h.u, h.v);
+        return h;
+    }
+    if (__float_as_uint(head.y) == (uint32_t)RT_PRIM_RECT) {
+        // Sprite::hit returns M (o' + t d') = o + t d and M (0,0,1) (sprite.rs:108-115): the world-space point needs no
+        // matrix at all and the normal is one precomputed column — 16 B instead of the 128-byte record
+        const uint32_t ri = __float_as_uint(head.z);
+        const float4 nrm = S.rect_nrm[ri];
+        h.p = fma3(t, d, o);
+        h.n = f3(nrm.x, nrm.y, nrm.z);
+        if (want_uv) {  // geometry.rs:170-171
+            const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
+            const float4 rx = __ldg(q + 1), ry = __ldg(q + 2), ext = __ldg(q + 3);
+            h.u = (dot3(rx, h.p) + rx.w + ext.x) / (2.0f * ext.x);
+            h.v = (dot3(ry, h.p) + ry.w + ext.y) / (2.0f * ext.y);
+        }
+        return h;
+    }
+    if (!GEN) { h.p = fma3(t, d, o); h.n = f3(0.0f, 0.0f, 0.0f); return h; }  // unreachable (prim_hit<.., GEN = false>)
+    return general_detail(&S.gen[__float_as_uint(head.x)], o, d, t, want_uv, key);
 }
 
 // ---- textures ------------------------------------------------------------------------------------
