@@ -288,6 +288,10 @@ class FlatScene:
         d = self.desc()
         return self._table(d.prims, d.n_prims, PRIM_DTYPE)
 
+    def boundary_prims(self):
+        d = self.desc()
+        return self._table(d.boundary_prims, d.n_boundary_prims, PRIM_DTYPE)
+
     def materials(self):
         d = self.desc()
         return self._table(d.materials, d.n_materials, MATERIAL_DTYPE)
