@@ -20,6 +20,17 @@
 
 #include "../../include/rt_b200.h"
 
+// Bounds / invariant checks of the debug library (make librt_b200_check.so: -DRT_CHECK_BOUNDS).  compute-sanitizer is closed on the
+// GPU pool this backend is developed on, so the kernels carry their own asserts: every queue slot, node, primitive, general record,
+// rectangle, material, stack and framebuffer index is checked where it is formed; a violation traps the kernel (cudaErrorAssert) and
+// the render returns RT_ERR_CUDA.  scripts/sanitize_target.py drives every kernel form through the checked library.
+#ifdef RT_CHECK_BOUNDS
+#include <cassert>
+#define RT_ASSERT(cond) assert(cond)
+#else
+#define RT_ASSERT(cond) ((void)0)
+#endif
+
 namespace rtb {
 
 constexpr uint32_t RT_NO_PRIM = 0xFFFFFFFFu;

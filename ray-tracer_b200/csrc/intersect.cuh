@@ -350,6 +350,7 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile(
 // argument marshalling) costs registers in the traversal loop (k_extend<., true>: 24 bytes of spills, -3 %; k_shade: -7 to -11 %).
 template <bool BIG, bool ALL = false, bool GEN = true>
 __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uint32_t i, const RayCtx& R, uint32_t self_prim, const MediumKey& key) {
+    RT_ASSERT(i < S.n_prims);
     const bool staged = ALL || i < S.n_staged_prims;
     float4 h;
     if (staged) h = lds128(sm.heads + 16u * i);
@@ -361,6 +362,7 @@ __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uin
     if (__float_as_uint(h.y) == (uint32_t)RT_PRIM_RECT) {
         if (i == self_prim) return CUDART_INF_F;  // a plane cannot re-hit itself
         const uint32_t ri = __float_as_uint(h.z);
+        RT_ASSERT(ri < S.n_rects);
         if (staged) {
             const uint32_t q = sm.rects + 64u * ri;
             return rect_hit(R, lds128(q), lds128(q + 16u), lds128(q + 32u), lds128(q + 48u));
@@ -368,6 +370,7 @@ __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uin
         const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
         return rect_hit(R, __ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
     }
+    RT_ASSERT(GEN && __float_as_uint(h.x) < S.n_gen);
     if (!GEN) return CUDART_INF_F;  // unreachable: a scene rendered by a GEN = false kernel has no such record
     return general_hit(&S.gen[__float_as_uint(h.x)], R.o, R.d, i == self_prim, key);
 }
@@ -406,6 +409,7 @@ __device__ __forceinline__ float4 load_node(const DScene& S, const Staged& sm, u
 // The four float4 of a sibling pair (64 contiguous bytes); `pair` is even, so the pair is staged or not as a whole.
 template <bool ALL = false>
 __device__ __forceinline__ void load_pair(const DScene& S, const Staged& sm, uint32_t pair, float4& llo, float4& lhi, float4& rlo, float4& rhi) {
+    RT_ASSERT((pair & 1u) == 0u && pair + 1u < S.n_nodes + (S.n_nodes & 1u));
     if (ALL || pair < S.n_staged_nodes) {
         const uint32_t a = sm.nodes + 32u * pair;
         llo = lds128(a); lhi = lds128(a + 16u); rlo = lds128(a + 32u); rhi = lds128(a + 48u);
@@ -482,9 +486,11 @@ __device__ __forceinline__ uint32_t node_step_core(const DScene& S, const Staged
         const bool swap = tr < tl;
         const uint32_t pushed = swap ? lp.lref : lp.rref;
         if (ALL) {
+            RT_ASSERT(sp >= 0 && (uint32_t)sp < S.bvh_depth + 2u);
             sts32(sm.stack + sp * sstride, pushed);
             ++sp;
         } else {
+            RT_ASSERT(sp >= 0 && sp < RT_STACK_DEPTH);
             if (sp < (int)RT_SMEM_STACK) sts32(sm.stack + sp * sstride, pushed);
             else stack_spill[sp - RT_SMEM_STACK] = pushed;
             sp += (sp < RT_STACK_DEPTH - 1);
@@ -532,6 +538,7 @@ template <bool COUNT>
 __device__ __forceinline__ uint32_t node_step_oct(const Staged& sm, const OctBase& ob, const RayCtx& R, const ClosestHit& best, uint32_t pair, int& sp,
                                                   LeafPair& lp, TraversalWork* work) {
     const uint32_t sstride = 4u * blockDim.x;
+    RT_ASSERT((pair & 1u) == 0u && sp >= 0);
     const uint32_t a = pair * (RT_OCT_PAIR_BYTES / 2u);  // `pair` is the (even) node index of the left child
     const float4 X = lds128(a + ob.x), Y = lds128(a + ob.y), Z = lds128(a + ob.z), M = lds128(a + ob.m);
     const float lnx = fmaf(X.x, R.inv.x, -R.oinv.x), lfx = fmaf(X.y, R.inv.x, -R.oinv.x);
@@ -569,6 +576,7 @@ __device__ __forceinline__ uint32_t node_step_oct(const Staged& sm, const OctBas
 template <bool COUNT, bool ALL = false, bool GEN = true>
 __device__ __forceinline__ void leaf_tests(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key, ClosestHit& best,
                                            uint32_t begin, uint32_t end, TraversalWork* work) {
+    RT_ASSERT(begin <= end && end <= S.n_prims);
     for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false, ALL, GEN>(S, sm, i, R, self_prim, key), best);
     if (COUNT) work->prim_tests += end - begin;
 }

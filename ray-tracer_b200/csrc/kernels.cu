@@ -100,6 +100,7 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
             camera_ray(rc.cam, x, y, rc.width, rc.height, rnd, o, d);
         }
         const uint32_t slot = surv + i;
+        RT_ASSERT(slot < rc.capacity && sample < rc.spp && gp < rc.width * rc.height);
         q.a[slot] = make_float4(o.x, o.y, o.z, __uint_as_float(RT_NO_PRIM));
         q.b[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(gp));
         q.c[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float((sample << 8) | 1u));
@@ -306,6 +307,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
                 const bool mine = ((want >> lane) & 1u) && rank < avail;
                 if (mine) {
                     const uint32_t slot = F.cur_pos + rank;
+                    RT_ASSERT(slot < 32u && F.cur_base + slot < n);
                     const uint32_t b = F.buf + F.cur * RT_FEED_BUF_BYTES;
                     const float4 ra = lds128(b + 16u * slot), rb = lds128(b + 512u + 16u * slot);
                     ray_i = F.cur_base + slot;
@@ -485,10 +487,12 @@ __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst
     r.o0 = r.o1 = r.o2 = make_float4(0.f, 0.f, 0.f, 0.f);
     const uint32_t prim = __float_as_uint(h.y);
     if (prim == RT_NO_PRIM) return r;  // miss -> black (render.rs:26)
+    RT_ASSERT(prim < S.n_prims);
     const uint2 meta = S.prim_meta[prim];
     const float4 head = S.prim_head[prim];
     const int32_t mi = (int32_t)meta.y;
     if (mi < 0) return r;  // no material -> black (render.rs:18-20)
+    RT_ASSERT((uint32_t)mi < S.n_mats);
     DMaterial m;
     {
         const float4* src = ((uint32_t)mi < n_staged_mats) ? &smats[2 * mi] : reinterpret_cast<const float4*>(S.mats) + 2 * (size_t)mi;
@@ -596,8 +600,10 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
         for (int r = 0; r < R; ++r) {
             if (res[r].alive) {
                 const uint32_t sl = slot + (uint32_t)__popc(ma[r] & lt);
+                RT_ASSERT(sl < rc.capacity);
                 qout.a[sl] = res[r].o0; qout.b[sl] = res[r].o1; qout.c[sl] = res[r].o2;
             }
+            RT_ASSERT(!res[r].record || dslot + (uint32_t)__popc(mb[r] & lt) < rc.capacity);
             if (res[r].record) done[dslot + (uint32_t)__popc(mb[r] & lt)] = res[r].o0;
             slot += (uint32_t)__popc(ma[r]);
             dslot += (uint32_t)__popc(mb[r]);
@@ -641,6 +647,7 @@ __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const 
         const uint32_t y = gp / rc.width, x = gp - y * rc.width;
         const uint32_t yl = (y - rc.row_begin) / rc.row_stride;
         const size_t o = ((size_t)yl * rc.width + x) * 3;
+        RT_ASSERT(y >= rc.row_begin && (y - rc.row_begin) % rc.row_stride == 0u && yl < rc.rows_local && x < rc.width);
         atomicAdd(&sum[o + 0], v[0]);
         atomicAdd(&sum[o + 1], v[1]);
         atomicAdd(&sum[o + 2], v[2]);

@@ -155,6 +155,7 @@ __device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, flo
 __device__ __forceinline__ float3 texture_value(const DScene& S, int32_t tex, float u, float v) {
     // CheckerTexture nests (material.rs:217-245): walk down at most 8 levels
     for (int depth = 0; depth < 8; ++depth) {
+        RT_ASSERT(tex >= 0 && (uint32_t)tex < S.n_texs);
         const RtTexture* __restrict__ t = &S.texs[tex];
         const uint32_t kind = t->kind;
         if (kind == RT_TEX_SOLID) return f3(t->rgb[0], t->rgb[1], t->rgb[2]);
@@ -254,9 +255,13 @@ __device__ __forceinline__ ScatterResult shade_material(const DScene& S, const D
             const float disc = 1.0f - ratio * ratio * (1.0f - dt * dt);
             if (disc > 0.0f) {
                 const float r0s = (ratio - 1.0f) / (ratio + 1.0f), r0 = r0s * r0s;
-                const float om = 1.0f - fminf(fmaxf(-dot3(d, n), -1.0f), 1.0f);  // 1 - cos(acos(-d.n)), material.rs:163
+                // material.rs:163-166: theta = acos(-d.n), reflect iff rand < r0 + (1 - r0)(1 - cos theta)^5.  acos of |x| > 1 is NaN and
+                // `rand < NaN` is false: under a SCALING transform (normals are not renormalised, sprite.rs:112-115) the reference always
+                // refracts — mirrored here.  Within a few f32 ulps of 1 the excess is rounding of a unit vector, not scaling: clamped.
+                const float c = -dot3(d, n);
+                const float om = 1.0f - fminf(fmaxf(c, -1.0f), 1.0f);
                 const float om2 = om * om;
-                const float prob = r0 + (1.0f - r0) * om2 * om2 * om;
+                const float prob = (fabsf(c) > 1.0f + 1e-5f) ? -1.0f : r0 + (1.0f - r0) * om2 * om2 * om;
                 if (u24f(rnd.x) < prob) r.dir = reflect3(d, h.n);
                 else r.dir = normalize3(fma3(-sqrtf(disc), n, (d - n * dt) * ratio));  // vec3.rs:113-124
             } else {

@@ -1,5 +1,9 @@
 """Tiny renders through every kernel form, as a compute-sanitizer target:
-    compute-sanitizer --tool memcheck python scripts/sanitize_target.py"""
+    compute-sanitizer --tool memcheck|racecheck|initcheck|synccheck python scripts/sanitize_target.py
+Covers k_generate, k_extend<., false / true>, k_extend_bvh (cp.async ray feed, per-warp shared buffers), k_extend_rects (frame boxes and
+loose rectangles), k_shade<1 / 2> (block-wide slot allocation), k_accumulate (segmented warp reduction + f64 atomics), k_finish,
+k_trace (incl. surface origins), k_resolve_u8, k_deinterleave (wavefront lanes), the LBVH build kernels, the general records and
+both medium forms — each with the default 4 M-ray queue and with a queue of 1056 rays (not a multiple of a block)."""
 import importlib
 import os
 import sys
@@ -10,21 +14,29 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 rt = importlib.import_module("ray-tracer_b200")
 
-dev = rt.Device(0)
-cases = [("book-one", {}), ("cornell-box", {}), ("cornell-box", {"RT_B200_RECT_FRAMES": "0"}), ("book-two", {"RT_B200_PERSISTENT": "1"}),
-         ("book-one", {"RT_B200_SHADE_PIPE": "1"}), ("stress:70000", {}), ("stress:70000", {"RT_B200_BVH_BUILDER": "host", "RT_B200_PERSISTENT": "0"})]
-for name, env in cases:
-    os.environ.update(env)
-    sc = rt.Scene.example(dev, name, 1)
+dev = rt.Device(0, options={"lanes": 2})
+cases = [("book-one", None, 0), ("cornell-box", None, 0), ("cornell-box", {"flags": rt.SCENE_NO_FRAME_BOXES}, 0), ("cornell-box", {"flags": rt.SCENE_NO_FRAME_RECTS}, 0),
+         ("book-two", None, rt.RENDER_EXTEND_PERSISTENT), ("book-two", None, 0), ("checker-lists", None, 0), ("checker-lists", {"flags": rt.SCENE_NO_SMALL_LIST}, 0),
+         ("stress:70000", None, 0), ("stress:70000", {"bvh_builder": rt.BVH_HOST_SAH}, rt.RENDER_EXTEND_PER_THREAD), ("book-one", None, rt.RENDER_COUNT_WORK),
+         ("book-one", None, rt.RENDER_SAMPLE_MAJOR | rt.RENDER_STAGE_TIMING)]
+for name, opts, flags in cases:
+    sc = rt.Scene.example(dev, name, 1, options=opts)
     cam = sc.flat.camera(16 / 9)
     for cap in (0, 1056):
-        s, q, st = sc.render(cam, 64, 36, 2, 50, seed=1, queue_capacity=cap)
-    rays = np.random.default_rng(1).normal(size=(999, 6)).astype(np.float32)
-    sc.trace(rays)
+        s, q, st = sc.render(cam, 64, 36, 2, 50, seed=1, queue_capacity=cap, flags=flags)
+    rng = np.random.default_rng(1)
+    rays = rng.normal(size=(999, 6)).astype(np.float32)
+    h = sc.trace(rays)
+    on = h["hit"] == 1
+    if on.any():  # scattered rays that start on the primitives just hit
+        d = rng.normal(size=(int(on.sum()), 3)).astype(np.float32)
+        sc.trace(np.concatenate([h["p"][on], d], axis=1), self_order=h["prim"][on].astype(np.uint32))
     c, _, _ = sc.color_rays(rays, 2, 8)
-    print(name, env, sc.bvh_info(), "rays", st.rays, "mean", float(s.mean()), flush=True)
+    print(name, opts, flags, sc.bvh_info(), sc.frame_rect_info(), "rays", st.rays, "mean", float(s.mean()), flush=True)
     sc.close()
-    for k in env:
-        os.environ.pop(k, None)
-img = dev.resolve_u8(s, 2)
+# enough paths for two wavefront lanes (render_lanes + k_deinterleave), ragged rows
+sc = rt.Scene.example(dev, "cornell-box", 1)
+s, q, st = sc.render(sc.flat.camera(1.0), 301, 203, 36, 50, seed=3)
+print("lanes", st.launches, float(s.mean()))
+img = dev.resolve_u8(s, 36)
 print("ok", img.shape)

@@ -902,3 +902,23 @@ def test_cpp_example_driver_writes_the_reference_ppm(rt, device, tmp_path):
     got = out.read_bytes()
     assert got.startswith(b"P3\n160 90\n255\n")
     assert got == want
+
+
+@pytest.mark.gpu
+def test_every_kernel_form_under_the_checked_library(rt):
+    """compute-sanitizer is closed on this GPU pool, so the kernels carry their own bounds / invariant asserts (RT_ASSERT in csrc/,
+    compiled in by `make librt_b200_check.so`): every queue slot, BVH node, primitive, general record, rectangle, material, texture,
+    traversal-stack and framebuffer index is checked where it is formed, and a violation traps the kernel.  scripts/sanitize_target.py
+    drives every kernel form — all extend variants, both shade variants, lanes, tiny queues, surface-origin traces, the LBVH build —
+    through that library in a subprocess; it must finish cleanly."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(root, "ray-tracer_b200", "librt_b200_check.so")
+    if not os.path.exists(lib):
+        subprocess.check_call(["make", "-s", "-C", os.path.dirname(lib), "librt_b200_check.so"])
+    env = dict(os.environ, RT_B200_LIB=lib)
+    res = subprocess.run([sys.executable, os.path.join(root, "scripts", "sanitize_target.py")], env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert "ok (36, 64, 3)" in res.stdout or "ok" in res.stdout.splitlines()[-1]
+    assert "Assertion" not in res.stderr
