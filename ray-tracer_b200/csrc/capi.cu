@@ -90,7 +90,7 @@ struct RtContext {
 struct RtScene {
     RtContext* ctx = nullptr;
     DScene d{};
-    DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm, fr_blob;
+    DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm, fr_blob, oct_blob, shade_blob;
     DevBuf<uint2> prim_meta;
     DevBuf<uint32_t> order_to_prim;
     DevBuf<RtPrim> gen;
@@ -661,6 +661,50 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     }
     s->shade_bytes = (size_t)std::min<uint32_t>(d.n_mats, RT_MAX_STAGED_MATS) * 32 + (size_t)d.n_staged_prims * (16 + 8) +
                      (d.n_staged_prims ? (size_t)d.n_rects * 16 : 0);
+    // ---- blobs the kernels stage with ONE bulk copy each (device_scene.h oct_blob / shade_blob) ----
+    {
+        const uint32_t n_sm = std::min<uint32_t>(d.n_mats, RT_MAX_STAGED_MATS), n_sp = d.n_staged_prims, n_sr = n_sp ? d.n_rects : 0u;
+        std::vector<float4> blob((size_t)2 * n_sm + n_sp + n_sr + (n_sp + 1) / 2, make_float4(0, 0, 0, 0));
+        if (n_sm) std::memcpy(blob.data(), mats.data(), (size_t)n_sm * sizeof(DMaterial));
+        if (n_sp) std::memcpy(blob.data() + 2 * (size_t)n_sm, head.data(), (size_t)n_sp * sizeof(float4));
+        if (n_sr) std::memcpy(blob.data() + 2 * (size_t)n_sm + n_sp, rect_nrm.data(), (size_t)n_sr * sizeof(float4));
+        if (n_sp) std::memcpy(blob.data() + 2 * (size_t)n_sm + n_sp + n_sr, meta.data(), (size_t)n_sp * sizeof(uint2));
+        e = upload(s->shade_blob, blob.data(), blob.size());
+        d.shade_blob = s->shade_blob.p; d.shade_blob4 = (uint32_t)blob.size();
+        s->shade_bytes = blob.size() * sizeof(float4);
+    }
+    const bool whole_tree = e == cudaSuccess && d.n_nodes > 0u && d.n_staged_nodes >= d.n_nodes && d.n_staged_prims >= d.n_prims && !d.n_small && !d.root_is_leaf;
+    if (whole_tree) {
+        // octant-ready pair records (intersect.cuh node_step_oct): per sibling pair 7 float4 — per axis (l.lo, l.hi, r.lo, r.hi) and its
+        // mirror (l.hi, l.lo, r.hi, r.lo), then (lref, lcnt, rref, rcnt) — laid out once here instead of by every block of every launch
+        std::vector<float4> host_nodes;
+        const float4* nodes4 = reinterpret_cast<const float4*>(bvh.nodes.data());
+        if (use_lbvh) {  // (a small scene forced onto the device builder: its nodes live in HBM only)
+            host_nodes.resize((size_t)d.n_nodes * 2);
+            e = cudaMemcpy(host_nodes.data(), s->nodes.p, host_nodes.size() * sizeof(float4), cudaMemcpyDeviceToHost);
+            nodes4 = host_nodes.data();
+        }
+        const uint32_t n_pairs = (d.n_nodes + 1u) / 2u;
+        std::vector<float4> blob((size_t)7 * n_pairs + n + 4 * (size_t)d.n_rects, make_float4(0, 0, 0, 0));
+        const float4 zero = make_float4(0, 0, 0, 0);
+        for (uint32_t j = 0; j < n_pairs && e == cudaSuccess; ++j) {
+            const bool has_right = 2u * j + 1u < d.n_nodes;
+            const float4 ll = nodes4[4u * j], lh = nodes4[4u * j + 1u], rl = has_right ? nodes4[4u * j + 2u] : zero, rh = has_right ? nodes4[4u * j + 3u] : zero;
+            float4* o = blob.data() + 7 * (size_t)j;
+            o[0] = make_float4(ll.x, lh.x, rl.x, rh.x); o[1] = make_float4(lh.x, ll.x, rh.x, rl.x);
+            o[2] = make_float4(ll.y, lh.y, rl.y, rh.y); o[3] = make_float4(lh.y, ll.y, rh.y, rl.y);
+            o[4] = make_float4(ll.z, lh.z, rl.z, rh.z); o[5] = make_float4(lh.z, ll.z, rh.z, rl.z);
+            o[6] = make_float4(ll.w, lh.w, rl.w, rh.w);
+        }
+        std::memcpy(blob.data() + 7 * (size_t)n_pairs, head.data(), (size_t)n * sizeof(float4));
+        if (d.n_rects) std::memcpy(blob.data() + 7 * (size_t)n_pairs + n, rects.data(), rects.size() * sizeof(float4));
+        if (e == cudaSuccess) e = upload(s->oct_blob, blob.data(), blob.size());
+        d.oct_blob = s->oct_blob.p; d.oct_blob4 = (uint32_t)blob.size();
+    }
+    if (e != cudaSuccess) {
+        rt_scene_destroy(s);
+        return fail(RT_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(e));
+    }
     e = kernels_configure_scene(ctx->device, d, s->staged_bytes, s->shade_bytes, s->fr_bytes, s->launch);
     if (e != cudaSuccess) {
         rt_scene_destroy(s);
@@ -673,7 +717,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
 void rt_scene_destroy(RtScene* s) {
     if (!s) return;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->order_to_prim.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->order_to_prim.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->oct_blob.release(); s->shade_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
     delete s;
 }
 

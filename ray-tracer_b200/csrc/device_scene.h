@@ -68,6 +68,13 @@ struct DScene {
     const DMaterial* mats;
     const RtTexture* texs;
     const float4* texels;
+    // Blobs staged into shared memory by ONE bulk copy each (csrc/bulk_copy.cuh), laid out by rt_scene_create exactly as the kernels read them:
+    //   oct_blob   (k_extend<., true>; null when the tree is not staged whole): [octant-ready pair records, 7 float4 per sibling pair
+    //              (intersect.cuh node_step_oct)][prim_head n_prims][rects 4 n_rects]
+    //   shade_blob (k_shade): [materials 2 float4 x min(n_mats, RT_MAX_STAGED_MATS)][prim_head n_staged_prims][rect_nrm][prim_meta uint2, padded to 16 B]
+    const float4* oct_blob;
+    const float4* shade_blob;
+    uint32_t oct_blob4, shade_blob4;  // sizes in float4
     const uint32_t* order_to_prim;  // DFS rank (RtPrim.order) -> device primitive index, RT_NO_PRIM for ranks without a primitive
     uint32_t n_orders;
     uint32_t n_nodes, n_prims, n_always, n_gen, n_mats, n_texs;

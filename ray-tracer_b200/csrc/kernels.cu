@@ -17,6 +17,7 @@
 
 #include <mutex>
 
+#include "bulk_copy.cuh"
 #include "device_scene.h"
 #include "intersect.cuh"
 #include "kernels.h"
@@ -124,41 +125,26 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
 
 // ---- extend ----------------------------------------------------------------------------------------
 
-// Copy the BVH prefix (and, for scenes that fit, the primitive heads and compact rectangle records) into shared
-// memory: [stack RT_SMEM_STACK x blockDim words][nodes 2*n_staged_nodes][heads n_staged_prims][rects 4*n_rects].
-__device__ __forceinline__ Staged stage_scene(const DScene& S, float4* smem_base) {
-    float4* smem4 = smem_base + (RT_SMEM_STACK * blockDim.x) / 4u;
+// Stage the BVH prefix (and, for scenes that fit, the primitive heads and compact rectangle records) into shared memory:
+// [stack RT_SMEM_STACK x blockDim words][nodes 2*n_staged_nodes][heads n_staged_prims][rects 4*n_rects] — three bulk copies on the
+// copy engine, one mbarrier; the caller waits (mbar_wait(mbar, 0)) after it has issued its first ray loads.
+__device__ __forceinline__ Staged stage_scene(const DScene& S, float4* smem_base, uint32_t mbar) {
     const uint32_t n_node4 = 2u * S.n_staged_nodes, n_head4 = S.n_staged_prims, n_rect4 = S.n_staged_prims ? 4u * S.n_rects : 0u;
-    for (uint32_t i = threadIdx.x; i < n_node4; i += blockDim.x) smem4[i] = S.nodes[i];
-    for (uint32_t i = threadIdx.x; i < n_head4; i += blockDim.x) smem4[n_node4 + i] = S.prim_head[i];
-    for (uint32_t i = threadIdx.x; i < n_rect4; i += blockDim.x) smem4[n_node4 + n_head4 + i] = S.rects[i];
-    __syncthreads();
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_base);
     const uint32_t scene = base + RT_SMEM_STACK * blockDim.x * 4u;
+    bulk_stage(mbar, BulkPart{S.nodes, scene, 16u * n_node4}, BulkPart{S.prim_head, scene + 16u * n_node4, 16u * n_head4},
+               BulkPart{S.rects, scene + 16u * (n_node4 + n_head4), 16u * n_rect4});
     return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
 }
 
 // Staging of the all-in-shared-memory variant: [stack (depth + 2) x blockDim words][pairs, 7 float4 each (intersect.cuh: octant-ready
-// records)][heads n_prims][rects 4*n_rects].
-__device__ __forceinline__ Staged stage_scene_oct(const DScene& S, float4* smem_base) {
+// records)][heads n_prims][rects 4*n_rects] — the blob is laid out once by rt_scene_create (S.oct_blob), so this is ONE bulk copy.
+__device__ __forceinline__ Staged stage_scene_oct(const DScene& S, float4* smem_base, uint32_t mbar) {
     const uint32_t stack_words = (S.bvh_depth + 2u) * blockDim.x;
-    float4* smem4 = smem_base + stack_words / 4u;
-    const uint32_t n_pairs = (S.n_nodes + 1u) / 2u, n_node4 = 7u * n_pairs, n_head4 = S.n_prims, n_rect4 = 4u * S.n_rects;
-    const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    for (uint32_t j = threadIdx.x; j < n_pairs; j += blockDim.x) {
-        const bool has_right = 2u * j + 1u < S.n_nodes;
-        const float4 ll = S.nodes[4u * j], lh = S.nodes[4u * j + 1u], rl = has_right ? S.nodes[4u * j + 2u] : zero, rh = has_right ? S.nodes[4u * j + 3u] : zero;
-        float4* o = smem4 + 7u * j;
-        o[0] = make_float4(ll.x, lh.x, rl.x, rh.x); o[1] = make_float4(lh.x, ll.x, rh.x, rl.x);
-        o[2] = make_float4(ll.y, lh.y, rl.y, rh.y); o[3] = make_float4(lh.y, ll.y, rh.y, rl.y);
-        o[4] = make_float4(ll.z, lh.z, rl.z, rh.z); o[5] = make_float4(lh.z, ll.z, rh.z, rl.z);
-        o[6] = make_float4(ll.w, lh.w, rl.w, rh.w);
-    }
-    for (uint32_t i = threadIdx.x; i < n_head4; i += blockDim.x) smem4[n_node4 + i] = S.prim_head[i];
-    for (uint32_t i = threadIdx.x; i < n_rect4; i += blockDim.x) smem4[n_node4 + n_head4 + i] = S.rects[i];
-    __syncthreads();
+    const uint32_t n_pairs = (S.n_nodes + 1u) / 2u, n_node4 = 7u * n_pairs, n_head4 = S.n_prims;
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_base);
     const uint32_t scene = base + stack_words * 4u;
+    bulk_stage(mbar, BulkPart{S.oct_blob, scene, 16u * S.oct_blob4});
     return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
 }
 size_t extend_all_smem_bytes(const DScene& S) {
@@ -171,21 +157,29 @@ template <bool COUNT, bool ALL, bool GEN>
 __global__ void __launch_bounds__(ALL ? RT_EXTEND_ALL_BLOCK : RT_EXTEND_BLOCK, ALL ? RT_EXTEND_ALL_MIN_BLOCKS : RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
                                                           uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
     extern __shared__ float4 smem4[];
-    const Staged sm = ALL ? stage_scene_oct(S, smem4) : stage_scene(S, smem4);
+    __shared__ __align__(8) uint64_t s_mbar;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+    const Staged sm = ALL ? stage_scene_oct(S, smem4, mbar) : stage_scene(S, smem4, mbar);
+    // the tables stream in on the copy engine while every thread requests its first ray from HBM
     const uint32_t n = wc->total[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x;
     TraversalWork work{0u, 0u};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const float4 a = q.a[i], b = q.b[i];
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    uint32_t sb = 0u;
+    if (i < n) { a = q.a[i]; b = q.b[i]; if (S.has_media) sb = __float_as_uint(q.c[i].w); }
+    mbar_wait(mbar, 0u);
+    while (i < n) {
         MediumKey key{0u, 0u, 0u, seed_lo, seed_hi};
         if (S.has_media) {
-            const uint32_t sb = __float_as_uint(q.c[i].w);
             key.k0 = __float_as_uint(b.w);
             key.k1 = sb >> 8;
             key.segment = sb & 0xFFu;
         }
         const ClosestHit h = closest_hit<COUNT, ALL, GEN>(S, sm, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w), key, &work);
         hits[i] = make_float2(h.t, __uint_as_float(h.prim));
+        i += stride;
+        if (i < n) { a = q.a[i]; b = q.b[i]; if (S.has_media) sb = __float_as_uint(q.c[i].w); }
     }
     if (COUNT) {  // instrumented build only (RT_RENDER_COUNT_WORK): one atomic pair per warp
         uint32_t bt = work.box_tests, pt = work.prim_tests;
@@ -257,7 +251,9 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
                                                                                   WaveCounters* __restrict__ wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                                                                                   uint32_t staged_bytes) {
     extern __shared__ float4 smem4[];
-    const Staged sm = stage_scene(S, smem4);
+    __shared__ __align__(8) uint64_t s_mbar;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+    const Staged sm = stage_scene(S, smem4, mbar);
     const uint32_t n = wc->total[k % RT_RING];
     uint32_t* cursor = &wc->cursor[k % RT_RING];
     const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
@@ -273,6 +269,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
     if (F.nxt_cnt) feed_prefetch(F, 1u, q, has_media, F.nxt_base, F.nxt_cnt);
     cp_async_wait_all();  // (the first refill needs buffer 0; waiting for both keeps the code simple)
     __syncwarp();
+    mbar_wait(mbar, 0u);  // the staged tree prefix (bulk copy issued by stage_scene, overlapped with the first two ray chunks)
 
     // per-lane traversal state
     RayCtx R = make_ray(f3(0.f, 0.f, 0.f), f3(1.f, 0.f, 0.f));
@@ -455,17 +452,21 @@ __device__ __forceinline__ ClosestHit frame_rects_closest(const DScene& S, uint3
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_RECTS_MIN_BLOCKS) k_extend_rects(const DScene S, const RayQueue q, float2* __restrict__ hits,
                                                                                       WaveCounters* __restrict__ wc, uint32_t k) {
     extern __shared__ float4 smem4[];
-    for (uint32_t i = threadIdx.x; i < S.fr_blob4; i += blockDim.x) smem4[i] = S.fr_blob[i];
-    __syncthreads();
+    __shared__ __align__(8) uint64_t s_mbar;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem4);
+    bulk_stage(mbar, BulkPart{S.fr_blob, base, 16u * S.fr_blob4});  // the frame-rect list streams in while the first rays are requested
     const uint32_t n = wc->total[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const float4 a = q.a[i], b = q.b[i];
-        const float3 o = f3(a.x, a.y, a.z), d = f3(b.x, b.y, b.z);
-        const uint32_t self_prim = __float_as_uint(a.w);
-        const ClosestHit h = frame_rects_closest(S, base, o, d, self_prim);
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (i < n) { a = q.a[i]; b = q.b[i]; }
+    mbar_wait(mbar, 0u);
+    while (i < n) {
+        const ClosestHit h = frame_rects_closest(S, base, f3(a.x, a.y, a.z), f3(b.x, b.y, b.z), __float_as_uint(a.w));
         hits[i] = make_float2(h.t, __uint_as_float(h.prim));
+        i += stride;
+        if (i < n) { a = q.a[i]; b = q.b[i]; }
     }
 }
 
@@ -540,12 +541,13 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
     float4* s_head = smats + 2u * n_staged;
     float4* s_nrm = s_head + n_sp;
     uint2* s_meta = reinterpret_cast<uint2*>(s_nrm + n_sr);
-    for (uint32_t i = threadIdx.x; i < 2u * n_staged; i += blockDim.x) smats[i] = reinterpret_cast<const float4*>(S0.mats)[i];
-    for (uint32_t i = threadIdx.x; i < n_sp; i += blockDim.x) { s_head[i] = S0.prim_head[i]; s_meta[i] = S0.prim_meta[i]; }
-    for (uint32_t i = threadIdx.x; i < n_sr; i += blockDim.x) s_nrm[i] = S0.rect_nrm[i];
+    // one bulk copy of the blob rt_scene_create laid out in exactly this order; it lands while the first round's rays are requested
+    __shared__ __align__(8) uint64_t s_mbar;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+    bulk_stage(mbar, BulkPart{S0.shade_blob, (uint32_t)__cvta_generic_to_shared(shade_smem), 16u * S0.shade_blob4});
+    bool tables_ready = false;
     DScene S = S0;
     if (n_sp) { S.prim_head = s_head; S.prim_meta = s_meta; S.rect_nrm = s_nrm; }
-    __syncthreads();
     const uint32_t s = k % RT_RING;
     const uint32_t n = wc->total[s];
     uint32_t* surv_next = &wc->surv[(k + 1) % RT_RING];
@@ -570,6 +572,7 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
             if (i < n) { h[r] = hits[i]; a[r] = qin.a[i]; b[r] = qin.b[i]; c[r] = qin.c[i]; }
             else { h[r] = make_float2(0.f, __uint_as_float(RT_NO_PRIM)); a[r] = b[r] = c[r] = make_float4(0.f, 0.f, 0.f, 0.f); }
         }
+        if (!tables_ready) { mbar_wait(mbar, 0u); tables_ready = true; }  // block-uniform
         ShadeOne res[R];
         uint32_t ma[R], mb[R], ca = 0u, cb = 0u;
 #pragma unroll
@@ -701,7 +704,10 @@ __global__ void __launch_bounds__(256) k_deinterleave(const float* __restrict__ 
 __global__ void __launch_bounds__(RT_EXTEND_BLOCK) k_trace(const DScene S, const RtRayIn* __restrict__ rays, const uint32_t* __restrict__ self_order,
                                                          uint64_t n, uint32_t seed_lo, uint32_t seed_hi, RtHitOut* __restrict__ out) {
     extern __shared__ float4 smem4[];
-    const Staged sm = stage_scene(S, smem4);
+    __shared__ __align__(8) uint64_t s_mbar;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+    const Staged sm = stage_scene(S, smem4, mbar);
+    mbar_wait(mbar, 0u);
     // scenes that render through the frame-rect list are traced through it too; its blob sits behind the staged scene prefix
     float4* fr_smem = smem4 + (RT_SMEM_STACK * blockDim.x) / 4u + 2u * S.n_staged_nodes + S.n_staged_prims + (S.n_staged_prims ? 4u * S.n_rects : 0u);
     if (S.fr_n) {
@@ -825,7 +831,7 @@ cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_by
     RT_TRY(occupancy(L.shade_blocks, shade1_k, RT_SHADE_BLOCK, shade_bytes));
     RT_TRY(occupancy(L.shade2_blocks, shade2_k, RT_SHADE_BLOCK, shade_bytes));
     // whole tree + heads in shared memory in the octant-ready layout, as long as that keeps the occupancy of the general kernel
-    L.all_staged = S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && !S.root_is_leaf;
+    L.all_staged = S.oct_blob != nullptr && S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && !S.root_is_leaf;
     if (L.all_staged) {
         L.all_smem = extend_all_smem_bytes(S);
         if (L.all_smem > RT_EXTEND_ALL_MAX_SMEM) L.all_staged = false;
