@@ -530,8 +530,13 @@ __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst
 // Each thread shades RT_SHADE_RAYS rays per block round (their queue words are all requested before the first is
 // used: RT_SHADE_RAYS x the memory-level parallelism) and the block allocates output slots for the whole round with
 // ONE barrier pair and ONE pair of global atomics (block_append2 generalised to RT_SHADE_RAYS ballots per warp).
+// k_shade<2> (two rays per thread per round) at 6 resident blocks of 128 threads (<= 85 registers) instead of 8 (<= 64): at 64 its
+// two in-flight rays spill in the hot path — 38.1 -> 44.3 Grays/s on cornell-box (profiles/r2_20_shade2_variants.txt)
+#ifndef RT_SHADE2_MIN_BLOCKS
+#define RT_SHADE2_MIN_BLOCKS 6
+#endif
 template <int R, bool GEN>
-__global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
+__global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS) k_shade(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
                                                const float2* __restrict__ hits, float4* __restrict__ done, WaveCounters* __restrict__ wc, uint32_t k) {
     extern __shared__ float4 shade_smem[];
     __shared__ uint32_t s_cnt[RT_SHADE_BLOCK / 32 + 1][2];
@@ -541,11 +546,22 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, RT_SHADE_MIN_BLOCKS) k_shade(c
     float4* s_head = smats + 2u * n_staged;
     float4* s_nrm = s_head + n_sp;
     uint2* s_meta = reinterpret_cast<uint2*>(s_nrm + n_sr);
+#ifndef RT_SHADE_BULK
+#define RT_SHADE_BULK 1
+#endif
+
+#if RT_SHADE_BULK
     // one bulk copy of the blob rt_scene_create laid out in exactly this order; it lands while the first round's rays are requested
     __shared__ __align__(8) uint64_t s_mbar;
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
     bulk_stage(mbar, BulkPart{S0.shade_blob, (uint32_t)__cvta_generic_to_shared(shade_smem), 16u * S0.shade_blob4});
     bool tables_ready = false;
+#else
+    for (uint32_t i = threadIdx.x; i < S0.shade_blob4; i += blockDim.x) shade_smem[i] = S0.shade_blob[i];
+    __syncthreads();
+    const uint32_t mbar = 0u;
+    bool tables_ready = true;
+#endif
     DScene S = S0;
     if (n_sp) { S.prim_head = s_head; S.prim_meta = s_meta; S.rect_nrm = s_nrm; }
     const uint32_t s = k % RT_RING;

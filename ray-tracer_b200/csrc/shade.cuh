@@ -51,9 +51,18 @@ __device__ __forceinline__ void sphere_uv(float3 unit, float& u, float& v) {  //
     v = 1.0f - acosf(fminf(fmaxf(unit.y, -1.0f), 1.0f)) * (1.0f / RT_PI);
 }
 
-// General 128-byte records (rotated / scaled spheres, media): the rare path, kept out of line so that the common one — translation-only
-// spheres and rectangles — keeps k_shade's registers (inlined, the generic-medium code cost every scene 7-11 % of k_shade).
-__device__ __noinline__ HitDetail general_detail(const RtPrim* __restrict__ g, float3 o, float3 d, float t, bool want_uv, const MediumKey key) {
+// General 128-byte records (rotated / scaled spheres, media): the rare path.
+// inline by default: k_shade<1, true> on book-two 20.6 vs 19.8 Grays/s out of line (profiles/r2_20_shade2_variants.txt); the kernels of scenes
+// WITHOUT general records (GEN = false) do not contain this code at all
+#ifndef RT_GENERAL_DETAIL_INLINE
+#define RT_GENERAL_DETAIL_INLINE 1
+#endif
+#if RT_GENERAL_DETAIL_INLINE
+__device__ __forceinline__ HitDetail general_detail(
+#else
+__device__ __noinline__ HitDetail general_detail(
+#endif
+    const RtPrim* __restrict__ g, float3 o, float3 d, float t, bool want_uv, const MediumKey key) {
     HitDetail h;
     h.u = h.v = 0.0f;
     h.t = t;
