@@ -331,7 +331,17 @@ bool buildFrameRects(const RtPrim* prims, const std::vector<uint32_t>& order, bo
         for (uint32_t i = 0; i < nb; ++i) {
             while (g <= boxes[i].frame) out.box_range[g++] = i;
             float4* rec = out.blob.data() + 3 * (size_t)nf + 10 * (size_t)i;
-            rec[0] = make_float4((float)boxes[i].lo[0], (float)boxes[i].lo[1], (float)boxes[i].lo[2], 0.0f);
+            // lo.w = 1: every rectangle of this box covers its WHOLE face (a Cube::new, the walls of a closed room) — a crossing of the box
+            // surface then lies inside the face's rectangle by construction and the kernel skips the per-face extent test
+            bool full = true;
+            for (int s2 = 0; s2 < 6 && full; ++s2) {
+                if (boxes[i].face[s2] < 0) continue;
+                const Rec& r = recs[(size_t)boxes[i].face[s2]];
+                const uint32_t k2 = (uint32_t)s2 >> 1, a2 = axA(k2), b2 = axB(k2);
+                full = near((double)r.ca - r.ha, boxes[i].lo[a2]) && near((double)r.ca + r.ha, boxes[i].hi[a2]) && near((double)r.cb - r.hb, boxes[i].lo[b2]) &&
+                       near((double)r.cb + r.hb, boxes[i].hi[b2]);
+            }
+            rec[0] = make_float4((float)boxes[i].lo[0], (float)boxes[i].lo[1], (float)boxes[i].lo[2], full ? 1.0f : 0.0f);
             rec[1] = make_float4((float)boxes[i].hi[0], (float)boxes[i].hi[1], (float)boxes[i].hi[2], 0.0f);
             uint32_t* ids = reinterpret_cast<uint32_t*>(rec + 8);
             for (int s = 0; s < 8; ++s) ids[s] = RT_NO_PRIM;

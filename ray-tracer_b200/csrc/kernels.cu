@@ -408,13 +408,17 @@ __device__ __forceinline__ void frame_box(uint32_t box, const float3 o, const fl
     const uint32_t slot_en = 2u * ke + (de > 0.0f ? 0u : 1u), slot_ex = 2u * kx + (dx > 0.0f ? 1u : 0u);
     // both crossings are evaluated; the entry crossing wins when it is a hit (it is the nearer one)
     const uint32_t id_en = lds32(box + 128u + 4u * slot_en), id_ex = lds32(box + 128u + 4u * slot_ex);
-    const float4 Fe = lds128(box + 32u + 16u * slot_en), Fx = lds128(box + 32u + 16u * slot_ex);  // centre a, centre b, half a, half b of the face's rectangle
-    const float ex = fmaf(t_en, d.x, o.x), ey = fmaf(t_en, d.y, o.y), ez = fmaf(t_en, d.z, o.z);
-    const float xx = fmaf(t_ex, d.x, o.x), xy = fmaf(t_ex, d.y, o.y), xz = fmaf(t_ex, d.z, o.z);
-    const float ea = (ke == 0u ? ey : ex) - Fe.x, eb = (ke == 2u ? ey : ez) - Fe.y;
-    const float xa = (kx == 0u ? xy : xx) - Fx.x, xb = (kx == 2u ? xy : xz) - Fx.y;
-    const bool hit_en = crosses & (t_en >= RT_T_EPS) & (id_en != RT_NO_PRIM) & (id_en != self_prim) & (fabsf(ea) <= Fe.z) & (fabsf(eb) <= Fe.w);
-    const bool hit_ex = crosses & (t_ex >= RT_T_EPS) & (id_ex != RT_NO_PRIM) & (id_ex != self_prim) & (fabsf(xa) <= Fx.z) & (fabsf(xb) <= Fx.w);
+    bool hit_en = crosses & (t_en >= RT_T_EPS) & (id_en != RT_NO_PRIM) & (id_en != self_prim);
+    bool hit_ex = crosses & (t_ex >= RT_T_EPS) & (id_ex != RT_NO_PRIM) & (id_ex != self_prim);
+    if (L.w == 0.0f) {  // (warp-uniform) some face rectangle is smaller than its face: test the crossing points against THEIR rectangles
+        const float4 Fe = lds128(box + 32u + 16u * slot_en), Fx = lds128(box + 32u + 16u * slot_ex);  // centre a, centre b, half a, half b
+        const float ex = fmaf(t_en, d.x, o.x), ey = fmaf(t_en, d.y, o.y), ez = fmaf(t_en, d.z, o.z);
+        const float xx = fmaf(t_ex, d.x, o.x), xy = fmaf(t_ex, d.y, o.y), xz = fmaf(t_ex, d.z, o.z);
+        const float ea = (ke == 0u ? ey : ex) - Fe.x, eb = (ke == 2u ? ey : ez) - Fe.y;
+        const float xa = (kx == 0u ? xy : xx) - Fx.x, xb = (kx == 2u ? xy : xz) - Fx.y;
+        hit_en &= (fabsf(ea) <= Fe.z) & (fabsf(eb) <= Fe.w);
+        hit_ex &= (fabsf(xa) <= Fx.z) & (fabsf(xb) <= Fx.w);
+    }
     const float t = hit_en ? t_en : t_ex;
     const uint32_t idx = hit_en ? id_en : id_ex;
     const bool closer = (t < best_t) | ((t == best_t) & (idx < best_i));
