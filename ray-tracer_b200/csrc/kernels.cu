@@ -72,25 +72,34 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
     const uint64_t left = rc.paths_total - issued;
     const uint32_t room = rc.capacity - surv;
     const uint32_t n_new = left < (uint64_t)room ? (uint32_t)left : room;
-    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     // Path order.  pixel-major (default): path = pixel * spp + sample, so the 32 lanes of a warp start as 32 samples of ONE pixel —
     // near-identical camera rays (coherent traversal and material branches) whose finished records stay adjacent in the `done`
-    // queue, where k_accumulate folds them into one atomic per run.  sample-major (RT_B200_PATH_ORDER=0): path = sample * pixels
-    // + pixel.  Either way one 64-bit division per thread, then (major, minor) advance by the grid stride.
+    // queue, where k_accumulate folds them into one atomic per run.  sample-major (RT_RENDER_SAMPLE_MAJOR): path = sample * pixels
+    // + pixel.
+    // Work split: every WARP takes one contiguous slice of the new paths and walks it 32 at a time (coalesced 512-byte stores per
+    // queue word); a lane's path index advances by 32 per step, so in pixel-major order its pixel changes only every spp / 32 steps
+    // and the tile decode (two integer divisions) is redone only then.  One 64-bit division per thread.
     const uint32_t mod = rc.pixel_major ? rc.spp : (uint32_t)rc.pixels_local;
+    const uint32_t lane = threadIdx.x & 31u, n_warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t per_warp = ((n_new + n_warps - 1u) / n_warps + 31u) & ~31u;
+    const uint32_t begin = min((tid >> 5) * per_warp, n_new), end = min(begin + per_warp, n_new);
     uint32_t major = 0u, minor = 0u;
-    if (tid < n_new) {
-        const uint64_t path0 = issued + tid;
+    if (begin + lane < end) {
+        const uint64_t path0 = issued + begin + lane;
         major = (uint32_t)(path0 / mod);
         minor = (uint32_t)(path0 - (uint64_t)major * mod);
     }
-    const uint32_t stride_major = stride / mod, stride_minor = stride - stride_major * mod;
-    for (uint32_t i = tid; i < n_new; i += stride) {
+    uint32_t cur_q = 0xFFFFFFFFu, x = 0u, y = 0u, gp = 0u;
+    for (uint32_t i = begin + lane; i < end; i += 32u) {
         const uint32_t sample = rc.pixel_major ? minor : major, qi = rc.pixel_major ? major : minor;
-        uint32_t x, yl;
-        pixel_from_index(qi, rc.width, rc.rows_local, x, yl);
-        const uint32_t y = rc.row_begin + yl * rc.row_stride;
-        const uint32_t gp = y * rc.width + x;
+        if (qi != cur_q) {
+            uint32_t yl;
+            pixel_from_index(qi, rc.width, rc.rows_local, x, yl);
+            y = rc.row_begin + yl * rc.row_stride;
+            gp = y * rc.width + x;
+            cur_q = qi;
+        }
         const Philox4 rnd = philox4x32_10(0u, RT_DIM_CAMERA, rc.seed_lo, rc.seed_hi, gp, sample);
         float3 o, d;
         if (rc.user_rays) {  // batched render::color(&ray, ..): the caller's ray as it is (direction not normalised, src/render.rs:5)
@@ -105,9 +114,8 @@ __global__ void __launch_bounds__(256) k_generate(const RenderConst rc, RayQueue
         q.a[slot] = make_float4(o.x, o.y, o.z, __uint_as_float(RT_NO_PRIM));
         q.b[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(gp));
         q.c[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float((sample << 8) | 1u));
-        major += stride_major;
-        minor += stride_minor;
-        if (minor >= mod) { minor -= mod; ++major; }
+        minor += 32u;
+        while (minor >= mod) { minor -= mod; ++major; }
     }
     if (tid == 0) {
         const uint32_t total = surv + n_new;
@@ -636,21 +644,29 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS 
 
 // ---- accumulate ------------------------------------------------------------------------------------
 
+// SUMSQ: the caller asked for per-pixel sums of squares too (standard errors); renders that do not (bench, rt_render with a null
+// out_sumsq) run the instantiation with half the shuffles.
+template <bool SUMSQ>
 __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const float4* __restrict__ done, const WaveCounters* __restrict__ wc,
                                                     uint32_t k, double* __restrict__ sum, double* __restrict__ sumsq) {
-    // f64 accumulators (native 64-bit atomics): an f32 running sum of 1024+ equal sky samples rounds the same way on
-    // every add and drifts by 1e-4 relative, which the 3-sigma image test sees on zero-variance pixels.
+    // f64 accumulators in the framebuffer (native 64-bit atomics): an f32 RUNNING sum of 1024+ equal sky samples rounds the same way
+    // on every add and drifts by 1e-4 relative, which the 3-sigma image test sees on zero-variance pixels.
     const uint32_t n = wc->done[k % RT_RING];
     const uint32_t stride = gridDim.x * blockDim.x, lane = threadIdx.x & 31u;
+    constexpr int NV = SUMSQ ? 6 : 3;
     // Runs of records of one pixel (pixel-major path order keeps the samples of a pixel together) are summed in the warp first — a
-    // segmented shuffle reduction over the run heads — and only the head of a run touches the framebuffer: 6 f64 atomics per run
-    // instead of per path (the L2 atomic units were the limit of this kernel: 164 G atomics/s on book-one 4K).
+    // segmented shuffle reduction over the run heads — and only the head of a run touches the framebuffer: 3-6 f64 atomics per run
+    // instead of per path (the L2 atomic units were the limit of this kernel: 164 G atomics/s on book-one 4K).  The in-warp tree is f32
+    // (<= 32 addends, 5 levels: <= 3e-7 relative, far below the f64 accumulation it feeds): a third of the shuffles and adds of an
+    // f64 tree, which had become the cost of the kernel (~150 instructions per record).
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {  // warp-uniform trip count
         const uint32_t i = base + threadIdx.x;
         const bool valid = i < n;
         const float4 r = valid ? done[i] : make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0xffffffffu));
         const uint32_t gp = __float_as_uint(r.w);
-        double v[6] = {(double)r.x, (double)r.y, (double)r.z, (double)r.x * (double)r.x, (double)r.y * (double)r.y, (double)r.z * (double)r.z};
+        float v[NV];
+        v[0] = r.x; v[1] = r.y; v[2] = r.z;
+        if (SUMSQ) { v[NV - 3] = r.x * r.x; v[NV - 2] = r.y * r.y; v[NV - 1] = r.z * r.z; }
         const uint32_t gp_prev = __shfl_up_sync(0xffffffffu, gp, 1);
         const bool head = lane == 0u || gp != gp_prev;
         const uint32_t heads = __ballot_sync(0xffffffffu, head);
@@ -660,8 +676,8 @@ __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const 
             for (uint32_t delta = 1u; delta < 32u; delta <<= 1) {
                 const bool same_run = lane + delta < 32u && (after & ((1u << delta) - 1u)) == 0u;
 #pragma unroll
-                for (int c = 0; c < 6; ++c) {
-                    const double other = __shfl_down_sync(0xffffffffu, v[c], delta);
+                for (int c = 0; c < NV; ++c) {
+                    const float other = __shfl_down_sync(0xffffffffu, v[c], delta);
                     if (same_run) v[c] += other;
                 }
             }
@@ -671,13 +687,13 @@ __global__ void __launch_bounds__(256) k_accumulate(const RenderConst rc, const 
         const uint32_t yl = (y - rc.row_begin) / rc.row_stride;
         const size_t o = ((size_t)yl * rc.width + x) * 3;
         RT_ASSERT(y >= rc.row_begin && (y - rc.row_begin) % rc.row_stride == 0u && yl < rc.rows_local && x < rc.width);
-        atomicAdd(&sum[o + 0], v[0]);
-        atomicAdd(&sum[o + 1], v[1]);
-        atomicAdd(&sum[o + 2], v[2]);
-        if (sumsq) {
-            atomicAdd(&sumsq[o + 0], v[3]);
-            atomicAdd(&sumsq[o + 1], v[4]);
-            atomicAdd(&sumsq[o + 2], v[5]);
+        atomicAdd(&sum[o + 0], (double)v[0]);
+        atomicAdd(&sum[o + 1], (double)v[1]);
+        atomicAdd(&sum[o + 2], (double)v[2]);
+        if (SUMSQ) {
+            atomicAdd(&sumsq[o + 0], (double)v[NV - 3]);
+            atomicAdd(&sumsq[o + 1], (double)v[NV - 2]);
+            atomicAdd(&sumsq[o + 2], (double)v[NV - 1]);
         }
     }
 }
@@ -925,7 +941,9 @@ void launch_shade(const Launch& L, const DScene& S, const RenderConst& rc, const
     }
 }
 void launch_accumulate(const Launch& L, const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq) {
-    k_accumulate<<<fit_grid(L, L.sl->num_sms * L.opt->acc_blocks, 256), 256, 0, L.st>>>(rc, done, wc, k, sum, sumsq);
+    const int g = fit_grid(L, L.sl->num_sms * L.opt->acc_blocks, 256);
+    if (sumsq) k_accumulate<true><<<g, 256, 0, L.st>>>(rc, done, wc, k, sum, sumsq);
+    else k_accumulate<false><<<g, 256, 0, L.st>>>(rc, done, wc, k, sum, sumsq);
 }
 void launch_finish(int sms, const double* acc, size_t n, float* out, cudaStream_t st) { k_finish<<<sms * 4, 256, 0, st>>>(acc, n, out); }
 void launch_resolve_u8(int sms, const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st) {

@@ -23,27 +23,50 @@ struct HitDetail {
     bool uv_valid;
 };
 
-// Hit point and unit normal of a translation-only sphere, re-solved in f64 for the primitive extend chose.
-// A far, small sphere (r = 0.2 seen from 15 units, r = 0.25 from 200) leaves f32 only ~1e-5 of absolute
-// position accuracy, i.e. up to 1e-4 of normal error; this runs once per path SEGMENT (not per candidate), so
-// ~100 DFMA-class instructions here are noise next to the traversal, and they make point and normal as exact
-// as their f32 storage allows.  `t32` (extend's answer) only selects which root is meant.
-__device__ __forceinline__ void sphere_record_f64(float3 o, float3 d, float3 ctr, float r, float t32, float3& p, float3& unit, float& t_out) {
-    const double ox = (double)o.x - (double)ctr.x, oy = (double)o.y - (double)ctr.y, oz = (double)o.z - (double)ctr.z;
-    const double dx = d.x, dy = d.y, dz = d.z;
-    const double a = dx * dx + dy * dy + dz * dz;
-    const double b = ox * dx + oy * dy + oz * dz;
-    const double c = ox * ox + oy * oy + oz * oz - (double)r * (double)r;
-    const double sq = sqrt(fmax(b * b - a * c, 0.0));
-    const double q = (b > 0.0) ? (-b - sq) : (sq - b);
-    const double t0 = q / a, t1 = (q != 0.0) ? c / q : 0.0;
-    const double t = (fabs(t0 - (double)t32) <= fabs(t1 - (double)t32)) ? t0 : t1;
-    const double qx = fma(t, dx, ox), qy = fma(t, dy, oy), qz = fma(t, dz, oz);
-    const double inv = 1.0 / sqrt(qx * qx + qy * qy + qz * qz);
-    const double ux = qx * inv, uy = qy * inv, uz = qz * inv;
-    unit = f3((float)ux, (float)uy, (float)uz);  // geometry.rs:68 normalize(p / r)
-    p = f3((float)fma((double)r, ux, (double)ctr.x), (float)fma((double)r, uy, (double)ctr.y), (float)fma((double)r, uz, (double)ctr.z));
-    t_out = (float)t;
+// Hit point and unit normal of a translation-only sphere for the primitive extend chose.  A far, small sphere (r = 0.2 seen from 15
+// units, r = 0.25 from 200) leaves extend's f32 t only ~1e-5 of absolute accuracy along the ray, i.e. up to 1e-4 (1e-3 at 200 units) of
+// normal error, so t is refined here — once per path SEGMENT, not per candidate.  Round 1 re-solved the quadratic in f64 (~100
+// DFMA-class instructions, 14 % of k_shade, the FP64 pipe at 13 %); this is the same refinement in compensated f32:
+//   * oc = o - c as an unevaluated sum hi + lo (Dekker's TwoDiff: lo is the exact rounding error of hi), so the centre-relative
+//     origin is exact although |o|, |c| >> r;
+//   * q(t) = oc + t d through ONE fma per component: the product is exact inside the fma and the sum is rounded once, to the
+//     precision of the RESULT, which is small (|q| = r) — the cancellation costs nothing;
+//   * one Newton step on f(t) = |q(t)|^2 - r^2 (f' = 2 q.d) from extend's t: quadratic convergence from a 1e-5-class error leaves
+//     r * 1e-7 / cos(theta) of error in t, and the normal q / |q| accurate to a few f32 ulps.
+// Checked by gate 1 on every scene, the 1 M-sphere cloud included (tests/test_gpu_parity.py: normals within 1e-4 of the f64 oracle).
+__device__ __forceinline__ void two_diff(float a, float b, float& hi, float& lo) {
+    hi = a - b;
+    const float v = hi - a;
+    lo = (a - (hi - v)) - (b + v);
+}
+__device__ __forceinline__ void sphere_record(float3 o, float3 d, float3 ctr, float r, float t32, float3& p, float3& unit, float& t_out) {
+    if (r > 8.0f * t32) {
+        // A sphere that is HUGE against the hit distance (the r = 1000 ground seen from a few units) is the opposite case: extend's t is
+        // already as good as f32 gets (intersect.cuh big_sphere_hit expands around the world origin), while here |q| = r, so f = |q|^2 - r^2
+        // would cancel at r^2 ~ 1e6 and c + r unit would round at ulp(r).  The reference's own formulas are the accurate ones in f32:
+        // intersection = ray.at(t) (geometry.rs:67), normal = normalize((p - c) / r) (geometry.rs:68).
+        p = fma3(t32, d, o);
+        unit = normalize3(p - ctr);
+        t_out = t32;
+        return;
+    }
+    float3 hi, lo;
+    two_diff(o.x, ctr.x, hi.x, lo.x);
+    two_diff(o.y, ctr.y, hi.y, lo.y);
+    two_diff(o.z, ctr.z, hi.z, lo.z);
+    float t = t32;
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {  // (the second step costs 15 instructions and removes any dependence on how good extend's t was)
+        const float3 q = f3(fmaf(t, d.x, hi.x) + lo.x, fmaf(t, d.y, hi.y) + lo.y, fmaf(t, d.z, hi.z) + lo.z);
+        const float f = fmaf(-r, r, dot3(q, q)), g = 2.0f * dot3(q, d);
+        const float step = __fdividef(f, g);
+        // a grazing hit has f' = 2 q.d -> 0 (the two roots meet): a step that is not tiny against the sphere is no refinement, keep t
+        if (fabsf(step) * sqrtf(dot3(d, d)) <= 0.2f * r) t -= step;
+    }
+    const float3 q = f3(fmaf(t, d.x, hi.x) + lo.x, fmaf(t, d.y, hi.y) + lo.y, fmaf(t, d.z, hi.z) + lo.z);
+    unit = q * rsqrtf(dot3(q, q));  // geometry.rs:68 normalize(p / r)
+    p = fma3(r, unit, ctr);
+    t_out = t;
 }
 
 __device__ __forceinline__ void sphere_uv(float3 unit, float& u, float& v) {  // geometry.rs:35-39, acos clamped (A.11)
@@ -136,7 +159,7 @@ __device__ __forceinline__ HitDetail hit_detail(const DScene& S, uint32_t i, flo
     h.t = t;
     h.uv_valid = want_uv;
     if (head.w > 0.0f) {  // translation-only sphere
-        sphere_record_f64(o, d, f3(head.x, head.y, head.z), head.w, t, h.p, h.n, h.t);
+        sphere_record(o, d, f3(head.x, head.y, head.z), head.w, t, h.p, h.n, h.t);
         if (want_uv) sphere_uv(h.n, h.u, h.v);
         return h;
     }

@@ -213,7 +213,7 @@ def test_golden_paired_render(rt, device):
         s, _, st = scene.render(scene.flat.camera(w / h), w, h, spp, depth, seed=1)
         ok = np.abs(s - g["paired_sum"]).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(g["paired_sum"]).max(axis=2))
         assert ok.mean() >= 0.97, f"{name}: {ok.mean():.3f}"
-        assert abs(int(st.rays) - int(g["paired_segments"][0])) <= max(4, 0.01 * int(g["paired_segments"][0]))
+        assert abs(int(st.rays) - int(g["paired_segments"][0])) <= max(4, 0.01 * int(g["paired_segments"][0])), (name, int(st.rays), int(g["paired_segments"][0]))
 
 
 def _psnr_resolved(mean_a, mean_b):
@@ -792,7 +792,7 @@ def test_checker_lists_scene_in_both_device_forms(rt, orc, device):
     a, b = forms["list"], forms["tree"]
     for f in ["hit", "prim", "material"]:
         assert np.array_equal(a[0][f], b[0][f]), f
-    assert np.array_equal(a[0]["t"], b[0]["t"])
+    assert np.allclose(a[0]["t"], b[0]["t"], rtol=2e-6, atol=0)  # (the tree form tests the two huge spheres through the always-list's own formula)
     assert a[2] == b[2] and np.allclose(a[1], b[1], rtol=1e-5, atol=1e-5)
     # the checker really is in the image: the floor alternates between its three colours
     s_o, _, _ = so.render(128, 72, 16, 50, seed=2, mode=orc.PAIRED)
