@@ -14,10 +14,12 @@ name, w, h, spp, depth = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sy
 dev = rt.Device(0)
 sc = rt.Scene.example(dev, name, 1)
 cam = sc.flat.camera(w / h)
-sc.render(cam, w, h, 8, depth, want_sumsq=False)
-_, _, st = sc.render(cam, w, h, spp, depth, flags=rt.RENDER_STAGE_TIMING, want_sumsq=False)
-_, _, two = sc.render(cam, w, h, spp, depth, want_sumsq=False)
-_, _, two = sc.render(cam, w, h, spp, depth, want_sumsq=False)
+import os
+fl = int(os.environ.get("AB_FLAGS", "0"))  # extra RtRenderParams.flags, e.g. 16 = RT_RENDER_EXTEND_PERSISTENT, 8 = .._PER_THREAD
+sc.render(cam, w, h, 8, depth, want_sumsq=False, flags=fl)
+_, _, st = sc.render(cam, w, h, spp, depth, flags=rt.RENDER_STAGE_TIMING | fl, want_sumsq=False)
+_, _, two = sc.render(cam, w, h, spp, depth, want_sumsq=False, flags=fl)
+_, _, two = sc.render(cam, w, h, spp, depth, want_sumsq=False, flags=fl)
 print(json.dumps({"g": st.ms_generate, "e": st.ms_extend, "s": st.ms_shade, "a": st.ms_accumulate, "one": st.ms_total, "two": two.ms_total, "rays": st.rays, "paths": st.paths}))
 ''' % ROOT
 scene = sys.argv[1:6]
