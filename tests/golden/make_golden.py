@@ -4,7 +4,7 @@ The reference itself cannot produce vectors (Rust, OS-seeded RNG, no toolchain h
 these pin the ORACLE's behaviour at the commit that generated them: tests/test_golden.py re-checks the
 oracle against them on every run (an edit that changes oracle semantics shows up as a diff here) and the
 GPU tests compare the CUDA path with the same files.  Run from the repo root:
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py [scene ...]      (no argument: every scene; name scenes to leave the other fixtures untouched)
 """
 import os
 import sys
@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import oracle_py as orc  # noqa: E402
 
-SCENES = ["book-one", "cornell-box", "book-two", "stress:5000"]
+SCENES = ["book-one", "cornell-box", "book-two", "stress:5000", "checker-lists"]
 
 
 def fixed_rays(scene, w=24, h=16, n_bounce=600, seed=7):
@@ -34,7 +34,7 @@ def fixed_rays(scene, w=24, h=16, n_bounce=600, seed=7):
 
 
 def main():
-    for name in SCENES:
+    for name in (sys.argv[1:] or SCENES):
         s = orc.Scene(name, 1)
         rays = fixed_rays(s)
         h = s.trace(rays.astype(np.float64), seed=1)

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-SCENES = ["book-one", "cornell-box", "book-two", "stress:5000"]
+SCENES = ["book-one", "cornell-box", "book-two", "stress:5000", "checker-lists"]
 
 
 def load(name):

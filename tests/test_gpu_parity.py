@@ -71,7 +71,7 @@ def _check_trace(hg, ho, label):
     return stable.mean(), bare.mean()
 
 
-@pytest.mark.parametrize("name", ["book-one", "cornell-box", "book-two", "stress:5000"])
+@pytest.mark.parametrize("name", ["book-one", "cornell-box", "book-two", "stress:5000", "checker-lists"])
 def test_trace_matches_golden_fixture(rt, device, name):
     g = _golden(name)
     scene = rt.Scene.example(device, name, 1)
@@ -206,7 +206,7 @@ def test_paired_paths_match_oracle(rt, orc, device, name, w, h, spp):
 
 
 def test_golden_paired_render(rt, device):
-    for name in ["book-one", "cornell-box", "book-two", "stress:5000"]:
+    for name in ["book-one", "cornell-box", "book-two", "stress:5000", "checker-lists"]:
         g = _golden(name)
         w, h, spp, depth = [int(v) for v in g["paired_shape"]]
         scene = rt.Scene.example(device, name, 1)
