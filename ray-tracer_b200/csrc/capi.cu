@@ -560,7 +560,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     std::vector<uint2> meta(n);
     std::vector<RtPrim> gen;
     std::vector<float4> rects, rect_nrm;
-    bool has_media = false;
+    bool has_media = false, has_general = false;
     float always_k[RT_MAX_ALWAYS] = {0};
     for (uint32_t i = 0; i < n; ++i) {
         const RtPrim& p = desc->prims[bvh.order[i]];
@@ -589,6 +589,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
             head[i] = make_float4(fx, fy, fz, -1.0f);
             gen.push_back(p);
             has_media |= (p.kind == RT_PRIM_MEDIUM_SPHERE || p.kind == RT_PRIM_MEDIUM);
+            has_general |= (p.kind != RT_PRIM_RECT);
         }
     }
     // materials with the solid colour inlined
@@ -655,6 +656,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     if (use_lbvh && d.n_nodes > RT_MAX_STAGED_NODES) staged = 2u;  // the LBVH's top levels are not a prefix of its node array: only the root pair
     d.n_staged_nodes = staged & ~1u;
     d.has_media = has_media ? 1u : 0u;
+    d.has_general = has_general ? 1u : 0u;
     d.n_rects = (uint32_t)(rects.size() / 4);
     d.n_small = small ? n : 0u;
     d.n_staged_prims = (n <= RT_MAX_STAGED_PRIMS && d.n_rects <= RT_MAX_STAGED_RECTS) ? n : 0u;

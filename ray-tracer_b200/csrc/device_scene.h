@@ -82,6 +82,8 @@ struct DScene {
     uint32_t bvh_depth;        // depth of the tree (levels below the root)
     uint32_t n_staged_nodes;   // prefix of `nodes` staged in shared memory
     uint32_t has_media;
+    uint32_t has_general;      // some primitive is reached through its general 128-byte record (rotated / scaled / negative-radius sphere, medium);
+                               // rectangles own a general record too but are tested through `rects` / `rect_nrm` and never read it
     uint32_t n_rects;
     uint32_t n_staged_prims;   // n_prims when heads (and all rects) are staged in shared memory, else 0
     uint32_t n_small;          // > 0: no tree, test primitives [0, n_small) in order

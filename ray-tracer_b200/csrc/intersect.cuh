@@ -345,7 +345,7 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile(
 
 // Test device primitive `i`.  Returns t or +inf.  BIG = primitive of the always-tested list.
 // ALL = every node and primitive head of the scene is staged in shared memory (k_extend<.., true>): no per-access range check.
-// GEN = the scene has general 128-byte records at all (S.n_gen > 0: rotated / scaled spheres, media).  Scenes without any — book-one,
+// GEN = some primitive of the scene is reached through its general 128-byte record (S.has_general: rotated / scaled spheres, media).  Scenes without any — book-one,
 // cornell-box, the sphere cloud — run kernels from which the out-of-line general path is compiled away: its mere presence (call ABI,
 // argument marshalling) costs registers in the traversal loop (k_extend<., true>: 24 bytes of spills, -3 %; k_shade: -7 to -11 %).
 template <bool BIG, bool ALL = false, bool GEN = true>

@@ -842,7 +842,7 @@ cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_by
     L.shade_smem = shade_bytes;
     L.rects_smem = fr_bytes;
 #define RT_TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
-    const bool gen = S.n_gen > 0u;  // general 128-byte records present: the kernels that carry the out-of-line general path
+    const bool gen = S.has_general != 0u;  // primitives reached through their general 128-byte record: the kernels that carry that path
     L.gen = gen;
     auto* const extend_k = gen ? k_extend<false, false, true> : k_extend<false, false, false>;
     auto* const all_k = gen ? k_extend<false, true, true> : k_extend<false, true, false>;

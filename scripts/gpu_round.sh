@@ -28,7 +28,7 @@ for s in $STEPS; do
         timeout 900 python bench.py --workload $wl --steps 2 --warmup 3 --no-cpu-baseline > $OUT/bench_$wl.json 2> $OUT/bench_$wl.err; echo "bench $wl rc=$?"; cat $OUT/bench_$wl.json
       done ;;
     launches)
-      timeout 300 python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $OUT/plain_launches.log 2>&1 &&
+      timeout 300 python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-book-one-4k > $OUT/plain_launches.log 2>&1 &&
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 2000 -c 4000 --csv --log-file $OUT/launches.csv \
         python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $OUT/ncu_launches.log 2>&1
       echo "launches rc=$?" ;;
