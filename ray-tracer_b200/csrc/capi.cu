@@ -971,14 +971,18 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
         const RayQueue& qout = q[(k + 1) & 1];
         const bool timed = timing && (k % tstride == 0);
         const uint64_t ts = n_timed;
+        // tail: every path has been issued (known from a status poll) — k_generate would only roll the counters; extend does that
+        // itself (kernels.cu tail_roll) and one of the three dependent launches of a draining iteration is gone
+        const bool tail = RT_TAIL_MODE && L.work_hint != RT_WORK_UNKNOWN;
+        const uint32_t kx = tail ? (ku | RT_K_TAIL) : ku;
         if (timed) RT_CUDA(stage_event(ts, 0, st));
-        launch_generate(L, rc, qin, wc, ku);
+        if (!tail) launch_generate(L, rc, qin, wc, ku);
         if (timed) RT_CUDA(stage_event(ts, 1, st));
-        launch_extend(L, scene->d, qin, ctx->hits.p, wc, ku, rc.seed_lo, rc.seed_hi, count_work);
+        launch_extend(L, scene->d, qin, ctx->hits.p, wc, kx, rc.seed_lo, rc.seed_hi, count_work);
         if (timed) RT_CUDA(stage_event(ts, 2, st));
         // shade_k refills done[k & 1]: accumulate_{k-2} must be through with it
         if (overlap && k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[k & 1], 0));
-        launch_shade(L, scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, ku);
+        launch_shade(L, scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, kx);
         if (timed) RT_CUDA(stage_event(ts, 3, st));
         if (overlap) {
             RT_CUDA(cudaEventRecord(ctx->ev_shaded[k & 1], st));
@@ -988,7 +992,7 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
         launch_accumulate(La, rc, ctx->done[k & 1].p, wc, ku, acc_sum, acc_sumsq);
         if (timed) { RT_CUDA(stage_event(ts, 5, acc_st)); ++n_timed; }
         if (overlap) RT_CUDA(cudaEventRecord(ctx->ev_accumulated[k & 1], acc_st));
-        launches += 4;
+        launches += tail ? 3 : 4;
         // a launch that cannot start (shared memory, bad configuration) must surface here, not as "did not terminate" 100 k iterations later
         if (k == 0) RT_CUDA(cudaPeekAtLastError());
         ++k;

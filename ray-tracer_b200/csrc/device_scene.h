@@ -39,6 +39,7 @@ constexpr int RT_STACK_DEPTH = 64;       // traversal stack entries (builder cap
 #define RT_SMEM_STACK_N 24
 #endif
 constexpr uint32_t RT_SMEM_STACK = RT_SMEM_STACK_N;   // of which this many per thread live in shared memory (96 B/thread)
+constexpr uint32_t RT_K_TAIL = 0x80000000u;  // flag on the iteration index handed to extend / shade: tail of a render, no k_generate (kernels.cu)
 constexpr uint32_t RT_RING = 4;          // ring length of the per-iteration queue counters
 constexpr uint32_t RT_MAX_STAGED_NODES = 2048;  // a BVH of at most this many nodes (64 KB) is staged whole in shared memory by extend
 constexpr uint32_t RT_TOP_STAGED_NODES = 256;   // larger trees: only this breadth-first prefix (top 8 levels, 8 KB)

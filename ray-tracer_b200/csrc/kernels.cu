@@ -27,6 +27,26 @@ namespace rtb {
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
+// Tail of a render (every path has been issued; the host knows it from its status poll): k_generate would only roll the counters, and
+// as the first of three dependent launches per iteration it is a third of the latency chain that the ~50 draining iterations of a
+// depth-50 render consist of.  The host then stops launching it and passes k | RT_K_TAIL: the queue size IS the survivor count, and
+// thread 0 of block 0 of the extend kernel rolls the ring (it runs after shade of k - 1 and before shade of k, where k_generate sat).
+__device__ __forceinline__ uint32_t queue_size(const WaveCounters* __restrict__ wc, uint32_t kf) {
+    const uint32_t s = (kf & ~RT_K_TAIL) % RT_RING;
+    return (kf & RT_K_TAIL) ? wc->surv[s] : wc->total[s];
+}
+__device__ __forceinline__ void tail_roll(WaveCounters* __restrict__ wc, uint32_t kf, uint32_t n) {
+    if (!(kf & RT_K_TAIL) || blockIdx.x != 0u || threadIdx.x != 0u) return;
+    const uint32_t k = kf & ~RT_K_TAIL;
+    wc->issued[(k + 1) % RT_RING] = wc->issued[k % RT_RING];
+    wc->surv[(k + 2) % RT_RING] = 0u;
+    wc->done[(k + 1) % RT_RING] = 0u;
+    wc->cursor[(k + 1) % RT_RING] = 0u;
+    wc->st_rays += n;
+    wc->st_total = n;
+    wc->st_iter = k;
+}
+
 // local linear index -> (x, local row): 8x4 pixel tiles per warp where they fit, scanline remainders
 __device__ __forceinline__ void pixel_from_index(uint32_t q, uint32_t W, uint32_t rows, uint32_t& x, uint32_t& yl) {
     const uint32_t W8 = W & ~7u, R4 = rows & ~3u;
@@ -169,7 +189,8 @@ __global__ void __launch_bounds__(ALL ? RT_EXTEND_ALL_BLOCK : RT_EXTEND_BLOCK, A
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
     const Staged sm = ALL ? stage_scene_oct(S, smem4, mbar) : stage_scene(S, smem4, mbar);
     // the tables stream in on the copy engine while every thread requests its first ray from HBM
-    const uint32_t n = wc->total[k % RT_RING];
+    const uint32_t n = queue_size(wc, k);
+    tail_roll(wc, k, n);
     const uint32_t stride = gridDim.x * blockDim.x;
     TraversalWork work{0u, 0u};
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -262,8 +283,9 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
     __shared__ __align__(8) uint64_t s_mbar;
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
     const Staged sm = stage_scene(S, smem4, mbar);
-    const uint32_t n = wc->total[k % RT_RING];
-    uint32_t* cursor = &wc->cursor[k % RT_RING];
+    const uint32_t n = queue_size(wc, k);
+    tail_roll(wc, k, n);
+    uint32_t* cursor = &wc->cursor[(k & ~RT_K_TAIL) % RT_RING];
     const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
     const bool has_media = S.has_media != 0u;
     TraversalWork work{0u, 0u};
@@ -468,7 +490,8 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_RECTS_MIN_BLOCKS) k_extend
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem4);
     bulk_stage(mbar, BulkPart{S.fr_blob, base, 16u * S.fr_blob4});  // the frame-rect list streams in while the first rays are requested
-    const uint32_t n = wc->total[k % RT_RING];
+    const uint32_t n = queue_size(wc, k);
+    tail_roll(wc, k, n);
     const uint32_t stride = gridDim.x * blockDim.x;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
@@ -576,9 +599,9 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS 
 #endif
     DScene S = S0;
     if (n_sp) { S.prim_head = s_head; S.prim_meta = s_meta; S.rect_nrm = s_nrm; }
-    const uint32_t s = k % RT_RING;
-    const uint32_t n = wc->total[s];
-    uint32_t* surv_next = &wc->surv[(k + 1) % RT_RING];
+    const uint32_t s = (k & ~RT_K_TAIL) % RT_RING;
+    const uint32_t n = queue_size(wc, k);
+    uint32_t* surv_next = &wc->surv[((k & ~RT_K_TAIL) + 1) % RT_RING];
     uint32_t* done_cnt = &wc->done[s];
     const uint32_t lane = lane_id(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     const uint32_t stride = gridDim.x * blockDim.x * R;

@@ -52,6 +52,9 @@ constexpr uint32_t RT_WORK_UNKNOWN = 0xFFFFFFFFu;
 
 // Tuning options of a context.  rt_init reads the RT_B200_* environment variables ONCE into this struct (RtInitOptions of the C ABI
 // overrides them); nothing is re-read per render.
+#ifndef RT_TAIL_MODE
+#define RT_TAIL_MODE 1  // 0: keep launching k_generate while the render drains (A/B of the tail iterations)
+#endif
 struct LaunchOptions {
     int persistent = 2;   // extend in its persistent lane-refilling form: 0 never, 1 always (where a tree exists), 2 from RT_PERSISTENT_MIN_NODES nodes
     int shade_rays2 = 1;  // two rays per thread per barrier round in k_shade on small all-rectangle scenes
