@@ -192,10 +192,12 @@ typedef enum RtSceneFlags {
     RT_SCENE_NO_FRAME_RECTS = 1u,  /* small all-rectangle scenes keep the general rectangle records (no frame-rect list) */
     RT_SCENE_NO_STAGED_PRIMS = 2u, /* primitive heads stay in global memory */
     RT_SCENE_NO_SMALL_LIST = 4u,   /* scenes of <= 32 primitives get a tree like any other */
-    RT_SCENE_NO_FRAME_BOXES = 8u   /* frame-rect list without grouping the faces of a box into one slab test */
+    RT_SCENE_NO_FRAME_BOXES = 8u,  /* frame-rect list without grouping the faces of a box into one slab test */
+    RT_SCENE_NO_BOX_PRIMS = 16u,   /* the six faces of an axis-aligned Cube stay six leaves of the tree (no box primitive) */
+    RT_SCENE_NO_WHOLE_TREE = 32u   /* extend never runs in its whole-tree-in-shared-memory form */
 } RtSceneFlags;
 /* Options of a scene build; all-zero = defaults (a context's defaults come from RT_B200_BVH_BUILDER=host|device,
- * RT_B200_BVH_MAX_LEAF, RT_B200_BVH_TREELET, RT_B200_BVH_THREADS, RT_B200_STAGED_NODES, RT_B200_RECT_FRAMES=0, RT_B200_RECT_BOXES=0, RT_B200_STAGE_PRIMS=0,
+ * RT_B200_BVH_MAX_LEAF, RT_B200_BVH_TREELET, RT_B200_BVH_THREADS, RT_B200_STAGED_NODES, RT_B200_RECT_FRAMES=0, RT_B200_RECT_BOXES=0, RT_B200_BOX_PRIMS=0, RT_B200_WHOLE_TREE=0, RT_B200_STAGE_PRIMS=0,
  * RT_B200_SMALL_SCENE=0 at rt_init). */
 typedef struct RtSceneOptions {
     uint32_t bvh_builder;   /* RtBvhBuilder: AUTO = device LBVH from 65 536 primitives, host binned SAH below */
@@ -290,6 +292,17 @@ int rt_scene_bvh_info(const RtScene* scene, uint32_t* n_nodes, uint32_t* n_alway
 /* Frame-rect list of a small all-rectangle scene (k_extend_rects): frames, frame boxes (faces of one box tested with one slab test)
  * and loose rectangles; all 0 when the scene does not use it. */
 int rt_scene_frame_rect_info(const RtScene* scene, uint32_t* n_frames, uint32_t* n_boxes, uint32_t* n_loose);
+/* How extend sees the scene: box primitives (six face rectangles of an axis-aligned Cube answered by one slab test), leaf items of the
+ * tree (primitives + boxes - 6 x boxes), and the threads per block of the whole-tree-in-shared-memory form (0: not used). */
+int rt_scene_extend_info(const RtScene* scene, uint32_t* n_box_prims, uint32_t* n_leaf_items, uint32_t* whole_tree_threads);
+/* The same answer WITHOUT a device (host planning only: box detection + host SAH build; no CUDA call): what rt_scene_create_ex would
+ * hand to extend.  n_nodes / bvh_depth are 0 for scenes whose tree would be built on the device (RT_BVH_DEVICE_LBVH). */
+typedef struct RtScenePlan {
+    uint32_t n_box_prims, n_leaf_items, n_nodes, bvh_depth, n_always;
+    uint32_t whole_tree_threads;   /* 0: the tables do not fit one block's shared memory */
+    uint64_t whole_tree_smem;      /* bytes of dynamic shared memory of that form */
+} RtScenePlan;
+int rt_scene_plan(const RtSceneDesc* desc, const RtSceneOptions* options, RtScenePlan* out);
 /* Bytes of device memory the scene occupies (= host->device bytes rt_scene_create copied). */
 uint64_t rt_scene_device_bytes(const RtScene* scene);
 const char* rt_last_error(void);

@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 RENDER_STAGE_TIMING, RENDER_COUNT_WORK, RENDER_SAMPLE_MAJOR, RENDER_EXTEND_PER_THREAD, RENDER_EXTEND_PERSISTENT, RENDER_TIME_EVERY_ITERATION = 1, 2, 4, 8, 16, 32
 CTX_NO_ACCUMULATE_OVERLAP, CTX_STAGE_TIMING, CTX_SHADE_ONE_RAY = 1, 2, 4
 BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
-SCENE_NO_FRAME_RECTS, SCENE_NO_STAGED_PRIMS, SCENE_NO_SMALL_LIST, SCENE_NO_FRAME_BOXES = 1, 2, 4, 8
+SCENE_NO_FRAME_RECTS, SCENE_NO_STAGED_PRIMS, SCENE_NO_SMALL_LIST, SCENE_NO_FRAME_BOXES, SCENE_NO_BOX_PRIMS, SCENE_NO_WHOLE_TREE = 1, 2, 4, 8, 16, 32
 RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM, RT_ERR_NCCL = 0, -1, -2, -3, -4, -5, -6
 PRIM_SPHERE, PRIM_RECT, PRIM_MEDIUM_SPHERE, PRIM_MEDIUM = 0, 1, 2, 3
 NO_PRIM = 0xFFFFFFFF
@@ -69,6 +69,11 @@ class RtStats(C.Structure):
                 ("timed_iterations", C.c_uint64)]
 
 
+class RtScenePlan(C.Structure):
+    _fields_ = [("n_box_prims", C.c_uint32), ("n_leaf_items", C.c_uint32), ("n_nodes", C.c_uint32), ("bvh_depth", C.c_uint32), ("n_always", C.c_uint32),
+                ("whole_tree_threads", C.c_uint32), ("whole_tree_smem", C.c_uint64)]
+
+
 class RthCameraArgs(C.Structure):
     _fields_ = [("eye", C.c_double * 3), ("center", C.c_double * 3), ("up", C.c_double * 3), ("fov", C.c_double), ("aspect", C.c_double),
                 ("focus_distance", C.c_double), ("lens_radius", C.c_double)]
@@ -78,7 +83,7 @@ class RthCameraArgs(C.Structure):
 ABI_SYMBOLS = ["rt_init", "rt_init_ex", "rt_options_from_env", "rt_shutdown", "rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_render", "rt_render_device",
                "rt_trace", "rt_trace_from", "rt_color_rays", "rt_resolve_u8", "rt_init_multi", "rt_shutdown_multi", "rt_multi_device_count", "rt_multi_context",
                "rt_multi_scene_create", "rt_multi_scene_destroy", "rt_render_multi",
-               "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_frame_rect_info", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
+               "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_frame_rect_info", "rt_scene_extend_info", "rt_scene_plan", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
                "rth_flat_desc", "rth_scene_upload", "rth_camera", "rth_encode_image", "rth_decode_image", "rth_set_earth_image"]
 
 
@@ -125,6 +130,8 @@ def _load():
     L.rt_scene_device_bytes.restype = u64
     L.rt_scene_bvh_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
     L.rt_scene_frame_rect_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
+    L.rt_scene_extend_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
+    L.rt_scene_plan.argtypes = [C.POINTER(RtSceneDesc), C.POINTER(RtSceneOptions), C.POINTER(RtScenePlan)]
     L.rt_last_error.restype = C.c_char_p
     L.rt_abi_version.restype = u32
     L.rth_example_scene.argtypes = [C.c_char_p, u64, C.POINTER(vp)]
@@ -300,6 +307,12 @@ class FlatScene:
         d = self.desc()
         return self._table(d.textures, d.n_textures, TEXTURE_DTYPE)
 
+    def plan(self, options=None):
+        """rt_scene_plan: what rt_scene_create_ex would hand to extend (box primitives, leaf items, tree size, whole-tree form) — no device needed."""
+        d, out = self.desc(), RtScenePlan()
+        _check(lib.rt_scene_plan(C.byref(d), C.byref(options) if options is not None else None, C.byref(out)))
+        return {k: int(getattr(out, k)) for k, _ in RtScenePlan._fields_}
+
     def camera_args(self, aspect):
         a = RthCameraArgs()
         lib.rth_flat_camera_args(self._h, float(aspect), C.byref(a))
@@ -363,6 +376,11 @@ class Scene:
         f, b, l = C.c_uint32(), C.c_uint32(), C.c_uint32()
         _check(lib.rt_scene_frame_rect_info(self._h, C.byref(f), C.byref(b), C.byref(l)))
         return {"frames": f.value, "boxes": b.value, "loose": l.value}
+
+    def extend_info(self):
+        b, n, t = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _check(lib.rt_scene_extend_info(self._h, C.byref(b), C.byref(n), C.byref(t)))
+        return {"box_prims": b.value, "leaf_items": n.value, "whole_tree_threads": t.value}
 
     def device_bytes(self):
         return int(lib.rt_scene_device_bytes(self._h))

@@ -16,6 +16,7 @@
 #include <thread>
 #include <vector>
 
+#include "box_prims.h"
 #include "bvh_build.h"
 #include "device_scene.h"
 #include "kernels.h"
@@ -90,7 +91,7 @@ struct RtContext {
 struct RtScene {
     RtContext* ctx = nullptr;
     DScene d{};
-    DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm, fr_blob, oct_blob, shade_blob;
+    DevBuf<float4> nodes, prim_head, texels, rects, rect_nrm, boxes, fr_blob, oct_blob, shade_blob;
     DevBuf<uint2> prim_meta;
     DevBuf<uint32_t> order_to_prim;
     DevBuf<RtPrim> gen;
@@ -369,6 +370,31 @@ bool buildFrameRects(const RtPrim* prims, const std::vector<uint32_t>& order, bo
     return true;
 }
 
+// Leaf items of the tree: every primitive that is not a face of a box primitive, then one item per box (csrc/box_prims.h).
+struct TreeItems {
+    std::vector<BoxGroup> groups;
+    std::vector<uint32_t> ids;   // < n_prims: that input primitive; else box group ids[i] - n_prims
+    std::vector<Box3> boxes;
+};
+void planItems(const RtSceneDesc* desc, bool find_boxes, TreeItems& it) {
+    const uint32_t n = desc->n_prims;
+    std::vector<int> group_of;
+    if (find_boxes) it.groups = find_box_groups(desc->prims, n, group_of);
+    it.ids.clear(); it.boxes.clear();
+    it.ids.reserve(n); it.boxes.reserve(n);
+    for (uint32_t i = 0; i < n; ++i)
+        if (it.groups.empty() || group_of[i] < 0) { it.ids.push_back(i); it.boxes.push_back(primBox(desc, desc->prims[i])); }
+    for (uint32_t g = 0; g < it.groups.size(); ++g) {
+        Box3 b{{INFINITY, INFINITY, INFINITY}, {-INFINITY, -INFINITY, -INFINITY}};
+        for (int f = 0; f < 6; ++f) {
+            const Box3 c = primBox(desc, desc->prims[it.groups[g].face[f]]);
+            for (int a = 0; a < 3; ++a) { b.lo[a] = std::min(b.lo[a], c.lo[a]); b.hi[a] = std::max(b.hi[a], c.hi[a]); }
+        }
+        it.ids.push_back(n + g);
+        it.boxes.push_back(b);
+    }
+}
+
 template <class T>
 cudaError_t upload(DevBuf<T>& buf, const T* src, size_t n) {
     cudaError_t e = buf.ensure(n);
@@ -412,6 +438,8 @@ void rt_options_from_env(RtContextOptions* co, RtSceneOptions* so) {
         so->staged_nodes = sn < 0 ? 0u : (uint32_t)sn + 1u;
         if (envInt("RT_B200_RECT_FRAMES", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_FRAME_RECTS;
         if (envInt("RT_B200_RECT_BOXES", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_FRAME_BOXES;
+        if (envInt("RT_B200_BOX_PRIMS", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_BOX_PRIMS;
+        if (envInt("RT_B200_WHOLE_TREE", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_WHOLE_TREE;
         if (envInt("RT_B200_STAGE_PRIMS", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_STAGED_PRIMS;
         if (envInt("RT_B200_SMALL_SCENE", 0, 1, 1) == 0) so->flags |= RT_SCENE_NO_SMALL_LIST;
     }
@@ -497,16 +525,23 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     RT_CUDA(cudaSetDevice(ctx->device));
     const RtSceneOptions so = options ? *options : ctx->scene_defaults;
 
-    const uint32_t n = desc->n_prims;
-    std::vector<Box3> boxes(n);
-    for (uint32_t i = 0; i < n; ++i) boxes[i] = primBox(desc, desc->prims[i]);
+    const uint32_t n_in = desc->n_prims;
+    const bool small = n_in <= RT_SMALL_SCENE && !(so.flags & RT_SCENE_NO_SMALL_LIST);
+    // Large scenes build their tree on the GPU (lbvh.cu: LBVH, one primitive per leaf; the node array never leaves HBM): on
+    // 1 M spheres rt_scene_create takes 152 ms instead of 373 ms (16 host threads) and the tree renders within 2.4 % of the
+    // SAH one (r1v).  Smaller scenes keep the host SAH build, whose trees are 10-20 % faster to traverse (book-two).
+    const bool want_device = !small && (so.bvh_builder == RT_BVH_DEVICE_LBVH || (so.bvh_builder == RT_BVH_AUTO && n_in >= RT_DEVICE_BUILD_MIN_PRIMS));
+    // leaf items: the primitives, with the six faces of every axis-aligned box folded into one item (host-built trees only)
+    TreeItems items;
+    planItems(desc, !small && !want_device && !(so.flags & RT_SCENE_NO_BOX_PRIMS), items);
+    const std::vector<Box3>& boxes = items.boxes;
+    const uint32_t n = (uint32_t)items.ids.size();  // leaf items
     BvhOptions opt;
     if (so.bvh_max_leaf >= 1 && so.bvh_max_leaf <= 16) opt.max_leaf = so.bvh_max_leaf;
     opt.max_always = RT_MAX_ALWAYS;
     if (so.bvh_treelet_nodes >= 2) opt.treelet_nodes = so.bvh_treelet_nodes;
     opt.top_nodes = RT_TOP_STAGED_NODES;
     opt.threads = so.bvh_threads;
-    const bool small = n <= RT_SMALL_SCENE && !(so.flags & RT_SCENE_NO_SMALL_LIST);
     BvhResult bvh;
     LbvhResult lbvh;
     bool use_lbvh = false;
@@ -516,10 +551,6 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
         for (uint32_t i = 0; i < n; ++i) bvh.order[i] = i;
         std::stable_sort(bvh.order.begin(), bvh.order.end(), [&](uint32_t a, uint32_t b) { return desc->prims[a].order < desc->prims[b].order; });
     } else {
-        // Large scenes build their tree on the GPU (lbvh.cu: LBVH, one primitive per leaf; the node array never leaves HBM): on
-        // 1 M spheres rt_scene_create takes 152 ms instead of 373 ms (16 host threads) and the tree renders within 2.4 % of the
-        // SAH one (r1v).  Smaller scenes keep the host SAH build, whose trees are 10-20 % faster to traverse (book-two).
-        const bool want_device = so.bvh_builder == RT_BVH_DEVICE_LBVH || (so.bvh_builder == RT_BVH_AUTO && n >= RT_DEVICE_BUILD_MIN_PRIMS);
         BvhOptions dopt = opt;
         if (!so.bvh_max_leaf) dopt.max_leaf = 1;
         std::vector<uint32_t> always;
@@ -555,15 +586,42 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     } lbvh_guard{lbvh, use_lbvh};
     if (bvh.depth + 2 > (uint32_t)RT_STACK_DEPTH) return fail(RT_ERR_UNSUPPORTED, "BVH depth %u exceeds the traversal stack", bvh.depth);
 
-    // primitives in leaf order
-    std::vector<float4> head(n);
-    std::vector<uint2> meta(n);
+    // device primitives: the items in leaf order, then the six faces of every box item (never in a leaf: box_hit answers for them)
+    const uint32_t n_boxes = (uint32_t)items.groups.size(), n_dev = n + 6u * n_boxes;
+    std::vector<uint32_t> src(n_dev, RT_NO_PRIM);  // input primitive of device primitive i; RT_NO_PRIM: a box item
+    std::vector<float4> box_recs;
+    box_recs.reserve(2 * (size_t)n_boxes);
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t id = items.ids[bvh.order[i]];
+        if (id < n_in) { src[i] = id; continue; }
+        const BoxGroup& g = items.groups[id - n_in];
+        const uint32_t first = n + 6u * (uint32_t)(box_recs.size() / 2);
+        for (uint32_t f = 0; f < 6; ++f) src[first + f] = g.face[f];
+        float ff;
+        std::memcpy(&ff, &first, 4);
+        box_recs.push_back(make_float4(g.lo[0], g.lo[1], g.lo[2], ff));
+        box_recs.push_back(make_float4(g.hi[0], g.hi[1], g.hi[2], 0.0f));
+    }
+    std::vector<float4> head(n_dev);
+    std::vector<uint2> meta(n_dev);
     std::vector<RtPrim> gen;
     std::vector<float4> rects, rect_nrm;
     bool has_media = false, has_general = false;
     float always_k[RT_MAX_ALWAYS] = {0};
-    for (uint32_t i = 0; i < n; ++i) {
-        const RtPrim& p = desc->prims[bvh.order[i]];
+    uint32_t n_leaf_rects = 0, next_box = 0;
+    for (uint32_t i = 0; i < n_dev; ++i) {
+        if (i == n) n_leaf_rects = (uint32_t)(rects.size() / 4);
+        if (src[i] == RT_NO_PRIM) {  // a box item: its record index and the device-only kind
+            const uint32_t bi = next_box++, kind = RT_DPRIM_BOX;
+            float fx, fy;
+            std::memcpy(&fx, &bi, 4);
+            std::memcpy(&fy, &kind, 4);
+            head[i] = make_float4(fx, fy, 0.0f, -1.0f);
+            const RtPrim& f0 = desc->prims[items.groups[items.ids[bvh.order[i]] - n_in].face[0]];
+            meta[i] = make_uint2(f0.order, (uint32_t)f0.material);  // never read: hits carry the face
+            continue;
+        }
+        const RtPrim& p = desc->prims[src[i]];
         meta[i] = make_uint2(p.order, (uint32_t)p.material);
         if (p.kind == RT_PRIM_SPHERE && p.param[0] > 0.0f && translationOnly(p)) {
             head[i] = make_float4(p.world_from_local[3], p.world_from_local[7], p.world_from_local[11], p.param[0]);
@@ -592,6 +650,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
             has_general |= (p.kind != RT_PRIM_RECT);
         }
     }
+    if (n_dev == n) n_leaf_rects = (uint32_t)(rects.size() / 4);
     // materials with the solid colour inlined
     std::vector<DMaterial> mats(desc->n_materials);
     for (uint32_t i = 0; i < desc->n_materials; ++i) {
@@ -618,7 +677,8 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     if (e == cudaSuccess) e = upload(s->prim_head, head.data(), head.size());
     if (e == cudaSuccess) e = upload(s->prim_meta, meta.data(), meta.size());
     std::vector<uint32_t> order_to_prim;
-    for (uint32_t i = 0; i < n; ++i) {
+    for (uint32_t i = 0; i < n_dev; ++i) {
+        if (src[i] == RT_NO_PRIM) continue;  // a box item has no rank of its own
         if (meta[i].x >= order_to_prim.size()) order_to_prim.resize((size_t)meta[i].x + 1, RT_NO_PRIM);
         if (order_to_prim[meta[i].x] == RT_NO_PRIM) order_to_prim[meta[i].x] = i;
     }
@@ -632,6 +692,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     if (e == cudaSuccess) e = upload(s->gen, gen.data(), gen.size());
     if (e == cudaSuccess) e = upload(s->rects, rects.data(), rects.size());
     if (e == cudaSuccess) e = upload(s->rect_nrm, rect_nrm.data(), rect_nrm.size());
+    if (e == cudaSuccess) e = upload(s->boxes, box_recs.data(), box_recs.size());
     FrameRects fr;
     const bool use_fr = small && !(so.flags & RT_SCENE_NO_FRAME_RECTS) && rects.size() / 4 == n && buildFrameRects(desc->prims, bvh.order, !(so.flags & RT_SCENE_NO_FRAME_BOXES), fr);
     if (e == cudaSuccess && use_fr) e = upload(s->fr_blob, fr.blob.data(), fr.blob.size());
@@ -643,10 +704,10 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
         return fail(e == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, "scene upload failed: %s", cudaGetErrorString(e));
     }
     DScene& d = s->d;
-    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.rects = s->rects.p; d.rect_nrm = s->rect_nrm.p;
+    d.nodes = s->nodes.p; d.prim_head = s->prim_head.p; d.prim_meta = s->prim_meta.p; d.gen = s->gen.p; d.rects = s->rects.p; d.rect_nrm = s->rect_nrm.p; d.boxes = s->boxes.p;
     d.mats = s->mats.p; d.texs = s->texs.p; d.texels = s->texels.p;
     d.order_to_prim = s->order_to_prim.p; d.n_orders = (uint32_t)order_to_prim.size();
-    d.n_nodes = use_lbvh ? lbvh.n_nodes : (uint32_t)bvh.nodes.size(); d.n_prims = n; d.n_always = bvh.n_always; d.n_gen = (uint32_t)gen.size();
+    d.n_nodes = use_lbvh ? lbvh.n_nodes : (uint32_t)bvh.nodes.size(); d.n_prims = n_dev; d.n_leaf_prims = n; d.n_leaf_rects = n_leaf_rects; d.n_boxes = n_boxes; d.n_always = bvh.n_always; d.n_gen = (uint32_t)gen.size();
     d.n_mats = desc->n_materials; d.n_texs = desc->n_textures;
     d.root_is_leaf = bvh.root_is_leaf ? 1u : 0u;
     // whole tree in shared memory when it fits; otherwise only the top levels (every ray walks them) so that
@@ -659,10 +720,10 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
     d.has_general = has_general ? 1u : 0u;
     d.n_rects = (uint32_t)(rects.size() / 4);
     d.n_small = small ? n : 0u;
-    d.n_staged_prims = (n <= RT_MAX_STAGED_PRIMS && d.n_rects <= RT_MAX_STAGED_RECTS) ? n : 0u;
+    d.n_staged_prims = (n_dev <= RT_MAX_STAGED_PRIMS && d.n_rects <= RT_MAX_STAGED_RECTS) ? n_dev : 0u;
     if (so.flags & RT_SCENE_NO_STAGED_PRIMS) d.n_staged_prims = 0u;
     std::memcpy(d.always_k, always_k, sizeof(always_k));
-    d.small_all_rects = (small && d.n_staged_prims == n && d.n_rects == n) ? 1u : 0u;
+    d.small_all_rects = (small && d.n_staged_prims == n_dev && d.n_rects == n_dev) ? 1u : 0u;
     s->staged_bytes = (size_t)d.n_staged_nodes * 32 + (size_t)d.n_staged_prims * 16 + (d.n_staged_prims ? (size_t)d.n_rects * 64 : 0);
     if (use_fr) {
         d.fr_blob = s->fr_blob.p; d.fr_n = fr.n; d.fr_frames = fr.frames; d.fr_identity = fr.identity;
@@ -685,7 +746,10 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
         d.shade_blob = s->shade_blob.p; d.shade_blob4 = (uint32_t)blob.size();
         s->shade_bytes = blob.size() * sizeof(float4);
     }
-    const bool whole_tree = e == cudaSuccess && d.n_nodes > 0u && d.n_staged_nodes >= d.n_nodes && d.n_staged_prims >= d.n_prims && !d.n_small && !d.root_is_leaf;
+    // whole tree + leaf heads + leaf rectangles + boxes in shared memory (k_extend<., true>) when that fits one block — two blocks of 512
+    // threads per SM up to 100 KB, one of 1024 threads up to 224 KB (kernels.cu)
+    const bool whole_tree = e == cudaSuccess && d.n_nodes > 0u && !d.n_small && !d.root_is_leaf && !(so.flags & RT_SCENE_NO_WHOLE_TREE) &&
+                            !(so.flags & RT_SCENE_NO_STAGED_PRIMS) && extend_all_smem_fits(d);
     if (whole_tree) {
         // octant-ready pair records (intersect.cuh node_step_oct): per sibling pair 7 float4 — per axis (l.lo, l.hi, r.lo, r.hi) and its
         // mirror (l.hi, l.lo, r.hi, r.lo), then (lref, lcnt, rref, rcnt) — laid out once here instead of by every block of every launch
@@ -697,7 +761,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
             nodes4 = host_nodes.data();
         }
         const uint32_t n_pairs = (d.n_nodes + 1u) / 2u;
-        std::vector<float4> blob((size_t)7 * n_pairs + n + 4 * (size_t)d.n_rects, make_float4(0, 0, 0, 0));
+        std::vector<float4> blob((size_t)7 * n_pairs + n + 4 * (size_t)n_leaf_rects + box_recs.size(), make_float4(0, 0, 0, 0));
         const float4 zero = make_float4(0, 0, 0, 0);
         for (uint32_t j = 0; j < n_pairs && e == cudaSuccess; ++j) {
             const bool has_right = 2u * j + 1u < d.n_nodes;
@@ -709,7 +773,8 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
             o[6] = make_float4(ll.w, lh.w, rl.w, rh.w);
         }
         std::memcpy(blob.data() + 7 * (size_t)n_pairs, head.data(), (size_t)n * sizeof(float4));
-        if (d.n_rects) std::memcpy(blob.data() + 7 * (size_t)n_pairs + n, rects.data(), rects.size() * sizeof(float4));
+        if (n_leaf_rects) std::memcpy(blob.data() + 7 * (size_t)n_pairs + n, rects.data(), 4 * (size_t)n_leaf_rects * sizeof(float4));
+        if (n_boxes) std::memcpy(blob.data() + 7 * (size_t)n_pairs + n + 4 * (size_t)n_leaf_rects, box_recs.data(), box_recs.size() * sizeof(float4));
         if (e == cudaSuccess) e = upload(s->oct_blob, blob.data(), blob.size());
         d.oct_blob = s->oct_blob.p; d.oct_blob4 = (uint32_t)blob.size();
     }
@@ -729,7 +794,7 @@ int rt_scene_create_ex(RtContext* ctx, const RtSceneDesc* desc, const RtSceneOpt
 void rt_scene_destroy(RtScene* s) {
     if (!s) return;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->order_to_prim.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->fr_blob.release(); s->oct_blob.release(); s->shade_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
+    s->nodes.release(); s->prim_head.release(); s->prim_meta.release(); s->order_to_prim.release(); s->gen.release(); s->rects.release(); s->rect_nrm.release(); s->boxes.release(); s->fr_blob.release(); s->oct_blob.release(); s->shade_blob.release(); s->mats.release(); s->texs.release(); s->texels.release();
     delete s;
 }
 
@@ -750,10 +815,53 @@ int rt_scene_frame_rect_info(const RtScene* s, uint32_t* n_frames, uint32_t* n_b
     return RT_OK;
 }
 
+int rt_scene_extend_info(const RtScene* s, uint32_t* n_box_prims, uint32_t* n_leaf_items, uint32_t* whole_tree_threads) {
+    if (!s) return fail(RT_ERR_INVALID, "scene is null");
+    if (n_box_prims) *n_box_prims = s->d.n_boxes;
+    if (n_leaf_items) *n_leaf_items = s->d.n_leaf_prims;
+    if (whole_tree_threads) *whole_tree_threads = s->launch.all_staged ? (uint32_t)s->launch.all_block : 0u;
+    return RT_OK;
+}
+
+int rt_scene_plan(const RtSceneDesc* desc, const RtSceneOptions* options, RtScenePlan* out) {
+    if (!out) return fail(RT_ERR_INVALID, "out is null");
+    if (int rc = validateDesc(desc)) return rc;
+    std::memset(out, 0, sizeof(*out));
+    RtSceneOptions so{};
+    if (options) so = *options;
+    const uint32_t n_in = desc->n_prims;
+    const bool small = n_in <= RT_SMALL_SCENE && !(so.flags & RT_SCENE_NO_SMALL_LIST);
+    const bool want_device = !small && (so.bvh_builder == RT_BVH_DEVICE_LBVH || (so.bvh_builder == RT_BVH_AUTO && n_in >= RT_DEVICE_BUILD_MIN_PRIMS));
+    TreeItems items;
+    planItems(desc, !small && !want_device && !(so.flags & RT_SCENE_NO_BOX_PRIMS), items);
+    out->n_box_prims = (uint32_t)items.groups.size();
+    out->n_leaf_items = (uint32_t)items.ids.size();
+    if (small || want_device) return RT_OK;
+    BvhOptions opt;
+    if (so.bvh_max_leaf >= 1 && so.bvh_max_leaf <= 16) opt.max_leaf = so.bvh_max_leaf;
+    opt.max_always = RT_MAX_ALWAYS;
+    if (so.bvh_treelet_nodes >= 2) opt.treelet_nodes = so.bvh_treelet_nodes;
+    opt.top_nodes = RT_TOP_STAGED_NODES;
+    opt.threads = so.bvh_threads;
+    const BvhResult bvh = build_bvh(items.boxes, opt);
+    out->n_nodes = (uint32_t)bvh.nodes.size();
+    out->bvh_depth = bvh.depth;
+    out->n_always = bvh.n_always;
+    DScene d{};
+    d.n_nodes = out->n_nodes; d.bvh_depth = bvh.depth; d.n_leaf_prims = out->n_leaf_items; d.n_boxes = out->n_box_prims;
+    for (uint32_t id : items.ids) d.n_leaf_rects += (id < n_in && desc->prims[id].kind == RT_PRIM_RECT) ? 1u : 0u;
+    if (!bvh.root_is_leaf && d.n_nodes > 0u && !(so.flags & (RT_SCENE_NO_WHOLE_TREE | RT_SCENE_NO_STAGED_PRIMS)) && extend_all_smem_fits(d)) {
+        const bool half = extend_all_smem_bytes(d, RT_EXTEND_ALL_BLOCK) <= 100u * 1024u;
+        out->whole_tree_threads = half ? RT_EXTEND_ALL_BLOCK : RT_EXTEND_ALL_BIG_BLOCK;
+        out->whole_tree_smem = extend_all_smem_bytes(d, out->whole_tree_threads);
+    }
+    return RT_OK;
+}
+
 uint64_t rt_scene_device_bytes(const RtScene* s) {
     if (!s) return 0;
     return (uint64_t)s->nodes.n * sizeof(float4) + (uint64_t)s->prim_head.n * sizeof(float4) + (uint64_t)s->prim_meta.n * sizeof(uint2) +
-           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)s->order_to_prim.n * sizeof(uint32_t) + (uint64_t)(s->rects.n + s->rect_nrm.n) * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
+           (uint64_t)s->gen.n * sizeof(RtPrim) + (uint64_t)s->order_to_prim.n * sizeof(uint32_t) + (uint64_t)(s->rects.n + s->rect_nrm.n + s->boxes.n) * sizeof(float4) + (uint64_t)s->mats.n * sizeof(DMaterial) + (uint64_t)s->texs.n * sizeof(RtTexture) +
            (uint64_t)s->texels.n * sizeof(float4);
 }
 

@@ -49,6 +49,7 @@ constexpr uint32_t RT_MAX_STAGED_RECTS = 256;   // compact rectangle records (16
 constexpr uint32_t RT_SMALL_SCENE = 32;         // at most this many primitives: linear list instead of a BVH
 constexpr uint32_t RT_MAX_ALWAYS = 8;           // always-tested list (sky / ground / fog)
 constexpr uint32_t RT_DEVICE_BUILD_MIN_PRIMS = 65536;  // from this many primitives the BVH is built on the GPU (lbvh.cu)
+constexpr uint32_t RT_DPRIM_BOX = 16;            // device-only primitive kind (prim_head.y): a box of six face rectangles, record index in prim_head.x
 constexpr uint32_t RT_MAX_FRAMES = 8;           // frame-rect list: distinct orthonormal frames the rectangles of a small scene are aligned to
 
 struct DMaterial {       // 32 B, read as two float4
@@ -66,12 +67,14 @@ struct DScene {
     const float4* rect_nrm;    // per rectangle: world-space normal M (0,0,1) (forward matrix, not renormalised: SURVEY A.5)
     const RtPrim* gen;         // general records (non translation-only-sphere primitives), then the boundary surfaces of the RT_PRIM_MEDIUM
                                // records (RtSceneDesc.boundary_prims); a medium record's `aux` is the distance IN RECORDS to its first surface
+    const float4* boxes;       // 2 float4 per box primitive (csrc/box_prims.h): (lo.xyz, first face primitive) (hi.xyz, 0); the six faces are the
+                               // device primitives first .. first + 5 in the order x-, x+, y-, y+, z-, z+ — behind the leaf primitives, never in a leaf
     const DMaterial* mats;
     const RtTexture* texs;
     const float4* texels;
     // Blobs staged into shared memory by ONE bulk copy each (csrc/bulk_copy.cuh), laid out by rt_scene_create exactly as the kernels read them:
     //   oct_blob   (k_extend<., true>; null when the tree is not staged whole): [octant-ready pair records, 7 float4 per sibling pair
-    //              (intersect.cuh node_step_oct)][prim_head n_prims][rects 4 n_rects]
+    //              (intersect.cuh node_step_oct)][prim_head n_leaf_prims][rects 4 n_leaf_rects][boxes 2 n_boxes]
     //   shade_blob (k_shade): [materials 2 float4 x min(n_mats, RT_MAX_STAGED_MATS)][prim_head n_staged_prims][rect_nrm][prim_meta uint2, padded to 16 B]
     const float4* oct_blob;
     const float4* shade_blob;
@@ -86,6 +89,9 @@ struct DScene {
     uint32_t has_general;      // some primitive is reached through its general 128-byte record (rotated / scaled / negative-radius sphere, medium);
                                // rectangles own a general record too but are tested through `rects` / `rect_nrm` and never read it
     uint32_t n_rects;
+    uint32_t n_leaf_prims;     // primitives the tree (or the list) references: [0, n_leaf_prims); the faces of the box primitives follow
+    uint32_t n_leaf_rects;     // rectangles among them: their compact records come first in `rects`
+    uint32_t n_boxes;
     uint32_t n_staged_prims;   // n_prims when heads (and all rects) are staged in shared memory, else 0
     uint32_t n_small;          // > 0: no tree, test primitives [0, n_small) in order
     uint32_t small_all_rects;  // n_small > 0, every primitive is a rectangle and the records are staged: specialised loop

@@ -329,6 +329,7 @@ struct Staged {
     uint32_t nodes;
     uint32_t heads;
     uint32_t rects;
+    uint32_t boxes;  // (ALL only; otherwise the box records are read from global memory)
     uint32_t stack;  // this thread's column of the shared-memory traversal stack: entry k at stack + k * 4 * blockDim.x
 };
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
@@ -348,9 +349,33 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile(
 // GEN = some primitive of the scene is reached through its general 128-byte record (S.has_general: rotated / scaled spheres, media).  Scenes without any — book-one,
 // cornell-box, the sphere cloud — run kernels from which the out-of-line general path is compiled away: its mere presence (call ABI,
 // argument marshalling) costs registers in the traversal loop (k_extend<., true>: 24 bytes of spills, -3 %; k_shade: -7 to -11 %).
+// Box primitive (csrc/box_prims.h): the closest hit among the six face rectangles of an axis-aligned box, each a Rectangle::hit
+// (src/geometry.rs:152-181: its own plane, t >= 1e-6) whose extents are the whole face.  The line crosses the box surface at t_en and
+// t_ex; the entry crossing answers unless it lies behind the origin or on the ray's own face, then the exit crossing.  t is
+// (plane - o_k) / d_k — the difference first, so a ray that starts near a plane does not lose its t to cancellation.
+__device__ __forceinline__ float box_hit(const RayCtx& R, const float4 L, const float4 H, uint32_t self_prim, uint32_t& id) {
+    const float x0 = (L.x - R.o.x) * R.inv.x, x1 = (H.x - R.o.x) * R.inv.x;
+    const float y0 = (L.y - R.o.y) * R.inv.y, y1 = (H.y - R.o.y) * R.inv.y;
+    const float z0 = (L.z - R.o.z) * R.inv.z, z1 = (H.z - R.o.z) * R.inv.z;
+    // fminf / fmaxf drop a NaN operand (0 * inf: origin on a plane of a zero direction component): that axis then does not constrain
+    const float nx = fminf(x0, x1), ny = fminf(y0, y1), nz = fminf(z0, z1);
+    const float fx = fmaxf(x0, x1), fy = fmaxf(y0, y1), fz = fmaxf(z0, z1);
+    const float t_en = fmaxf(fmaxf(nx, ny), nz), t_ex = fminf(fminf(fx, fy), fz);
+    if (!(t_en <= t_ex)) return CUDART_INF_F;  // (also NaN) the line misses the box: it crosses none of the faces inside their bounds
+    const uint32_t ke = (nx == t_en) ? 0u : ((ny == t_en) ? 1u : 2u), kx = (fx == t_ex) ? 0u : ((fy == t_ex) ? 1u : 2u);
+    const float de = ke == 0u ? R.d.x : (ke == 1u ? R.d.y : R.d.z), dx = kx == 0u ? R.d.x : (kx == 1u ? R.d.y : R.d.z);
+    const uint32_t first = __float_as_uint(L.w);
+    const uint32_t id_en = first + 2u * ke + (de > 0.0f ? 0u : 1u), id_ex = first + 2u * kx + (dx > 0.0f ? 1u : 0u);
+    if (t_en >= RT_T_EPS && id_en != self_prim) { id = id_en; return t_en; }
+    if (t_ex >= RT_T_EPS && t_ex < CUDART_INF_F && id_ex != self_prim) { id = id_ex; return t_ex; }
+    return CUDART_INF_F;
+}
+
+// `id` = the device primitive the returned t belongs to: i itself, or the crossed face of a box primitive.
 template <bool BIG, bool ALL = false, bool GEN = true>
-__device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uint32_t i, const RayCtx& R, uint32_t self_prim, const MediumKey& key) {
-    RT_ASSERT(i < S.n_prims);
+__device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uint32_t i, const RayCtx& R, uint32_t self_prim, const MediumKey& key, uint32_t& id) {
+    RT_ASSERT(i < S.n_leaf_prims);
+    id = i;
     const bool staged = ALL || i < S.n_staged_prims;
     float4 h;
     if (staged) h = lds128(sm.heads + 16u * i);
@@ -362,7 +387,7 @@ __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uin
     if (__float_as_uint(h.y) == (uint32_t)RT_PRIM_RECT) {
         if (i == self_prim) return CUDART_INF_F;  // a plane cannot re-hit itself
         const uint32_t ri = __float_as_uint(h.z);
-        RT_ASSERT(ri < S.n_rects);
+        RT_ASSERT(ri < S.n_leaf_rects);
         if (staged) {
             const uint32_t q = sm.rects + 64u * ri;
             return rect_hit(R, lds128(q), lds128(q + 16u), lds128(q + 32u), lds128(q + 48u));
@@ -370,11 +395,17 @@ __device__ __forceinline__ float prim_hit(const DScene& S, const Staged& sm, uin
         const float4* __restrict__ q = S.rects + 4u * (size_t)ri;
         return rect_hit(R, __ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
     }
+    if (__float_as_uint(h.y) == RT_DPRIM_BOX) {
+        const uint32_t bi = __float_as_uint(h.x);
+        RT_ASSERT(bi < S.n_boxes);
+        if (ALL) return box_hit(R, lds128(sm.boxes + 32u * bi), lds128(sm.boxes + 32u * bi + 16u), self_prim, id);
+        const float4* __restrict__ q = S.boxes + 2u * (size_t)bi;
+        return box_hit(R, __ldg(q), __ldg(q + 1), self_prim, id);
+    }
     RT_ASSERT(GEN && __float_as_uint(h.x) < S.n_gen);
     if (!GEN) return CUDART_INF_F;  // unreachable: a scene rendered by a GEN = false kernel has no such record
     return general_hit(&S.gen[__float_as_uint(h.x)], R.o, R.d, i == self_prim, key);
 }
-
 // Closest-hit update with the reference's tie rule (strict <, the DFS-earlier leaf wins an exact tie).
 template <bool ORDERED>
 __device__ __forceinline__ void take(const DScene& S, uint32_t i, float t, ClosestHit& best) {
@@ -383,6 +414,14 @@ __device__ __forceinline__ void take(const DScene& S, uint32_t i, float t, Close
     if (t == best.t && t < CUDART_INF_F) {
         if (__ldg(&S.prim_meta[i]).x < __ldg(&S.prim_meta[best.prim]).x) best.prim = i;
     }
+}
+
+// test primitive i and keep the closer hit
+template <bool BIG, bool ORDERED, bool ALL = false, bool GEN = true>
+__device__ __forceinline__ void test_prim(const DScene& S, const Staged& sm, uint32_t i, const RayCtx& R, uint32_t self_prim, const MediumKey& key, ClosestHit& best) {
+    uint32_t id;
+    const float t = prim_hit<BIG, ALL, GEN>(S, sm, i, R, self_prim, key, id);
+    take<ORDERED>(S, id, t, best);
 }
 
 // Slab test against [0, tmax]; returns entry distance or +inf.  fminf/fmaxf drop NaNs (0 * inf when the
@@ -576,8 +615,8 @@ __device__ __forceinline__ uint32_t node_step_oct(const Staged& sm, const OctBas
 template <bool COUNT, bool ALL = false, bool GEN = true>
 __device__ __forceinline__ void leaf_tests(const DScene& S, const Staged& sm, const RayCtx& R, uint32_t self_prim, const MediumKey& key, ClosestHit& best,
                                            uint32_t begin, uint32_t end, TraversalWork* work) {
-    RT_ASSERT(begin <= end && end <= S.n_prims);
-    for (uint32_t i = begin; i < end; ++i) take<false>(S, i, prim_hit<false, ALL, GEN>(S, sm, i, R, self_prim, key), best);
+    RT_ASSERT(begin <= end && end <= S.n_leaf_prims);
+    for (uint32_t i = begin; i < end; ++i) test_prim<false, false, ALL, GEN>(S, sm, i, R, self_prim, key, best);
     if (COUNT) work->prim_tests += end - begin;
 }
 
@@ -607,11 +646,11 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
     }
     if (S.n_small) {
         // small scene: the whole primitive list in DFS order, warp-uniform (geometry.rs:76-116)
-        for (uint32_t i = 0; i < S.n_small; ++i) take<true>(S, i, prim_hit<false, false, GEN>(S, sm, i, R, self_prim, key), best);
+        for (uint32_t i = 0; i < S.n_small; ++i) test_prim<false, true, false, GEN>(S, sm, i, R, self_prim, key, best);
         if (COUNT) work->prim_tests += S.n_small;
         return best;
     }
-    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true, ALL, GEN>(S, sm, i, R, self_prim, key), best);
+    for (uint32_t i = 0; i < S.n_always; ++i) test_prim<true, false, ALL, GEN>(S, sm, i, R, self_prim, key, best);
     if (COUNT) work->prim_tests += S.n_always;
     if (S.n_nodes == 0) return best;
 
@@ -620,7 +659,7 @@ __device__ __forceinline__ ClosestHit closest_hit(const DScene& S, const Staged&
         if (COUNT) work->box_tests += 1;
         if (slab(lo, hi, R, best.t) < CUDART_INF_F) {
             const uint32_t first = __float_as_uint(lo.w), cnt = __float_as_uint(hi.w);
-            for (uint32_t i = first; i < first + cnt; ++i) take<false>(S, i, prim_hit<false, false, GEN>(S, sm, i, R, self_prim, key), best);
+            for (uint32_t i = first; i < first + cnt; ++i) test_prim<false, false, false, GEN>(S, sm, i, R, self_prim, key, best);
             if (COUNT) work->prim_tests += cnt;
         }
         return best;

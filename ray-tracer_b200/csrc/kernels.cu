@@ -162,27 +162,29 @@ __device__ __forceinline__ Staged stage_scene(const DScene& S, float4* smem_base
     const uint32_t scene = base + RT_SMEM_STACK * blockDim.x * 4u;
     bulk_stage(mbar, BulkPart{S.nodes, scene, 16u * n_node4}, BulkPart{S.prim_head, scene + 16u * n_node4, 16u * n_head4},
                BulkPart{S.rects, scene + 16u * (n_node4 + n_head4), 16u * n_rect4});
-    return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
+    return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), 0u, base + 4u * threadIdx.x};
 }
 
 // Staging of the all-in-shared-memory variant: [stack (depth + 2) x blockDim words][pairs, 7 float4 each (intersect.cuh: octant-ready
-// records)][heads n_prims][rects 4*n_rects] — the blob is laid out once by rt_scene_create (S.oct_blob), so this is ONE bulk copy.
+// records)][heads n_leaf_prims][rects 4*n_leaf_rects][boxes 2*n_boxes] — the blob is laid out once by rt_scene_create (S.oct_blob), so this
+// is ONE bulk copy.
 __device__ __forceinline__ Staged stage_scene_oct(const DScene& S, float4* smem_base, uint32_t mbar) {
     const uint32_t stack_words = (S.bvh_depth + 2u) * blockDim.x;
-    const uint32_t n_pairs = (S.n_nodes + 1u) / 2u, n_node4 = 7u * n_pairs, n_head4 = S.n_prims;
+    const uint32_t n_pairs = (S.n_nodes + 1u) / 2u, n_node4 = 7u * n_pairs, n_head4 = S.n_leaf_prims, n_rect4 = 4u * S.n_leaf_rects;
     const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_base);
     const uint32_t scene = base + stack_words * 4u;
     bulk_stage(mbar, BulkPart{S.oct_blob, scene, 16u * S.oct_blob4});
-    return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), base + 4u * threadIdx.x};
+    return Staged{scene, scene + 16u * n_node4, scene + 16u * (n_node4 + n_head4), scene + 16u * (n_node4 + n_head4 + n_rect4), base + 4u * threadIdx.x};
 }
-size_t extend_all_smem_bytes(const DScene& S) {
-    return (size_t)(S.bvh_depth + 2u) * RT_EXTEND_ALL_BLOCK * 4u + (size_t)RT_OCT_PAIR_BYTES * ((S.n_nodes + 1u) / 2u) + 16u * (size_t)S.n_prims + 64u * (size_t)S.n_rects;
+size_t extend_all_smem_bytes(const DScene& S, uint32_t block) {
+    return (size_t)(S.bvh_depth + 2u) * block * 4u + (size_t)RT_OCT_PAIR_BYTES * ((S.n_nodes + 1u) / 2u) + 16u * (size_t)S.n_leaf_prims + 64u * (size_t)S.n_leaf_rects +
+           32u * (size_t)S.n_boxes;
 }
 
 // ALL: the whole tree and every primitive head are in shared memory (book-one: 836 nodes, 487 heads) — the per-access
 // "staged or global" range checks compile away.
 template <bool COUNT, bool ALL, bool GEN>
-__global__ void __launch_bounds__(ALL ? RT_EXTEND_ALL_BLOCK : RT_EXTEND_BLOCK, ALL ? RT_EXTEND_ALL_MIN_BLOCKS : RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
+__global__ void __launch_bounds__(ALL ? RT_EXTEND_ALL_BIG_BLOCK : RT_EXTEND_BLOCK, ALL ? 1 : RT_EXTEND_MIN_BLOCKS) k_extend(const DScene S, const RayQueue q, float2* __restrict__ hits, WaveCounters* __restrict__ wc,
                                                           uint32_t k, uint32_t seed_lo, uint32_t seed_hi) {
     extern __shared__ float4 smem4[];
     __shared__ __align__(8) uint64_t s_mbar;
@@ -348,7 +350,7 @@ __global__ void __launch_bounds__(RT_EXTEND_BLOCK, RT_BVH_MIN_BLOCKS) k_extend_b
                     R = make_ray(f3(ra.x, ra.y, ra.z), f3(rb.x, rb.y, rb.z));
                     best.t = CUDART_INF_F;
                     best.prim = RT_NO_PRIM;
-                    for (uint32_t i = 0; i < S.n_always; ++i) take<false>(S, i, prim_hit<true, false, GEN>(S, sm, i, R, self_prim, key), best);
+                    for (uint32_t i = 0; i < S.n_always; ++i) test_prim<true, false, false, GEN>(S, sm, i, R, self_prim, key, best);
                     if (COUNT) work.prim_tests += S.n_always;
                     sp = 0;
                     pair = root_pair;
@@ -849,7 +851,11 @@ cudaError_t kernels_num_sms(int device, int* sms) {
     return cudaSuccess;
 }
 
+bool extend_all_smem_fits(const DScene& S) {
+    return extend_all_smem_bytes(S, RT_EXTEND_ALL_BLOCK) <= 100u * 1024u || extend_all_smem_bytes(S, RT_EXTEND_ALL_BIG_BLOCK) <= 224u * 1024u;
+}
 constexpr size_t RT_EXTEND_ALL_MAX_SMEM = 100u * 1024u;
+constexpr size_t RT_EXTEND_ALL_BIG_MAX_SMEM = 224u * 1024u;  // of the 227 KB a block may own (the kernel adds 16 bytes of static shared memory)
 
 // The calling thread must have `device` current.
 cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_bytes, size_t shade_bytes, size_t fr_bytes, SceneLaunch& L) {
@@ -890,14 +896,19 @@ cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_by
     RT_TRY(occupancy(L.shade_blocks, shade1_k, RT_SHADE_BLOCK, shade_bytes));
     RT_TRY(occupancy(L.shade2_blocks, shade2_k, RT_SHADE_BLOCK, shade_bytes));
     // whole tree + heads in shared memory in the octant-ready layout, as long as that keeps the occupancy of the general kernel
-    L.all_staged = S.oct_blob != nullptr && S.n_nodes > 0u && S.n_staged_nodes >= S.n_nodes && S.n_staged_prims >= S.n_prims && !S.n_small && !S.root_is_leaf;
+    L.all_staged = S.oct_blob != nullptr && S.n_nodes > 0u && !S.n_small && !S.root_is_leaf;
     if (L.all_staged) {
-        L.all_smem = extend_all_smem_bytes(S);
-        if (L.all_smem > RT_EXTEND_ALL_MAX_SMEM) L.all_staged = false;
+        L.all_block = RT_EXTEND_ALL_BLOCK;
+        L.all_smem = extend_all_smem_bytes(S, RT_EXTEND_ALL_BLOCK);
+        if (L.all_smem > RT_EXTEND_ALL_MAX_SMEM) {  // more than half an SM: one block of twice the threads
+            L.all_block = RT_EXTEND_ALL_BIG_BLOCK;
+            L.all_smem = extend_all_smem_bytes(S, RT_EXTEND_ALL_BIG_BLOCK);
+        }
+        if (L.all_smem > RT_EXTEND_ALL_BIG_MAX_SMEM) L.all_staged = false;
         else {
             RT_TRY(grant(d, SLOT_EXTEND_ALL + gen, all_k, L.all_smem));
-            RT_TRY(occupancy(L.all_blocks, all_k, RT_EXTEND_ALL_BLOCK, L.all_smem));
-            if (L.all_blocks * RT_EXTEND_ALL_BLOCK < L.extend_blocks * RT_EXTEND_BLOCK) L.all_staged = false;
+            RT_TRY(occupancy(L.all_blocks, all_k, L.all_block, L.all_smem));
+            if (L.all_blocks * L.all_block < L.extend_blocks * RT_EXTEND_BLOCK) L.all_staged = false;
         }
     }
 #undef RT_TRY
@@ -939,9 +950,9 @@ void launch_extend(const Launch& L, const DScene& S, const RayQueue& q, float2* 
     const int grid = sms * sl.extend_blocks;
     if (count_work) k_extend<true, false, true><<<grid, RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
     else if (sl.all_staged) {
-        const int g = fit_grid(L, sms * sl.all_blocks, RT_EXTEND_ALL_BLOCK);
-        if (sl.gen) k_extend<false, true, true><<<g, RT_EXTEND_ALL_BLOCK, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
-        else k_extend<false, true, false><<<g, RT_EXTEND_ALL_BLOCK, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+        const int g = fit_grid(L, sms * sl.all_blocks, sl.all_block);
+        if (sl.gen) k_extend<false, true, true><<<g, sl.all_block, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
+        else k_extend<false, true, false><<<g, sl.all_block, sl.all_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);
     } else {
         const int g = fit_grid(L, grid, RT_EXTEND_BLOCK);
         if (sl.gen) k_extend<false, false, true><<<g, RT_EXTEND_BLOCK, sl.extend_smem, L.st>>>(S, q, hits, wc, k, seed_lo, seed_hi);

@@ -11,9 +11,10 @@
 #ifndef RT_EXTEND_ALL_BLOCK
 #define RT_EXTEND_ALL_BLOCK 512
 #endif
-#ifndef RT_EXTEND_ALL_MIN_BLOCKS
-#define RT_EXTEND_ALL_MIN_BLOCKS 2
-#endif
+// ... and ONE block of 1024 threads (the same 32 warps, one copy of the tables) for scenes whose tables need more than half an SM's
+// shared memory (book-two with its ground blocks as box primitives: ~1 800 nodes, 1 400 heads, 400 boxes).  Both forms run the same
+// kernel: __launch_bounds__(1024, 1) and (512, 2) cap it at the same 64 registers.
+#define RT_EXTEND_ALL_BIG_BLOCK 1024
 #endif
 // k_shade: 8 blocks of 128 threads per SM.  The two barriers per round wait for the slowest of a block's warps (divergent material
 // code) and for the slot-allocation atomics: 4 warps per barrier instead of 8 is +3.5 % (book-one) to +5 % (cornell) on the kernel,
@@ -55,6 +56,9 @@ constexpr uint32_t RT_WORK_UNKNOWN = 0xFFFFFFFFu;
 #ifndef RT_TAIL_MODE
 #define RT_TAIL_MODE 1  // 0: keep launching k_generate while the render drains (A/B of the tail iterations)
 #endif
+// shared memory of k_extend<., true> at `block` threads; whether the scene's tables fit one of its two block forms
+size_t extend_all_smem_bytes(const DScene& S, uint32_t block);
+bool extend_all_smem_fits(const DScene& S);
 struct LaunchOptions {
     int persistent = 2;   // extend in its persistent lane-refilling form: 0 never, 1 always (where a tree exists), 2 from RT_PERSISTENT_MIN_NODES nodes
     int shade_rays2 = 1;  // two rays per thread per barrier round in k_shade on small all-rectangle scenes
@@ -66,6 +70,7 @@ struct LaunchOptions {
 struct SceneLaunch {
     int device = -1, num_sms = 0;
     size_t scene_smem = 0, extend_smem = 0, trace_smem = 0, bvh_smem = 0, shade_smem = 0, rects_smem = 0, all_smem = 0;
+    int all_block = RT_EXTEND_ALL_BLOCK;  // threads per block of k_extend<., true>: 512 (two blocks per SM) or RT_EXTEND_ALL_BIG_BLOCK (one)
     int extend_blocks = 1, trace_blocks = 1, bvh_blocks = 1, shade_blocks = 1, shade2_blocks = 1, rects_blocks = 1, all_blocks = 1;
     bool gen = true;          // the scene has general 128-byte records: GEN = true instantiations of extend / shade
     bool all_staged = false;  // k_extend<., true>: whole tree + heads in shared memory, octant-ready records

@@ -210,6 +210,18 @@ pub mod ffi {
     } // 32 B
 
     #[repr(C)]
+    #[derive(Clone, Copy, Debug, Default)]
+    pub struct RtScenePlan {
+        pub n_box_prims: u32,
+        pub n_leaf_items: u32,
+        pub n_nodes: u32,
+        pub bvh_depth: u32,
+        pub n_always: u32,
+        pub whole_tree_threads: u32,
+        pub whole_tree_smem: u64,
+    } // 32 B
+
+    #[repr(C)]
     pub struct RtContext {
         _private: [u8; 0],
     }
@@ -255,6 +267,8 @@ pub mod ffi {
                                out_sumsq_rgb: *mut f32, stats: *mut RtStats) -> c_int;
         pub fn rt_scene_bvh_info(scene: *const RtScene, n_nodes: *mut u32, n_always: *mut u32, max_depth: *mut u32) -> c_int;
         pub fn rt_scene_frame_rect_info(scene: *const RtScene, n_frames: *mut u32, n_boxes: *mut u32, n_loose: *mut u32) -> c_int;
+        pub fn rt_scene_extend_info(scene: *const RtScene, n_box_prims: *mut u32, n_leaf_items: *mut u32, whole_tree_threads: *mut u32) -> c_int;
+        pub fn rt_scene_plan(desc: *const RtSceneDesc, options: *const RtSceneOptions, out: *mut RtScenePlan) -> c_int;
         pub fn rt_scene_device_bytes(scene: *const RtScene) -> u64;
         pub fn rt_last_error() -> *const c_char;
         pub fn rt_abi_version() -> u32;

@@ -922,3 +922,107 @@ def test_every_kernel_form_under_the_checked_library(rt):
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "ok (36, 64, 3)" in res.stdout or "ok" in res.stdout.splitlines()[-1]
     assert "Assertion" not in res.stderr
+
+
+@pytest.mark.gpu
+def test_box_primitives_match_six_rectangle_leaves(rt, orc, device):
+    """Box primitives (csrc/box_prims.h: the six faces of an axis-aligned Cube answered by ONE slab test, intersect.cuh box_hit) against
+    the same scene with the faces as six rectangle leaves, ray by ray and image by image; book-two (400 ground blocks) and a table
+    scene whose cubes touch, share planes with a loose rectangle and enclose ray origins."""
+    box = rt.Scene.example(device, "book-two", 1)
+    rec = rt.Scene.example(device, "book-two", 1, options={"flags": rt.SCENE_NO_BOX_PRIMS})
+    info = box.extend_info()
+    assert info["box_prims"] == 400 and info["leaf_items"] == 3408 - 6 * 400 + 400 and info["whole_tree_threads"] == 1024
+    assert rec.extend_info() == {"box_prims": 0, "leaf_items": 3408, "whole_tree_threads": 0}
+    assert box.bvh_info()["nodes"] < rec.bvh_info()["nodes"] // 2
+    rng = np.random.default_rng(5)
+    n = 60000
+    dd = rng.normal(size=(n, 3))
+    dd /= np.linalg.norm(dd, axis=1, keepdims=True)
+    oo = np.stack([rng.uniform(-1100, 1100, n), rng.uniform(-20, 400, n), rng.uniform(-1100, 1100, n)], axis=1)  # above, between and INSIDE the blocks
+    axis = np.concatenate([np.eye(3), -np.eye(3)])[rng.integers(0, 6, 4000)]
+    ao = np.stack([rng.uniform(-1000, 1000, 4000), rng.uniform(0, 120, 4000), rng.uniform(-1000, 1000, 4000)], axis=1)
+    rays = np.concatenate([np.concatenate([oo, dd], axis=1), np.concatenate([ao, axis], axis=1)]).astype(np.float32)
+    hb, hr = box.trace(rays), rec.trace(rays)
+    differ = (hb["prim"] != hr["prim"]) | (hb["hit"] != hr["hit"])
+    assert differ.mean() <= 2e-4, differ.mean()  # rays through the very edge of a block: its two faces tie
+    ok = ~differ & (hr["hit"] == 1)
+    assert ok.sum() > 0.5 * len(rays)
+    assert np.allclose(hb["t"][ok], hr["t"][ok], rtol=2e-5, atol=1e-4)
+    assert np.allclose(hb["n"][ok], hr["n"][ok], atol=1e-5) and np.allclose(hb["p"][ok], hr["p"][ok], rtol=2e-5, atol=2e-3)
+    # bounce rays that START on faces (self_prim = the face): oracle hits on the blocks, scattered on
+    o_sc = orc.Scene("book-two", 1)
+    first = o_sc.trace(orc.camera_rays(o_sc.camera(1.0), 96, 96), rel_perturb=0.0)
+    kinds = o_sc.prims()["kind"]
+    sel = (first["hit"] == 1) & (kinds[np.maximum(first["prim"], 0)] == 1)  # starts on rectangles: the blocks' faces (and the light)
+    p, nrm = first["p"][sel], first["n"][sel]
+    assert len(p) > 2000
+    d2 = rng.normal(size=p.shape)
+    d2 /= np.linalg.norm(d2, axis=1, keepdims=True)
+    r2 = np.concatenate([p, d2], axis=1).astype(np.float32)  # both hemispheres: into the block (comes out of another face) and away from it
+    so = first["prim"][sel].astype(np.uint32)
+    h2b, h2r = box.trace(r2, self_order=so), rec.trace(r2, self_order=so)
+    d2f = (h2b["prim"] != h2r["prim"]) | (h2b["hit"] != h2r["hit"])
+    assert d2f.mean() <= 1e-3, d2f.mean()
+    assert np.all(h2b["prim"][h2b["hit"] == 1] != so[h2b["hit"] == 1])  # a face never re-hits itself
+    ok2 = ~d2f & (h2r["hit"] == 1)
+    assert np.allclose(h2b["t"][ok2], h2r["t"][ok2], rtol=2e-5, atol=1e-4)
+    # images: same Philox keys, same hits -> same paths up to the edge grazers
+    a, qa, sa = _render_with(rt, device, "book-two", 96, 96, 8, scene_opts={"flags": rt.SCENE_NO_BOX_PRIMS})
+    b, qb, sb = _render_with(rt, device, "book-two", 96, 96, 8)
+    c, qc, sc = _render_with(rt, device, "book-two", 96, 96, 8, scene_opts={"flags": rt.SCENE_NO_WHOLE_TREE})  # boxes read from global memory
+    assert abs(int(sa.rays) - int(sb.rays)) <= 2e-3 * sa.rays and abs(int(sc.rays) - int(sb.rays)) <= 1e-4 * sb.rays
+    same = np.abs(c - b).max(axis=2) <= 1e-5 * np.maximum(1.0, np.abs(c).max(axis=2))
+    assert same.mean() >= 0.998, same.mean()
+    close = np.abs(a - b).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(a).max(axis=2))
+    assert close.mean() >= 0.97, close.mean()
+    assert abs(a.mean() - b.mean()) <= 5e-3 * a.mean()
+
+    # a table scene: touching cubes (shared planes), a cube with a loose rectangle on one of its planes, glass cubes (rays start inside)
+    I = np.eye(3)
+    face = {"+x": _rot([0, 1, 0], 90), "-x": _rot([0, 1, 0], -90), "+y": _rot([1, 0, 0], -90), "-y": _rot([1, 0, 0], 90), "+z": I, "-z": _rot([0, 1, 0], 180)}
+    mats = [(rt.MAT_LAMBERTIAN, (0.7, 0.6, 0.5), 0, 0), (rt.MAT_DIFFUSE_LIGHT, (3, 3, 3), 0, 0), (rt.MAT_METAL, (0.8, 0.8, 0.9), 0.05, 0),
+            (rt.MAT_DIELECTRIC, (1, 1, 1), 0, 1.5)]
+    rects = []
+
+    def cube(centre, half, m):
+        for name, sgn, ax in [("+x", 1, 0), ("-x", -1, 0), ("+y", 1, 1), ("-y", -1, 1), ("+z", 1, 2), ("-z", -1, 2)]:
+            off = np.zeros(3)
+            off[ax] = sgn * half[ax]
+            ext = np.abs(face[name].T @ (2 * np.asarray(half, dtype=np.float64)))
+            rects.append((face[name], np.asarray(centre, dtype=np.float64) + off, ext[0], ext[1], m))
+
+    for i in range(5):
+        for j in range(5):  # a 5 x 5 floor of touching blocks of random height
+            cube([2.0 * i - 4.0, 0.5 * (0.5 + 0.3 * ((i * 7 + j * 3) % 5)) - 2.0, 2.0 * j - 4.0], [1.0, 0.5 * (0.5 + 0.3 * ((i * 7 + j * 3) % 5)), 1.0], (i + j) % 2 * 2)
+    cube([0.0, 1.0, 0.0], [0.8, 0.8, 0.8], 3)    # glass: rays refract into it and start on its faces going inward
+    cube([2.5, 0.5, -1.0], [0.5, 0.9, 0.5], 2)
+    rects.append((face["-y"], [0, 6.0, 0], 6.0, 6.0, 1))          # light
+    rects.append((face["+y"], [2.5, 1.4, -1.0], 2.0, 2.0, 0))     # a loose rectangle ON the top plane of the metal cube, overhanging it
+    tilted = _rot([1, 1, 0], 30)                                  # a cube that is NOT axis-aligned: stays six rectangles
+    for name, sgn, ax in [("+x", 1, 0), ("-x", -1, 0), ("+y", 1, 1), ("-y", -1, 1), ("+z", 1, 2), ("-z", -1, 2)]:
+        off = np.zeros(3)
+        off[ax] = sgn * 0.6
+        rects.append((tilted @ face[name], np.array([-2.5, 1.5, 1.0]) + tilted @ off, 1.2, 1.2, 0))
+    tables = _rect_tables(rt, rects, mats)
+    sb2 = rt.Scene.from_tables(device, *tables)
+    sr2 = rt.Scene.from_tables(device, *tables, options={"flags": rt.SCENE_NO_BOX_PRIMS})
+    assert sb2.extend_info()["box_prims"] == 27 and sr2.extend_info()["box_prims"] == 0
+    n = 50000
+    dd = rng.normal(size=(n, 3))
+    dd /= np.linalg.norm(dd, axis=1, keepdims=True)
+    oo = rng.uniform(-6, 6, size=(n, 3))
+    rays = np.concatenate([oo, dd], axis=1).astype(np.float32)
+    hb, hr = sb2.trace(rays), sr2.trace(rays)
+    differ = (hb["prim"] != hr["prim"]) | (hb["hit"] != hr["hit"])
+    assert differ.mean() <= 5e-4, differ.mean()
+    ok = ~differ & (hr["hit"] == 1)
+    assert np.allclose(hb["t"][ok], hr["t"][ok], rtol=2e-5, atol=1e-5)
+    cam2 = rt.make_camera(rt.camera_args([0, 5, -14], [0, 0, 0], [0, 1, 0], math.radians(40), 1.0, 1.0, 0.0))
+    a, qa, sa = _render_with(rt, device, None, 96, 96, 16, depth=20, tables=tables, cam=cam2, scene_opts={"flags": rt.SCENE_NO_BOX_PRIMS})
+    b, qb, sb = _render_with(rt, device, None, 96, 96, 16, depth=20, tables=tables, cam=cam2)
+    assert sa.rays > 96 * 96 * 16 * 2
+    assert abs(int(sa.rays) - int(sb.rays)) <= 3e-3 * sa.rays
+    close = np.abs(a - b).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(a).max(axis=2))
+    assert close.mean() >= 0.97, close.mean()
+    assert abs(a.mean() - b.mean()) <= 1e-2 * a.mean()

@@ -361,3 +361,19 @@ def test_jpeg_decoder_matches_libjpeg_bit_for_bit(rt):
     data = bytearray(data)
     with pytest.raises(rt.BackendError):
         rt.decode_image(bytes(data[:len(data) // 3]))  # truncated stream
+
+
+def test_scene_plan_folds_axis_aligned_cubes_into_box_primitives(rt):
+    """rt_scene_plan (host only): book-two's 400 ground blocks — six consecutive world-aligned rectangles each, every one a whole face —
+    become 400 leaf items; the tree shrinks enough for extend's whole-tree-in-shared-memory form.  Rotated cubes (cornell-box is a
+    small scene anyway) and scenes without rectangles are left alone."""
+    plan = rt.FlatScene("book-two", 1).plan()
+    assert plan["n_box_prims"] == 400 and plan["n_leaf_items"] == 3408 - 2400 + 400
+    assert plan["whole_tree_threads"] == 1024 and plan["whole_tree_smem"] <= 224 * 1024
+    o = rt.RtSceneOptions()
+    o.flags = rt.SCENE_NO_BOX_PRIMS
+    plain = rt.FlatScene("book-two", 1).plan(o)
+    assert plain["n_box_prims"] == 0 and plain["n_leaf_items"] == 3408 and plain["whole_tree_threads"] == 0 and plain["n_nodes"] > 2 * plan["n_nodes"]
+    one = rt.FlatScene("book-one", 1).plan()
+    assert one["n_box_prims"] == 0 and one["whole_tree_threads"] == 512 and one["n_leaf_items"] == 485
+    assert rt.FlatScene("cornell-box", 1).plan()["n_box_prims"] == 0  # a small scene: the frame-rect list handles its cubes
