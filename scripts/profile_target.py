@@ -12,6 +12,7 @@ cap = int(sys.argv[6]) if len(sys.argv) > 6 else 0
 dev = rt.Device(0)
 scene = rt.Scene.example(dev, name, 1)
 cam = scene.flat.camera(w / h)
-s, _, st = scene.render(cam, w, h, spp, depth, seed=1, queue_capacity=cap, want_sumsq=False)
+fl = int(os.environ.get("AB_FLAGS", "0"))  # extra RtRenderParams.flags (8 = extend per thread, 16 = persistent / refill)
+s, _, st = scene.render(cam, w, h, spp, depth, seed=1, queue_capacity=cap, want_sumsq=False, flags=fl)
 print(f"{name} {w}x{h}x{spp} d{depth}: paths={st.paths} rays={st.rays} iters={st.iterations} launches={st.launches} dev_ms={st.ms_total:.2f} "
       f"Mpaths/s={st.paths / st.ms_total / 1e3:.1f} Grays/s={st.rays / st.ms_total / 1e6:.3f} mean={s.mean() / spp:.4f}")
