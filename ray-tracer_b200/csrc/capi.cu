@@ -85,6 +85,7 @@ struct RtContext {
     cudaEvent_t ev_lane_begin = nullptr;
     DevBuf<float> lane_sum, lane_sumsq;  // the lanes' compact row shards before they are interleaved into the caller's buffer
     uint32_t n_lanes = 2;
+    bool lanes_auto = true;   // RtContextOptions.lanes was 0: render_lanes picks by render size
     uint32_t default_capacity = 1u << 22;  // 4 M live rays (570 MB of wavefront state): per-launch fixed costs amortise, +20 % over 1 M (r1c)
 };
 
@@ -458,6 +459,7 @@ static int context_create(int device_id, const RtContextOptions& co, const RtSce
     if (!ctx) return fail(RT_ERR_OOM, "out of host memory");
     ctx->device = device_id;
     ctx->n_lanes = co.lanes >= 1 && co.lanes <= 4 ? co.lanes : 2u;
+    ctx->lanes_auto = !(co.lanes >= 1 && co.lanes <= 4);
     if (co.queue_capacity) ctx->default_capacity = co.queue_capacity;
     ctx->overlap_accumulate = !(co.flags & RT_CTX_NO_ACCUMULATE_OVERLAP);
     ctx->stage_timing = (co.flags & RT_CTX_STAGE_TIMING) != 0;
@@ -921,6 +923,10 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
     if (prm->row_stride == 0 || prm->row_begin >= prm->height || prm->width == 0) return render_core(ctx, scene, cam, nullptr, prm, d_sum, d_sumsq, cuda_stream, stats);
     const uint32_t rows_local = (prm->height - prm->row_begin + prm->row_stride - 1) / prm->row_stride;
     uint32_t L = ctx->n_lanes;
+    // A short render of a small all-rectangle scene (one GPU's 1/8 shard of cornell-box: 46 M paths, 11 ms) spends a tenth of its time
+    // in the ~50 nearly empty iterations that drain a depth-50 wavefront; a third lane hides more of that (r2_41: 4189 -> 4314 Mpaths/s
+    // on the shard; neutral to slightly negative on full-size renders and on the tree scenes)
+    if (ctx->lanes_auto && scene->d.fr_n && (uint64_t)prm->width * rows_local * prm->spp <= (1ull << 27)) L = 3;
     if ((prm->flags & (RT_RENDER_STAGE_TIMING | RT_RENDER_COUNT_WORK)) || ctx->stage_timing) L = 1;
     if (rows_local < 4u * L || prm->max_depth == 0) L = 1;
     if ((uint64_t)prm->width * rows_local * prm->spp < (uint64_t)L * (1u << 20)) L = 1;  // too little work to fill two queues

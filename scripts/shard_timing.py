@@ -8,7 +8,7 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 stride = int(sys.argv[1]) if len(sys.argv) > 1 else 8
-for lanes in ("1", "2", "3"):
+for lanes in ("1", "2", "3", "4"):
     os.environ["RT_B200_LANES"] = lanes
     rt = importlib.import_module("ray-tracer_b200")
     dev = rt.Device(0)
