@@ -287,6 +287,21 @@ void rt_multi_scene_destroy(RtMultiScene* scene);
 int rt_render_multi(RtMultiScene* scene, const RtCamera* cam, const RtRenderParams* params, float* out_sum_rgb, float* out_sumsq_rgb,
                     RtStats* stats);
 
+/* rt_render without any allocation.  No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, image and
+ * RtStats as rt_render (host output buffers; the Philox keys do not depend on queue size or lane count, so the sums agree with
+ * rt_render's up to the order of the f64 accumulations), but ALL device scratch — ray queues of RT_NOALLOC_QUEUE_RAYS rays, hit and
+ * finished-path records, counters, f64 accumulators, device framebuffers — is one static device array of RT_NOALLOC_SCRATCH_BYTES that
+ * every GPU which loads the library holds until exit.  The call performs no cudaMalloc / cudaFree / cudaMallocHost and creates no stream
+ * or event; scene and context must exist already (rt_init / rt_scene_create allocate).  Limits: width x rendered rows <=
+ * RT_NOALLOC_MAX_PIXELS, else RT_ERR_INVALID with a message naming the limit; RT_RENDER_STAGE_TIMING / RT_RENDER_COUNT_WORK are ignored.
+ * Every call on a device shares the one array (it keeps the previous call's contents; the call clears what must start at zero): calls
+ * that overlap on the same GPU — from any context or thread — race.  One wavefront lane, small queues: slower than rt_render. */
+#define RT_NOALLOC_MAX_PIXELS 65536u
+#define RT_NOALLOC_QUEUE_RAYS 32768u
+#define RT_NOALLOC_SCRATCH_BYTES (9u << 20)
+int rt_render_noalloc(RtScene* scene, const RtCamera* cam, const RtRenderParams* params, float* out_sum_rgb, float* out_sumsq_rgb, RtStats* stats);
+
 /* Introspection used by tests / the roofline accounting. */
 int rt_scene_bvh_info(const RtScene* scene, uint32_t* n_nodes, uint32_t* n_always, uint32_t* max_depth);
 /* Frame-rect list of a small all-rectangle scene (k_extend_rects): frames, frame boxes (faces of one box tested with one slab test)

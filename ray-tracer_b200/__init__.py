@@ -22,6 +22,7 @@ SCENE_NO_FRAME_RECTS, SCENE_NO_STAGED_PRIMS, SCENE_NO_SMALL_LIST, SCENE_NO_FRAME
 RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM, RT_ERR_NCCL = 0, -1, -2, -3, -4, -5, -6
 PRIM_SPHERE, PRIM_RECT, PRIM_MEDIUM_SPHERE, PRIM_MEDIUM = 0, 1, 2, 3
 NO_PRIM = 0xFFFFFFFF
+NOALLOC_MAX_PIXELS, NOALLOC_QUEUE_RAYS, NOALLOC_SCRATCH_BYTES = 65536, 32768, 9 << 20
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT, MAT_ISOTROPIC = 0, 1, 2, 3, 4
 TEX_SOLID, TEX_CHECKER, TEX_IMAGE = 0, 1, 2
 
@@ -82,7 +83,7 @@ class RthCameraArgs(C.Structure):
 # every symbol include/rt_b200.h and include/rt_b200_host.h declare
 ABI_SYMBOLS = ["rt_init", "rt_init_ex", "rt_options_from_env", "rt_shutdown", "rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_render", "rt_render_device",
                "rt_trace", "rt_trace_from", "rt_color_rays", "rt_resolve_u8", "rt_init_multi", "rt_shutdown_multi", "rt_multi_device_count", "rt_multi_context",
-               "rt_multi_scene_create", "rt_multi_scene_destroy", "rt_render_multi",
+               "rt_multi_scene_create", "rt_multi_scene_destroy", "rt_render_multi", "rt_render_noalloc",
                "rt_deinterleave_rows", "rt_scene_bvh_info", "rt_scene_frame_rect_info", "rt_scene_extend_info", "rt_scene_plan", "rt_scene_device_bytes", "rt_last_error", "rt_abi_version", "rth_example_scene", "rth_flat_destroy", "rth_flat_camera_args",
                "rth_flat_desc", "rth_scene_upload", "rth_camera", "rth_encode_image", "rth_decode_image", "rth_set_earth_image"]
 
@@ -121,6 +122,7 @@ def _load():
     L.rt_scene_destroy.argtypes = [vp]
     L.rt_scene_destroy.restype = None
     L.rt_render.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
+    L.rt_render_noalloc.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
     L.rt_render_device.argtypes = [vp, C.POINTER(RtCamera), C.POINTER(RtRenderParams), vp, vp, vp, C.POINTER(RtStats)]
     L.rt_trace.argtypes = [vp, vp, u64, u64, vp]
     L.rt_color_rays.argtypes = [vp, vp, u64, u32, u32, u64, vp, vp, C.POINTER(RtStats)]
@@ -400,6 +402,16 @@ class Scene:
         q = np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows] if want_sumsq else None
         st = RtStats()
         _check(lib.rt_render(self._h, C.byref(cam), C.byref(prm), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
+        return s, q, st
+
+    def render_noalloc(self, cam, width, height, spp, max_depth, seed=1, row_begin=0, row_stride=1, want_sumsq=True, flags=0):
+        """rt_render_noalloc: rt_render out of the library's static device scratch (no allocation; width x rows <= NOALLOC_MAX_PIXELS)."""
+        prm = self.params(width, height, spp, max_depth, seed, row_begin, row_stride, 0, flags)
+        rows = len(range(row_begin, height, row_stride)) if row_stride > 0 else 0
+        s = np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows]
+        q = np.zeros((max(rows, 1), width, 3), dtype=np.float32)[:rows] if want_sumsq else None
+        st = RtStats()
+        _check(lib.rt_render_noalloc(self._h, C.byref(cam), C.byref(prm), _ptr(s), _ptr(q) if want_sumsq else None, C.byref(st)))
         return s, q, st
 
     def render_device(self, cam, prm, d_sum_ptr, d_sumsq_ptr=None, stream=None):

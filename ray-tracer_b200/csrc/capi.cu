@@ -1176,6 +1176,98 @@ int rt_render(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, fl
     return RT_OK;
 }
 
+// ---- rt_render_noalloc: a render that allocates nothing ------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid it).  The wavefront's scratch — two ray queues, the hit and
+// finished-path records, the ring counters, the f64 accumulators and the device framebuffers — lives in ONE file-scope device array of
+// RT_NOALLOC_SCRATCH_BYTES that every GPU which loads this library holds until exit.  In host code `g_noalloc_scratch` is only a
+// stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per device (noalloc_scratch below).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RT_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[64] = {nullptr};  // per device: device address of g_noalloc_scratch
+
+// the calling thread has `device` current
+int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= 64) return fail(RT_ERR_INVALID, "device %d out of range", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        unsigned char* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(RT_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) failed on device %d: %s", device, cudaGetErrorString(e));
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return RT_OK;
+}
+
+// Lends slices of the static array to a context's wavefront buffers for the duration of one render and puts the context's own
+// (pointer, size) pairs back afterwards, whichever way the render returns.  DevBuf::ensure is a no-op for a buffer that is large enough.
+struct NoallocLoan {
+    RtContext* ctx;
+    DevBuf<float4> qa[2], qb[2], qc[2], done[2];
+    DevBuf<float2> hits;
+    DevBuf<WaveCounters> counters;
+    DevBuf<double> acc;
+    bool stage_timing;
+    NoallocLoan(RtContext* c, unsigned char* base) : ctx(c) {
+        for (int i = 0; i < 2; ++i) { qa[i] = c->qa[i]; qb[i] = c->qb[i]; qc[i] = c->qc[i]; done[i] = c->done[i]; }
+        hits = c->hits; counters = c->counters; acc = c->acc; stage_timing = c->stage_timing;
+        const size_t cap = RT_NOALLOC_QUEUE_RAYS, q = cap * sizeof(float4);
+        size_t off = 0;
+        auto take = [&](size_t bytes) { unsigned char* p = base + off; off += (bytes + 255u) & ~(size_t)255u; return p; };
+        for (int i = 0; i < 2; ++i) {
+            c->qa[i].p = (float4*)take(q); c->qa[i].n = cap;
+            c->qb[i].p = (float4*)take(q); c->qb[i].n = cap;
+            c->qc[i].p = (float4*)take(q); c->qc[i].n = cap;
+            c->done[i].p = (float4*)take(q); c->done[i].n = cap;
+        }
+        c->hits.p = (float2*)take(cap * sizeof(float2)); c->hits.n = cap;
+        c->counters.p = (WaveCounters*)take(sizeof(WaveCounters)); c->counters.n = 1;
+        c->acc.p = (double*)take((size_t)RT_NOALLOC_MAX_PIXELS * 6 * sizeof(double)); c->acc.n = (size_t)RT_NOALLOC_MAX_PIXELS * 6;
+        fb_sum = (float*)take((size_t)RT_NOALLOC_MAX_PIXELS * 3 * sizeof(float));
+        fb_sumsq = (float*)take((size_t)RT_NOALLOC_MAX_PIXELS * 3 * sizeof(float));
+        bytes = off;
+        c->stage_timing = false;  // (stage timing creates events on demand)
+    }
+    ~NoallocLoan() {
+        for (int i = 0; i < 2; ++i) { ctx->qa[i] = qa[i]; ctx->qb[i] = qb[i]; ctx->qc[i] = qc[i]; ctx->done[i] = done[i]; }
+        ctx->hits = hits; ctx->counters = counters; ctx->acc = acc; ctx->stage_timing = stage_timing;
+    }
+    float* fb_sum;
+    float* fb_sumsq;
+    size_t bytes;
+};
+}  // namespace
+
+int rt_render_noalloc(RtScene* scene, const RtCamera* cam, const RtRenderParams* prm, float* out_sum, float* out_sumsq, RtStats* stats) {
+    if (!scene || !cam || !prm || !out_sum) return fail(RT_ERR_INVALID, "null argument");
+    if (prm->width == 0 || prm->height == 0 || prm->spp == 0) return fail(RT_ERR_INVALID, "width/height/spp must be > 0");
+    if (prm->row_stride == 0 || prm->row_begin >= prm->height) return fail(RT_ERR_INVALID, "bad row_begin/row_stride");
+    const uint64_t rows = ((uint64_t)prm->height - prm->row_begin + prm->row_stride - 1) / prm->row_stride;
+    const uint64_t pixels = (uint64_t)prm->width * rows;
+    if (pixels > RT_NOALLOC_MAX_PIXELS)
+        return fail(RT_ERR_INVALID, "rt_render_noalloc: %llu pixels exceed the static scratch maximum of %u (RT_NOALLOC_MAX_PIXELS); use rt_render",
+                    (unsigned long long)pixels, (unsigned)RT_NOALLOC_MAX_PIXELS);
+    RtContext* ctx = scene->ctx;
+    RT_CUDA(cudaSetDevice(ctx->device));
+    unsigned char* base = nullptr;
+    if (int rc = noalloc_scratch(ctx->device, &base)) return rc;
+    NoallocLoan loan(ctx, base);
+    static_assert(sizeof(WaveCounters) <= 256, "counter block");
+    if (loan.bytes > RT_NOALLOC_SCRATCH_BYTES) return fail(RT_ERR_INVALID, "static scratch layout exceeds RT_NOALLOC_SCRATCH_BYTES");
+    RtRenderParams p = *prm;
+    p.queue_capacity = RT_NOALLOC_QUEUE_RAYS;  // the queues of the static array, whatever the caller asked for
+    p.flags &= (RT_RENDER_SAMPLE_MAJOR | RT_RENDER_EXTEND_PER_THREAD | RT_RENDER_EXTEND_PERSISTENT);  // no instrumentation: it creates events
+    // one wavefront on the context's own stream (render_core; the lanes of rt_render own device buffers of their own)
+    const int rc = render_core(ctx, scene, cam, nullptr, &p, loan.fb_sum, out_sumsq ? loan.fb_sumsq : nullptr, nullptr, stats);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(cudaMemcpy(out_sum, loan.fb_sum, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+    if (out_sumsq) RT_CUDA(cudaMemcpy(out_sumsq, loan.fb_sumsq, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
 int rt_trace(RtScene* scene, const RtRayIn* rays, uint64_t n, uint64_t seed, RtHitOut* out) { return rt_trace_from(scene, rays, nullptr, n, seed, out); }
 
 int rt_trace_from(RtScene* scene, const RtRayIn* rays, const uint32_t* self_order, uint64_t n, uint64_t seed, RtHitOut* out) {

@@ -248,6 +248,8 @@ pub mod ffi {
         pub fn rt_scene_destroy(scene: *mut RtScene);
         pub fn rt_render(scene: *mut RtScene, cam: *const RtCamera, params: *const RtRenderParams, out_sum_rgb: *mut f32, out_sumsq_rgb: *mut f32,
                          stats: *mut RtStats) -> c_int;
+        pub fn rt_render_noalloc(scene: *mut RtScene, cam: *const RtCamera, params: *const RtRenderParams, out_sum_rgb: *mut f32, out_sumsq_rgb: *mut f32,
+                                 stats: *mut RtStats) -> c_int;
         pub fn rt_render_device(scene: *mut RtScene, cam: *const RtCamera, params: *const RtRenderParams, d_sum_rgb: *mut f32, d_sumsq_rgb: *mut f32,
                                 cuda_stream: *mut c_void, stats: *mut RtStats) -> c_int;
         pub fn rt_color_rays(scene: *mut RtScene, rays: *const RtRayIn, n: u64, spp: u32, max_depth: u32, seed: u64, out_sum_rgb: *mut f32,
