@@ -173,11 +173,12 @@ typedef struct RtMultiScene RtMultiScene; /* a scene replicated on every device 
 
 /* Options of a context; all-zero = defaults.  rt_init(device, ..) == rt_init_ex(device, NULL, ..): defaults from the RT_B200_*
  * environment variables (RT_B200_LANES, RT_B200_QUEUE_CAPACITY, RT_B200_OVERLAP_ACCUMULATE, RT_B200_STAGE_TIMING,
- * RT_B200_GEN_BLOCKS, RT_B200_ACC_BLOCKS, RT_B200_SHADE_RAYS2 and the RtSceneOptions ones), read once. */
+ * RT_B200_GEN_BLOCKS, RT_B200_ACC_BLOCKS, RT_B200_SHADE_RAYS2, RT_B200_FUSE_RECTS and the RtSceneOptions ones), read once. */
 typedef enum RtContextFlags {
     RT_CTX_NO_ACCUMULATE_OVERLAP = 1u, /* run accumulate on the render stream instead of a side stream */
     RT_CTX_STAGE_TIMING = 2u,          /* every render behaves as if RT_RENDER_STAGE_TIMING were set */
-    RT_CTX_SHADE_ONE_RAY = 4u          /* k_shade shades one ray per thread per round on every scene */
+    RT_CTX_SHADE_ONE_RAY = 4u,         /* k_shade shades one ray per thread per round on every scene */
+    RT_CTX_NO_FUSED_RECTS = 8u         /* small all-rectangle scenes: extend stays its own kernel (k_extend_rects) instead of running inside k_shade */
 } RtContextFlags;
 typedef struct RtContextOptions {
     uint32_t lanes;          /* concurrent wavefronts per render, 1..4; 0 = default (2) */

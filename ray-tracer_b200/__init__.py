@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")  # override: tuning variants only
 
 RENDER_STAGE_TIMING, RENDER_COUNT_WORK, RENDER_SAMPLE_MAJOR, RENDER_EXTEND_PER_THREAD, RENDER_EXTEND_PERSISTENT, RENDER_TIME_EVERY_ITERATION = 1, 2, 4, 8, 16, 32
-CTX_NO_ACCUMULATE_OVERLAP, CTX_STAGE_TIMING, CTX_SHADE_ONE_RAY = 1, 2, 4
+CTX_NO_ACCUMULATE_OVERLAP, CTX_STAGE_TIMING, CTX_SHADE_ONE_RAY, CTX_NO_FUSED_RECTS = 1, 2, 4, 8
 BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
 SCENE_NO_FRAME_RECTS, SCENE_NO_STAGED_PRIMS, SCENE_NO_SMALL_LIST, SCENE_NO_FRAME_BOXES, SCENE_NO_BOX_PRIMS, SCENE_NO_WHOLE_TREE = 1, 2, 4, 8, 16, 32
 RT_OK, RT_ERR_INVALID, RT_ERR_UNSUPPORTED, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_OOM, RT_ERR_NCCL = 0, -1, -2, -3, -4, -5, -6

@@ -426,6 +426,7 @@ void rt_options_from_env(RtContextOptions* co, RtSceneOptions* so) {
         if (envInt("RT_B200_OVERLAP_ACCUMULATE", 0, 1, 1) == 0) co->flags |= RT_CTX_NO_ACCUMULATE_OVERLAP;
         if (envInt("RT_B200_STAGE_TIMING", 0, 1, 0) == 1) co->flags |= RT_CTX_STAGE_TIMING;
         if (envInt("RT_B200_SHADE_RAYS2", 0, 1, 1) == 0) co->flags |= RT_CTX_SHADE_ONE_RAY;
+        if (envInt("RT_B200_FUSE_RECTS", 0, 1, 1) == 0) co->flags |= RT_CTX_NO_FUSED_RECTS;
         co->gen_blocks = (uint32_t)envInt("RT_B200_GEN_BLOCKS", 1, 16, 0);
         co->acc_blocks = (uint32_t)envInt("RT_B200_ACC_BLOCKS", 1, 16, 0);
     }
@@ -464,6 +465,7 @@ static int context_create(int device_id, const RtContextOptions& co, const RtSce
     ctx->overlap_accumulate = !(co.flags & RT_CTX_NO_ACCUMULATE_OVERLAP);
     ctx->stage_timing = (co.flags & RT_CTX_STAGE_TIMING) != 0;
     ctx->lopt.shade_rays2 = (co.flags & RT_CTX_SHADE_ONE_RAY) ? 0 : 1;
+    ctx->lopt.fuse_rects = (co.flags & RT_CTX_NO_FUSED_RECTS) ? 0 : 1;
     if (co.gen_blocks >= 1 && co.gen_blocks <= 16) ctx->lopt.gen_blocks = (int)co.gen_blocks;
     if (co.acc_blocks >= 1 && co.acc_blocks <= 16) ctx->lopt.acc_blocks = (int)co.acc_blocks;
     ctx->scene_defaults = so;
@@ -923,10 +925,10 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
     if (prm->row_stride == 0 || prm->row_begin >= prm->height || prm->width == 0) return render_core(ctx, scene, cam, nullptr, prm, d_sum, d_sumsq, cuda_stream, stats);
     const uint32_t rows_local = (prm->height - prm->row_begin + prm->row_stride - 1) / prm->row_stride;
     uint32_t L = ctx->n_lanes;
-    // A short render of a small all-rectangle scene (one GPU's 1/8 shard of cornell-box: 46 M paths, 11 ms) spends a tenth of its time
-    // in the ~50 nearly empty iterations that drain a depth-50 wavefront; a third lane hides more of that (r2_41: 4189 -> 4314 Mpaths/s
-    // on the shard; neutral to slightly negative on full-size renders and on the tree scenes)
-    if (ctx->lanes_auto && scene->d.fr_n && (uint64_t)prm->width * rows_local * prm->spp <= (1ull << 27)) L = 3;
+    // Small all-rectangle scenes run three lanes: their iterations are short (extend is fused into shade: two kernels + accumulate) and
+    // the ~50 nearly empty iterations that drain a depth-50 wavefront weigh more — cornell-box 600x600x512: 4776 -> 4833 Mpaths/s, a
+    // 1/8 shard (one GPU of eight) 4190 -> 4313 (profiles/r2_41_*, r2_42_*); neutral to slightly negative on the tree scenes
+    if (ctx->lanes_auto && scene->d.fr_n) L = 3;
     if ((prm->flags & (RT_RENDER_STAGE_TIMING | RT_RENDER_COUNT_WORK)) || ctx->stage_timing) L = 1;
     if (rows_local < 4u * L || prm->max_depth == 0) L = 1;
     if ((uint64_t)prm->width * rows_local * prm->spp < (uint64_t)L * (1u << 20)) L = 1;  // too little work to fill two queues
@@ -1075,6 +1077,7 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
 
     RT_CUDA(cudaEventRecord(ctx->ev0, st));
     Launch L{&scene->launch, &lopt, RT_WORK_UNKNOWN, st};
+    const bool fused = extend_is_fused(L, scene->d, count_work);  // extend inside k_shade: one launch fewer per iteration
     Launch La = L;  // accumulate's launch site (its own stream when overlapped)
     La.st = acc_st;
     uint64_t k = 0;
@@ -1096,7 +1099,7 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
         if (timed) RT_CUDA(stage_event(ts, 2, st));
         // shade_k refills done[k & 1]: accumulate_{k-2} must be through with it
         if (overlap && k >= 2) RT_CUDA(cudaStreamWaitEvent(st, ctx->ev_accumulated[k & 1], 0));
-        launch_shade(L, scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, kx);
+        launch_shade(L, scene->d, rc, qin, qout, ctx->hits.p, ctx->done[k & 1].p, wc, kx, count_work);
         if (timed) RT_CUDA(stage_event(ts, 3, st));
         if (overlap) {
             RT_CUDA(cudaEventRecord(ctx->ev_shaded[k & 1], st));
@@ -1106,7 +1109,7 @@ static int render_core(RtContext* ctx, RtScene* scene, const RtCamera* cam, cons
         launch_accumulate(La, rc, ctx->done[k & 1].p, wc, ku, acc_sum, acc_sumsq);
         if (timed) { RT_CUDA(stage_event(ts, 5, acc_st)); ++n_timed; }
         if (overlap) RT_CUDA(cudaEventRecord(ctx->ev_accumulated[k & 1], acc_st));
-        launches += tail ? 3 : 4;
+        launches += (tail ? 3 : 4) - (fused ? 1 : 0);
         // a launch that cannot start (shared memory, bad configuration) must surface here, not as "did not terminate" 100 k iterations later
         if (k == 0) RT_CUDA(cudaPeekAtLastError());
         ++k;

@@ -572,8 +572,15 @@ __device__ __forceinline__ ShadeOne shade_one(const DScene& S, const RenderConst
 #ifndef RT_SHADE2_MIN_BLOCKS
 #define RT_SHADE2_MIN_BLOCKS 6
 #endif
-template <int R, bool GEN>
-__global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS) k_shade(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
+// FR (small all-rectangle scenes, S.fr_n > 0): the closest hit is computed HERE, from the frame-rect list (frame_rects_closest, the body of
+// k_extend_rects), instead of being read back from the hit queue — extend + shade as one kernel.  The ray is read once instead of
+// twice and the 8-byte hit record is neither written nor read: 96 + 8 instead of 144 + 8 bytes of queue traffic per segment
+// (cornell-box is bound by exactly that traffic), and a wavefront iteration is three dependent launches instead of four.
+template <int R, bool GEN, bool FR = false>
+#ifndef RT_SHADE_FR_MIN_BLOCKS
+#define RT_SHADE_FR_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS : (FR ? RT_SHADE_FR_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS)) k_shade(const DScene S0, const RenderConst rc, const RayQueue qin, RayQueue qout,
                                                const float2* __restrict__ hits, float4* __restrict__ done, WaveCounters* __restrict__ wc, uint32_t k) {
     extern __shared__ float4 shade_smem[];
     __shared__ uint32_t s_cnt[RT_SHADE_BLOCK / 32 + 1][2];
@@ -591,18 +598,22 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS 
     // one bulk copy of the blob rt_scene_create laid out in exactly this order; it lands while the first round's rays are requested
     __shared__ __align__(8) uint64_t s_mbar;
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
-    bulk_stage(mbar, BulkPart{S0.shade_blob, (uint32_t)__cvta_generic_to_shared(shade_smem), 16u * S0.shade_blob4});
+    const uint32_t fr_base = (uint32_t)__cvta_generic_to_shared(shade_smem) + 16u * S0.shade_blob4;  // FR: the frame-rect list behind the shade tables
+    if (FR) bulk_stage(mbar, BulkPart{S0.shade_blob, (uint32_t)__cvta_generic_to_shared(shade_smem), 16u * S0.shade_blob4}, BulkPart{S0.fr_blob, fr_base, 16u * S0.fr_blob4});
+    else bulk_stage(mbar, BulkPart{S0.shade_blob, (uint32_t)__cvta_generic_to_shared(shade_smem), 16u * S0.shade_blob4});
     bool tables_ready = false;
 #else
     for (uint32_t i = threadIdx.x; i < S0.shade_blob4; i += blockDim.x) shade_smem[i] = S0.shade_blob[i];
     __syncthreads();
-    const uint32_t mbar = 0u;
+    const uint32_t mbar = 0u, fr_base = 0u;
+    static_assert(!FR, "the fused form stages its tables with the bulk copy");
     bool tables_ready = true;
 #endif
     DScene S = S0;
     if (n_sp) { S.prim_head = s_head; S.prim_meta = s_meta; S.rect_nrm = s_nrm; }
     const uint32_t s = (k & ~RT_K_TAIL) % RT_RING;
     const uint32_t n = queue_size(wc, k);
+    if (FR) tail_roll(wc, k, n);  // no extend launch in front of this kernel: it rolls the ring counters of a tail iteration itself
     uint32_t* surv_next = &wc->surv[((k & ~RT_K_TAIL) + 1) % RT_RING];
     uint32_t* done_cnt = &wc->done[s];
     const uint32_t lane = lane_id(), warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
@@ -614,7 +625,7 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS 
             const uint32_t nx = base + stride + r * blockDim.x + threadIdx.x;
             if (nx < n) {
                 if ((lane & 7u) == 0u) { prefetch_l2(&qin.a[nx]); prefetch_l2(&qin.b[nx]); prefetch_l2(&qin.c[nx]); }
-                if ((lane & 15u) == 0u) prefetch_l2(&hits[nx]);
+                if (!FR && (lane & 15u) == 0u) prefetch_l2(&hits[nx]);
             }
         }
         float4 a[R], b[R], c[R];
@@ -622,10 +633,20 @@ __global__ void __launch_bounds__(RT_SHADE_BLOCK, R == 2 ? RT_SHADE2_MIN_BLOCKS 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const uint32_t i = base + r * blockDim.x + threadIdx.x;
-            if (i < n) { h[r] = hits[i]; a[r] = qin.a[i]; b[r] = qin.b[i]; c[r] = qin.c[i]; }
-            else { h[r] = make_float2(0.f, __uint_as_float(RT_NO_PRIM)); a[r] = b[r] = c[r] = make_float4(0.f, 0.f, 0.f, 0.f); }
+            h[r] = make_float2(0.f, __uint_as_float(RT_NO_PRIM));
+            if (i < n) { if (!FR) h[r] = hits[i]; a[r] = qin.a[i]; b[r] = qin.b[i]; c[r] = qin.c[i]; }
+            else { a[r] = b[r] = c[r] = make_float4(0.f, 0.f, 0.f, 0.f); }
         }
         if (!tables_ready) { mbar_wait(mbar, 0u); tables_ready = true; }  // block-uniform
+        if (FR) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (base + r * blockDim.x + threadIdx.x < n) {
+                    const ClosestHit ch = frame_rects_closest(S0, fr_base, f3(a[r].x, a[r].y, a[r].z), f3(b[r].x, b[r].y, b[r].z), __float_as_uint(a[r].w));
+                    h[r] = make_float2(ch.t, __uint_as_float(ch.prim));
+                }
+            }
+        }
         ShadeOne res[R];
         uint32_t ma[R], mb[R], ca = 0u, cb = 0u;
 #pragma unroll
@@ -820,7 +841,7 @@ struct DeviceState {
 };
 DeviceState g_dev[RT_MAX_DEVICES];
 // (kernels that exist in a GEN = false and a GEN = true instantiation take two consecutive slots: slot + gen)
-enum KernelSlot { SLOT_EXTEND = 0, SLOT_EXTEND_ALL = 2, SLOT_BVH = 4, SLOT_SHADE1 = 6, SLOT_SHADE2 = 8, SLOT_EXTEND_COUNT = 10, SLOT_BVH_COUNT, SLOT_RECTS, SLOT_TRACE };
+enum KernelSlot { SLOT_EXTEND = 0, SLOT_EXTEND_ALL = 2, SLOT_BVH = 4, SLOT_SHADE1 = 6, SLOT_SHADE2 = 8, SLOT_EXTEND_COUNT = 10, SLOT_BVH_COUNT, SLOT_RECTS, SLOT_TRACE, SLOT_SHADE_FR1, SLOT_SHADE_FR2 };
 
 // the ceiling only ever grows: a launch may use any size up to it, so scenes of different sizes never invalidate each other
 template <class K>
@@ -893,6 +914,14 @@ cudaError_t kernels_configure_scene(int device, const DScene& S, size_t scene_by
     }
     RT_TRY(grant(d, SLOT_SHADE1 + gen, shade1_k, shade_bytes));
     RT_TRY(grant(d, SLOT_SHADE2 + gen, shade2_k, shade_bytes));
+    if (fr_bytes && !gen) {  // extend fused into shade (k_shade<., ., true>): the shade tables plus the frame-rect list
+        L.shade_fr_smem = shade_bytes + fr_bytes;
+        RT_TRY(grant(d, SLOT_SHADE_FR1, k_shade<1, false, true>, L.shade_fr_smem));
+        RT_TRY(grant(d, SLOT_SHADE_FR2, k_shade<2, false, true>, L.shade_fr_smem));
+        RT_TRY(occupancy(L.shade_fr_blocks, k_shade<1, false, true>, RT_SHADE_BLOCK, L.shade_fr_smem));
+        RT_TRY(occupancy(L.shade2_fr_blocks, k_shade<2, false, true>, RT_SHADE_BLOCK, L.shade_fr_smem));
+        L.fused_rects = true;
+    }
     RT_TRY(occupancy(L.shade_blocks, shade1_k, RT_SHADE_BLOCK, shade_bytes));
     RT_TRY(occupancy(L.shade2_blocks, shade2_k, RT_SHADE_BLOCK, shade_bytes));
     // whole tree + heads in shared memory in the octant-ready layout, as long as that keeps the occupancy of the general kernel
@@ -928,10 +957,12 @@ void launch_generate(const Launch& L, const RenderConst& rc, const RayQueue& q, 
     // nothing left to issue: thread 0 rolls the counters
     k_generate<<<L.work_hint == RT_WORK_UNKNOWN ? L.sl->num_sms * L.opt->gen_blocks : 1, 256, 0, L.st>>>(rc, q, wc, k);
 }
+bool extend_is_fused(const Launch& L, const DScene& S, bool count_work) { return S.fr_n && !count_work && L.sl->fused_rects && L.opt->fuse_rects; }
 void launch_extend(const Launch& L, const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                    bool count_work) {
     const SceneLaunch& sl = *L.sl;
     const int sms = sl.num_sms;
+    if (extend_is_fused(L, S, count_work)) return;  // k_shade<., ., true> intersects
     if (S.fr_n && !count_work) {
         k_extend_rects<<<fit_grid(L, sms * sl.rects_blocks, RT_EXTEND_BLOCK), RT_EXTEND_BLOCK, sl.rects_smem, L.st>>>(S, q, hits, wc, k);
         return;
@@ -960,8 +991,16 @@ void launch_extend(const Launch& L, const DScene& S, const RayQueue& q, float2* 
     }
 }
 void launch_shade(const Launch& L, const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
-                  WaveCounters* wc, uint32_t k) {
+                  WaveCounters* wc, uint32_t k, bool count_work) {
     const SceneLaunch& sl = *L.sl;
+    if (extend_is_fused(L, S, count_work)) {
+        // one ray per thread per round at 8 resident blocks (51 registers): 4776 Mpaths/s on cornell-box against 4422 for two rays per
+        // round at 6 blocks (74 registers) — with the intersection in the kernel, resident warps count for more than loads in flight
+        // (profiles/r2_42_fused_extend_shade.txt); 10 / 12 blocks (48 / 40 registers) are slower again
+        if (L.opt->fuse_rects == 2) k_shade<2, false, true><<<fit_grid(L, sl.num_sms * sl.shade2_fr_blocks, 2 * RT_SHADE_BLOCK), RT_SHADE_BLOCK, sl.shade_fr_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+        else k_shade<1, false, true><<<fit_grid(L, sl.num_sms * sl.shade_fr_blocks, RT_SHADE_BLOCK), RT_SHADE_BLOCK, sl.shade_fr_smem, L.st>>>(S, rc, qin, qout, hits, done, wc, k);
+        return;
+    }
     // two rays per thread per barrier round where shading is light on registers (small all-rectangle scenes: no f64 sphere re-solve);
     // +5 % there, -7 % on the sphere scenes (r1f), hence per scene
     if (S.fr_n && L.opt->shade_rays2) {

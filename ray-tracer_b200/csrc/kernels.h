@@ -61,6 +61,7 @@ size_t extend_all_smem_bytes(const DScene& S, uint32_t block);
 bool extend_all_smem_fits(const DScene& S);
 struct LaunchOptions {
     int persistent = 2;   // extend in its persistent lane-refilling form: 0 never, 1 always (where a tree exists), 2 from RT_PERSISTENT_MIN_NODES nodes
+    int fuse_rects = 1;   // small all-rectangle scenes: extend runs inside k_shade (k_shade<., ., true>) instead of as k_extend_rects; 2 = two rays per round (A/B)
     int shade_rays2 = 1;  // two rays per thread per barrier round in k_shade on small all-rectangle scenes
     int gen_blocks = 4, acc_blocks = 8;  // blocks per SM of k_generate / k_accumulate
 };
@@ -70,6 +71,9 @@ struct LaunchOptions {
 struct SceneLaunch {
     int device = -1, num_sms = 0;
     size_t scene_smem = 0, extend_smem = 0, trace_smem = 0, bvh_smem = 0, shade_smem = 0, rects_smem = 0, all_smem = 0;
+    size_t shade_fr_smem = 0;
+    int shade_fr_blocks = 1, shade2_fr_blocks = 1;
+    bool fused_rects = false;  // the scene can run extend fused into shade (frame-rect list, no general records)
     int all_block = RT_EXTEND_ALL_BLOCK;  // threads per block of k_extend<., true>: 512 (two blocks per SM) or RT_EXTEND_ALL_BIG_BLOCK (one)
     int extend_blocks = 1, trace_blocks = 1, bvh_blocks = 1, shade_blocks = 1, shade2_blocks = 1, rects_blocks = 1, all_blocks = 1;
     bool gen = true;          // the scene has general 128-byte records: GEN = true instantiations of extend / shade
@@ -93,7 +97,9 @@ void launch_generate(const Launch& L, const RenderConst& rc, const RayQueue& q, 
 void launch_extend(const Launch& L, const DScene& S, const RayQueue& q, float2* hits, WaveCounters* wc, uint32_t k, uint32_t seed_lo, uint32_t seed_hi,
                    bool count_work);
 void launch_shade(const Launch& L, const DScene& S, const RenderConst& rc, const RayQueue& qin, const RayQueue& qout, const float2* hits, float4* done,
-                  WaveCounters* wc, uint32_t k);
+                  WaveCounters* wc, uint32_t k, bool count_work = false);
+// extend runs inside k_shade for this scene / these options (launch_extend is then a no-op)
+bool extend_is_fused(const Launch& L, const DScene& S, bool count_work);
 void launch_accumulate(const Launch& L, const RenderConst& rc, const float4* done, const WaveCounters* wc, uint32_t k, double* sum, double* sumsq);
 void launch_finish(int sms, const double* acc, size_t n, float* out, cudaStream_t st);
 void launch_resolve_u8(int sms, const float* sum, uint32_t width, uint32_t height, uint32_t spp, uint8_t* out, cudaStream_t st);

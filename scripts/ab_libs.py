@@ -37,5 +37,5 @@ for rnd in range(3):
         for k in ("g", "e", "s", "a", "one", "two"):
             b[k] = min(b[k], r[k])
 for lib, b in best.items():
-    print(f"{os.path.basename(lib):36s} gen {b['g']:7.2f} extend {b['e']:8.2f} ({b['rays'] / b['e'] / 1e6:6.2f} Grays/s) shade {b['s']:8.2f} ({b['rays'] / b['s'] / 1e6:6.2f}) acc {b['a']:6.2f} | "
+    print(f"{os.path.basename(lib):36s} gen {b['g']:7.2f} extend {b['e']:8.2f} ({b['rays'] / max(b['e'], 1e-9) / 1e6:6.2f} Grays/s) shade {b['s']:8.2f} ({b['rays'] / b['s'] / 1e6:6.2f}) acc {b['a']:6.2f} | "
           f"one lane {b['one']:8.2f} ms, two lanes {b['two']:8.2f} ms = {b['paths'] / b['two'] / 1e3:7.1f} Mpaths/s", flush=True)

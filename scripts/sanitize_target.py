@@ -38,5 +38,16 @@ for name, opts, flags in cases:
 sc = rt.Scene.example(dev, "cornell-box", 1)
 s, q, st = sc.render(sc.flat.camera(1.0), 301, 203, 36, 50, seed=3)
 print("lanes", st.launches, float(s.mean()))
+# the same scene with extend as its own kernel (k_extend_rects + k_shade<2>) and with two rays per round in the fused kernel; rt_render_noalloc
+for o in ({"lanes": 2, "flags": rt.CTX_NO_FUSED_RECTS}, {"lanes": 1, "flags": rt.CTX_SHADE_ONE_RAY | rt.CTX_NO_FUSED_RECTS}):
+    dev2 = rt.Device(0, options=o)
+    sc2 = rt.Scene.example(dev2, "cornell-box", 1)
+    for cap in (0, 1056):
+        s2, _, st2 = sc2.render(sc2.flat.camera(1.0), 301, 203, 36, 50, seed=3, queue_capacity=cap)
+    print("unfused", o, st2.launches, float(s2.mean()), st2.rays == st.rays)
+    s3, _, st3 = sc2.render_noalloc(sc2.flat.camera(1.0), 128, 64, 9, 50, seed=3)
+    print("noalloc", st3.launches, float(s3.mean()))
+    sc2.close()
+    dev2.close()
 img = dev.resolve_u8(s, 36)
 print("ok", img.shape)

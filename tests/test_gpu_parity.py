@@ -1026,3 +1026,25 @@ def test_box_primitives_match_six_rectangle_leaves(rt, orc, device):
     close = np.abs(a - b).max(axis=2) <= 2e-3 * np.maximum(1.0, np.abs(a).max(axis=2))
     assert close.mean() >= 0.97, close.mean()
     assert abs(a.mean() - b.mean()) <= 1e-2 * a.mean()
+
+
+@pytest.mark.gpu
+def test_fused_extend_shade_matches_separate_kernels(rt, device):
+    """Small all-rectangle scenes intersect inside k_shade (k_shade<., ., true>: frame_rects_closest, the body of k_extend_rects, then
+    the shading of the same thread) instead of through the hit queue.  Same arithmetic on the same rays: identical hits, paths and ray
+    counts; the sums differ by the order of the f64 accumulations only.  Queues smaller than a block round and tail iterations
+    (the fused kernel rolls the ring counters itself) included."""
+    for w, h, spp, cap in [(96, 96, 32, 0), (97, 61, 40, 5000), (64, 64, 3, 1056)]:
+        a, qa, sa = _render_with(rt, device, "cornell-box", w, h, spp, queue_capacity=cap, ctx_opts={"flags": rt.CTX_NO_FUSED_RECTS})
+        b, qb, sb = _render_with(rt, device, "cornell-box", w, h, spp, queue_capacity=cap, ctx_opts={"flags": 0})
+        assert sa.rays == sb.rays and sa.paths == sb.paths == w * h * spp
+        assert sb.launches < sa.launches  # one dependent launch fewer per wavefront iteration
+        assert np.allclose(a, b, rtol=1e-5, atol=1e-5) and np.allclose(qa, qb, rtol=1e-5, atol=1e-5)
+    # a full-size render takes the lanes path (three lanes on frame-rect scenes) in both forms
+    a, _, sa = _render_with(rt, device, "cornell-box", 600, 600, 12, ctx_opts={"flags": rt.CTX_NO_FUSED_RECTS})
+    b, _, sb = _render_with(rt, device, "cornell-box", 600, 600, 12, ctx_opts={"flags": 0})
+    assert sa.rays == sb.rays and np.allclose(a, b, rtol=1e-5, atol=1e-5)
+    # scenes that do not use the frame-rect list are not affected by the option
+    c, _, sc = _render_with(rt, device, "checker-lists", 64, 36, 4, ctx_opts={"flags": rt.CTX_NO_FUSED_RECTS})
+    d, _, sd = _render_with(rt, device, "checker-lists", 64, 36, 4, ctx_opts={"flags": 0})
+    assert sc.rays == sd.rays and sc.launches == sd.launches and np.allclose(c, d, rtol=1e-5, atol=1e-5)
