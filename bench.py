@@ -312,6 +312,11 @@ def measure(ctx, workload, steps, warmup, want_work=True):
         extend_kernel = "k_extend_rects" if fr["frames"] else ("k_extend_bvh" if info["nodes"] >= 65536 else
                                                                 ("k_extend<false, true>" if 0 < info["nodes"] <= 2048 else "k_extend<false, false>"))
         shade_kernel = "k_shade<2>" if fr["frames"] else "k_shade<1>"
+        # small all-rectangle scenes: extend runs INSIDE k_shade (k_shade<1, false, true>: frame_rects_closest + shading per thread) —
+        # no extend launch, no hit record, the ray read once
+        fused = bool(fr["frames"]) and os.environ.get("RT_B200_FUSE_RECTS", "1") != "0"
+        if fused:
+            extend_kernel = shade_kernel = "k_shade<1, false, true>"
         kernel_of = {"generate": "k_generate", "extend": extend_kernel, "shade": shade_kernel, "accumulate": "k_accumulate"}
         launches_rank = tot_iters / world  # launches of each stage kernel on one rank = its wavefront iterations
         rays_rank = tot_rays / world
@@ -319,7 +324,8 @@ def measure(ctx, workload, steps, warmup, want_work=True):
         survive = 1.0 - tot_paths / tot_rays  # every path ends exactly once: the other segments scatter on
         # algorithmic HBM bytes per ray segment of the two queue-streaming stages: extend reads a, b (32 B) and writes
         # the hit (8 B); shade reads a, b, c and the hit (56 B) and writes a, b, c of the rays that scatter on (48 B each)
-        bytes_of = {"extend": float(EXTEND_BYTES_PER_RAY), "shade": 56.0 + 48.0 * survive}
+        # fused form: the one kernel reads a, b, c (48 B) and writes the survivors (48 B each); no hit record either way
+        bytes_of = {"extend": float(EXTEND_BYTES_PER_RAY), "shade": (48.0 if fused else 56.0) + 48.0 * survive}
         dominant = max(("extend", "shade"), key=lambda s_: stage_max[STAGES.index(s_)])
         sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
 
@@ -338,7 +344,7 @@ def measure(ctx, workload, steps, warmup, want_work=True):
             "config": {"workload": cfg, "scene": scene_name, "width": W, "height": H, "spp": spp, "max_depth": depth},
             "run": {"seed_scene": 1, "sharding": f"rows y % {world} == rank, NCCL all-gather + de-interleave" if world > 1 else "single GPU",
                     "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": info, "frame_rects": fr,
-                    "queue_capacity": args.queue_capacity or 1 << 22, "wavefront_lanes": int(os.environ.get("RT_B200_LANES", "2"))},
+                    "queue_capacity": args.queue_capacity or 1 << 22, "wavefront_lanes": int(os.environ.get("RT_B200_LANES", "3" if fr["frames"] else "2"))},
             "grays_per_s": tot_rays / (ms_all * 1e-3) / 1e9, "rays_per_path": tot_rays / tot_paths, "mean_radiance": mean_check,
             "gpu_launches": tot_launches,
             "stage_ms_per_step": {s_: stage_max[i] / steps for i, s_ in enumerate(STAGES)},
@@ -346,11 +352,15 @@ def measure(ctx, workload, steps, warmup, want_work=True):
                     "ms_per_step": float(e2e_t[0]) / steps * 1e3,
                     "api": "rt_scene_create + rt_render (host pointers)" if world == 1 else "rt_scene_create + rt_render_device + NCCL all-gather + D2H on rank 0"},
             "roofline": hbm_roofline(dominant),
-            "roofline_" + ("shade" if dominant == "extend" else "extend") + "_hbm": hbm_roofline("shade" if dominant == "extend" else "extend"),
             "clocks": clocks,
         }
+        if fused:
+            out["roofline"]["fused"] = "extend + shade in one kernel: intersection (frame-rect list in shared memory) and shading per thread"
+        else:
+            other = "shade" if dominant == "extend" else "extend"
+            out["roofline_" + other + "_hbm"] = hbm_roofline(other)
         if want_work:
-            extend_s = stage_max[1] * 1e-3
+            extend_s = stage_max[2 if fused else 1] * 1e-3  # fused: the intersection's instructions issue inside the shade stage
             instr_per_ray = box_per_ray * FP32_PER_BOX + prim_per_ray * (rect_frac * FP32_PER_RECT + (1 - rect_frac) * FP32_PER_SPHERE)
             rays_per_s_kernel = rays_rank / max(extend_s, 1e-12)  # per GPU, inside the extend kernel
             fp32_peak = 148 * 128 * sm_mhz * 1e6
@@ -373,7 +383,8 @@ def measure(ctx, workload, steps, warmup, want_work=True):
         # the whole wavefront against HBM: every stage's algorithmic queue traffic over the timed step (lanes on).  Per ray segment:
         # extend 40 B, shade 56 B read; a surviving ray is written back (48 B), a finished path writes and accumulate reads a 16-byte
         # record, generate writes 48 B per path  ->  144 B x rays + 32 B x paths
-        wf_bytes = 144.0 * tot_rays + 32.0 * tot_paths
+        # (fused extend + shade: no extend pass over the rays and no hit record -> 96 B x rays + 32 B x paths)
+        wf_bytes = (96.0 if fused else 144.0) * tot_rays + 32.0 * tot_paths
         wf_gbs = wf_bytes / (ms_all * 1e-3) / 1e9 / world  # per GPU
         out["roofline_wavefront_hbm"] = {"bound": "hbm", "achieved": wf_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": wf_gbs / hbm_peak,
                                          "bytes_per_ray": wf_bytes / max(tot_rays, 1.0), "per": "GPU, all four stage kernels over the timed step",
