@@ -85,6 +85,7 @@ struct RtContext {
     cudaEvent_t ev_lane_begin = nullptr;
     DevBuf<float> lane_sum, lane_sumsq;  // the lanes' compact row shards before they are interleaved into the caller's buffer
     uint32_t n_lanes = 2;
+    bool capacity_auto = true;  // RtContextOptions.queue_capacity was 0
     bool lanes_auto = true;   // RtContextOptions.lanes was 0: render_lanes picks by render size
     uint32_t default_capacity = 1u << 22;  // 4 M live rays (570 MB of wavefront state): per-launch fixed costs amortise, +20 % over 1 M (r1c)
 };
@@ -461,7 +462,7 @@ static int context_create(int device_id, const RtContextOptions& co, const RtSce
     ctx->device = device_id;
     ctx->n_lanes = co.lanes >= 1 && co.lanes <= 4 ? co.lanes : 2u;
     ctx->lanes_auto = !(co.lanes >= 1 && co.lanes <= 4);
-    if (co.queue_capacity) ctx->default_capacity = co.queue_capacity;
+    if (co.queue_capacity) { ctx->default_capacity = co.queue_capacity; ctx->capacity_auto = false; }
     ctx->overlap_accumulate = !(co.flags & RT_CTX_NO_ACCUMULATE_OVERLAP);
     ctx->stage_timing = (co.flags & RT_CTX_STAGE_TIMING) != 0;
     ctx->lopt.shade_rays2 = (co.flags & RT_CTX_SHADE_ONE_RAY) ? 0 : 1;
@@ -929,6 +930,11 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
     // the ~50 nearly empty iterations that drain a depth-50 wavefront weigh more — cornell-box 600x600x512: 4776 -> 4833 Mpaths/s, a
     // 1/8 shard (one GPU of eight) 4190 -> 4313 (profiles/r2_41_*, r2_42_*); neutral to slightly negative on the tree scenes
     if (ctx->lanes_auto && scene->d.fr_n) L = 3;
+    // Very large renders of tree scenes (book-one 3840x2160x1024: 8.5 G paths): four lanes with 8 Mi-ray queues, 4.4 GB of wavefront
+    // state — 5891 -> 5980 Mpaths/s (profiles/r2_44_*); below ~2 G paths the extra lanes' drain costs what their overlap buys
+    const bool huge = !scene->d.fr_n && (uint64_t)prm->width * rows_local * prm->spp >= (1ull << 31);
+    if (ctx->lanes_auto && huge) L = 4;
+    const uint32_t lane_capacity = (huge && ctx->capacity_auto) ? (1u << 23) : ctx->default_capacity;
     if ((prm->flags & (RT_RENDER_STAGE_TIMING | RT_RENDER_COUNT_WORK)) || ctx->stage_timing) L = 1;
     if (rows_local < 4u * L || prm->max_depth == 0) L = 1;
     if ((uint64_t)prm->width * rows_local * prm->spp < (uint64_t)L * (1u << 20)) L = 1;  // too little work to fill two queues
@@ -964,7 +970,7 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
             RtRenderParams lp = *prm;
             lp.row_begin = prm->row_begin + l * prm->row_stride;
             lp.row_stride = prm->row_stride * L;
-            if (!lp.queue_capacity) lp.queue_capacity = ctx->default_capacity;
+            if (!lp.queue_capacity) lp.queue_capacity = lane_capacity;
             cudaSetDevice(ctx->device);
             cudaError_t e = cudaStreamWaitEvent(lane->stream, ctx->ev_lane_begin, 0);  // after whatever the caller queued before the render
             if (e != cudaSuccess) { lane_rc[l] = RT_ERR_CUDA; lane_err[l] = cudaGetErrorString(e); return; }
