@@ -70,26 +70,47 @@ class ClockSampler:
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
 
-    def start(self):
+    def start(self, wait_s=4.0):
+        """Starts nvidia-smi (one row every 50 ms) and waits for its first row, so that even a timed region of a few tens of
+        milliseconds (8 GPUs: 10 ms per step) has the sampler running."""
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
             return
         threading.Thread(target=self._read, daemon=True).start()
+        t_end = time.perf_counter() + wait_s
+        while not self.rows and time.perf_counter() < t_end:
+            time.sleep(0.01)
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append([time.perf_counter()] + [c.strip() for c in line.split(",")])
 
-    def stop(self):
+    def stop(self, t0=None, t1=None, t2=None):
+        """Clocks over the rows that arrived in [t0, t1] (the timed region); when the region was too short to catch one, over [t0, t2]
+        (the region plus the untimed single-lane repeat of the same steps that follows it) — `window` says which."""
         if self.proc:
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=2)
             except subprocess.TimeoutExpired:
                 self.proc.kill()
+        window = "all samples"
+        rows = self.rows
+        if t0 is not None:
+            rows = [r for r in self.rows if t0 <= r[0] <= t1 + 0.05]
+            window = "timed region"
+            if not rows and t2 is not None:
+                rows = [r for r in self.rows if t0 <= r[0] <= t2 + 0.05]
+                window = "timed region + the untimed repeat of the same steps right after it"
+        self.rows = [r[1:] for r in rows]
+        out = self._summary()
+        out["window"] = window
+        return out
+
+    def _summary(self):
         sm, reasons, mx = [], set(), None
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
@@ -223,14 +244,15 @@ def measure(ctx, workload, steps, warmup, want_work=True):
         flush.zero_()
         return rtdist.render_sharded(scene, cam, W, H, spp, depth, seed, rank, world, args.queue_capacity, flags)
 
+    sampler = ClockSampler(ctx["local_rank"])
+    if rank == 0:
+        sampler.start()  # before the warm-up: nvidia-smi needs a few hundred ms to come up
     for i in range(warmup):
         step(1000 + i)
     barrier()
-    sampler = ClockSampler(ctx["local_rank"])
-    if rank == 0:
-        sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    t_region0 = time.perf_counter()
     ev0.record(stream)
     paths = rays = launches = 0
     for i in range(steps):
@@ -240,7 +262,7 @@ def measure(ctx, workload, steps, warmup, want_work=True):
         launches += st.launches + (1 if world > 1 else 0) + 1  # + de-interleave kernel, + the L2-flush memset
     ev1.record(stream)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    t_region1 = time.perf_counter()
     ms = ev0.elapsed_time(ev1)
     # ---- per-stage launch durations: the same steps again with CUDA events around the launches of every 8th wavefront iteration.
     # A stage-timed render runs as ONE wavefront lane, so that a timed launch has the device to itself (the timed region above runs
@@ -252,6 +274,7 @@ def measure(ctx, workload, steps, warmup, want_work=True):
         iters += st.iterations
         ms_stage += [st.ms_generate, st.ms_extend, st.ms_shade, st.ms_accumulate]
     barrier()
+    clocks = sampler.stop(t_region0, t_region1, time.perf_counter()) if rank == 0 else None
     red = torch.tensor([ms, *ms_stage], dtype=torch.float64, device="cuda")
     tot = torch.tensor([float(paths), float(rays), float(launches), float(iters)], dtype=torch.float64, device="cuda")
     if world > 1:
