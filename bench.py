@@ -512,9 +512,9 @@ def main():
                 line[k] = v
         if b4k is not None:
             b4k["metric"], b4k["unit"], b4k["n_gpus"] = "Mpaths/s", "Mpaths/s", world
-            b4k["warp_execution_efficiency"] = {"kernel": "k_extend<false, true>", "value": 0.66, "measured_in_run": False,
-                                                "source": "profiles/r3a_full_metrics_cornell_book-one.txt: smsp__thread_inst_executed_per_inst_executed 21.2 / 32 "
-                                                          "(ncu --set full; hardware counters need the profiler)"}
+            b4k["warp_execution_efficiency"] = {"kernel": "k_extend<false, true>", "value": 0.68, "measured_in_run": False,
+                                                "source": "profiles/r2_50_full_metrics_book-one_extend_steady_state.txt: smsp__thread_inst_executed_per_inst_executed "
+                                                          "21.7 / 32, mean of six consecutive steady-state launches (ncu --set full; hardware counters need the profiler)"}
             line["book_one_4k"] = b4k
         if multi is not None:
             line["multi_c_abi"] = multi
