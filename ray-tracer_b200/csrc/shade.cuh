@@ -209,16 +209,40 @@ __device__ __forceinline__ float3 texture_value(const DScene& S, int32_t tex, fl
 
 // ---- samplers (identical in distribution to util.rs:6-42; identical variates to the oracle's PAIRED mode) ----
 
+// Sampling maps on the hardware approximations (MUFU.SIN / COS / LG2 / EX2 / SQRT): absolute errors of a few 1e-7 in a unit vector's
+// components and ~1e-6 relative in the ball radius, against ~60 instructions for sincospif + cbrtf + sqrtf — on cornell-box, where every
+// bounce is Lambertian, that was 5 % of the fused kernel's instructions.  RT_FAST_SAMPLING=0 keeps the libm forms for A/B.
+#ifndef RT_FAST_SAMPLING
+#define RT_FAST_SAMPLING 1
+#endif
+// sin and cos of 2 pi u, u in [0, 1)
+__device__ __forceinline__ void sincos_2pi(float u, float& s, float& c) {
+#if RT_FAST_SAMPLING
+    const float t = 6.283185307179586f * (u - 0.5f);  // [-pi, pi): the range in which __sinf / __cosf are accurate to 2^-21
+    s = -__sinf(t);
+    c = -__cosf(t);
+#else
+    sincospif(2.0f * u, &s, &c);
+#endif
+}
 __device__ __forceinline__ float3 ball_from_uniforms(float u0, float u1, float u2) {
+#if RT_FAST_SAMPLING
+    const float z = 1.0f - 2.0f * u0, rho = fast_sqrt(fmaxf(0.0f, 1.0f - z * z)), r = exp2f(__log2f(u2) * 0.33333334f);  // u2 = 0: exp2(-inf) = 0
+#else
     const float z = 1.0f - 2.0f * u0, rho = sqrtf(fmaxf(0.0f, 1.0f - z * z)), r = cbrtf(u2);
+#endif
     float s, c;
-    sincospif(2.0f * u1, &s, &c);
+    sincos_2pi(u1, s, c);
     return f3(r * rho * c, r * rho * s, r * z);
 }
 __device__ __forceinline__ float2 disk_from_uniforms(float u0, float u1) {
+#if RT_FAST_SAMPLING
+    const float r = fast_sqrt(u0);
+#else
     const float r = sqrtf(u0);
+#endif
     float s, c;
-    sincospif(2.0f * u1, &s, &c);
+    sincos_2pi(u1, s, c);
     return make_float2(r * c, r * s);
 }
 
@@ -226,8 +250,13 @@ __device__ __forceinline__ float2 disk_from_uniforms(float u0, float u1) {
 
 __device__ __forceinline__ void camera_ray(const RtCamera& cam, uint32_t x, uint32_t y, uint32_t width, uint32_t height, const Philox4& rnd,
                                            float3& o, float3& d) {
+#if RT_FAST_SAMPLING
+    const float u = ((float)x + u24f(rnd.x)) * __frcp_rn((float)width);  // (the compiler hoists the two reciprocals out of k_generate's loop)
+    const float v = ((float)y + u24f(rnd.y)) * __frcp_rn((float)height);
+#else
     const float u = ((float)x + u24f(rnd.x)) / (float)width;
     const float v = ((float)y + u24f(rnd.y)) / (float)height;
+#endif
     const float3 eye = f3(cam.eye[0], cam.eye[1], cam.eye[2]);
     const float3 ll = f3(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
     const float3 hz = f3(cam.horizontal[0], cam.horizontal[1], cam.horizontal[2]);
