@@ -17,12 +17,6 @@ for s in $STEPS; do
     variants)
       RT_B200_LIB=$PWD/ray-tracer_b200/librt_b200.so python scripts/time_scenes.py $VSCENES > $OUT/variants.log 2>&1
       bash scripts/bench_variants.sh $VSCENES >> $OUT/variants.log 2>&1; echo "variants rc=$?"; cat $OUT/variants.log ;;
-    persist)
-      RT_B200_PERSISTENT=0 python scripts/time_scenes.py book-one book-two stress 2>&1 | sed "s/^/[non-persistent] /" > $OUT/persist.log
-      python scripts/time_scenes.py book-one book-two stress >> $OUT/persist.log 2>&1; cat $OUT/persist.log ;;
-    caps)
-      for cap in 524288 2097152 4194304; do RT_B200_QUEUE_CAPACITY=$cap python scripts/time_scenes.py cornell-box book-one 2>&1 | sed "s/^/[cap $cap] /"; done > $OUT/caps.log
-      RT_B200_RECT_FRAMES=0 python scripts/time_scenes.py cornell-box 2>&1 | sed "s/^/[no frame-rects] /" >> $OUT/caps.log; cat $OUT/caps.log ;;
     allbench)
       for wl in book-one book-two stress-1m book-one-4k; do
         timeout 900 python bench.py --workload $wl --steps 2 --warmup 3 --no-cpu-baseline > $OUT/bench_$wl.json 2> $OUT/bench_$wl.err; echo "bench $wl rc=$?"; cat $OUT/bench_$wl.json
