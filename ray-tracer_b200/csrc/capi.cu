@@ -977,7 +977,7 @@ int rt_color_rays(RtScene* scene, const RtRayIn* rays, uint64_t n, uint32_t spp,
 // the launch of the next: ~7-12 % of each launch, ncu cycles_active vs elapsed) and during the drain at the end of the image.
 // rt_render_device therefore splits its rows over `n_lanes` interleaved sub-shards — the same partition as the multi-GPU one — and
 // runs one complete wavefront per lane, each with its own streams, queues and accumulators, driven by its own host thread; the
-// blocks of one lane's kernel start as the other lane's blocks retire.  Measured (profiles/r2a_*, r2b_lanes_sweep.txt):
+// blocks of one lane's kernel start as the other lane's blocks retire.  Measured (profiles/r2b_lanes_sweep.txt):
 // cornell-box 2987 -> 3613 Mpaths/s, book-one 1080p 2930 -> 3423.  Philox keys are functions of the global pixel, so the image
 // does not depend on the number of lanes.  Instrumented renders (stage timing, work counters) run as one lane so that a timed
 // launch has the device to itself.
