@@ -32,6 +32,7 @@ const UNITS: &[(&str, &str, bool)] = &[
 
 /// Headers whose change must trigger a rebuild (the Makefile's HDR list).
 const HEADERS: &[&str] = &[
+    "csrc/box_prims.h",
     "csrc/bulk_copy.cuh",
     "csrc/device_scene.h",
     "csrc/intersect.cuh",
