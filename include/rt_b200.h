@@ -29,6 +29,7 @@ extern "C" {
 #endif
 
 #define RT_ABI_VERSION 2u
+#define RT_NO_PRIM 0xFFFFFFFFu /* "no primitive": rt_trace_from's self_order for a ray that starts on nothing */
 
 typedef enum RtStatus {
     RT_OK = 0,

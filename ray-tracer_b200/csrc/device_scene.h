@@ -33,6 +33,7 @@
 
 namespace rtb {
 
+#undef RT_NO_PRIM  // (the public header's macro of the same value; inside the library it is a typed constant)
 constexpr uint32_t RT_NO_PRIM = 0xFFFFFFFFu;
 constexpr int RT_STACK_DEPTH = 64;       // traversal stack entries (builder caps tree depth below this)
 #ifndef RT_SMEM_STACK_N

@@ -72,6 +72,28 @@ pub mod ffi {
 
     pub const RT_NO_PRIM: u32 = 0xFFFF_FFFF;
 
+    // RtRenderFlags / RtContextFlags / RtSceneFlags (all-zero = defaults; the flags exist for A/B measurements and tests)
+    pub const RT_RENDER_STAGE_TIMING: u32 = 1;
+    pub const RT_RENDER_COUNT_WORK: u32 = 2;
+    pub const RT_RENDER_SAMPLE_MAJOR: u32 = 4;
+    pub const RT_RENDER_EXTEND_PER_THREAD: u32 = 8;
+    pub const RT_RENDER_EXTEND_PERSISTENT: u32 = 16;
+    pub const RT_RENDER_TIME_EVERY_ITERATION: u32 = 32;
+    pub const RT_CTX_NO_ACCUMULATE_OVERLAP: u32 = 1;
+    pub const RT_CTX_STAGE_TIMING: u32 = 2;
+    pub const RT_CTX_SHADE_ONE_RAY: u32 = 4;
+    pub const RT_CTX_NO_FUSED_RECTS: u32 = 8;
+    pub const RT_SCENE_NO_FRAME_RECTS: u32 = 1;
+    pub const RT_SCENE_NO_STAGED_PRIMS: u32 = 2;
+    pub const RT_SCENE_NO_SMALL_LIST: u32 = 4;
+    pub const RT_SCENE_NO_FRAME_BOXES: u32 = 8;
+    pub const RT_SCENE_NO_BOX_PRIMS: u32 = 16;
+    pub const RT_SCENE_NO_WHOLE_TREE: u32 = 32;
+    // rt_render_noalloc: limits of the static device scratch
+    pub const RT_NOALLOC_MAX_PIXELS: u32 = 65536;
+    pub const RT_NOALLOC_QUEUE_RAYS: u32 = 32768;
+    pub const RT_NOALLOC_SCRATCH_BYTES: u32 = 9 << 20;
+
     #[repr(C)]
     #[derive(Clone, Copy, Debug, Default)]
     pub struct RtPrim {

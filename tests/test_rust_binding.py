@@ -187,3 +187,35 @@ def test_every_reference_implementor_has_its_hook_and_the_patch_applies(tmp_path
         assert re.search(rf"pub fn {getter}\b", everything), getter
     assert "crate::gpu::Flatten" in patched["ray.rs"] and "pub mod gpu;" in patched["lib.rs"]
     assert "crate::gpu::Describe" in patched["material.rs"] and "crate::gpu::DescribeTexture" in patched["material.rs"]
+
+
+def test_rust_constants_match_the_header_enumerators():
+    """Every `pub const RT_*` of gpu.rs carries the value include/rt_b200.h gives that enumerator / macro (flags, kinds, error codes,
+    the rt_render_noalloc limits)."""
+    import os
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "rt_b200.h")).read()
+    rs = open(os.path.join(root, "rust", "src", "gpu.rs")).read()
+
+    def value(text):
+        text = text.strip().rstrip("uU").replace("_", "")
+        m = re.fullmatch(r"\(?\s*(\d+)u?\s*<<\s*(\d+)\s*\)?", text)
+        if m:
+            return int(m.group(1)) << int(m.group(2))
+        return int(text, 0)
+
+    c_vals = {}
+    for name, v in re.findall(r"\b(RT_[A-Z0-9_]+)\s*=\s*(-?(?:0x[0-9A-Fa-f]+|\d+))u?\s*[,/}\n]", hdr):
+        c_vals[name] = value(v)
+    for name, v in re.findall(r"#define[ \t]+(RT_[A-Z0-9_]+)[ \t]+(\(?[0-9xA-Fa-fuU< \t]+\)?)[ \t]*(?:/\*.*)?$", hdr, flags=re.M):
+        c_vals[name] = value(v)
+    rust = re.findall(r"pub const (RT_[A-Z0-9_]+):\s*\w+\s*=\s*([^;]+);", rs)
+    assert len(rust) >= 40
+    checked = 0
+    for name, v in rust:
+        assert name in c_vals, f"{name} is not declared in include/rt_b200.h"
+        assert value(v) == c_vals[name], (name, v, c_vals[name])
+        checked += 1
+    assert checked == len(rust)
