@@ -356,6 +356,14 @@ class Scene:
                         textures.ctypes.data, texels.ctypes.data, texels.size // 4, bnd.ctypes.data, len(bnd), 0)
         return d, (prims, materials, textures, texels, bnd)
 
+    @staticmethod
+    def plan_tables(prims, materials, textures, texels=None, boundary_prims=None, options=None):
+        """rt_scene_plan on flat tables (host only, no device): what extend would see."""
+        d, keep = Scene.tables_desc(prims, materials, textures, texels, boundary_prims)
+        out = RtScenePlan()
+        _check(lib.rt_scene_plan(C.byref(d), C.byref(options) if options is not None else None, C.byref(out)))
+        return {k: int(getattr(out, k)) for k, _ in RtScenePlan._fields_}
+
     @classmethod
     def from_tables(cls, device, prims, materials, textures, texels=None, boundary_prims=None, options=None):
         d, keep = cls.tables_desc(prims, materials, textures, texels, boundary_prims)

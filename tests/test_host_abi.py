@@ -377,3 +377,90 @@ def test_scene_plan_folds_axis_aligned_cubes_into_box_primitives(rt):
     one = rt.FlatScene("book-one", 1).plan()
     assert one["n_box_prims"] == 0 and one["whole_tree_threads"] == 512 and one["n_leaf_items"] == 485
     assert rt.FlatScene("cornell-box", 1).plan()["n_box_prims"] == 0  # a small scene: the frame-rect list handles its cubes
+
+
+def _cube_rects(centre, half, first_order, material=0, rot=None):
+    """The six face rectangles of a box, Cube::new style: [(R world<-local, centre, width, height)], normals outward."""
+    import math
+
+    def rot_axis(axis, deg):
+        a = np.asarray(axis, dtype=np.float64)
+        a /= np.linalg.norm(a)
+        th = math.radians(deg)
+        K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+        return np.eye(3) + math.sin(th) * K + (1 - math.cos(th)) * (K @ K)
+
+    face = {"+x": rot_axis([0, 1, 0], 90), "-x": rot_axis([0, 1, 0], -90), "+y": rot_axis([1, 0, 0], -90), "-y": rot_axis([1, 0, 0], 90),
+            "+z": np.eye(3), "-z": rot_axis([0, 1, 0], 180)}
+    F = np.eye(3) if rot is None else rot_axis(*rot)
+    out = []
+    for name, sgn, ax in [("+x", 1, 0), ("-x", -1, 0), ("+y", 1, 1), ("-y", -1, 1), ("+z", 1, 2), ("-z", -1, 2)]:
+        off = np.zeros(3)
+        off[ax] = sgn * half[ax]
+        ext = np.abs(face[name].T @ (2 * np.asarray(half, dtype=np.float64)))
+        out.append((F @ face[name], np.asarray(centre, dtype=np.float64) + F @ off, ext[0], ext[1]))
+    return out
+
+
+def _rect_prims(rt, rects, orders=None):
+    prims = np.zeros(len(rects), dtype=rt.PRIM_DTYPE)
+    for i, (R, c, wd, ht) in enumerate(rects):
+        prims[i]["kind"], prims[i]["material"], prims[i]["order"] = rt.PRIM_RECT, 0, i if orders is None else orders[i]
+        prims[i]["param"][0], prims[i]["param"][1] = wd, ht
+        prims[i]["world_from_local"] = np.concatenate([R, c[:, None]], axis=1).reshape(12).astype(np.float32)
+        prims[i]["local_from_world"] = np.concatenate([R.T, (-R.T @ c)[:, None]], axis=1).reshape(12).astype(np.float32)
+    mats = np.zeros(1, dtype=rt.MATERIAL_DTYPE)
+    mats[0] = (rt.MAT_LAMBERTIAN, 0, 0, 0)
+    texs = np.zeros(1, dtype=rt.TEXTURE_DTYPE)
+    texs[0]["kind"], texs[0]["a"], texs[0]["b"] = rt.TEX_SOLID, -1, -1
+    texs[0]["rgb"][:3] = (0.5, 0.5, 0.5)
+    return prims, mats, texs
+
+
+def test_box_primitive_detection_is_conservative(rt):
+    """csrc/box_prims.h through rt_scene_plan: only six rectangles with CONSECUTIVE DFS ranks that are exactly the whole faces of one
+    world-aligned box fold into a box primitive.  Rotated cubes, a cube with one face shrunk or missing, faces whose ranks are
+    interleaved with another object's, and six coplanar-paired rectangles that do not close a box all stay rectangles."""
+    filler = [_cube_rects([20.0 + 3 * k, 0, 0], [1, 1, 1], 0, rot=([1, 2, 3], 10.0 + k)) for k in range(6)]  # 36 rotated faces: never boxes, keep the scene > 32 prims
+
+    def plan(cubes, orders=None):
+        rects = [r for cube in cubes for r in cube] + [r for cube in filler for r in cube]
+        if orders is not None:
+            orders = list(orders) + list(range(len(orders), len(rects)))
+        return rt.Scene.plan_tables(*_rect_prims(rt, rects, orders))
+
+    n_fill = 36
+    a = _cube_rects([0, 0, 0], [1, 2, 3], 0)
+    b = _cube_rects([2, 0, 0], [1, 1, 1], 0)  # touches a's +x plane
+    p = plan([a, b])
+    assert p["n_box_prims"] == 2 and p["n_leaf_items"] == 2 + n_fill
+    # rotated by 30 degrees: not world-aligned
+    assert plan([_cube_rects([0, 0, 0], [1, 1, 1], 0, rot=([0, 1, 0], 30.0)), b])["n_box_prims"] == 1
+    # rotated by exactly 90 degrees: still world-aligned (rows are signed unit vectors)
+    assert plan([_cube_rects([0, 0, 0], [1, 2, 3], 0, rot=([0, 0, 1], 90.0))])["n_box_prims"] == 1
+    # one face narrower than the box
+    c = _cube_rects([0, 0, 0], [1, 1, 1], 0)
+    R, ctr, wd, ht = c[2]
+    c[2] = (R, ctr, wd * 0.9, ht)
+    assert plan([c])["n_box_prims"] == 0
+    # one face moved off its plane
+    d = _cube_rects([0, 0, 0], [1, 1, 1], 0)
+    R, ctr, wd, ht = d[5]
+    d[5] = (R, ctr + np.array([0, 0, -0.01]), wd, ht)
+    assert plan([d])["n_box_prims"] == 0
+    # five faces only (an open box) followed by an unrelated rectangle
+    e = _cube_rects([0, 0, 0], [1, 1, 1], 0)[:5] + [(np.eye(3), np.array([9.0, 9.0, 9.0]), 1.0, 1.0)]
+    assert plan([e])["n_box_prims"] == 0
+    # DFS ranks of two cubes interleaved: the faces are there but not as consecutive runs
+    inter = [x for pair in zip(a, b) for x in pair]
+    assert plan([inter])["n_box_prims"] == 0
+    # same two cubes, table order shuffled but ranks consecutive per cube: detection goes by rank, not by table position
+    rects = a + b
+    perm = [7, 0, 9, 3, 11, 5, 1, 8, 2, 10, 4, 6]
+    shuffled = [rects[j] for j in perm]
+    assert plan([shuffled], orders=perm)["n_box_prims"] == 2
+    # the option switches it off
+    o = rt.RtSceneOptions()
+    o.flags = rt.SCENE_NO_BOX_PRIMS
+    rects = a + b + [r for cube in filler for r in cube]
+    assert rt.Scene.plan_tables(*_rect_prims(rt, rects), options=o)["n_box_prims"] == 0
