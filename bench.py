@@ -362,14 +362,16 @@ def measure(ctx, workload, steps, warmup, want_work=True):
                     "timing": "CUDA events around the kernel's launches of every 8th wavefront iteration, in a single-lane repeat of the timed "
                               "steps right after the timed region (the timed region itself overlaps two wavefront lanes)"}
 
-        huge = not fr["frames"] and W * ((H + world - 1) // world) * spp >= 1 << 31  # capi.cu render_lanes: four lanes, 8 Mi-ray queues
+        paths_rank = W * ((H + world - 1) // world) * spp
+        huge = not fr["frames"] and paths_rank >= 1 << 31  # capi.cu render_lanes: 8 Mi-ray queues
+        big = not fr["frames"] and paths_rank >= 1 << 29   # ... four lanes
         out = {
             "value": value, "ms_per_step": ms_all / steps, "steps": steps, "warmup": warmup,
             "config": {"workload": cfg, "scene": scene_name, "width": W, "height": H, "spp": spp, "max_depth": depth},
             "run": {"seed_scene": 1, "sharding": f"rows y % {world} == rank, NCCL all-gather + de-interleave" if world > 1 else "single GPU",
                     "l2": "flushed between steps (256 MiB memset inside the timed region)", "bvh": info, "frame_rects": fr,
                     "queue_capacity": args.queue_capacity or ((1 << 23) if huge else (1 << 22)),
-                    "wavefront_lanes": int(os.environ.get("RT_B200_LANES", "3" if fr["frames"] else ("4" if huge else "2")))},
+                    "wavefront_lanes": int(os.environ.get("RT_B200_LANES", "3" if fr["frames"] else ("4" if big else "2")))},
             "grays_per_s": tot_rays / (ms_all * 1e-3) / 1e9, "rays_per_path": tot_rays / tot_paths, "mean_radiance": mean_check,
             "gpu_launches": tot_launches,
             "stage_ms_per_step": {s_: stage_max[i] / steps for i, s_ in enumerate(STAGES)},

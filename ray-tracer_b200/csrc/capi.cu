@@ -990,10 +990,12 @@ static int render_lanes(RtScene* scene, const RtCamera* cam, const RtRenderParam
     // the ~50 nearly empty iterations that drain a depth-50 wavefront weigh more — cornell-box 600x600x512: 4776 -> 4833 Mpaths/s, a
     // 1/8 shard (one GPU of eight) 4190 -> 4313 (profiles/r2_41_*, r2_42_*); neutral to slightly negative on the tree scenes
     if (ctx->lanes_auto && scene->d.fr_n) L = 3;
-    // Very large renders of tree scenes (book-one 3840x2160x1024: 8.5 G paths): four lanes with 8 Mi-ray queues, 4.4 GB of wavefront
-    // state — 5891 -> 5980 Mpaths/s (profiles/r2_44_*); below ~2 G paths the extra lanes' drain costs what their overlap buys
-    const bool huge = !scene->d.fr_n && (uint64_t)prm->width * rows_local * prm->spp >= (1ull << 31);
-    if (ctx->lanes_auto && huge) L = 4;
+    // Large renders of tree scenes run four lanes (from 2^29 paths: book-two 800x800x1024 2045 -> 2078 Mpaths/s, book-one 1080p x 256
+    // 5786 -> 5873; below that the extra lanes' drain costs what their overlap buys), the very large ones (from 2^31 paths: book-one
+    // 3840x2160x1024, 8.5 G paths) with 8 Mi-ray queues, 4.4 GB of wavefront state — 5891 -> 5980 Mpaths/s (profiles/r2_44_*)
+    const uint64_t n_paths = (uint64_t)prm->width * rows_local * prm->spp;
+    const bool huge = !scene->d.fr_n && n_paths >= (1ull << 31);
+    if (ctx->lanes_auto && !scene->d.fr_n && n_paths >= (1ull << 29)) L = 4;
     const uint32_t lane_capacity = (huge && ctx->capacity_auto) ? (1u << 23) : ctx->default_capacity;
     if ((prm->flags & (RT_RENDER_STAGE_TIMING | RT_RENDER_COUNT_WORK)) || ctx->stage_timing) L = 1;
     if (rows_local < 4u * L || prm->max_depth == 0) L = 1;
